@@ -1,0 +1,287 @@
+#!/usr/bin/env python
+"""EEND-EDA diarized frames/sec on B200 (BASELINE.json metric), one process per GPU.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step = one pass of the hot path over one batch of synthetic mixtures of the shape
+BASELINE.json:configs[1] names: 64 recordings x 50 s @ 8 kHz -> feature front end
+(STFT/log-mel/splice/subsample) -> 64 x 500-frame chunks -> 4-layer 256-d encoder -> EDA LSTM
+-> 14 posteriors per frame + thresholded labels.  Weights are seeded random-init.
+See DESIGN.md §Measurement for what each key means.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+B, SECONDS, RATE, FRAME, SHIFT, CTX, SUB = 64, 50, 8000, 200, 80, 7, 10
+LAYERS, HEADS, UNITS, FF, IN, MAXSPK = 4, 4, 256, 2048, 345, 15
+T = SECONDS * RATE // SHIFT // SUB            # 500 model frames per recording
+METRIC, UNIT = "eend_eda_diarized_frames_per_sec", "frames/s"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(hbm=float(p["hbm_gbs"]), tf_burst=float(p["bf16_tflops"]),
+                    tf_sust=float(p.get("bf16_tflops_sustained", p["bf16_tflops"])), src="measured")
+    except Exception:
+        return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
+
+
+def synth_audio_batch(n_rec: int, seed: int) -> torch.Tensor:
+    """(n_rec, SECONDS*RATE) float32 synthetic 2-speaker mixtures: gated, low-passed noise.
+    Cheap vectorised stand-in for oracle.feature_oracle.synth_audio (same spirit: talk spurts
+    of coloured noise), generated with torch on the CPU."""
+    g = torch.Generator().manual_seed(0xBE7C4 + seed)
+    n = SECONDS * RATE
+    mix = torch.zeros((n_rec, n))
+    for _ in range(2):
+        noise = torch.randn((n_rec, n), generator=g)
+        k = torch.hann_window(33).view(1, 1, -1)
+        col = torch.nn.functional.conv1d(noise.unsqueeze(1), k / k.sum(), padding=16).squeeze(1)
+        spurts = (torch.rand((n_rec, n // 4000 + 1), generator=g) < 0.55).float()
+        gate = spurts.repeat_interleave(4000, dim=1)[:, :n]
+        mix += (0.05 + 0.45 * torch.rand((n_rec, 1), generator=g)) * gate * col * 4.0
+    mix += 1e-3 * torch.randn((n_rec, n), generator=g)
+    return mix.clamp_(-1, 1).contiguous()
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi-equivalent clock / throttle-reason samples (NVML) during the timed region."""
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._halt = threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                     "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                     "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                     "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+            while not self._halt.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.reasons.update(k for k, bit in names.items() if r & bit)
+                time.sleep(0.02)
+        except Exception as e:  # pragma: no cover
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return dict(sm_mhz=(s[len(s) // 2] if s else None), sm_max_mhz=self.max_mhz, reasons=sorted(self.reasons))
+
+
+# ------------------------------------------------------------------ CPU reference arm ----
+def cpu_reference(n_rec: int, steps: int, warmup: int, threads: int):
+    """The reference's CPU path restated by oracle/ (the reference is pure Python and does not
+    exist on the GPU box): feature_oracle.frontend + OracleEda.infer, fp32 torch, all threads.
+    Returns (frames/s, seconds per step)."""
+    from oracle import feature_oracle as fo
+    from oracle.eend_eda_oracle import OracleEda
+    from oracle.weights import EdaConfig, synth_state_dict
+    torch.set_num_threads(threads)
+    sd = synth_state_dict(EdaConfig(n_layers=LAYERS), 777)
+    model = OracleEda(sd, n_heads=HEADS, library_lstm=True)
+    audio = synth_audio_batch(n_rec, 0).double().numpy()          # soundfile hands float64 (kaldi_data.py:82)
+    def step():
+        feats = [torch.from_numpy(fo.frontend(a, RATE, FRAME, SHIFT, CTX, SUB)) for a in audio]
+        return model.infer(feats, attractor_threshold=0.5, max_n_speakers=MAXSPK)
+    torch.manual_seed(0)
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    return n_rec * T / dt, dt
+
+
+# ------------------------------------------------------------------------- B200 arm ----
+def flops_linear(args) -> float:
+    # eda_linear(A, lda, W, ldw, bias, resid, ldr, g, b, C, ldc, M, N, K, epi, prec, stream)
+    M, N, K = args[11], args[12], args[13]
+    return 2.0 * M * N * min(K, IN if K == 352 else K)
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from oracle.weights import EdaConfig, synth_state_dict     # seeded weights only (not the oracle path)
+    from speaker_diarization_b200 import _lib as L, feature
+    from speaker_diarization_b200.eend_eda.models import TransformerEdaModel
+
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    precision = os.environ.get("EDA_B200_PRECISION", args.precision)
+    model = TransformerEdaModel(2, IN, HEADS, UNITS, LAYERS, dim_feedforward=FF, precision=precision)
+    model.load_state_dict(synth_state_dict(EdaConfig(n_layers=LAYERS), 777))
+    model = model.to(dev).eval()
+    fe = feature.FrontEnd(RATE, FRAME, SHIFT, CTX, SUB, device=dev)
+    host_audio = [synth_audio_batch(B, 2 * rank + i).pin_memory() for i in range(2)]   # 2 x 102 MB
+    dev_audio = [a.to(dev) for a in host_audio]
+    ns = [SECONDS * RATE] * B
+    gather_buf = [torch.empty((B, T, MAXSPK - 1), device=dev) for _ in range(world)] if (world > 1 and rank == 0) else None
+
+    def step(i, audio_list):
+        feats = fe.features(audio_list[i & 1], ld=352, counts=ns)
+        ys = model.infer(feats, attractor_threshold=0.5, max_n_speakers=MAXSPK, activity_threshold=0.5)
+        post = model.last["posteriors"]
+        if world > 1:                      # the path's one collective: result collection on rank 0
+            dist.gather(post, gather_buf, dst=0)
+        return ys, post
+
+    torch.manual_seed(1234 + rank)
+    for i in range(max(3, args.warmup)):
+        step(i, dev_audio)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    n0 = L.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    for i in range(args.steps):
+        step(i, dev_audio)
+    ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    launches = L.launch_count() - n0
+    ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_step = ms.item() / args.steps
+    value = world * B * T / (ms_step * 1e-3)
+
+    # ---- end to end through the public API with HOST buffers (pinned), result read back ----
+    def e2e_step(i):
+        ys, post = step(i, host_audio)
+        return post.cpu() if (world == 1 or rank == 0) else None
+    for i in range(2):
+        e2e_step(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        e2e_step(i)
+    torch.cuda.synchronize()
+    e2e_s = torch.tensor([(time.perf_counter() - t0) / args.steps], device=dev)
+    if world > 1:
+        dist.barrier()
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    clocks = sampler.stop()
+    h2d = B * SECONDS * RATE * 4 + B * T * 4 + 3 * (B + 1) * 8 + (2 * B + 1) * 8 + B * 4
+    d2h = B * T * (MAXSPK - 1) * 4 + B * MAXSPK * 4
+
+    out = None
+    if rank == 0:
+        # ---- roofline leg: per-entry-point device time of one instrumented step ------------
+        L.PROFILE = {}
+        step(0, dev_audio)
+        prof = L.profile_ms()
+        L.PROFILE = None
+        tot = sum(ms_ for v in prof.values() for ms_, _ in v)
+        shares = {k: round(sum(m for m, _ in v) / tot, 4) for k, v in prof.items()}
+        lin_ms = sum(m for m, _ in prof["eda_linear"])
+        lin_fl = sum(flops_linear(a) for _, a in prof["eda_linear"])
+        pk = peaks()
+        issued = 3.0 if precision == "bf16x3" else 1.0
+        achieved = lin_fl / (lin_ms * 1e-3) / 1e12
+        roof = dict(bound="tensor", kernel="eda_linear", achieved=round(achieved, 2), peak=pk["tf_sust"],
+                    unit="TFLOP/s", frac=round(achieved / pk["tf_sust"], 4), traffic=None,
+                    peak_source=pk["src"] + " (bf16 sustained)", issued_mma_factor=issued,
+                    launches_per_step=len(prof["eda_linear"]), avg_launch_ms=round(lin_ms / len(prof["eda_linear"]), 4),
+                    share_of_step=shares)
+        fe_ms = sum(m for k in ("eda_frontend_logmel", "eda_frontend_splice_subsample") for m, _ in prof[k])
+        fe_bytes = B * T * (4 * SHIFT * SUB + 4 * IN)            # 4580 B / model frame @8 kHz
+        roof["frontend"] = dict(bound="hbm", achieved=round(fe_bytes / (fe_ms * 1e-3) / 1e9, 1), peak=pk["hbm"],
+                                unit="GB/s", frac=round(fe_bytes / (fe_ms * 1e-3) / 1e9 / pk["hbm"], 4))
+        # ---- CPU baseline on this box's host cores, bounded sample of the same workload ------
+        cores = os.cpu_count() or 1
+        n_cpu = 8
+        cpu_fps, cpu_dt = cpu_reference(n_cpu, 2, 1, cores)
+        out = {
+            "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "bf16x3": "bf16x3(f32 accum)", "bf16": "bf16"}[precision],
+            "data": "synthetic",
+            "config": {"workload": f"configs[1]: EEND-EDA {LAYERS}-layer {UNITS}-d encoder, batch {B} x {T}-frame chunks "
+                                   f"({B} x {SECONDS}s @ {RATE} Hz audio through the front end), 2 speakers, per GPU",
+                       "global_batch": world * B, "frames_per_step": world * B * T, "precision": precision,
+                       "parallelism": f"dp{world} (recordings sharded, one NCCL gather of posteriors)",
+                       "l2": "two alternating 102 MB audio batches + 262 MB FFN intermediates per step exceed the 126 MB L2"},
+            "e2e": {"value": round(world * B * T / e2e_s.item(), 1), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
+            "cpu_baseline": {"value": round(cpu_fps, 1), "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"{n_cpu} of the {B} recordings per step, 2 timed steps after 1 warm-up "
+                                       f"({cpu_dt:.2f} s/step), oracle/ torch-fp32 port incl. numpy front end"},
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return None
+    cores = os.cpu_count() or 1
+    n_cpu = 8
+    fps, dt = cpu_reference(n_cpu, max(1, args.steps), max(1, min(args.warmup, 2)), cores)
+    return {
+        "impl": "reference", "metric": METRIC, "value": round(fps, 1), "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt * 1e3, 3), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"configs[1] bounded sample: {n_cpu} of {B} recordings x {T} frames per step, "
+                               f"{LAYERS}-layer {UNITS}-d encoder, CPU"},
+        "cpu_baseline": {"value": round(fps, 1), "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{n_cpu} recordings x {SECONDS}s per step; oracle/ restatement of the reference "
+                                   "(feature.py + models.py infer) since the Python reference cannot travel to the GPU box"},
+        "e2e": {"value": round(fps, 1), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16x3", "bf16"])
+    args = ap.parse_args()
+    out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if out is not None:
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

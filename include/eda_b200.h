@@ -1,0 +1,163 @@
+/*
+ * eda_b200.h — C ABI of the B200-native EEND-EDA hot path (libeda_b200.so).
+ *
+ * This is the drop-in boundary.  The reference (shanguanma/speaker_diarization) has no
+ * FFI layer: its hot path is PyTorch library calls inside
+ *   speaker_diarization/feature.py                       (front end)
+ *   speaker_diarization/eend_eda/models.py               (TransformerEdaModel)
+ *   speaker_diarization/eend_eda/encoder_decoder_attractor.py
+ * so every entry point below names the reference function (file:line) it replaces.  All
+ * pointers are DEVICE pointers unless the name says `host`; all calls are asynchronous on
+ * `stream` (a cudaStream_t passed as void*), allocate nothing unless documented, and return
+ * 0 on success or a negative EDA_E* code (text via eda_last_error_string()).  No torch types
+ * cross this boundary.  Row-major everywhere; "ld*" arguments are row strides in ELEMENTS.
+ */
+#ifndef EDA_B200_H_
+#define EDA_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EDA_ABI_VERSION 1
+
+enum {
+  EDA_OK = 0,
+  EDA_EINVAL = -1,   /* bad argument (shape, alignment, unsupported size) */
+  EDA_ECUDA = -2,    /* CUDA runtime / launch error                         */
+  EDA_EUNSUPPORTED = -3
+};
+
+int eda_abi_version(void);
+const char* eda_last_error_string(void);
+/* Number of kernels this library has launched since load (bench.py's gpu_launches). */
+int64_t eda_launch_count(void);
+
+/* ------------------------------------------------------------------ front end ----
+ * Replaces feature.stft (feature.py:155-184; librosa.stft with n_fft = next pow2 of
+ * frame_size, periodic Hann, center=True zero padding, last frame dropped when
+ * n % shift == 0), the 'logmel23_mn' branch of feature.transform (feature.py:64-73),
+ * feature.splice (feature.py:130-152) and the [::subsampling] of feature.subsample
+ * (feature.py:122-127) / infer_eda.py:98.
+ *
+ * A plan owns the device tables (window, twiddles, sparse Slaney mel filterbank).   */
+typedef struct eda_frontend_plan eda_frontend_plan;
+
+int eda_frontend_plan_create(int sample_rate, int frame_size, int frame_shift, int n_mels,
+                             eda_frontend_plan** plan);            /* allocates tables */
+int eda_frontend_plan_destroy(eda_frontend_plan* plan);
+/* host helper: number of STFT frames feature.stft returns for n_samples (feature.py:186-193) */
+int64_t eda_frontend_num_frames(int64_t n_samples, int frame_shift);
+
+/* Pass 1: audio -> log10(max(|STFT|^2 . mel^T, 1e-10)) per frame, plus per-recording
+ * per-bin sums (for the mean).  `audio` holds n_rec recordings back to back;
+ * rec_sample_off / rec_frame_off are (n_rec+1) int64 prefix offsets (device).
+ * logmel: (total_frames, n_mels) fp32.  colsum: (n_rec, n_mels) fp64, zeroed by the call. */
+int eda_frontend_logmel(const eda_frontend_plan* plan, const void* audio, int audio_is_f64,
+                        const int64_t* rec_sample_off, const int64_t* rec_frame_off,
+                        int n_rec, int64_t total_frames,
+                        float* logmel, double* colsum, void* stream);
+
+/* Pass 2: subtract the recording mean, splice +-context frames (zeros beyond the edges,
+ * of the MEAN-NORMALISED signal, exactly like np.pad after transform) and keep every
+ * `subsampling`-th row.  feats: (total_rows, ld_feats) fp32 with (2c+1)*n_mels valid
+ * columns; columns beyond that up to ld_feats are written as 0.
+ * rec_row_off: (n_rec+1) int64 prefix offsets of output rows (ceil(frames/subsampling)). */
+int eda_frontend_splice_subsample(const eda_frontend_plan* plan, const float* logmel,
+                                  const double* colsum, const int64_t* rec_frame_off,
+                                  const int64_t* rec_row_off, int n_rec, int64_t total_rows,
+                                  int context, int subsampling,
+                                  float* feats, int ld_feats, void* stream);
+
+/* ------------------------------------------------------------------- encoder -----
+ * Building blocks of TransformerEdaModel.forward_embedding (models.py:213-234).     */
+
+/* pad_sequence(padding_value) of models.py:217 into a K-padded staging matrix:
+ * dst (B*Tmax, ld_dst); row (b,t) = src row (seq_off[b]+t) for t < len[b] else `pad`;
+ * columns >= n_cols are 0.  src is the concatenation of the sequences, (sum len, n_cols). */
+int eda_pad_pack(const float* src, const int64_t* seq_off, const int32_t* lens, int B, int Tmax,
+                 int n_cols, float pad, float* dst, int ld_dst, void* stream);
+
+enum {
+  EDA_EPI_BIAS = 0,        /* C = A.W^T + bias                                   */
+  EDA_EPI_BIAS_RELU = 1,   /* C = relu(A.W^T + bias)          (linear1, models.py:193) */
+  EDA_EPI_BIAS_LN = 2,     /* C = LN(A.W^T + bias)            (encoder+encoder_norm, models.py:220-221) */
+  EDA_EPI_BIAS_RES_LN = 3  /* C = LN(resid + A.W^T + bias)    (post-LN residual blocks) */
+};
+enum { EDA_PREC_FP32 = 0, EDA_PREC_BF16X3 = 1, EDA_PREC_BF16 = 2 };
+
+/* nn.Linear (+ fused epilogue).  A (M,K) lda, W (N,K) ldw (PyTorch weight layout),
+ * C (M,N) ldc, all fp32 in HBM.  LN epilogues need N == 256; eps = 1e-5.
+ * prec selects the arithmetic: FP32 = CUDA-core FFMA; BF16X3 = tcgen05 with error-
+ * compensated bf16 split operands (3 MMAs, fp32 TMEM accumulation); BF16 = one MMA.  */
+int eda_linear(const float* A, int lda, const float* W, int ldw, const float* bias,
+               const float* resid, int ldr, const float* ln_gamma, const float* ln_beta,
+               float* C, int ldc, int M, int N, int K, int epilogue, int prec, void* stream);
+
+/* Multi-head self-attention core of nn.TransformerEncoderLayer (no masks: padded frames
+ * are attended to, models.py:223).  qkv (B*T, 3*D) = [q | k | v], head h owns columns
+ * h*dh..; out (B*T, D) = softmax(q k^T / sqrt(dh)) v per (b, h).  dh must be 64.      */
+int eda_mha_fwd(const float* qkv, int ld_qkv, float* out, int ld_out, int B, int T,
+                int n_heads, int head_dim, int prec, void* stream);
+
+/* --------------------------------------------------------------------- EDA -------
+ * LstmEncoderDedecoderAttractor.forward (encoder_decoder_attractor.py:19-59) on the
+ * frames shuffled by models.py:228-232.
+ *
+ * xproj (B*Tmax, 4*D) = emb . W_ih^T + b_ih + b_hh (an eda_linear call; the shuffle is
+ * applied as an index: step s of sequence b reads row b*Tmax + perm[b*Tmax + s]).
+ * The encoder LSTM stops at lens[b] (packed-sequence semantics); its (h, c) seed the
+ * decoder LSTM, stepped n_dec times on zero input (gates = W_hh h + dec_bias).
+ * w_hh_* are (4*D, D) fp32 in PyTorch gate order i,f,g,o; dec_bias = b_ih + b_hh (4*D).
+ * attractors: (B, n_dec, D) fp32.  hc_out (optional, may be NULL): (B, 2, D) final
+ * encoder (h, c).  `order` (optional, may be NULL = identity): a permutation of 0..B-1;
+ * sequences are co-scheduled in groups in that order (pass them sorted by length so a
+ * group finishes together).  D must be 256.                                             */
+int eda_lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens,
+                        const int32_t* order, const float* w_hh_enc, const float* w_hh_dec, const float* dec_bias,
+                        int B, int Tmax, int D, int n_dec,
+                        float* attractors, float* hc_out, void* stream);
+
+/* Existence head: probs[b,n] = sigmoid(attractors[b,n,:] . w + bias)
+ * (encoder_decoder_attractor.py:50-54) and, when n_spk_label >= 0, the attractor loss of
+ * models.py:350-371 (BCE-with-logits applied to the probabilities against
+ * [1]*n_spk_label + [0]) into loss_att[0].                                              */
+int eda_attractor_head(const float* attractors, const float* w, const float* bias,
+                       int B, int n_dec, int D, float* probs, int n_spk_label,
+                       float* loss_att, void* stream);
+
+/* ---------------------------------------------------------- posterior + threshold --
+ * pred = bmm(emb, attractors[:, :n_att]^T) (models.py:254, :329), sigmoid (models.py:333)
+ * and the activity decision p > threshold (bin/make_rttm.py:29), fused.
+ * emb (B*Tmax, ld_emb); attractors (B, att_stride_rows, D) of which the first n_att rows
+ * are used.  Any of logits / post (fp32 (B*Tmax, n_att)) / labels (uint8, same shape) may
+ * be NULL.  n_att <= 16.                                                                */
+int eda_posterior(const float* emb, int ld_emb, const float* attractors, int att_stride_rows,
+                  int B, int Tmax, int D, int n_att, float threshold,
+                  float* logits, float* post, uint8_t* labels, void* stream);
+
+/* ------------------------------------------------------------------- PIT loss ------
+ * TransformerEdaModel.pit_loss (models.py:373-421).  pred, label (B, T, S) fp32; lens (B).
+ * Outputs: loss[0] = sum_b min_p cost[b,p] / sum_b lens[b]; min_idx (B) int64 = index
+ * into itertools.permutations(range(S)) with the lowest index on ties;
+ * label_perm (B, T, S) fp32 = label[b, :, perm[min_idx[b]]]; perm_out (B, S) int32
+ * (optional).  S <= 8.  Deterministic (fixed summation order).                           */
+int eda_pit_loss(const float* pred, const float* label, const int32_t* lens, int B, int T, int S,
+                 float* loss, int64_t* min_idx, float* label_perm, int32_t* perm_out,
+                 void* stream);
+/* d loss / d pred = mask * (sigmoid(pred) - label_perm) / (S * sum lens) * grad_scale. */
+int eda_pit_loss_bwd(const float* pred, const float* label_perm, const int32_t* lens,
+                     int B, int T, int S, float grad_scale, float* dpred, void* stream);
+
+/* TransformerEdaModel.calc_diarization_error (models.py:423-463).  counts (9) int64,
+ * zeroed by the call: [n_equal (= correct * S), num_frames, speech_scored, speech_miss,
+ * speech_falarm, speaker_scored, speaker_miss, speaker_falarm, speaker_error].          */
+int eda_der_counters(const float* pred, const float* label_perm, const int32_t* lens,
+                     int B, int T, int S, int64_t* counts, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EDA_B200_H_ */

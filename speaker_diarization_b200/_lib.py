@@ -1,0 +1,105 @@
+"""ctypes binding of libeda_b200.so (the C ABI declared in include/eda_b200.h).
+
+Thin by design: tensors are unpacked to raw device pointers + sizes here and nothing else
+happens on the Python side.  There is NO fallback: if the shared library is missing or a
+call fails, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libeda_b200.so")
+
+EPI_BIAS, EPI_BIAS_RELU, EPI_BIAS_LN, EPI_BIAS_RES_LN = 0, 1, 2, 3
+PREC_FP32, PREC_BF16X3, PREC_BF16 = 0, 1, 2
+PRECISIONS = {"fp32": PREC_FP32, "bf16x3": PREC_BF16X3, "bf16": PREC_BF16}
+
+_p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
+
+# name -> (restype, argtypes); must list every symbol include/eda_b200.h declares
+SIGNATURES = {
+    "eda_abi_version": (_i, []),
+    "eda_last_error_string": (C.c_char_p, []),
+    "eda_launch_count": (_i64, []),
+    "eda_frontend_plan_create": (_i, [_i, _i, _i, _i, C.POINTER(_p)]),
+    "eda_frontend_plan_destroy": (_i, [_p]),
+    "eda_frontend_num_frames": (_i64, [_i64, _i]),
+    "eda_frontend_logmel": (_i, [_p, _p, _i, _p, _p, _i, _i64, _p, _p, _p]),
+    "eda_frontend_splice_subsample": (_i, [_p, _p, _p, _p, _p, _i, _i64, _i, _i, _p, _i, _p]),
+    "eda_pad_pack": (_i, [_p, _p, _p, _i, _i, _i, _f, _p, _i, _p]),
+    "eda_linear": (_i, [_p, _i, _p, _i, _p, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "eda_mha_fwd": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "eda_lstm_attractors": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p]),
+    "eda_attractor_head": (_i, [_p, _p, _p, _i, _i, _i, _p, _i, _p, _p]),
+    "eda_posterior": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p, _p]),
+    "eda_pit_loss": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p]),
+    "eda_pit_loss_bwd": (_i, [_p, _p, _p, _i, _i, _i, _f, _p, _p]),
+    "eda_der_counters": (_i, [_p, _p, _p, _i, _i, _i, _p, _p]),
+}
+
+_lib = None
+
+
+class EdaError(RuntimeError):
+    pass
+
+
+def load() -> C.CDLL:
+    """Load the shared library (no GPU needed to load; needed to call compute entry points)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise EdaError(
+                f"{LIB_PATH} is missing: build it with `python -m speaker_diarization_b200.build` "
+                "(there is no CPU or PyTorch fallback for this path)")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        if lib.eda_abi_version() != 1:
+            raise EdaError("libeda_b200.so ABI version mismatch")
+        _lib = lib
+    return _lib
+
+
+def ptr(t):
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous(), "device-resident contiguous tensor required"
+    return t.data_ptr()
+
+
+def stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+# Optional per-entry-point device timing (bench.py's roofline leg): when PROFILE is a dict,
+# every call is bracketed by CUDA events on the launching stream; read with profile_ms().
+PROFILE = None
+
+
+def call(name: str, *args) -> None:
+    if PROFILE is None:
+        rc = getattr(load(), name)(*args)
+    else:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = getattr(load(), name)(*args)
+        e1.record()
+        PROFILE.setdefault(name, []).append((e0, e1, args))
+    if rc != 0:
+        raise EdaError(f"{name} failed ({rc}): {load().eda_last_error_string().decode()}")
+
+
+def profile_ms():
+    """{entry point: [(milliseconds, args), ...]} for the calls recorded in PROFILE."""
+    torch.cuda.synchronize()
+    return {k: [(a.elapsed_time(b), args) for a, b, args in v] for k, v in (PROFILE or {}).items()}
+
+
+def launch_count() -> int:
+    return int(load().eda_launch_count())

@@ -1,0 +1,133 @@
+// Bandwidth-bound glue kernels of the model path: pad/pack, attractor existence head,
+// fused posterior (bmm + sigmoid + threshold).
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace eda {
+
+// ---------------------------------------------------------------- pad_pack ----------
+// models.py:217 pad_sequence(padding_value=-1) into a K-padded staging matrix.
+__global__ void pad_pack_kernel(const float* __restrict__ src, const int64_t* __restrict__ seq_off,
+                                const int32_t* __restrict__ lens, int Tmax, int n_cols, float pad,
+                                float* __restrict__ dst, int ld_dst, int64_t n_rows) {
+  const int warps_per_block = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31;
+  for (int64_t row = (int64_t)blockIdx.x * warps_per_block + (threadIdx.x >> 5); row < n_rows;
+       row += (int64_t)gridDim.x * warps_per_block) {
+    const int b = (int)(row / Tmax), t = (int)(row % Tmax);
+    const bool valid = t < lens[b];
+    const float* s = src + (seq_off[b] + t) * (int64_t)n_cols;
+    float* d = dst + row * (int64_t)ld_dst;
+    for (int c = lane; c < ld_dst; c += 32) d[c] = c < n_cols ? (valid ? __ldg(s + c) : pad) : 0.f;
+  }
+}
+
+int pad_pack(const float* src, const int64_t* seq_off, const int32_t* lens, int B, int Tmax,
+             int n_cols, float pad, float* dst, int ld_dst, cudaStream_t st) {
+  EDA_REQUIRE(ld_dst >= n_cols && B > 0 && Tmax > 0, "eda_pad_pack: bad sizes");
+  const int64_t n_rows = (int64_t)B * Tmax;
+  const int blocks = (int)std::min<int64_t>(ceil_div<int64_t>(n_rows, 8), (int64_t)num_sms() * 8);
+  pad_pack_kernel<<<blocks, 256, 0, st>>>(src, seq_off, lens, Tmax, n_cols, pad, dst, ld_dst, n_rows);
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
+}
+
+// ---------------------------------------------------------- attractor head ----------
+// encoder_decoder_attractor.py:50-54 and models.py:350-371.  One CTA; warp per (b, n).
+__global__ void attractor_head_kernel(const float* __restrict__ att, const float* __restrict__ w,
+                                      const float* __restrict__ bias, int B, int n_dec, int D,
+                                      float* __restrict__ probs, int n_spk_label,
+                                      float* __restrict__ loss_att) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int total = B * n_dec;
+  for (int i = warp; i < total; i += nwarps) {
+    const float* a = att + (size_t)i * D;
+    float s = 0.f;
+    for (int d = lane; d < D; d += 32) s = fmaf(__ldg(a + d), __ldg(w + d), s);
+    s = warp_sum(s);
+    if (lane == 0) probs[i] = sigmoidf_ref(s + __ldg(bias));
+  }
+  if (n_spk_label < 0 || loss_att == nullptr) return;
+  __syncthreads();
+  // BCE-with-logits on the PROBABILITIES (reference behaviour), fixed summation order.
+  if (threadIdx.x == 0) {
+    float total_loss = 0.f;
+    for (int b = 0; b < B; ++b) {
+      float row = 0.f;
+      for (int n = 0; n < n_dec; ++n) {
+        const float x = probs[b * n_dec + n], y = n < n_spk_label ? 1.f : 0.f;
+        row += fmaxf(x, 0.f) - x * y + log1pf(expf(-fabsf(x)));
+      }
+      total_loss += row / (float)n_dec;
+    }
+    loss_att[0] = total_loss / (float)B;
+  }
+}
+
+int attractor_head(const float* att, const float* w, const float* bias, int B, int n_dec, int D,
+                   float* probs, int n_spk_label, float* loss_att, cudaStream_t st) {
+  EDA_REQUIRE(B > 0 && n_dec > 0 && D > 0, "eda_attractor_head: bad sizes");
+  attractor_head_kernel<<<1, 1024, 0, st>>>(att, w, bias, B, n_dec, D, probs, n_spk_label, loss_att);
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
+}
+
+// --------------------------------------------------------------- posterior ----------
+// models.py:329 bmm(emb, attractor[:, :-1]^T) -> :333 sigmoid -> make_rttm.py:29 threshold.
+// Warp per frame: the 256-d embedding row is read once (two float4 per lane, coalesced),
+// attractors of the sequence sit in shared memory, the n_att dot products are reduced with
+// a shuffle butterfly, lane s writes column s.
+template <int NATT>
+__global__ void __launch_bounds__(256)
+posterior_kernel(const float* __restrict__ emb, int ld_emb, const float* __restrict__ att,
+                 int att_stride_rows, int Tmax, int n_att, float thr, float* __restrict__ logits,
+                 float* __restrict__ post, uint8_t* __restrict__ labels) {
+  constexpr int D = 256;
+  __shared__ __align__(16) float As[NATT][D];
+  const int b = blockIdx.y;
+  for (int i = threadIdx.x; i < n_att * D; i += blockDim.x)
+    As[i / D][i % D] = __ldg(att + (size_t)b * att_stride_rows * D + i);
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int t = blockIdx.x * 8 + warp; t < Tmax; t += gridDim.x * 8) {
+    const size_t row = (size_t)b * Tmax + t;
+    const float4* e = reinterpret_cast<const float4*>(emb + row * ld_emb);
+    const float4 e0 = __ldg(e + lane), e1 = __ldg(e + 32 + lane);
+    float mine = 0.f;
+#pragma unroll
+    for (int s = 0; s < NATT; ++s) {
+      if (s < n_att) {
+        const float4 a0 = *reinterpret_cast<const float4*>(&As[s][lane * 4]);
+        const float4 a1 = *reinterpret_cast<const float4*>(&As[s][128 + lane * 4]);
+        float v = e0.x * a0.x;
+        v = fmaf(e0.y, a0.y, v); v = fmaf(e0.z, a0.z, v); v = fmaf(e0.w, a0.w, v);
+        v = fmaf(e1.x, a1.x, v); v = fmaf(e1.y, a1.y, v); v = fmaf(e1.z, a1.z, v); v = fmaf(e1.w, a1.w, v);
+        v = warp_sum(v);
+        if (lane == s) mine = v;
+      }
+    }
+    if (lane < n_att) {
+      const size_t o = row * n_att + lane;
+      const float p = sigmoidf_ref(mine);
+      if (logits) logits[o] = mine;
+      if (post) post[o] = p;
+      if (labels) labels[o] = p > thr ? 1 : 0;
+    }
+  }
+}
+
+int posterior(const float* emb, int ld_emb, const float* att, int att_stride_rows, int B, int Tmax,
+              int D, int n_att, float thr, float* logits, float* post, uint8_t* labels,
+              cudaStream_t st) {
+  EDA_REQUIRE(D == 256, "eda_posterior: D must be 256 (got %d)", D);
+  EDA_REQUIRE(n_att >= 1 && n_att <= 16, "eda_posterior: n_att must be in [1,16] (got %d)", n_att);
+  EDA_REQUIRE(ld_emb % 4 == 0 && (uintptr_t)emb % 16 == 0, "eda_posterior: emb must be 16B aligned");
+  EDA_REQUIRE(B <= 65535, "eda_posterior: B too large");
+  dim3 grid(max(1, min(ceil_div(Tmax, 8), ceil_div(num_sms() * 8, B))), B);
+  posterior_kernel<16><<<grid, 256, 0, st>>>(emb, ld_emb, att, att_stride_rows, Tmax, n_att, thr, logits, post, labels);
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
+}
+
+}  // namespace eda

@@ -1,0 +1,254 @@
+"""B200-native ``TransformerEdaModel``.
+
+Drop-in for the reference class of the same name
+(speaker_diarization/eend_eda/models.py:160-463): same constructor arguments, same
+``state_dict`` key set (checkpoints interchange with ``torch.load`` as in
+infer_eda.py:88), same ``forward`` / ``infer`` / ``pit_loss`` / ``attractor_loss`` /
+``calc_diarization_error`` / ``forward_embedding`` call signatures and return contracts.
+
+The torch sub-modules are parameter CONTAINERS only (they give the reference's key names
+and default initialisation for free); no arithmetic goes through them.  Everything on the
+path runs in the hand-written sm_100a kernels of libeda_b200.so via ``..ops``.  There is
+no CPU path: the model must live on a CUDA device.
+
+Not covered (reference features outside BASELINE.json's north_star): autograd through the
+kernels (``forward`` returns a loss tensor without ``grad_fn``), train-mode
+dropout > 0, ``has_pos=True`` (never enabled by the reference drivers, train_eda.py:81).
+"""
+from __future__ import annotations
+
+import os
+from itertools import permutations
+from typing import List, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+from torch import Tensor
+from torch.nn import TransformerEncoder, TransformerEncoderLayer
+
+from .. import _lib as L
+from .. import ops
+from .encoder_decoder_attractor import LstmEncoderDedecoderAttractor
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class TransformerEdaModel(nn.Module):
+    def __init__(self, n_speakers, in_size, n_heads, n_units, n_layers, dim_feedforward=2048,
+                 dropout=0.5, has_pos=False, diar_weight: float = 1.0, attractor_weight: float = 1.0,
+                 precision: Optional[str] = None):
+        super().__init__()
+        if has_pos:
+            raise NotImplementedError("has_pos=True is never used by the reference drivers (train_eda.py:81)")
+        if n_units != 256 or n_units // n_heads != 64:
+            raise NotImplementedError("kernels are specialised for n_units=256, head_dim=64 (conf/eend_eda/*.yaml)")
+        self.n_speakers, self.in_size, self.n_heads = n_speakers, in_size, n_heads
+        self.n_units, self.n_layers, self.has_pos = n_units, n_layers, has_pos
+        self.dim_feedforward, self.dropout_p = dim_feedforward, dropout
+        self.src_mask = None
+        self.encoder = nn.Linear(in_size, n_units)
+        self.encoder_norm = nn.LayerNorm(n_units)
+        layer = TransformerEncoderLayer(n_units, n_heads, dim_feedforward, dropout, batch_first=True)
+        self.transformer_encoder = TransformerEncoder(layer, n_layers, enable_nested_tensor=False)
+        self.eda = LstmEncoderDedecoderAttractor(input_size=n_units, num_layers=1, dropout=0.1)
+        self.diar_weight, self.attractor_weight = diar_weight, attractor_weight
+        self.init_weights()
+        self.set_precision(precision or os.environ.get("EDA_B200_PRECISION", "fp32"))
+        self._prep = None
+
+    def set_precision(self, name: str) -> None:
+        """'fp32' (CUDA-core FFMA), 'bf16x3' (tcgen05, split-bf16 operands) or 'bf16'."""
+        if name not in L.PRECISIONS:
+            raise ValueError(f"unknown precision {name!r}; choose from {sorted(L.PRECISIONS)}")
+        self.precision_name, self.precision = name, L.PRECISIONS[name]
+        self.eda.precision = self.precision
+
+    def init_weights(self):
+        """models.py:207-210."""
+        self.encoder.bias.data.zero_()
+        self.encoder.weight.data.uniform_(-0.1, 0.1)
+
+    # ---------------------------------------------------------------- parameters --------
+    def _prepared(self):
+        key = tuple((p.data_ptr(), p._version) for p in self.parameters())
+        if self._prep is None or self._prep[0] != key:
+            kpad = _round_up(self.in_size, 16)
+            w = self.encoder.weight.detach()
+            w_in = torch.zeros((self.n_units, kpad), dtype=torch.float32, device=w.device)
+            w_in[:, : self.in_size] = w
+            layers = []
+            for lyr in self.transformer_encoder.layers:
+                g = lambda t: t.detach().contiguous()
+                layers.append(dict(
+                    w_qkv=g(lyr.self_attn.in_proj_weight), b_qkv=g(lyr.self_attn.in_proj_bias),
+                    w_o=g(lyr.self_attn.out_proj.weight), b_o=g(lyr.self_attn.out_proj.bias),
+                    w_1=g(lyr.linear1.weight), b_1=g(lyr.linear1.bias),
+                    w_2=g(lyr.linear2.weight), b_2=g(lyr.linear2.bias),
+                    g1=g(lyr.norm1.weight), be1=g(lyr.norm1.bias),
+                    g2=g(lyr.norm2.weight), be2=g(lyr.norm2.bias)))
+            self._prep = (key, dict(kpad=kpad, w_in=w_in, b_in=self.encoder.bias.detach().contiguous(),
+                                    g_in=self.encoder_norm.weight.detach().contiguous(),
+                                    be_in=self.encoder_norm.bias.detach().contiguous(), layers=layers))
+        return self._prep[1]
+
+    def _device(self) -> torch.device:
+        dev = self.encoder.weight.device
+        if dev.type != "cuda":
+            raise L.EdaError("speaker_diarization_b200 has no CPU path: call .cuda() on the model first")
+        return dev
+
+    def _check_mode(self):
+        if self.training and self.dropout_p > 0:
+            raise NotImplementedError(
+                "train-mode dropout is not implemented in the CUDA path; call .eval() "
+                "(as the reference's dev loop does, train_eda.py:205) or build with dropout=0")
+
+    # ------------------------------------------------------------------- encoder --------
+    def _to_device_flat(self, seqs: List[Tensor], dev) -> Tensor:
+        """Concatenate a list of (T_i, C) tensors into one device matrix with ONE H2D copy."""
+        if seqs[0].is_cuda:
+            return torch.cat([s.float() for s in seqs], dim=0).contiguous()
+        total = sum(int(s.shape[0]) for s in seqs)
+        stage = torch.empty((total, seqs[0].shape[1]), dtype=torch.float32, pin_memory=True)
+        torch.cat([s.float() for s in seqs], dim=0, out=stage)
+        return stage.to(dev, non_blocking=True)
+
+    def _embed(self, src: List[Tensor]):
+        """models.py:213-226 up to ``emb``; returns emb2d (B*Tmax, D) plus batch geometry."""
+        dev = self._device()
+        self._check_mode()
+        w = self._prepared()
+        ilens = [int(x.shape[0]) for x in src]
+        B, Tmax = len(ilens), max(ilens)
+        off = np.zeros(B + 1, dtype=np.int64)
+        np.cumsum(ilens, out=off[1:])
+        meta = torch.from_numpy(np.concatenate([off, np.asarray(ilens, dtype=np.int64)])).to(dev, non_blocking=True)
+        seq_off = meta[: B + 1]
+        lens_dev = meta[B + 1:].to(torch.int32)
+        flat = self._to_device_flat(src, dev)
+        x = ops.pad_pack(flat, seq_off, lens_dev, B, Tmax, w["kpad"], -1.0)
+        P = self.precision
+        x = ops.linear(x, w["w_in"], w["b_in"], L.EPI_BIAS_LN, P, gamma=w["g_in"], beta=w["be_in"])
+        for lw in w["layers"]:
+            qkv = ops.linear(x, lw["w_qkv"], lw["b_qkv"], L.EPI_BIAS, P)
+            att = ops.mha(qkv, B, Tmax, self.n_heads, P)
+            x = ops.linear(att, lw["w_o"], lw["b_o"], L.EPI_BIAS_RES_LN, P, resid=x, gamma=lw["g1"], beta=lw["be1"])
+            ff = ops.linear(x, lw["w_1"], lw["b_1"], L.EPI_BIAS_RELU, P)
+            x = ops.linear(ff, lw["w_2"], lw["b_2"], L.EPI_BIAS_RES_LN, P, resid=x, gamma=lw["g2"], beta=lw["be2"])
+        return x, ilens, lens_dev, seq_off, B, Tmax
+
+    @staticmethod
+    def _draw_perm(ilens: List[int], Tmax: int, dev, perms=None) -> Tensor:
+        """models.py:229-232: one ``torch.randperm(ilen)`` per sequence from the global CPU
+        generator, in batch order; shipped as an int32 (B, Tmax) index (identity beyond ilen).
+        ``perms`` (extension): use these frame orders instead of drawing (callers that batch
+        chunks out of order draw them first, in the reference's order)."""
+        perm = torch.arange(Tmax, dtype=torch.int32).repeat(len(ilens), 1).pin_memory()
+        for i, n in enumerate(ilens):
+            perm[i, :n] = (torch.randperm(n) if perms is None else perms[i]).to(torch.int32)
+        return perm.to(dev, non_blocking=True)
+
+    def forward_embedding(self, src: List[Tensor]):
+        """Reference signature (models.py:213): (encoder_out_shuffled, emb, ilens)."""
+        x, ilens, _, _, B, Tmax = self._embed(src)
+        emb = x.view(B, Tmax, self.n_units)
+        perm = self._draw_perm(ilens, Tmax, emb.device)
+        shuffled = torch.gather(emb, 1, perm.long().unsqueeze(-1).expand(-1, -1, self.n_units))
+        return shuffled, emb, ilens
+
+    # --------------------------------------------------------------------- forward -------
+    def forward(self, src: List[Tensor], ts: List[Tensor], has_mask=False, activation=None):
+        """models.py:236-295: (loss, stats).  ``loss`` is a 0-d CUDA tensor (no grad_fn)."""
+        x, ilens, lens_dev, seq_off, B, Tmax = self._embed(src)
+        dev = x.device
+        S = int(ts[0].shape[1])
+        label = ops.pad_pack(self._to_device_flat(list(ts), dev), seq_off, lens_dev, B, Tmax, S, -1.0)
+        label = label.view(B, Tmax, S)
+        perm = self._draw_perm(ilens, Tmax, dev)
+        att, probs, loss_att = self.eda.attractors(x, perm, lens_dev, ilens, B, Tmax, S + 1, n_spk_label=S)
+        pred, _, _ = ops.posterior(x, att, B, Tmax, S, want_logits=True, want_post=False)
+        loss_pit, min_idx, label_perm, _ = ops.pit_loss(pred, label, lens_dev)
+        counts = ops.der_counters(pred, label_perm, lens_dev)
+        loss = (self.diar_weight * loss_pit + self.attractor_weight * loss_att).reshape(())
+        c = counts.tolist()                       # the step's single device->host sync
+        correct, num_frames = c[0] / S, float(c[1])
+        sp_sc, sp_ms, sp_fa, spk_sc, spk_ms, spk_fa, spk_er = (float(v) for v in c[2:])
+        stats = dict(
+            loss=loss.detach(), loss_att=loss_att.reshape(()).detach(), loss_pit=loss_pit.reshape(()).detach(),
+            sad_mr=sp_ms / sp_sc, sad_fr=sp_fa / sp_sc, mi=spk_ms / spk_sc, fa=spk_fa / spk_sc,
+            cf=spk_er / spk_sc, acc=correct / num_frames, der=(spk_ms + spk_fa + spk_er) / spk_sc)
+        self.last = dict(emb=x.view(B, Tmax, -1), attractors=att, probs=probs, pred=pred,
+                         min_idx=min_idx, label_permute=label_perm, counts=counts)
+        return loss, stats
+
+    # ----------------------------------------------------------------------- infer -------
+    @torch.no_grad()
+    def infer(self, src: List[Tensor], infer_num_speakers=None, max_n_speakers=15, attractor_threshold=0.5,
+              activity_threshold: Optional[float] = None, perms=None):
+        """models.py:297-347: list of (Tmax, n_spk_b) posterior tensors.
+
+        ``activity_threshold`` (extension): also keep the fused ``posterior > threshold``
+        uint8 decisions of bin/make_rttm.py:29 in ``self.last['labels']``."""
+        x, ilens, lens_dev, _, B, Tmax = self._embed(src)
+        perm = self._draw_perm(ilens, Tmax, x.device, perms)
+        att, probs, _ = self.eda.attractors(x, perm, lens_dev, ilens, B, Tmax, max_n_speakers)
+        n_att = max_n_speakers - 1
+        _, post, labels = ops.posterior(x, att, B, Tmax, n_att,
+                                        threshold=0.5 if activity_threshold is None else activity_threshold,
+                                        want_labels=activity_threshold is not None)
+        self.last = dict(emb=x.view(B, Tmax, -1), attractors=att, probs=probs, posteriors=post, labels=labels)
+        ys_active = []
+        if infer_num_speakers is not None:
+            order = torch.sort(probs, dim=1, descending=True, stable=False)[1][:, :infer_num_speakers]
+            if bool((order >= n_att).any()):      # the reference indexes 14 columns with it (models.py:339)
+                raise IndexError(f"index {n_att} is out of bounds for dimension 1 with size {n_att}")
+            for b in range(B):
+                ys_active.append(post[b][:, order[b]])
+        elif attractor_threshold is not None:
+            p_host = probs.cpu().numpy()          # the call's single device->host sync
+            for b in range(B):
+                silence = np.where(p_host[b] < attractor_threshold)[0]
+                n_spk = int(silence[0]) if silence.size else None
+                ys_active.append(post[b][:, :n_spk])
+        return ys_active
+
+    # ---------------------------------------------------------------- loss pieces --------
+    def attractor_loss(self, att_prob, label: Tensor):
+        """models.py:350-371 (list of (S+1,) probabilities, label (B,T,S))."""
+        assert isinstance(label, Tensor), f"label: {label}"
+        probs = torch.stack(list(att_prob)).float().contiguous().to(self._device())
+        B, n_dec = probs.shape
+        # the head kernel owns this formula; feed it logits whose sigmoid is `probs`
+        att = torch.logit(probs.double()).float().reshape(B, n_dec, 1).contiguous()
+        one = torch.ones(1, device=att.device)
+        _, loss = ops.attractor_head(att, one, torch.zeros(1, device=att.device), int(label.size(2)))
+        return loss.reshape(())
+
+    def pit_loss(self, pred: Tensor, label: Tensor, lengths: List[int]):
+        """models.py:389-413: (loss, min_idx, permute_list, label_permute[CPU float32])."""
+        assert isinstance(lengths, List), f"length: {lengths}"
+        dev = self._device()
+        S = label.size(2)
+        permute_list = [np.array(p) for p in permutations(range(S))]
+        lens_dev = torch.tensor([int(v) for v in lengths], dtype=torch.int32, device=dev)
+        loss, min_idx, label_perm, _ = ops.pit_loss(pred.detach().float().contiguous().to(dev),
+                                                    label.detach().float().contiguous().to(dev), lens_dev)
+        return loss.reshape(()), min_idx, permute_list, label_perm.cpu()
+
+    def pit_loss_backward(self, pred: Tensor, label_permute: Tensor, lengths: List[int], grad_scale=1.0):
+        """d pit_loss / d pred for the winning permutation."""
+        dev = self._device()
+        lens_dev = torch.tensor([int(v) for v in lengths], dtype=torch.int32, device=dev)
+        return ops.pit_loss_bwd(pred.detach().float().contiguous().to(dev),
+                                label_permute.float().contiguous().to(dev), lens_dev, grad_scale)
+
+    def calc_diarization_error(self, pred: Tensor, label: Tensor, length: List[int]):
+        """models.py:423-463: the 9-tuple of Python floats."""
+        dev = self._device()
+        lens_dev = torch.tensor([int(v) for v in length], dtype=torch.int32, device=dev)
+        c = ops.der_counters(pred.detach().float().contiguous().to(dev),
+                             label.detach().float().contiguous().to(dev), lens_dev).tolist()
+        return (c[0] / label.size(2), float(c[1]), *(float(v) for v in c[2:]))

@@ -1,0 +1,145 @@
+"""B200-native feature front end.
+
+Mirrors the part of the reference's ``speaker_diarization/feature.py`` that the EEND-EDA
+drivers use (infer_eda.py:46-49,94-98; diarization_dataset.py:93-115):
+
+    Y = feature.stft(data, frame_size, frame_shift)            # feature.py:155-184
+    Y = feature.transform(Y, 'logmel23_mn', sample_rate=rate)  # feature.py:64-73
+    Y = feature.splice(Y, context_size)                        # feature.py:130-152
+    Y = Y[::subsampling]                                       # feature.py:122-127
+
+On the GPU the first two calls are one kernel (audio -> log-mel + per-bin sums) and the last
+two another (mean-norm + splice + subsample), so the public surface here is the fused chain:
+``extract`` for one recording (reference argument names) and ``FrontEnd`` for batches.
+There is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Sequence, Union
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+Array = Union[np.ndarray, torch.Tensor]
+
+
+def get_input_dim(frame_size: int, context_size: int, transform_type: str) -> int:
+    """feature.py:10-21."""
+    if transform_type.startswith("logmel23"):
+        width = 23
+    else:
+        width = (1 << (frame_size - 1).bit_length()) // 2 + 1
+    return (2 * context_size + 1) * width
+
+
+def count_frames(n_samples: int, frame_shift: int) -> int:
+    """feature.py:186-193 (``_count_frames``): frames ``stft`` returns."""
+    return int(L.load().eda_frontend_num_frames(int(n_samples), int(frame_shift)))
+
+
+class FrontEnd:
+    """Batched ``stft -> logmel23_mn -> splice -> subsample`` on one CUDA device."""
+
+    def __init__(self, sample_rate: int = 8000, frame_size: int = 200, frame_shift: int = 80,
+                 context_size: int = 7, subsampling: int = 10, n_mels: int = 23, device="cuda"):
+        self.sample_rate, self.frame_size, self.frame_shift = sample_rate, frame_size, frame_shift
+        self.context_size, self.subsampling, self.n_mels = context_size, subsampling, n_mels
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise L.EdaError("speaker_diarization_b200 has no CPU path")
+        self._plan = C.c_void_p()
+        with torch.cuda.device(self.device):
+            L.call("eda_frontend_plan_create", sample_rate, frame_size, frame_shift, n_mels, C.byref(self._plan))
+
+    def __del__(self):
+        try:
+            if getattr(self, "_plan", None):
+                L.load().eda_frontend_plan_destroy(self._plan)
+                self._plan = None
+        except Exception:
+            pass
+
+    @property
+    def feat_dim(self) -> int:
+        return (2 * self.context_size + 1) * self.n_mels
+
+    # ------------------------------------------------------------------ batching ------
+    def _stage(self, recs, counts=None):
+        """Concatenate recordings into one device buffer (one H2D copy) + prefix offsets.
+        ``recs`` may also be ONE flat/2-D tensor holding the recordings back to back, with
+        ``counts`` giving each recording's sample count (no concatenation copy then)."""
+        if counts is not None:
+            flat = recs.reshape(-1)
+            is_f64 = flat.dtype == torch.float64
+            audio = flat if flat.is_cuda else flat.to(self.device, non_blocking=True)
+            return (audio.contiguous(), is_f64) + self._offsets([int(c) for c in counts])
+        first = recs[0]
+        is_f64 = (first.dtype == np.float64) if isinstance(first, np.ndarray) else (first.dtype == torch.float64)
+        tdt = torch.float64 if is_f64 else torch.float32
+        ns = [int(r.shape[0]) for r in recs]
+        if isinstance(first, torch.Tensor) and first.is_cuda:
+            audio = torch.cat([r.to(tdt) for r in recs]).contiguous()
+        else:
+            stage = torch.empty((sum(ns),), dtype=tdt, pin_memory=True)
+            pos = 0
+            for r, n in zip(recs, ns):
+                stage[pos:pos + n] = torch.as_tensor(r).to(tdt)
+                pos += n
+            audio = stage.to(self.device, non_blocking=True)
+        return (audio, is_f64) + self._offsets(ns)
+
+    def _offsets(self, ns):
+        frames = [count_frames(n, self.frame_shift) for n in ns]
+        rows = [(f + self.subsampling - 1) // self.subsampling for f in frames]
+        off = np.zeros((3, len(ns) + 1), dtype=np.int64)
+        np.cumsum(ns, out=off[0, 1:]); np.cumsum(frames, out=off[1, 1:]); np.cumsum(rows, out=off[2, 1:])
+        offs = torch.from_numpy(off).to(self.device, non_blocking=True)
+        return offs, frames, rows
+
+    def logmel(self, recs, counts=None):
+        """Pass 1.  Returns (logmel (total_frames, n_mels) fp32, colsum (n_rec, n_mels) fp64,
+        staging tuple)."""
+        with torch.cuda.device(self.device):
+            audio, is_f64, offs, frames, rows = self._stage(recs, counts)
+            n_rec = len(frames)
+            total = int(sum(frames))
+            lm = torch.empty((total, self.n_mels), dtype=torch.float32, device=self.device)
+            colsum = torch.empty((n_rec, self.n_mels), dtype=torch.float64, device=self.device)
+            L.call("eda_frontend_logmel", self._plan, L.ptr(audio), int(is_f64), L.ptr(offs[0]), L.ptr(offs[1]),
+                   n_rec, total, L.ptr(lm), L.ptr(colsum), L.stream())
+        return lm, colsum, (offs, frames, rows)
+
+    def features(self, recs, ld: int = 0, counts=None) -> List[torch.Tensor]:
+        """The whole chain for a batch of recordings: list of (ceil(frames/sub), feat_dim)
+        fp32 CUDA tensors (views into one buffer; row stride ``ld`` if given, e.g. 352)."""
+        lm, colsum, (offs, frames, rows) = self.logmel(recs, counts)
+        ld = ld or self.feat_dim
+        total_rows = int(sum(rows))
+        with torch.cuda.device(self.device):
+            feats = torch.empty((total_rows, ld), dtype=torch.float32, device=self.device)
+            L.call("eda_frontend_splice_subsample", self._plan, L.ptr(lm), L.ptr(colsum), L.ptr(offs[1]),
+                   L.ptr(offs[2]), len(rows), total_rows, self.context_size, self.subsampling,
+                   L.ptr(feats), ld, L.stream())
+        out, pos = [], 0
+        for r in rows:
+            out.append(feats[pos:pos + r, : self.feat_dim])
+            pos += r
+        return out
+
+
+_frontends = {}
+
+
+def extract(data: Array, frame_size: int = 200, frame_shift: int = 80, transform_type: str = "logmel23_mn",
+            sample_rate: int = 8000, context_size: int = 7, subsampling: int = 10, device="cuda") -> torch.Tensor:
+    """One recording through ``stft -> transform -> splice -> [::subsampling]``
+    (infer_eda.py:94-98) -> (T, 345) fp32 CUDA tensor."""
+    if transform_type != "logmel23_mn":
+        raise NotImplementedError("only 'logmel23_mn' (the transform every conf/eend_eda yaml uses)")
+    key = (sample_rate, frame_size, frame_shift, context_size, subsampling, str(device))
+    if key not in _frontends:
+        _frontends[key] = FrontEnd(sample_rate, frame_size, frame_shift, context_size, subsampling, device=device)
+    return _frontends[key].features([data])[0]

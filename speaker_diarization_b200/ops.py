@@ -1,0 +1,115 @@
+"""Tensor-level wrappers over the C ABI (one Python function per entry point).
+
+Only unpacking happens here: shape bookkeeping, output allocation through torch's caching
+allocator, and the ctypes call on torch's current CUDA stream.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+
+Tensor = torch.Tensor
+
+
+def _f32(t: Tensor) -> Tensor:
+    assert t.dtype == torch.float32 and t.is_cuda and t.is_contiguous(), (t.dtype, t.device, t.is_contiguous())
+    return t
+
+
+def pad_pack(flat: Tensor, seq_off: Tensor, lens: Tensor, B: int, Tmax: int, ld_dst: int, pad: float) -> Tensor:
+    """flat (sum T_i, C) -> (B*Tmax, ld_dst) padded with `pad` (models.py:217)."""
+    _f32(flat)
+    out = torch.empty((B * Tmax, ld_dst), dtype=torch.float32, device=flat.device)
+    L.call("eda_pad_pack", L.ptr(flat), L.ptr(seq_off), L.ptr(lens), B, Tmax, flat.shape[1], float(pad),
+           L.ptr(out), ld_dst, L.stream())
+    return out
+
+
+def linear(a: Tensor, w: Tensor, bias: Optional[Tensor], epilogue: int = L.EPI_BIAS, prec: int = L.PREC_FP32,
+           resid: Optional[Tensor] = None, gamma: Optional[Tensor] = None, beta: Optional[Tensor] = None,
+           out: Optional[Tensor] = None) -> Tensor:
+    """nn.Linear + fused epilogue.  a (M,K), w (N,K) -> (M,N)."""
+    _f32(a), _f32(w)
+    M, K = a.shape
+    N = w.shape[0]
+    assert w.shape[1] == K, (a.shape, w.shape)
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float32, device=a.device)
+    L.call("eda_linear", L.ptr(a), a.stride(0), L.ptr(w), w.stride(0), L.ptr(bias),
+           L.ptr(resid), resid.stride(0) if resid is not None else 0, L.ptr(gamma), L.ptr(beta),
+           L.ptr(out), out.stride(0), M, N, K, epilogue, prec, L.stream())
+    return out
+
+
+def mha(qkv: Tensor, B: int, T: int, n_heads: int, prec: int = L.PREC_FP32) -> Tensor:
+    _f32(qkv)
+    D = qkv.shape[1] // 3
+    out = torch.empty((B * T, D), dtype=torch.float32, device=qkv.device)
+    L.call("eda_mha_fwd", L.ptr(qkv), qkv.stride(0), L.ptr(out), out.stride(0), B, T, n_heads,
+           D // n_heads, prec, L.stream())
+    return out
+
+
+def lstm_attractors(xproj: Tensor, perm: Tensor, lens: Tensor, order: Optional[Tensor], w_hh_enc: Tensor,
+                    w_hh_dec: Tensor, dec_bias: Tensor, B: int, Tmax: int, n_dec: int, want_hc: bool = False):
+    D = w_hh_enc.shape[1]
+    att = torch.empty((B, n_dec, D), dtype=torch.float32, device=xproj.device)
+    hc = torch.empty((B, 2, D), dtype=torch.float32, device=xproj.device) if want_hc else None
+    assert perm.dtype == torch.int32 and lens.dtype == torch.int32
+    L.call("eda_lstm_attractors", L.ptr(_f32(xproj)), L.ptr(perm), L.ptr(lens), L.ptr(order),
+           L.ptr(_f32(w_hh_enc)), L.ptr(_f32(w_hh_dec)), L.ptr(_f32(dec_bias)), B, Tmax, D, n_dec,
+           L.ptr(att), L.ptr(hc), L.stream())
+    return att, hc
+
+
+def attractor_head(att: Tensor, w: Tensor, bias: Tensor, n_spk_label: int = -1):
+    B, n_dec, D = att.shape
+    probs = torch.empty((B, n_dec), dtype=torch.float32, device=att.device)
+    loss = torch.zeros((1,), dtype=torch.float32, device=att.device) if n_spk_label >= 0 else None
+    L.call("eda_attractor_head", L.ptr(_f32(att)), L.ptr(_f32(w)), L.ptr(_f32(bias)), B, n_dec, D,
+           L.ptr(probs), n_spk_label, L.ptr(loss), L.stream())
+    return probs, loss
+
+
+def posterior(emb: Tensor, att: Tensor, B: int, Tmax: int, n_att: int, threshold: float = 0.5,
+              want_logits: bool = False, want_post: bool = True, want_labels: bool = False):
+    """emb (B*Tmax, D), att (B, rows>=n_att, D) -> logits/post (B,Tmax,n_att) fp32, labels uint8."""
+    D = emb.shape[1]
+    mk = lambda dt: torch.empty((B, Tmax, n_att), dtype=dt, device=emb.device)
+    logits = mk(torch.float32) if want_logits else None
+    post = mk(torch.float32) if want_post else None
+    labels = mk(torch.uint8) if want_labels else None
+    L.call("eda_posterior", L.ptr(_f32(emb)), emb.stride(0), L.ptr(_f32(att)), att.shape[1], B, Tmax, D,
+           n_att, float(threshold), L.ptr(logits), L.ptr(post), L.ptr(labels), L.stream())
+    return logits, post, labels
+
+
+def pit_loss(pred: Tensor, label: Tensor, lens: Tensor):
+    B, T, S = pred.shape
+    dev = pred.device
+    loss = torch.empty((1,), dtype=torch.float32, device=dev)
+    min_idx = torch.empty((B,), dtype=torch.int64, device=dev)
+    label_perm = torch.empty((B, T, S), dtype=torch.float32, device=dev)
+    perm = torch.empty((B, S), dtype=torch.int32, device=dev)
+    L.call("eda_pit_loss", L.ptr(_f32(pred)), L.ptr(_f32(label)), L.ptr(lens), B, T, S, L.ptr(loss),
+           L.ptr(min_idx), L.ptr(label_perm), L.ptr(perm), L.stream())
+    return loss, min_idx, label_perm, perm
+
+
+def pit_loss_bwd(pred: Tensor, label_perm: Tensor, lens: Tensor, grad_scale: float = 1.0) -> Tensor:
+    B, T, S = pred.shape
+    dpred = torch.empty_like(pred)
+    L.call("eda_pit_loss_bwd", L.ptr(_f32(pred)), L.ptr(_f32(label_perm)), L.ptr(lens), B, T, S,
+           float(grad_scale), L.ptr(dpred), L.stream())
+    return dpred
+
+
+def der_counters(pred: Tensor, label_perm: Tensor, lens: Tensor) -> Tensor:
+    B, T, S = pred.shape
+    counts = torch.empty((9,), dtype=torch.int64, device=pred.device)
+    L.call("eda_der_counters", L.ptr(_f32(pred)), L.ptr(_f32(label_perm)), L.ptr(lens), B, T, S,
+           L.ptr(counts), L.stream())
+    return counts

@@ -1,0 +1,166 @@
+"""Per-kernel parity: each C-ABI entry point against the CPU oracle on seeded inputs.
+
+Tolerances are written per test.  PIT assignments, permuted labels, DER counters and
+thresholded activity labels are compared bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import cases_of, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+PREC = ["fp32"]
+
+
+def _prec(name):
+    from speaker_diarization_b200 import _lib as L
+    return L.PRECISIONS[name]
+
+
+@pytest.mark.parametrize("prec", PREC)
+@pytest.mark.parametrize("M,N,K,epi", [
+    (300, 768, 256, "bias"), (1000, 2048, 256, "relu"), (257, 256, 352, "ln"),
+    (515, 256, 2048, "res_ln"), (64, 1024, 256, "bias"), (1, 256, 256, "res_ln"), (129, 40, 64, "bias"),
+])
+def test_linear(dev, prec, M, N, K, epi):
+    from speaker_diarization_b200 import _lib as L, ops
+    g = torch.Generator().manual_seed(M * 7 + N)
+    a = torch.randn((M, K), generator=g)
+    w = (torch.rand((N, K), generator=g) * 2 - 1) / K ** 0.5
+    b = torch.randn((N,), generator=g) * 0.1
+    r = torch.randn((M, N), generator=g)
+    gm, bt = 1 + 0.1 * torch.randn((N,), generator=g), 0.1 * torch.randn((N,), generator=g)
+    ref = F.linear(a, w, b)
+    code = {"bias": L.EPI_BIAS, "relu": L.EPI_BIAS_RELU, "ln": L.EPI_BIAS_LN, "res_ln": L.EPI_BIAS_RES_LN}[epi]
+    if epi == "relu":
+        ref = ref.relu()
+    if epi == "ln":
+        ref = F.layer_norm(ref, (N,), gm, bt, 1e-5)
+    if epi == "res_ln":
+        ref = F.layer_norm(ref + r, (N,), gm, bt, 1e-5)
+    out = ops.linear(a.to(dev), w.to(dev), b.to(dev), code, _prec(prec),
+                     resid=r.to(dev) if epi == "res_ln" else None,
+                     gamma=gm.to(dev) if "ln" in epi else None, beta=bt.to(dev) if "ln" in epi else None)
+    tol = 2e-5 if prec == "fp32" else 2e-4
+    assert (out.cpu() - ref).abs().max().item() < tol
+
+
+@pytest.mark.parametrize("prec", PREC)
+@pytest.mark.parametrize("B,T", [(2, 130), (1, 64), (3, 500), (1, 1), (1, 2000)])
+def test_mha(dev, prec, B, T):
+    from speaker_diarization_b200 import ops
+    g = torch.Generator().manual_seed(B * 1000 + T)
+    qkv = torch.randn((B, T, 768), generator=g) * 1.5
+    q, k, v = (t.reshape(B, T, 4, 64).transpose(1, 2) for t in qkv.split(256, dim=-1))
+    ref = (torch.softmax(q @ k.transpose(-1, -2) * 0.125, dim=-1) @ v).transpose(1, 2).reshape(B * T, 256)
+    out = ops.mha(qkv.reshape(B * T, 768).to(dev), B, T, 4, _prec(prec))
+    tol = 5e-6 if prec == "fp32" else 1e-4
+    assert (out.cpu() - ref).abs().max().item() < tol
+
+
+@pytest.mark.parametrize("lens,n_dec", [([40, 17, 1, 40, 33], 3), ([300] * 9, 15), ([5], 15), ([64, 0, 20], 4)])
+def test_lstm_attractors(dev, lens, n_dec):
+    from oracle.eend_eda_oracle import eda as oracle_eda
+    from oracle.weights import EdaConfig, synth_state_dict
+    from speaker_diarization_b200 import _lib as L, ops
+    sd = synth_state_dict(EdaConfig(n_layers=1), 3)
+    B, T = len(lens), max(lens)
+    g = torch.Generator().manual_seed(sum(lens))
+    emb = torch.randn((B, T, 256), generator=g)
+    perms = [torch.randperm(n, generator=g) for n in lens]
+    # torch's packed LSTM rejects empty sequences; the python-loop oracle handles them (h=c=0)
+    att_ref, p_ref = oracle_eda(emb, lens, perms, n_dec, sd, library_lstm=(0 not in lens))
+    perm = torch.arange(T, dtype=torch.int32).repeat(B, 1)
+    for i, p in enumerate(perms):
+        perm[i, : lens[i]] = p.to(torch.int32)
+    be = (sd["eda.encoder.bias_ih_l0"] + sd["eda.encoder.bias_hh_l0"]).to(dev)
+    xproj = ops.linear(emb.reshape(B * T, 256).to(dev), sd["eda.encoder.weight_ih_l0"].to(dev), be, L.EPI_BIAS, L.PREC_FP32)
+    lens_d = torch.tensor(lens, dtype=torch.int32, device=dev)
+    order = torch.tensor(sorted(range(B), key=lambda b: -lens[b]), dtype=torch.int32, device=dev)
+    bd = (sd["eda.decoder.bias_ih_l0"] + sd["eda.decoder.bias_hh_l0"]).to(dev)
+    att, _ = ops.lstm_attractors(xproj, perm.to(dev), lens_d, order, sd["eda.encoder.weight_hh_l0"].to(dev),
+                                 sd["eda.decoder.weight_hh_l0"].to(dev), bd, B, T, n_dec)
+    probs, _ = ops.attractor_head(att, sd["eda.linear.weight"].reshape(-1).to(dev), sd["eda.linear.bias"].to(dev))
+    assert (att.cpu() - att_ref).abs().max().item() < 2e-5
+    assert (probs.cpu() - p_ref).abs().max().item() < 2e-6
+    # identity `order` (NULL) must give the same result
+    att2, _ = ops.lstm_attractors(xproj, perm.to(dev), lens_d, None, sd["eda.encoder.weight_hh_l0"].to(dev),
+                                  sd["eda.decoder.weight_hh_l0"].to(dev), bd, B, T, n_dec)
+    assert torch.equal(att, att2)
+
+
+@pytest.mark.parametrize("B,T,n_att", [(3, 77, 14), (2, 500, 2), (1, 1, 1), (70, 40, 4)])
+def test_posterior_and_threshold(dev, B, T, n_att):
+    from speaker_diarization_b200 import ops
+    g = torch.Generator().manual_seed(B + T + n_att)
+    emb = torch.randn((B, T, 256), generator=g)
+    att = torch.randn((B, n_att + 1, 256), generator=g) * 0.2
+    ref_logit = emb @ att[:, :n_att].transpose(1, 2)
+    logits, post, labels = ops.posterior(emb.reshape(B * T, 256).to(dev), att.to(dev), B, T, n_att, 0.5,
+                                         want_logits=True, want_post=True, want_labels=True)
+    assert (logits.cpu() - ref_logit).abs().max().item() < 2e-5
+    assert (post.cpu() - torch.sigmoid(ref_logit)).abs().max().item() < 2e-6
+    # the fused decision is exactly `posterior > threshold` on the posteriors it wrote
+    assert torch.equal(labels.cpu(), (post.cpu() > 0.5).to(torch.uint8))
+    # and agrees with the oracle wherever the oracle posterior is not within 1e-5 of 0.5
+    ref_lab = (torch.sigmoid(ref_logit) > 0.5)
+    far = (torch.sigmoid(ref_logit) - 0.5).abs() > 1e-5
+    assert torch.equal(labels.cpu().bool()[far], ref_lab[far])
+
+
+@pytest.mark.parametrize("name", cases_of("pit"))
+def test_pit_loss_and_der_golden(dev, name, manifest):
+    from oracle.weights import synth_labels
+    from speaker_diarization_b200 import ops
+    case = manifest["cases"][name]
+    B, T, S, seed = case["B"], case["T"], case["S"], case["seed"]
+    gen = torch.Generator().manual_seed(seed)
+    lens = [int(x) for x in torch.randint(T // 3, T + 1, (B,), generator=gen)]
+    lens[0] = T
+    pred = torch.randn((B, T, S), generator=gen) * 2.0
+    ts = synth_labels(lens, S, seed, silent=tuple(case["silent"]))
+    label = torch.nn.utils.rnn.pad_sequence(ts, padding_value=-1, batch_first=True)
+    gold = load_golden(name)
+    lens_d = torch.tensor(lens, dtype=torch.int32, device=dev)
+    loss, idx, lab, perm = ops.pit_loss(pred.to(dev), label.to(dev), lens_d)
+    assert idx.cpu().tolist() == gold["min_idx"].tolist()                       # bit-exact assignment
+    assert np.array_equal(lab.cpu().numpy().astype(np.int8), gold["label_permute"])
+    assert abs(loss.item() - float(gold["loss"])) < 2e-6
+    counts = ops.der_counters(pred.to(dev), lab, lens_d).cpu().tolist()
+    want = gold["der_counts"].tolist()
+    assert counts[0] == round(want[0] * S) and [float(c) for c in counts[1:]] == want[1:]
+    # gradient of the winning permutation vs autograd on the oracle formula
+    p = pred.clone().requires_grad_(True)
+    mask = (torch.arange(T)[None, :] < torch.tensor(lens)[:, None]).float()[:, :, None]
+    l = (F.binary_cross_entropy_with_logits(p, lab.cpu().clamp(min=0), reduction="none") * mask).mean(2).sum() / sum(lens)
+    l.backward()
+    d = ops.pit_loss_bwd(pred.to(dev), lab, lens_d)
+    assert (d.cpu() - p.grad).abs().max().item() < 1e-7
+
+
+def test_pit_edge_cases(dev):
+    from oracle.eend_eda_oracle import pit_loss as oracle_pit
+    from speaker_diarization_b200 import ops
+    g = torch.Generator().manual_seed(99)
+    for B, T, S in [(1, 1, 1), (2, 5, 2), (4, 300, 5), (2, 50, 7)]:
+        lens = [T] + [max(1, T // 2)] * (B - 1)
+        pred = torch.randn((B, T, S), generator=g)
+        label = (torch.rand((B, T, S), generator=g) < 0.4).float()
+        label[:, :, S // 2] = label[:, :, 0]          # duplicate column -> exact ties
+        for b in range(B):
+            label[b, lens[b]:] = -1
+        loss_o, idx_o, _, lab_o = oracle_pit(pred, label, lens)
+        loss, idx, lab, _ = ops.pit_loss(pred.to(dev), label.to(dev), torch.tensor(lens, dtype=torch.int32, device=dev))
+        assert idx.cpu().tolist() == idx_o.tolist(), (B, T, S)
+        assert torch.equal(lab.cpu(), lab_o)
+        assert abs(loss.item() - loss_o.item()) < 1e-5

@@ -64,7 +64,7 @@ def test_mha(dev, prec, B, T):
     q, k, v = (t.reshape(B, T, 4, 64).transpose(1, 2) for t in qkv.split(256, dim=-1))
     ref = (torch.softmax(q @ k.transpose(-1, -2) * 0.125, dim=-1) @ v).transpose(1, 2).reshape(B * T, 256)
     out = ops.mha(qkv.reshape(B * T, 768).to(dev), B, T, 4, _prec(prec))
-    tol = 5e-6 if prec == "fp32" else 1e-4
+    tol = 2e-5 if prec == "fp32" else 1e-4   # logits reach |20|: 1 ulp there is 2e-6 before exp
     assert (out.cpu() - ref).abs().max().item() < tol
 
 

@@ -12,3 +12,5 @@ done
 timeout 600 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?" | tee -a gpurun_out/summary.txt; tail -3 gpurun_out/smoke.log
 timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?" | tee -a gpurun_out/summary.txt
 cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
+timeout 900 python bench.py --steps 10 --warmup 3 --precision bf16x3 > gpurun_out/bench_bf16x3.json 2> gpurun_out/bench_bf16x3.err; echo "bench bf16x3 exit $?" | tee -a gpurun_out/summary.txt
+cat gpurun_out/bench_bf16x3.json; tail -5 gpurun_out/bench_bf16x3.err

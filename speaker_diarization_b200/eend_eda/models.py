@@ -65,6 +65,8 @@ class TransformerEdaModel(nn.Module):
             raise ValueError(f"unknown precision {name!r}; choose from {sorted(L.PRECISIONS)}")
         self.precision_name, self.precision = name, L.PRECISIONS[name]
         self.eda.precision = self.precision
+        # attention core: fp32 CUDA-core kernel until the tcgen05 flash kernel replaces it
+        self.attn_precision = L.PREC_FP32
 
     def init_weights(self):
         """models.py:207-210."""
@@ -134,7 +136,7 @@ class TransformerEdaModel(nn.Module):
         x = ops.linear(x, w["w_in"], w["b_in"], L.EPI_BIAS_LN, P, gamma=w["g_in"], beta=w["be_in"])
         for lw in w["layers"]:
             qkv = ops.linear(x, lw["w_qkv"], lw["b_qkv"], L.EPI_BIAS, P)
-            att = ops.mha(qkv, B, Tmax, self.n_heads, P)
+            att = ops.mha(qkv, B, Tmax, self.n_heads, self.attn_precision)
             x = ops.linear(att, lw["w_o"], lw["b_o"], L.EPI_BIAS_RES_LN, P, resid=x, gamma=lw["g1"], beta=lw["be1"])
             ff = ops.linear(x, lw["w_1"], lw["b_1"], L.EPI_BIAS_RELU, P)
             x = ops.linear(ff, lw["w_2"], lw["b_2"], L.EPI_BIAS_RES_LN, P, resid=x, gamma=lw["g2"], beta=lw["be2"])

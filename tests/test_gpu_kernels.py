@@ -20,6 +20,7 @@ def dev():
 
 
 PREC = ["fp32"]
+LIN_PREC = ["fp32", "bf16x3", "bf16"]
 
 
 def _prec(name):
@@ -27,7 +28,7 @@ def _prec(name):
     return L.PRECISIONS[name]
 
 
-@pytest.mark.parametrize("prec", PREC)
+@pytest.mark.parametrize("prec", LIN_PREC)
 @pytest.mark.parametrize("M,N,K,epi", [
     (300, 768, 256, "bias"), (1000, 2048, 256, "relu"), (257, 256, 352, "ln"),
     (515, 256, 2048, "res_ln"), (64, 1024, 256, "bias"), (1, 256, 256, "res_ln"), (129, 40, 64, "bias"),
@@ -51,8 +52,12 @@ def test_linear(dev, prec, M, N, K, epi):
     out = ops.linear(a.to(dev), w.to(dev), b.to(dev), code, _prec(prec),
                      resid=r.to(dev) if epi == "res_ln" else None,
                      gamma=gm.to(dev) if "ln" in epi else None, beta=bt.to(dev) if "ln" in epi else None)
-    tol = 2e-5 if prec == "fp32" else 2e-4
-    assert (out.cpu() - ref).abs().max().item() < tol
+    # fp32: FFMA reorder only; bf16x3: dropped lo*lo term ~2^-18 rel; bf16: 2^-9 operand rounding
+    tol = {"fp32": 2e-5, "bf16x3": 1e-4, "bf16": 6e-2}[prec]
+    err = (out.cpu() - ref).abs().max().item()
+    assert err < tol, err
+    if prec == "bf16":
+        assert err > 1e-5      # the single-pass mode really is the cheaper arithmetic
 
 
 @pytest.mark.parametrize("prec", PREC)

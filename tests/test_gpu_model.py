@@ -13,7 +13,7 @@ from conftest import cases_of, load_golden
 pytestmark = pytest.mark.gpu
 
 POST_TOL = {"fp32": 5e-5, "bf16x3": 1e-3}
-PRECISIONS = ["fp32"]
+PRECISIONS = ["fp32", "bf16x3"]
 
 
 def build(case, precision):

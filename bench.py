@@ -226,7 +226,7 @@ def run_ours(args):
         # ---- CPU baseline on this box's host cores, bounded sample of the same workload ------
         cores = os.cpu_count() or 1
         n_cpu = 8
-        cpu_fps, cpu_dt = cpu_reference(n_cpu, 2, 1, cores)
+        cpu_fps, cpu_dt = (0.0, 0.0) if args.skip_cpu else cpu_reference(n_cpu, 2, 1, cores)
         out = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
@@ -277,6 +277,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16x3", "bf16"])
+    ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     out = run_reference(args) if args.impl == "reference" else run_ours(args)
     if out is not None:

@@ -1,0 +1,496 @@
+// nn.Linear with fused epilogues on the 5th-generation tensor cores (tcgen05 / TMEM / TMA).
+//
+//   C[m,n] = sum_k A[m,k] W[n,k]      fp32 accumulation in TMEM
+//
+// Operands live in HBM as bf16 "split" pairs: x = hi + lo, hi = bf16(x), lo = bf16(x - hi).
+// EDA_PREC_BF16X3 issues three MMAs per k-step (Ahi.Bhi + Ahi.Blo + Alo.Bhi; the dropped
+// lo.lo term is ~2^-18 relative), which is what the parity bar needs (one bf16
+// pass cannot meet it).  EDA_PREC_BF16 issues only hi.hi.
+//
+// The producing kernel writes its output already split (and/or as fp32 for the residual
+// stream), so no separate conversion pass touches HBM between two GEMMs.
+//
+// Kernel: persistent, one CTA per SM, 128 x 256 output tiles handed out round-robin.
+//   warp 0      TMA producer   (SWIZZLE_128B K-major tiles {A_hi, A_lo, B_hi, B_lo}, 2 stages)
+//   warp 1      MMA issuer (one thread) + TMEM owner: 2 accumulator buffers x 256 columns,
+//               so the epilogue of tile i overlaps the MMAs of tile i+1
+//   warps 2-5   epilogue: tcgen05.ld -> bias / ReLU / residual + LayerNorm (row kept in TMEM
+//               between the statistics passes) -> smem transpose -> coalesced stores of the
+//               fp32 and/or split-bf16 output; the QKV variant pre-scales q by 1/sqrt(dh) and
+//               stores v TRANSPOSED per (batch, head) for the attention kernel.
+#include <algorithm>
+#include <mutex>
+#include <unordered_map>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace eda {
+
+using namespace tc;
+typedef __nv_bfloat16 bf16;
+
+constexpr int GBM = 128, GBN = 256, GBK = 64, GSTAGES = 2;
+constexpr int G_A_TILE = GBM * GBK * 2;                  // 16 KB
+constexpr int G_B_TILE = GBN * GBK * 2;                  // 32 KB
+constexpr int G_STAGE = 2 * G_A_TILE + 2 * G_B_TILE;     // 96 KB
+constexpr int G_STG_LD = 36;                             // floats per staged row (32 + pad)
+constexpr int G_STG_BYTES = 4 * 32 * G_STG_LD * 4;       // 4 epilogue warps
+constexpr int G_SMEM = GSTAGES * G_STAGE + G_STG_BYTES + 256 + 1024;
+
+enum { GEPI_QKV = 4 };
+
+struct GemmParams {
+  const float* bias;
+  const float* resid; int ldr;
+  const float* gamma; const float* beta;
+  float* C; int ldc;                       // optional fp32 output
+  bf16* Chi; bf16* Clo; int lds;           // optional split output
+  int M, N, Kp, passes;
+  // QKV variant: rows are (b, t) with t < T; v goes to vt[(b*H + h)*64 + d][t], row stride Tp
+  bf16* vt_hi; bf16* vt_lo; int T, Tp, H; float q_scale;
+};
+
+__device__ __forceinline__ void split2(float x0, float x1, __nv_bfloat162& hi, __nv_bfloat162& lo) {
+  const bf16 h0 = __float2bfloat16_rn(x0), h1 = __float2bfloat16_rn(x1);
+  hi = __halves2bfloat162(h0, h1);
+  lo = __halves2bfloat162(__float2bfloat16_rn(x0 - __bfloat162float(h0)),
+                          __float2bfloat16_rn(x1 - __bfloat162float(h1)));
+}
+
+// fp32 (rows x K, ld) -> hi, lo bf16 (rows x ldk), zero padded columns [K, ldk)
+__global__ void split_bf16_kernel(const float* __restrict__ src, int ld, int rows, int K, int ldk,
+                                  bf16* __restrict__ hi, bf16* __restrict__ lo) {
+  const int64_t n = (int64_t)rows * (ldk / 2);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / (ldk / 2)), c = (int)(i % (ldk / 2)) * 2;
+    const float x0 = c < K ? src[(size_t)r * ld + c] : 0.f;
+    const float x1 = c + 1 < K ? src[(size_t)r * ld + c + 1] : 0.f;
+    __nv_bfloat162 h, l;
+    split2(x0, x1, h, l);
+    *reinterpret_cast<__nv_bfloat162*>(hi + (size_t)r * ldk + c) = h;
+    *reinterpret_cast<__nv_bfloat162*>(lo + (size_t)r * ldk + c) = l;
+  }
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(192, 1)
+gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
+                  const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
+                  const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* stg_all = reinterpret_cast<float*>(smem + GSTAGES * G_STAGE);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + GSTAGES * G_STAGE + G_STG_BYTES);
+  uint64_t* empty = full + GSTAGES;
+  uint64_t* tfull = empty + GSTAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles_n = (p.N + GBN - 1) / GBN, n_tiles_m = (p.M + GBM - 1) / GBM;
+  const int n_tiles = n_tiles_n * n_tiles_m;
+  const int nkb = (p.Kp + GBK - 1) / GBK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA_hi); tma_prefetch_desc(&tmA_lo); tma_prefetch_desc(&tmB_hi); tma_prefetch_desc(&tmB_lo);
+    for (int s = 0; s < GSTAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      const uint32_t stage_tx = p.passes == 3 ? G_STAGE : (G_A_TILE + G_B_TILE);
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int m0 = (tile / n_tiles_n) * GBM, n0 = (tile % n_tiles_n) * GBN;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % GSTAGES;
+          mbar_wait(&empty[s], ((it / GSTAGES) & 1) ^ 1);
+          uint8_t* st = smem + s * G_STAGE;
+          mbar_expect_tx(&full[s], stage_tx);
+          tma_load_2d(st, &tmA_hi, &full[s], kb * GBK, m0);
+          tma_load_2d(st + 2 * G_A_TILE, &tmB_hi, &full[s], kb * GBK, n0);
+          if (p.passes == 3) {
+            tma_load_2d(st + G_A_TILE, &tmA_lo, &full[s], kb * GBK, m0);
+            tma_load_2d(st + 2 * G_A_TILE + G_B_TILE, &tmB_lo, &full[s], kb * GBK, n0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16_f32(GBM, GBN);
+      uint32_t it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
+        const uint32_t ab = lt & 1;
+        mbar_wait(&tempty[ab], ((lt >> 1) & 1) ^ 1);       // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t acc = tmem_base + ab * GBN;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % GSTAGES;
+          mbar_wait(&full[s], (it / GSTAGES) & 1);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * G_STAGE);
+          const uint64_t a_hi = smem_desc_sw128(sa), a_lo = smem_desc_sw128(sa + G_A_TILE);
+          const uint64_t b_hi = smem_desc_sw128(sa + 2 * G_A_TILE), b_lo = smem_desc_sw128(sa + 2 * G_A_TILE + G_B_TILE);
+#pragma unroll
+          for (int k = 0; k < GBK / 16; ++k) {
+            const uint64_t adv = uint64_t(k * 32 >> 4);          // +32 B per 16-element k-step
+            umma_bf16(acc, a_hi + adv, b_hi + adv, idesc, (kb | k) != 0);
+            if (p.passes == 3) {
+              umma_bf16(acc, a_hi + adv, b_lo + adv, idesc, 1);
+              umma_bf16(acc, a_lo + adv, b_hi + adv, idesc, 1);
+            }
+          }
+          umma_commit(&empty[s]);        // frees this smem stage once the MMAs above have read it
+        }
+        umma_commit(&tfull[ab]);         // accumulator complete
+      }
+    }
+  } else {
+    // ===== epilogue: warps 2..5; warp w may touch TMEM lanes 32*(w%4) .. +31 =====
+    const int q = warp & 3;
+    float* stg = stg_all + q * 32 * G_STG_LD;
+    const int srow = lane >> 3, scol = (lane & 7) * 4;               // staged-copy role
+    uint32_t lt = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
+      const int m0 = (tile / n_tiles_n) * GBM, n_blk = tile % n_tiles_n, n0 = n_blk * GBN;
+      const uint32_t ab = lt & 1;
+      mbar_wait(&tfull[ab], (lt >> 1) & 1);
+      tc_fence_after();
+      const uint32_t trow = tmem_base + ab * GBN + (uint32_t(q * 32) << 16);
+
+      // registers (thread = row) -> smem transpose -> coalesced row segments of fp32 / split bf16
+      auto store_chunk = [&](const float (&v)[32], int c, int col_base, bf16* out_hi, bf16* out_lo, int lds) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(&stg[lane * G_STG_LD + 4 * j]) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+#pragma unroll
+        for (int it2 = 0; it2 < 8; ++it2) {
+          const int r = it2 * 4 + srow, grow = m0 + q * 32 + r, gcol = col_base + c * 32 + scol;
+          const float4 x = *reinterpret_cast<const float4*>(&stg[r * G_STG_LD + scol]);
+          if (grow < p.M && gcol < p.N) {
+            if (p.C && EPI != GEPI_QKV) {
+              float* dst = p.C + (size_t)grow * p.ldc + gcol;
+              if (gcol + 3 < p.N) *reinterpret_cast<float4*>(dst) = x;
+              else {
+                dst[0] = x.x;
+                if (gcol + 1 < p.N) dst[1] = x.y;
+                if (gcol + 2 < p.N) dst[2] = x.z;
+              }
+            }
+            if (out_hi) {      // split outputs require N % 4 == 0 (checked on the host)
+              __nv_bfloat162 h0, l0, h1, l1;
+              split2(x.x, x.y, h0, l0);
+              split2(x.z, x.w, h1, l1);
+              uint2 hv, lv;
+              hv.x = *reinterpret_cast<uint32_t*>(&h0); hv.y = *reinterpret_cast<uint32_t*>(&h1);
+              lv.x = *reinterpret_cast<uint32_t*>(&l0); lv.y = *reinterpret_cast<uint32_t*>(&l1);
+              *reinterpret_cast<uint2*>(out_hi + (size_t)grow * lds + gcol) = hv;
+              *reinterpret_cast<uint2*>(out_lo + (size_t)grow * lds + gcol) = lv;
+            }
+          }
+        }
+        __syncwarp();
+      };
+
+      if constexpr (EPI == EDA_EPI_BIAS || EPI == EDA_EPI_BIAS_RELU) {
+        for (int c = 0; c < GBN / 32; ++c) {
+          if (n0 + c * 32 >= p.N) break;
+          float v[32];
+          tmem_ld32(trow + c * 32, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int col = n0 + c * 32 + j;
+            v[j] += (p.bias && col < p.N) ? __ldg(p.bias + col) : 0.f;
+            if (EPI == EDA_EPI_BIAS_RELU) v[j] = fmaxf(v[j], 0.f);
+          }
+          store_chunk(v, c, n0, p.Chi, p.Clo, p.lds);
+        }
+      } else if constexpr (EPI == GEPI_QKV) {
+        // n_blk 0: q (pre-scaled), 1: k -> split (M, 2*GBN); 2: v -> transposed per (b, h)
+        const int row = m0 + q * 32 + lane;
+        const int b = row / p.T, t = row - b * p.T;
+        for (int c = 0; c < GBN / 32; ++c) {
+          float v[32];
+          tmem_ld32(trow + c * 32, v);
+          const float sc = n_blk == 0 ? p.q_scale : 1.0f;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = (v[j] + __ldg(p.bias + n0 + c * 32 + j)) * sc;
+          if (n_blk < 2) {
+            store_chunk(v, c, n0, p.Chi, p.Clo, p.lds);
+          } else if (row < p.M) {
+            const int h = c >> 1, d0 = (c & 1) * 32;
+            const size_t base = ((size_t)(b * p.H + h) * 64 + d0) * p.Tp + t;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const bf16 hv = __float2bfloat16_rn(v[j]);
+              p.vt_hi[base + (size_t)j * p.Tp] = hv;
+              p.vt_lo[base + (size_t)j * p.Tp] = __float2bfloat16_rn(v[j] - __bfloat162float(hv));
+            }
+          }
+        }
+      } else {
+        // LayerNorm epilogues: N == 256 == GBN, the thread owns the whole row (kept in TMEM).
+        float sum = 0.f;
+        for (int c = 0; c < GBN / 32; ++c) {
+          float v[32];
+          tmem_ld32(trow + c * 32, v);
+          if constexpr (EPI == EDA_EPI_BIAS_RES_LN) {
+            // coalesced read of the residual chunk, transposed through smem to thread-per-row
+#pragma unroll
+            for (int it2 = 0; it2 < 8; ++it2) {
+              const int r = it2 * 4 + srow, grow = m0 + q * 32 + r;
+              float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (grow < p.M) x = __ldg(reinterpret_cast<const float4*>(p.resid + (size_t)grow * p.ldr + c * 32 + scol));
+              *reinterpret_cast<float4*>(&stg[r * G_STG_LD + scol]) = x;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 x = *reinterpret_cast<const float4*>(&stg[lane * G_STG_LD + 4 * j]);
+              v[4 * j] += x.x; v[4 * j + 1] += x.y; v[4 * j + 2] += x.z; v[4 * j + 3] += x.w;
+            }
+            __syncwarp();
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { v[j] += __ldg(p.bias + c * 32 + j); sum += v[j]; }
+          tmem_st32(trow + c * 32, v);
+        }
+        tmem_wait_st();
+        const float mean = sum * (1.0f / GBN);
+        float sq = 0.f;
+        for (int c = 0; c < GBN / 32; ++c) {
+          float v[32];
+          tmem_ld32(trow + c * 32, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { const float d = v[j] - mean; sq = fmaf(d, d, sq); }
+        }
+        const float rstd = 1.0f / sqrtf(sq * (1.0f / GBN) + 1e-5f);
+        for (int c = 0; c < GBN / 32; ++c) {
+          float v[32];
+          tmem_ld32(trow + c * 32, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            v[j] = (v[j] - mean) * rstd * __ldg(p.gamma + c * 32 + j) + __ldg(p.beta + c * 32 + j);
+          store_chunk(v, c, 0, p.Chi, p.Clo, p.lds);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[ab]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------- host ---------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  }
+  return fn;
+}
+
+// bf16 tensor maps with a SWIZZLE_128B box whose inner extent is 64 elements (128 B).  Encoding
+// costs a few microseconds on the host, so maps are cached on (pointer, geometry).
+struct TmapKey {
+  const void* ptr; uint64_t d0, d1, d2, s1, s2; uint32_t b1;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && d0 == o.d0 && d1 == o.d1 && d2 == o.d2 && s1 == o.s1 && s2 == o.s2 && b1 == o.b1;
+  }
+};
+struct TmapHash {
+  size_t operator()(const TmapKey& k) const {
+    size_t h = std::hash<const void*>()(k.ptr);
+    for (uint64_t v : {k.d0, k.d1, k.d2, k.s1, k.s2, (uint64_t)k.b1}) h = h * 1000003u ^ std::hash<uint64_t>()(v);
+    return h;
+  }
+};
+static std::unordered_map<TmapKey, CUtensorMap, TmapHash> g_tmaps;
+static std::mutex g_tmap_mu;
+
+// rank-3 view: dims (d0 inner, d1, d2), byte strides s1 (of d1) and s2 (of d2); box {64, b1, 1}
+static int make_tmap_impl(CUtensorMap* m, int rank, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2,
+                          uint64_t s1_bytes, uint64_t s2_bytes, uint32_t box_rows) {
+  const TmapKey key{ptr, d0, d1, d2, s1_bytes, s2_bytes, box_rows | (uint32_t(rank) << 16)};
+  {
+    std::lock_guard<std::mutex> g(g_tmap_mu);
+    auto it = g_tmaps.find(key);
+    if (it != g_tmaps.end()) { *m = it->second; return EDA_OK; }
+  }
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return EDA_ECUDA; }
+  cuuint64_t gdim[3] = {d0, d1, d2};
+  cuuint64_t gstr[2] = {s1_bytes, s2_bytes};
+  cuuint32_t box[3] = {64, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) dims=(%llu,%llu,%llu) strides=(%llu,%llu) ptr=%p", (int)r,
+              (unsigned long long)d0, (unsigned long long)d1, (unsigned long long)d2,
+              (unsigned long long)s1_bytes, (unsigned long long)s2_bytes, ptr);
+    return EDA_ECUDA;
+  }
+  std::lock_guard<std::mutex> g(g_tmap_mu);
+  if (g_tmaps.size() > 8192) g_tmaps.clear();
+  g_tmaps.emplace(key, *m);
+  return EDA_OK;
+}
+
+int make_tmap_bf16_3d(CUtensorMap* m, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1_bytes,
+                      uint64_t s2_bytes, uint32_t box_rows) {
+  return make_tmap_impl(m, 3, ptr, d0, d1, d2, s1_bytes, s2_bytes, box_rows);
+}
+
+// 2-D bf16 row-major (rows x cols, row stride ld elements) with a {64, box_rows} box
+int make_tmap_bf16(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  return make_tmap_impl(m, 2, ptr, cols, rows, 1, ld * 2, 0, box_rows);
+}
+
+int split_bf16(const float* src, int ld, int rows, int K, void* hi, void* lo, int ldk, cudaStream_t st) {
+  EDA_REQUIRE(src && hi && lo && rows > 0 && K > 0 && ldk >= K && ldk % 8 == 0, "eda_split_bf16: bad arguments (ldk must be a multiple of 8 and >= K)");
+  const int64_t n = (int64_t)rows * (ldk / 2);
+  split_bf16_kernel<<<(int)std::min<int64_t>(ceil_div<int64_t>(n, 256), num_sms() * 16), 256, 0, st>>>(
+      src, ld, rows, K, ldk, (bf16*)hi, (bf16*)lo);
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
+}
+
+template <int EPI>
+static int launch_gemm(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi, const CUtensorMap& b_lo,
+                       const GemmParams& p, cudaStream_t st) {
+  static bool attr = false;
+  if (!attr) {
+    EDA_CUDA(cudaFuncSetAttribute(gemm_split_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
+    attr = true;
+  }
+  const int n_tiles = ceil_div(p.N, GBN) * ceil_div(p.M, GBM);
+  gemm_split_kernel<EPI><<<std::min(n_tiles, num_sms()), 192, G_SMEM, st>>>(a_hi, a_lo, b_hi, b_lo, p);
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
+}
+
+// A: split (M x K, row stride lda elements), W: split (N x K, row stride ldw).
+int gemm_split(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
+               GemmParams p, int K, int epi, int prec, cudaStream_t st) {
+  EDA_REQUIRE(a_hi && a_lo && w_hi && w_lo && p.M > 0 && p.N > 0 && K > 0, "eda_gemm_split: bad arguments");
+  EDA_REQUIRE(lda % 8 == 0 && ldw % 8 == 0, "eda_gemm_split: operand row strides must be multiples of 8 elements");
+  EDA_REQUIRE(((uintptr_t)a_hi | (uintptr_t)a_lo | (uintptr_t)w_hi | (uintptr_t)w_lo) % 16 == 0, "eda_gemm_split: operands must be 16B aligned");
+  EDA_REQUIRE(prec == EDA_PREC_BF16X3 || prec == EDA_PREC_BF16, "eda_gemm_split: precision must be BF16X3 or BF16");
+  if (p.C) EDA_REQUIRE(p.ldc % 4 == 0 && (uintptr_t)p.C % 16 == 0, "eda_gemm_split: C must be 16B aligned with ldc %% 4 == 0");
+  if (p.Chi) EDA_REQUIRE(p.Clo && p.lds % 4 == 0 && p.N % 4 == 0 && ((uintptr_t)p.Chi | (uintptr_t)p.Clo) % 8 == 0, "eda_gemm_split: split output needs N %% 4 == 0, lds %% 4 == 0, 8B alignment");
+  const bool ln = epi == EDA_EPI_BIAS_LN || epi == EDA_EPI_BIAS_RES_LN;
+  if (ln) {
+    EDA_REQUIRE(p.N == 256 && p.gamma && p.beta && p.bias, "eda_gemm_split: LayerNorm epilogues need N == 256, bias, gamma, beta");
+    EDA_REQUIRE(epi != EDA_EPI_BIAS_RES_LN || (p.resid && p.ldr % 4 == 0 && (uintptr_t)p.resid % 16 == 0), "eda_gemm_split: residual missing/misaligned");
+  }
+  p.Kp = K;
+  p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
+  CUtensorMap ta_hi, ta_lo, tb_hi, tb_lo;
+  int rc;
+  if ((rc = make_tmap_bf16(&ta_hi, a_hi, p.M, K, lda, GBM)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16(&ta_lo, a_lo, p.M, K, lda, GBM)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16(&tb_hi, w_hi, p.N, K, ldw, GBN)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16(&tb_lo, w_lo, p.N, K, ldw, GBN)) != EDA_OK) return rc;
+  switch (epi) {
+    case EDA_EPI_BIAS: return launch_gemm<EDA_EPI_BIAS>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
+    case EDA_EPI_BIAS_RELU: return launch_gemm<EDA_EPI_BIAS_RELU>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
+    case EDA_EPI_BIAS_LN: return launch_gemm<EDA_EPI_BIAS_LN>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
+    case EDA_EPI_BIAS_RES_LN: return launch_gemm<EDA_EPI_BIAS_RES_LN>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
+    case GEPI_QKV: return launch_gemm<GEPI_QKV>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
+  }
+  set_error("eda_gemm_split: unknown epilogue %d", epi);
+  return EDA_EINVAL;
+}
+
+// grow-only scratch for eda_linear's on-the-fly operand split (stream-ordered reuse)
+static bf16* g_split[2] = {nullptr, nullptr};
+static size_t g_split_cap[2] = {0, 0};
+static int ensure_split(int which, size_t elems) {
+  if (elems > g_split_cap[which]) {
+    if (g_split[which]) { EDA_CUDA(cudaDeviceSynchronize()); EDA_CUDA(cudaFree(g_split[which])); }
+    g_split_cap[which] = elems + elems / 4;
+    EDA_CUDA(cudaMalloc(&g_split[which], g_split_cap[which] * sizeof(bf16)));
+  }
+  return EDA_OK;
+}
+
+// eda_linear on the tensor cores: fp32 operands are split on the fly, fp32 result.
+int linear_tc(const float* A, int lda, const float* W, int ldw, const float* bias, const float* resid, int ldr,
+              const float* gamma, const float* beta, float* C, int ldc, int M, int N, int K, int epi, int prec,
+              cudaStream_t st) {
+  const int Kp = (K + 7) / 8 * 8;
+  const size_t a_el = (size_t)M * Kp, w_el = (size_t)N * Kp;
+  int rc;
+  if ((rc = ensure_split(0, 2 * a_el)) != EDA_OK) return rc;
+  if ((rc = ensure_split(1, 2 * w_el)) != EDA_OK) return rc;
+  bf16 *a_hi = g_split[0], *a_lo = g_split[0] + a_el, *w_hi = g_split[1], *w_lo = g_split[1] + w_el;
+  if ((rc = split_bf16(A, lda, M, K, a_hi, a_lo, Kp, st)) != EDA_OK) return rc;
+  if ((rc = split_bf16(W, ldw, N, K, w_hi, w_lo, Kp, st)) != EDA_OK) return rc;
+  GemmParams p = {};
+  p.bias = bias; p.resid = resid; p.ldr = ldr; p.gamma = gamma; p.beta = beta;
+  p.C = C; p.ldc = ldc; p.M = M; p.N = N;
+  return gemm_split(a_hi, a_lo, Kp, w_hi, w_lo, Kp, p, Kp, epi, prec, st);
+}
+
+}  // namespace eda
+
+extern "C" {
+
+int eda_split_bf16(const float* src, int ld, int rows, int K, void* hi, void* lo, int ldk, void* stream) {
+  return eda::split_bf16(src, ld, rows, K, hi, lo, ldk, (cudaStream_t)stream);
+}
+
+int eda_gemm_split(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
+                   const float* bias, const float* resid, int ldr, const float* ln_gamma, const float* ln_beta,
+                   float* C, int ldc, void* c_hi, void* c_lo, int ldcs, int M, int N, int K, int epilogue,
+                   int prec, void* stream) {
+  EDA_REQUIRE(epilogue >= EDA_EPI_BIAS && epilogue <= EDA_EPI_BIAS_RES_LN, "eda_gemm_split: unknown epilogue %d", epilogue);
+  EDA_REQUIRE(C || c_hi, "eda_gemm_split: no output requested");
+  eda::GemmParams p = {};
+  p.bias = bias; p.resid = resid; p.ldr = ldr; p.gamma = ln_gamma; p.beta = ln_beta;
+  p.C = C; p.ldc = ldc; p.Chi = (eda::bf16*)c_hi; p.Clo = (eda::bf16*)c_lo; p.lds = ldcs; p.M = M; p.N = N;
+  return eda::gemm_split(a_hi, a_lo, lda, w_hi, w_lo, ldw, p, K, epilogue, prec, (cudaStream_t)stream);
+}
+
+int eda_gemm_qkv(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
+                 const float* bias, void* qk_hi, void* qk_lo, int ld_qk, void* vt_hi, void* vt_lo,
+                 int B, int T, int Tp, int D, int n_heads, int prec, void* stream) {
+  EDA_REQUIRE(D == eda::GBN && n_heads * 64 == D, "eda_gemm_qkv: D must be 256 with head_dim 64");
+  EDA_REQUIRE(bias && qk_hi && qk_lo && vt_hi && vt_lo && B > 0 && T > 0 && Tp >= T && Tp % 8 == 0, "eda_gemm_qkv: bad arguments");
+  EDA_REQUIRE(ld_qk >= 2 * D, "eda_gemm_qkv: ld_qk too small");
+  eda::GemmParams p = {};
+  p.bias = bias; p.Chi = (eda::bf16*)qk_hi; p.Clo = (eda::bf16*)qk_lo; p.lds = ld_qk;
+  p.M = B * T; p.N = 3 * D;
+  p.vt_hi = (eda::bf16*)vt_hi; p.vt_lo = (eda::bf16*)vt_lo; p.T = T; p.Tp = Tp; p.H = n_heads; p.q_scale = 0.125f;
+  return eda::gemm_split(a_hi, a_lo, lda, w_hi, w_lo, ldw, p, D, eda::GEPI_QKV, prec, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,361 @@
+// Multi-head self-attention forward on tcgen05 / TMEM / TMA (EDA_PREC_BF16X3 / BF16).
+//
+// softmax(q k^T / sqrt(64)) v per (batch, head), NO mask: the reference attends to the
+// -1-padded frames too (models.py:223).  Flash-style: one CTA owns 128 queries of one (b, h)
+// and streams 128-key tiles.
+//
+// Operands are split-bf16 pairs written by the QKV GEMM epilogue: q (pre-scaled by 1/8) and k
+// as K-major rows of a (B*T, 512) matrix, v TRANSPOSED per (b, h) as (64, Tp) so that keys are
+// the contraction-major dimension of the second product.  Every product is three MMAs
+// (hi.hi + hi.lo + lo.hi), fp32 accumulation in TMEM.
+//
+//   warp 0     TMA producer: Q once, then K_j / V_j tiles (single stage each; two CTAs share an
+//              SM, so one CTA's softmax overlaps the other's MMAs)
+//   warp 1     MMA issuer (one thread) + TMEM owner (256 columns: S/P 0..127, O 128..191)
+//   warps 2-5  softmax: thread = query row.  S -> running max / sum, P = exp(S - m) split into
+//              bf16 hi/lo and written BACK INTO TMEM over S (A operand of P.V comes from
+//              TMEM), O rescaled in TMEM when the running max moves; final O / l -> split bf16
+//              (and/or fp32) through a shared-memory transpose.
+#include <algorithm>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace eda {
+
+using namespace tc;
+typedef __nv_bfloat16 bf16;
+
+int make_tmap_bf16_3d(CUtensorMap* m, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1_bytes,
+                      uint64_t s2_bytes, uint32_t box_rows);
+
+constexpr int ABM = 128, ABN = 128, ADH = 64;
+constexpr int A_TILE16 = 128 * 64 * 2;                   // 16 KB: one 128-row x 64-col bf16 tile
+constexpr int A_OFF_Q = 0;                               // Q_hi, Q_lo
+constexpr int A_OFF_K = 2 * A_TILE16;                    // K_hi, K_lo
+constexpr int A_OFF_V = 4 * A_TILE16;                    // Vt_hi (2 chunks x 8 KB), Vt_lo
+constexpr int A_OFF_BAR = 6 * A_TILE16;
+constexpr int A_SMEM = 6 * A_TILE16 + 128 + 1024;
+constexpr int A_OST_LD = 68;                             // floats per staged output row
+constexpr uint32_t TM_S = 0, TM_O = 128;
+
+struct MhaParams {
+  int T, H, passes;
+  float* out; int ld_out;                 // optional fp32 (B*T, H*64)
+  bf16* out_hi; bf16* out_lo; int ld_os;  // optional split
+};
+
+// D[tmem] (+)= A[tmem] * B[smem desc]
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%16], "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15};"
+      ::"r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+        "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+        "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t pack_bf16(bf16 a, bf16 b) {   // a -> low half (element 2c), b -> high
+  __nv_bfloat162 v = __halves2bfloat162(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+__global__ void __launch_bounds__(192, 2)
+mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant__ CUtensorMap tmQK_lo,
+              const __grid_constant__ CUtensorMap tmV_hi, const __grid_constant__ CUtensorMap tmV_lo,
+              const MhaParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bar_q = reinterpret_cast<uint64_t*>(smem + A_OFF_BAR);
+  uint64_t* k_full = bar_q + 1;
+  uint64_t* k_empty = bar_q + 2;
+  uint64_t* v_full = bar_q + 3;
+  uint64_t* v_empty = bar_q + 4;
+  uint64_t* bar_s = bar_q + 5;
+  uint64_t* bar_p = bar_q + 6;
+  uint64_t* bar_o = bar_q + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * ABM, h = blockIdx.y, b = blockIdx.z;
+  const int n_kt = (p.T + ABN - 1) / ABN;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQK_hi); tma_prefetch_desc(&tmQK_lo); tma_prefetch_desc(&tmV_hi); tma_prefetch_desc(&tmV_lo);
+    mbar_init(bar_q, 1); mbar_init(k_full, 1); mbar_init(k_empty, 1); mbar_init(v_full, 1); mbar_init(v_empty, 1);
+    mbar_init(bar_s, 1); mbar_init(bar_p, 4); mbar_init(bar_o, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 256);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const bool x3 = p.passes == 3;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      mbar_expect_tx(bar_q, x3 ? 2 * A_TILE16 : A_TILE16);
+      tma_load_3d(smem + A_OFF_Q, &tmQK_hi, bar_q, h * ADH, q0, b);
+      if (x3) tma_load_3d(smem + A_OFF_Q + A_TILE16, &tmQK_lo, bar_q, h * ADH, q0, b);
+      for (int j = 0; j < n_kt; ++j) {
+        const uint32_t ph = j & 1;
+        mbar_wait(k_empty, ph ^ 1);
+        mbar_expect_tx(k_full, x3 ? 2 * A_TILE16 : A_TILE16);
+        tma_load_3d(smem + A_OFF_K, &tmQK_hi, k_full, p.H * ADH + h * ADH, j * ABN, b);
+        if (x3) tma_load_3d(smem + A_OFF_K + A_TILE16, &tmQK_lo, k_full, p.H * ADH + h * ADH, j * ABN, b);
+        mbar_wait(v_empty, ph ^ 1);
+        mbar_expect_tx(v_full, x3 ? 2 * A_TILE16 : A_TILE16);
+        tma_load_3d(smem + A_OFF_V, &tmV_hi, v_full, j * ABN, 0, b * p.H + h);
+        tma_load_3d(smem + A_OFF_V + 8192, &tmV_hi, v_full, j * ABN + 64, 0, b * p.H + h);
+        if (x3) {
+          tma_load_3d(smem + A_OFF_V + A_TILE16, &tmV_lo, v_full, j * ABN, 0, b * p.H + h);
+          tma_load_3d(smem + A_OFF_V + A_TILE16 + 8192, &tmV_lo, v_full, j * ABN + 64, 0, b * p.H + h);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc_s = idesc_bf16_f32(ABM, ABN), idesc_o = idesc_bf16_f32(ABM, ADH);
+      const uint32_t sbase = smem_u32(smem);
+      const uint64_t q_hi = smem_desc_sw128(sbase + A_OFF_Q), q_lo = smem_desc_sw128(sbase + A_OFF_Q + A_TILE16);
+      const uint64_t k_hi = smem_desc_sw128(sbase + A_OFF_K), k_lo = smem_desc_sw128(sbase + A_OFF_K + A_TILE16);
+      const uint32_t tS = tmem_base + TM_S, tO = tmem_base + TM_O;
+      const uint32_t tPhi = tS, tPlo = tS + 64;
+      mbar_wait(bar_q, 0);
+      for (int j = 0; j < n_kt; ++j) {
+        const uint32_t ph = j & 1;
+        mbar_wait(k_full, ph);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < ADH / 16; ++k) {
+          const uint64_t adv = uint64_t(k * 32 >> 4);
+          umma_bf16(tS, q_hi + adv, k_hi + adv, idesc_s, k != 0);
+          if (x3) {
+            umma_bf16(tS, q_hi + adv, k_lo + adv, idesc_s, 1);
+            umma_bf16(tS, q_lo + adv, k_hi + adv, idesc_s, 1);
+          }
+        }
+        umma_commit(k_empty);
+        umma_commit(bar_s);
+        mbar_wait(bar_p, ph);          // P_j is in TMEM (over S), O has been rescaled if needed
+        mbar_wait(v_full, ph);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < ABN / 16; ++k) {
+          const uint32_t voff = A_OFF_V + (k >> 2) * 8192 + (k & 3) * 32;
+          const uint64_t v_hi = smem_desc_sw128(sbase + voff), v_lo = smem_desc_sw128(sbase + voff + A_TILE16);
+          umma_bf16_ts(tO, tPhi + k * 8, v_hi, idesc_o, (j | k) != 0);
+          if (x3) {
+            umma_bf16_ts(tO, tPhi + k * 8, v_lo, idesc_o, 1);
+            umma_bf16_ts(tO, tPlo + k * 8, v_hi, idesc_o, 1);
+          }
+        }
+        umma_commit(v_empty);
+        if (j == n_kt - 1) umma_commit(bar_o);
+      }
+    }
+  } else {
+    // ===== softmax + output: warps 2..5, thread = query row (TMEM lane) =====
+    const int qd = warp & 3;
+    const uint32_t lane_off = uint32_t(qd * 32) << 16;
+    const uint32_t tS = tmem_base + TM_S + lane_off, tO = tmem_base + TM_O + lane_off;
+    constexpr float kLog2e = 1.4426950408889634f;
+    float m_cur = -INFINITY, l_sum = 0.f;
+    for (int j = 0; j < n_kt; ++j) {
+      mbar_wait(bar_s, j & 1);
+      tc_fence_after();
+      const int n_valid = min(ABN, p.T - j * ABN);      // keys of this tile that exist
+      // pass 1: row maximum
+      float mx = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float v[32];
+        tmem_ld32(tS + c * 32, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i < n_valid) ? v[i] : -INFINITY);
+      }
+      const float m_new = fmaxf(m_cur, mx);             // finite: key 0 of every tile exists
+      if (j > 0 && __any_sync(0xffffffffu, m_new > m_cur)) {
+        // O *= exp(m_old - m_new): every earlier P.V has completed (bar_s was committed after it)
+        const float alpha = exp2f((m_cur - m_new) * kLog2e);
+        l_sum *= alpha;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          float o[32];
+          tmem_ld32(tO + c * 32, o);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] *= alpha;
+          tmem_st32(tO + c * 32, o);
+        }
+      }
+      m_cur = m_new;
+      const float mb = m_new * kLog2e;
+      // pass 2: P = exp(S - m) -> split bf16, written over S (hi: cols 0..63, lo: cols 64..127)
+      uint32_t plo[4][16];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float v[32];
+        tmem_ld32(tS + c * 32, v);
+        uint32_t phi[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float p0 = exp2f(fmaf(v[i], kLog2e, -mb)), p1 = exp2f(fmaf(v[i + 1], kLog2e, -mb));
+          if (c * 32 + i >= n_valid) p0 = 0.f;
+          if (c * 32 + i + 1 >= n_valid) p1 = 0.f;
+          l_sum += p0 + p1;
+          const bf16 h0 = __float2bfloat16_rn(p0), h1 = __float2bfloat16_rn(p1);
+          phi[i >> 1] = pack_bf16(h0, h1);
+          plo[c][i >> 1] = pack_bf16(__float2bfloat16_rn(p0 - __bfloat162float(h0)),
+                                     __float2bfloat16_rn(p1 - __bfloat162float(h1)));
+        }
+        tmem_st16(tS + c * 16, phi);       // lands on S columns that were already consumed
+      }
+      if (x3) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tmem_st16(tS + 64 + c * 16, plo[c]);
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_p);
+    }
+    // ---- epilogue: O / l -> smem (thread = row) -> coalesced row stores -------------------
+    mbar_wait(bar_o, 0);
+    tc_fence_after();
+    const float inv = 1.0f / l_sum;
+    float* ost = reinterpret_cast<float*>(smem) + qd * 32 * A_OST_LD;     // Q/K tiles are dead now
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      float o[32];
+      tmem_ld32(tO + c * 32, o);
+#pragma unroll
+      for (int i = 0; i < 32; i += 4)
+        *reinterpret_cast<float4*>(&ost[lane * A_OST_LD + c * 32 + i]) =
+            make_float4(o[i] * inv, o[i + 1] * inv, o[i + 2] * inv, o[i + 3] * inv);
+    }
+    __syncwarp();
+    for (int r = 0; r < 32; ++r) {
+      const int q = q0 + qd * 32 + r;
+      if (q >= p.T) break;
+      const float2 x = *reinterpret_cast<const float2*>(&ost[r * A_OST_LD + 2 * lane]);
+      const size_t row = (size_t)b * p.T + q;
+      const int col = h * ADH + 2 * lane;
+      if (p.out) *reinterpret_cast<float2*>(p.out + row * p.ld_out + col) = x;
+      if (p.out_hi) {
+        const bf16 h0 = __float2bfloat16_rn(x.x), h1 = __float2bfloat16_rn(x.y);
+        *reinterpret_cast<uint32_t*>(p.out_hi + row * p.ld_os + col) = pack_bf16(h0, h1);
+        *reinterpret_cast<uint32_t*>(p.out_lo + row * p.ld_os + col) =
+            pack_bf16(__float2bfloat16_rn(x.x - __bfloat162float(h0)), __float2bfloat16_rn(x.y - __bfloat162float(h1)));
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
+// ------------------------------------------------------------------------- host ---------
+int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
+              int B, int T, int H, float* out, int ld_out, void* out_hi, void* out_lo, int ld_os, int prec,
+              cudaStream_t st) {
+  EDA_REQUIRE(qk_hi && qk_lo && vt_hi && vt_lo && B > 0 && T > 0 && H > 0, "eda_mha_split: bad arguments");
+  EDA_REQUIRE(ld_qk >= 2 * H * ADH && ld_qk % 8 == 0 && Tp >= T && Tp % 8 == 0, "eda_mha_split: ld_qk / Tp must be multiples of 8 and large enough");
+  EDA_REQUIRE(out || (out_hi && out_lo), "eda_mha_split: no output requested");
+  EDA_REQUIRE(!out || (ld_out % 2 == 0 && (uintptr_t)out % 8 == 0), "eda_mha_split: fp32 output misaligned");
+  EDA_REQUIRE(!out_hi || (ld_os % 2 == 0), "eda_mha_split: split output stride must be even");
+  EDA_REQUIRE(B <= 65535 && H <= 65535, "eda_mha_split: B / n_heads too large for the grid");
+  EDA_REQUIRE(prec == EDA_PREC_BF16X3 || prec == EDA_PREC_BF16, "eda_mha_split: precision must be BF16X3 or BF16");
+  static bool attr = false;
+  if (!attr) {
+    EDA_CUDA(cudaFuncSetAttribute(mha_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, A_SMEM));
+    attr = true;
+  }
+  CUtensorMap tq_hi, tq_lo, tv_hi, tv_lo;
+  int rc;
+  const uint64_t row_b = (uint64_t)ld_qk * 2;
+  if ((rc = make_tmap_bf16_3d(&tq_hi, qk_hi, 2 * H * ADH, T, B, row_b, row_b * T, 128)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16_3d(&tq_lo, qk_lo, 2 * H * ADH, T, B, row_b, row_b * T, 128)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16_3d(&tv_hi, vt_hi, T, ADH, (uint64_t)B * H, (uint64_t)Tp * 2, (uint64_t)Tp * 2 * ADH, 64)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16_3d(&tv_lo, vt_lo, T, ADH, (uint64_t)B * H, (uint64_t)Tp * 2, (uint64_t)Tp * 2 * ADH, 64)) != EDA_OK) return rc;
+  MhaParams p = {};
+  p.T = T; p.H = H; p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
+  p.out = out; p.ld_out = ld_out; p.out_hi = (bf16*)out_hi; p.out_lo = (bf16*)out_lo; p.ld_os = ld_os;
+  dim3 grid(ceil_div(T, ABM), H, B);
+  mha_tc_kernel<<<grid, 192, A_SMEM, st>>>(tq_hi, tq_lo, tv_hi, tv_lo, p);
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
+}
+
+// fp32 qkv (B*T, 3*D) -> the split operand layout (eda_mha_fwd's compatibility path)
+__global__ void qkv_split_kernel(const float* __restrict__ qkv, int ld_qkv, int B, int T, int H, int Tp,
+                                 bf16* __restrict__ qk_hi, bf16* __restrict__ qk_lo,
+                                 bf16* __restrict__ vt_hi, bf16* __restrict__ vt_lo) {
+  const int D = H * ADH;
+  const int64_t n = (int64_t)B * T * 3 * D;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = i / (3 * D);
+    const int col = (int)(i - row * 3 * D);
+    float x = qkv[row * ld_qkv + col];
+    if (col < D) x *= 0.125f;
+    const bf16 hv = __float2bfloat16_rn(x), lv = __float2bfloat16_rn(x - __bfloat162float(hv));
+    if (col < 2 * D) {
+      qk_hi[row * 2 * D + col] = hv;
+      qk_lo[row * 2 * D + col] = lv;
+    } else {
+      const int b = (int)(row / T), t = (int)(row - (int64_t)b * T), hd = col - 2 * D;
+      const size_t o = ((size_t)b * D + hd) * Tp + t;     // (b*H + h)*64 + d == b*D + hd
+      vt_hi[o] = hv;
+      vt_lo[o] = lv;
+    }
+  }
+}
+
+static bf16* g_mha_scratch = nullptr;
+static size_t g_mha_cap = 0;
+
+int mha_tc(const float* qkv, int ld_qkv, float* out, int ld_out, int B, int T, int H, int prec, cudaStream_t st) {
+  const int D = H * ADH, Tp = (T + 7) / 8 * 8;
+  const size_t qk_el = (size_t)B * T * 2 * D, vt_el = (size_t)B * D * Tp;
+  const size_t need = 2 * qk_el + 2 * vt_el;
+  if (need > g_mha_cap) {
+    if (g_mha_scratch) { EDA_CUDA(cudaDeviceSynchronize()); EDA_CUDA(cudaFree(g_mha_scratch)); }
+    g_mha_cap = need + need / 4;
+    EDA_CUDA(cudaMalloc(&g_mha_scratch, g_mha_cap * sizeof(bf16)));
+  }
+  bf16 *qk_hi = g_mha_scratch, *qk_lo = qk_hi + qk_el, *vt_hi = qk_lo + qk_el, *vt_lo = vt_hi + vt_el;
+  const int64_t n = (int64_t)B * T * 3 * D;
+  qkv_split_kernel<<<(int)std::min<int64_t>(ceil_div<int64_t>(n, 256), num_sms() * 16), 256, 0, st>>>(
+      qkv, ld_qkv, B, T, H, Tp, qk_hi, qk_lo, vt_hi, vt_lo);
+  EDA_LAUNCH_CHECK();
+  return mha_split(qk_hi, qk_lo, 2 * D, vt_hi, vt_lo, Tp, B, T, H, out, ld_out, nullptr, nullptr, 0, prec, st);
+}
+
+}  // namespace eda
+
+extern "C" int eda_mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
+                             int Tp, int B, int T, int n_heads, float* out, int ld_out, void* out_hi, void* out_lo,
+                             int ld_os, int prec, void* stream) {
+  return eda::mha_split(qk_hi, qk_lo, ld_qk, vt_hi, vt_lo, Tp, B, T, n_heads, out, ld_out, out_hi, out_lo, ld_os,
+                        prec, (cudaStream_t)stream);
+}

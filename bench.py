@@ -209,16 +209,35 @@ def run_ours(args):
         L.PROFILE = None
         tot = sum(ms_ for v in prof.values() for ms_, _ in v)
         shares = {k: round(sum(m for m, _ in v) / tot, 4) for k, v in prof.items()}
-        lin_ms = sum(m for m, _ in prof["eda_linear"])
-        lin_fl = sum(flops_linear(a) for _, a in prof["eda_linear"])
+        gemm = [(m, flops_linear(a)) for m, a in prof.get("eda_linear", [])]
+        gemm += [(m, 2.0 * a[16] * a[17] * min(a[18], IN if a[18] == 352 else a[18])) for m, a in prof.get("eda_gemm_split", [])]
+        gemm += [(m, 2.0 * a[12] * a[13] * 3 * a[15] * a[15]) for m, a in prof.get("eda_gemm_qkv", [])]
+        lin_ms, lin_fl = sum(m for m, _ in gemm), sum(f for _, f in gemm)
         pk = peaks()
         issued = 3.0 if precision == "bf16x3" else 1.0
-        achieved = lin_fl / (lin_ms * 1e-3) / 1e12
-        roof = dict(bound="tensor", kernel="eda_linear", achieved=round(achieved, 2), peak=pk["tf_sust"],
+        achieved = lin_fl / (lin_ms * 1e-3) / 1e12            # ALGORITHMIC flops (2*M*N*K) per second
+        roof = dict(bound="tensor", kernel="gemm_split_kernel (eda_linear / eda_gemm_split / eda_gemm_qkv)",
+                    achieved=round(achieved, 2), peak=pk["tf_sust"],
                     unit="TFLOP/s", frac=round(achieved / pk["tf_sust"], 4), traffic=None,
                     peak_source=pk["src"] + " (bf16 sustained)", issued_mma_factor=issued,
-                    launches_per_step=len(prof["eda_linear"]), avg_launch_ms=round(lin_ms / len(prof["eda_linear"]), 4),
+                    issued_tflops=round(issued * achieved, 2), tensor_pipe_frac_issued=round(issued * achieved / pk["tf_sust"], 4),
+                    launches_per_step=len(gemm), avg_launch_ms=round(lin_ms / len(gemm), 4),
                     share_of_step=shares)
+        att = prof.get("eda_mha_split", [])
+        if att:
+            att_ms = sum(m for m, _ in att)
+            att_fl = sum(4.0 * a[6] * a[8] * a[7] * a[7] * 64 for _, a in att)
+            roof["attention"] = dict(bound="tensor", achieved=round(att_fl / (att_ms * 1e-3) / 1e12, 2),
+                                     peak=pk["tf_sust"], unit="TFLOP/s", issued_mma_factor=issued,
+                                     frac=round(att_fl / (att_ms * 1e-3) / 1e12 / pk["tf_sust"], 4),
+                                     tensor_pipe_frac_issued=round(issued * att_fl / (att_ms * 1e-3) / 1e12 / pk["tf_sust"], 4),
+                                     avg_launch_ms=round(att_ms / len(att), 4))
+        lstm_ms = sum(m for m, _ in prof.get("eda_lstm_attractors", []))
+        if lstm_ms:
+            lstm_bytes = B * T * (4 * 4 * UNITS + 4)           # xproj row (4 gates x 256 fp32) + perm index
+            roof["lstm"] = dict(bound="latency (T sequential steps)", achieved=round(lstm_bytes / (lstm_ms * 1e-3) / 1e9, 1),
+                                peak=pk["hbm"], unit="GB/s", frac=round(lstm_bytes / (lstm_ms * 1e-3) / 1e9 / pk["hbm"], 4),
+                                us_per_step=round(lstm_ms * 1e3 / (T + MAXSPK), 3))
         fe_ms = sum(m for k in ("eda_frontend_logmel", "eda_frontend_splice_subsample") for m, _ in prof[k])
         fe_bytes = B * T * (4 * SHIFT * SUB + 4 * IN)            # 4580 B / model frame @8 kHz
         roof["frontend"] = dict(bound="hbm", achieved=round(fe_bytes / (fe_ms * 1e-3) / 1e9, 1), peak=pk["hbm"],
@@ -276,7 +295,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16x3", "bf16"])
+    ap.add_argument("--precision", default="bf16x3", choices=["fp32", "bf16x3", "bf16"])
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     out = run_reference(args) if args.impl == "reference" else run_ours(args)

@@ -102,6 +102,42 @@ int eda_linear(const float* A, int lda, const float* W, int ldw, const float* bi
 int eda_mha_fwd(const float* qkv, int ld_qkv, float* out, int ld_out, int B, int T,
                 int n_heads, int head_dim, int prec, void* stream);
 
+/* ---------------------------------------------------- split-bf16 tensor-core pipeline --
+ * The tensor-core precisions keep activations in HBM as "split" bf16 pairs (x = hi + lo,
+ * hi = bf16(x), lo = bf16(x - hi); two bf16 matrices with the same row stride) so that a
+ * producing kernel's epilogue feeds the next kernel without a conversion pass.  These entry
+ * points are what TransformerEdaModel.forward_embedding (models.py:213-226) runs on for
+ * prec = EDA_PREC_BF16X3 / EDA_PREC_BF16; eda_linear / eda_mha_fwd above are the fp32-in,
+ * fp32-out forms of the same kernels.  hi/lo pointers are bf16 device pointers (void*).     */
+
+/* fp32 (rows, K) row stride ld -> hi, lo (rows, ldk) with columns [K, ldk) zeroed. ldk % 8 == 0. */
+int eda_split_bf16(const float* src, int ld, int rows, int K, void* hi, void* lo, int ldk, void* stream);
+
+/* eda_pad_pack (models.py:217) writing the split layout directly. src rows have stride ld_src. */
+int eda_pad_pack_split(const float* src, int ld_src, const int64_t* seq_off, const int32_t* lens, int B,
+                       int Tmax, int n_cols, float pad, void* dst_hi, void* dst_lo, int ld_dst, void* stream);
+
+/* nn.Linear + fused epilogue (EDA_EPI_*) on split operands: A (M,K) stride lda, W (N,K) stride
+ * ldw.  Outputs: fp32 C (may be NULL) and/or split c_hi/c_lo with stride ldcs (may be NULL). */
+int eda_gemm_split(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
+                   const float* bias, const float* resid, int ldr, const float* ln_gamma, const float* ln_beta,
+                   float* C, int ldc, void* c_hi, void* c_lo, int ldcs, int M, int N, int K, int epilogue,
+                   int prec, void* stream);
+
+/* The packed in_proj of nn.MultiheadAttention (in_proj_weight (3D, D)): rows are (b, t), t < T.
+ * q (pre-scaled by 1/sqrt(head_dim)) and k go to split qk (B*T, ld_qk >= 2D) as [q | k];
+ * v goes TRANSPOSED per (b, head) to split vt ((B*n_heads*64), Tp): vt[(b*H + h)*64 + d][t],
+ * Tp >= T, Tp % 8 == 0.  D must be 256.                                                       */
+int eda_gemm_qkv(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
+                 const float* bias, void* qk_hi, void* qk_lo, int ld_qk, void* vt_hi, void* vt_lo,
+                 int B, int T, int Tp, int D, int n_heads, int prec, void* stream);
+
+/* eda_mha_fwd on the layouts eda_gemm_qkv writes.  Outputs (B*T, n_heads*64): fp32 `out`
+ * (may be NULL) and/or split out_hi/out_lo (may be NULL).                                     */
+int eda_mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
+                  int Tp, int B, int T, int n_heads, float* out, int ld_out, void* out_hi, void* out_lo,
+                  int ld_os, int prec, void* stream);
+
 /* --------------------------------------------------------------------- EDA -------
  * LstmEncoderDedecoderAttractor.forward (encoder_decoder_attractor.py:19-59) on the
  * frames shuffled by models.py:228-232.

@@ -33,6 +33,11 @@ SIGNATURES = {
     "eda_pad_pack": (_i, [_p, _p, _p, _i, _i, _i, _f, _p, _i, _p]),
     "eda_linear": (_i, [_p, _i, _p, _i, _p, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "eda_mha_fwd": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "eda_split_bf16": (_i, [_p, _i, _i, _i, _p, _p, _i, _p]),
+    "eda_pad_pack_split": (_i, [_p, _i, _p, _p, _i, _i, _i, _f, _p, _p, _i, _p]),
+    "eda_gemm_split": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "eda_gemm_qkv": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "eda_mha_split": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _i, _p, _p, _i, _i, _p]),
     "eda_lstm_attractors": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p]),
     "eda_attractor_head": (_i, [_p, _p, _p, _i, _i, _i, _p, _i, _p, _p]),
     "eda_posterior": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p, _p]),

@@ -11,6 +11,7 @@ int mha_tc(const float*, int, float*, int, int, int, int, int, cudaStream_t);
 int lstm_attractors(const float*, const int32_t*, const int32_t*, const int32_t*, const float*,
                     const float*, const float*, int, int, int, int, float*, float*, cudaStream_t);
 int pad_pack(const float*, const int64_t*, const int32_t*, int, int, int, float, float*, int, cudaStream_t);
+int pad_pack_split(const float*, int, const int64_t*, const int32_t*, int, int, int, float, void*, void*, int, cudaStream_t);
 int attractor_head(const float*, const float*, const float*, int, int, int, float*, int, float*, cudaStream_t);
 int posterior(const float*, int, const float*, int, int, int, int, int, float, float*, float*, uint8_t*, cudaStream_t);
 int pit_loss(const float*, const float*, const int32_t*, int, int, int, float*, int64_t*, float*, int32_t*, cudaStream_t);
@@ -23,6 +24,12 @@ extern "C" {
 int eda_pad_pack(const float* src, const int64_t* seq_off, const int32_t* lens, int B, int Tmax,
                  int n_cols, float pad, float* dst, int ld_dst, void* stream) {
   return eda::pad_pack(src, seq_off, lens, B, Tmax, n_cols, pad, dst, ld_dst, (cudaStream_t)stream);
+}
+
+int eda_pad_pack_split(const float* src, int ld_src, const int64_t* seq_off, const int32_t* lens, int B,
+                       int Tmax, int n_cols, float pad, void* dst_hi, void* dst_lo, int ld_dst, void* stream) {
+  EDA_REQUIRE(src && seq_off && lens && dst_hi && dst_lo, "eda_pad_pack_split: null argument");
+  return eda::pad_pack_split(src, ld_src, seq_off, lens, B, Tmax, n_cols, pad, dst_hi, dst_lo, ld_dst, (cudaStream_t)stream);
 }
 
 int eda_linear(const float* A, int lda, const float* W, int ldw, const float* bias,

@@ -2,6 +2,8 @@
 // fused posterior (bmm + sigmoid + threshold).
 #include <algorithm>
 
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace eda {
@@ -29,6 +31,41 @@ int pad_pack(const float* src, const int64_t* seq_off, const int32_t* lens, int 
   const int64_t n_rows = (int64_t)B * Tmax;
   const int blocks = (int)std::min<int64_t>(ceil_div<int64_t>(n_rows, 8), (int64_t)num_sms() * 8);
   pad_pack_kernel<<<blocks, 256, 0, st>>>(src, seq_off, lens, Tmax, n_cols, pad, dst, ld_dst, n_rows);
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
+}
+
+// pad_sequence(-1) straight into the split-bf16 operand layout of the tensor-core GEMMs:
+// hi = bf16(x), lo = bf16(x - hi); columns [n_cols, ld_dst) are zero.  One bf16x2 per thread.
+__global__ void pad_pack_split_kernel(const float* __restrict__ src, const int64_t* __restrict__ seq_off,
+                                      const int32_t* __restrict__ lens, int Tmax, int n_cols, int ld_src, float pad,
+                                      __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo, int ld_dst,
+                                      int64_t n_rows) {
+  const int warps_per_block = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31;
+  for (int64_t row = (int64_t)blockIdx.x * warps_per_block + (threadIdx.x >> 5); row < n_rows;
+       row += (int64_t)gridDim.x * warps_per_block) {
+    const int b = (int)(row / Tmax), t = (int)(row % Tmax);
+    const bool valid = t < lens[b];
+    const float* s = src + (seq_off[b] + t) * (int64_t)ld_src;
+    for (int c = lane * 2; c < ld_dst; c += 64) {
+      const float x0 = c < n_cols ? (valid ? __ldg(s + c) : pad) : 0.f;
+      const float x1 = c + 1 < n_cols ? (valid ? __ldg(s + c + 1) : pad) : 0.f;
+      const __nv_bfloat16 h0 = __float2bfloat16_rn(x0), h1 = __float2bfloat16_rn(x1);
+      *reinterpret_cast<__nv_bfloat162*>(hi + row * ld_dst + c) = __halves2bfloat162(h0, h1);
+      *reinterpret_cast<__nv_bfloat162*>(lo + row * ld_dst + c) = __halves2bfloat162(
+          __float2bfloat16_rn(x0 - __bfloat162float(h0)), __float2bfloat16_rn(x1 - __bfloat162float(h1)));
+    }
+  }
+}
+
+int pad_pack_split(const float* src, int ld_src, const int64_t* seq_off, const int32_t* lens, int B, int Tmax,
+                   int n_cols, float pad, void* hi, void* lo, int ld_dst, cudaStream_t st) {
+  EDA_REQUIRE(ld_dst >= n_cols && ld_dst % 8 == 0 && ld_src >= n_cols && B > 0 && Tmax > 0, "eda_pad_pack_split: bad sizes");
+  const int64_t n_rows = (int64_t)B * Tmax;
+  const int blocks = (int)std::min<int64_t>(ceil_div<int64_t>(n_rows, 8), (int64_t)num_sms() * 8);
+  pad_pack_split_kernel<<<blocks, 256, 0, st>>>(src, seq_off, lens, Tmax, n_cols, ld_src, pad,
+                                                (__nv_bfloat16*)hi, (__nv_bfloat16*)lo, ld_dst, n_rows);
   EDA_LAUNCH_CHECK();
   return EDA_OK;
 }

@@ -49,11 +49,19 @@ class LstmEncoderDedecoderAttractor(nn.Module):
 
     def attractors(self, emb2d: torch.Tensor, perm: torch.Tensor, lens_dev: torch.Tensor,
                    lens_host: List[int], B: int, Tmax: int, n_dec: int,
-                   n_spk_label: int = -1):
+                   n_spk_label: int = -1, emb_split=None):
         """emb2d (B*Tmax, D) UNshuffled; perm (B, Tmax) int32 frame order per sequence.
         Returns attractors (B, n_dec, D), probs (B, n_dec), attractor loss (1,) or None."""
         w = self._prepared()
-        xproj = ops.linear(emb2d, w["w_ih"], w["b_enc"], L.EPI_BIAS, self.precision)
+        if emb_split is not None and self.precision != L.PREC_FP32:
+            # the encoder left emb as a split-bf16 pair: the input projection reads it directly
+            es, xproj = emb_split
+            if "sw_ih" not in w:
+                w["sw_ih"] = ops.split_bf16(w["w_ih"])
+            ops.gemm_split(es, w["sw_ih"], w["b_enc"], B * Tmax, 4 * self.input_size, self.input_size,
+                           L.EPI_BIAS, self.precision, out=xproj)
+        else:
+            xproj = ops.linear(emb2d, w["w_ih"], w["b_enc"], L.EPI_BIAS, self.precision)
         order = torch.tensor(sorted(range(B), key=lambda b: -lens_host[b]), dtype=torch.int32).to(
             emb2d.device, non_blocking=True)
         att, _ = ops.lstm_attractors(xproj, perm, lens_dev, order, w["u_enc"], w["u_dec"], w["b_dec"],

@@ -58,6 +58,7 @@ class TransformerEdaModel(nn.Module):
         self.init_weights()
         self.set_precision(precision or os.environ.get("EDA_B200_PRECISION", "fp32"))
         self._prep = None
+        self._ws = {}
 
     def set_precision(self, name: str) -> None:
         """'fp32' (CUDA-core FFMA), 'bf16x3' (tcgen05, split-bf16 operands) or 'bf16'."""
@@ -65,8 +66,7 @@ class TransformerEdaModel(nn.Module):
             raise ValueError(f"unknown precision {name!r}; choose from {sorted(L.PRECISIONS)}")
         self.precision_name, self.precision = name, L.PRECISIONS[name]
         self.eda.precision = self.precision
-        # attention core: fp32 CUDA-core kernel until the tcgen05 flash kernel replaces it
-        self.attn_precision = L.PREC_FP32
+        self.attn_precision = self.precision
 
     def init_weights(self):
         """models.py:207-210."""
@@ -91,10 +91,36 @@ class TransformerEdaModel(nn.Module):
                     w_2=g(lyr.linear2.weight), b_2=g(lyr.linear2.bias),
                     g1=g(lyr.norm1.weight), be1=g(lyr.norm1.bias),
                     g2=g(lyr.norm2.weight), be2=g(lyr.norm2.bias)))
-            self._prep = (key, dict(kpad=kpad, w_in=w_in, b_in=self.encoder.bias.detach().contiguous(),
-                                    g_in=self.encoder_norm.weight.detach().contiguous(),
-                                    be_in=self.encoder_norm.bias.detach().contiguous(), layers=layers))
+            prep = dict(kpad=kpad, w_in=w_in, b_in=self.encoder.bias.detach().contiguous(),
+                        g_in=self.encoder_norm.weight.detach().contiguous(),
+                        be_in=self.encoder_norm.bias.detach().contiguous(), layers=layers)
+            if w.is_cuda:
+                # split-bf16 copies of the weight matrices for the tensor-core pipeline (made once)
+                prep["ws_in"] = ops.split_bf16(w_in)
+                for lw in layers:
+                    for k in ("w_qkv", "w_o", "w_1", "w_2"):
+                        lw["s" + k] = ops.split_bf16(lw[k])
+            self._prep = (key, prep)
         return self._prep[1]
+
+    def _workspace(self, B: int, Tmax: int, dev):
+        """Persistent per-shape buffers of the tensor-core pipeline (stable pointers keep the
+        TMA descriptor cache of libeda_b200 warm)."""
+        key = (B, Tmax, str(dev))
+        ws = self._ws.get(key)
+        if ws is None:
+            if len(self._ws) >= 4:
+                self._ws.clear()
+            M, D, H = B * Tmax, self.n_units, self.n_heads
+            Tp = _round_up(Tmax, 8)
+            ws = dict(Tp=Tp, xin=ops.Split.empty(M, _round_up(self.in_size, 16), dev),
+                      xs=[ops.Split.empty(M, D, dev) for _ in range(2)],
+                      xf=[torch.empty((M, D), dtype=torch.float32, device=dev) for _ in range(2)],
+                      qk=ops.Split.empty(M, 2 * D, dev), vt=ops.Split.empty(B * H * (D // H), Tp, dev),
+                      att=ops.Split.empty(M, D, dev), ff=ops.Split.empty(M, self.dim_feedforward, dev),
+                      xproj=torch.empty((M, 4 * D), dtype=torch.float32, device=dev))
+            self._ws[key] = ws
+        return ws
 
     def _device(self) -> torch.device:
         dev = self.encoder.weight.device
@@ -131,8 +157,11 @@ class TransformerEdaModel(nn.Module):
         seq_off = meta[: B + 1]
         lens_dev = meta[B + 1:].to(torch.int32)
         flat = self._to_device_flat(src, dev)
-        x = ops.pad_pack(flat, seq_off, lens_dev, B, Tmax, w["kpad"], -1.0)
         P = self.precision
+        if P != L.PREC_FP32:
+            return self._embed_tc(flat, w, seq_off, lens_dev, ilens, B, Tmax, dev)
+        self._emb_split = None
+        x = ops.pad_pack(flat, seq_off, lens_dev, B, Tmax, w["kpad"], -1.0)
         x = ops.linear(x, w["w_in"], w["b_in"], L.EPI_BIAS_LN, P, gamma=w["g_in"], beta=w["be_in"])
         for lw in w["layers"]:
             qkv = ops.linear(x, lw["w_qkv"], lw["b_qkv"], L.EPI_BIAS, P)
@@ -141,6 +170,32 @@ class TransformerEdaModel(nn.Module):
             ff = ops.linear(x, lw["w_1"], lw["b_1"], L.EPI_BIAS_RELU, P)
             x = ops.linear(ff, lw["w_2"], lw["b_2"], L.EPI_BIAS_RES_LN, P, resid=x, gamma=lw["g2"], beta=lw["be2"])
         return x, ilens, lens_dev, seq_off, B, Tmax
+
+    def _embed_tc(self, flat, w, seq_off, lens_dev, ilens, B, Tmax, dev):
+        """The encoder on the split-bf16 tensor-core pipeline: every GEMM epilogue writes the
+        next kernel's operands (split bf16) and, where needed, the fp32 residual stream."""
+        P, D, H = self.precision, self.n_units, self.n_heads
+        M = B * Tmax
+        ws = self._workspace(B, Tmax, dev)
+        Tp = ws["Tp"]
+        xin, (sa, sb), (xa, xb) = ws["xin"], ws["xs"], ws["xf"]
+        ops.pad_pack_split(flat, seq_off, lens_dev, B, Tmax, xin, -1.0)
+        n_layers = len(w["layers"])
+        emb = torch.empty((M, D), dtype=torch.float32, device=dev)      # returned to the caller: fresh
+        ops.gemm_split(xin, w["ws_in"], w["b_in"], M, D, xin.ld, L.EPI_BIAS_LN, P, gamma=w["g_in"], beta=w["be_in"],
+                       out=xa if n_layers else emb, out_split=sa)
+        for i, lw in enumerate(w["layers"]):
+            last = i == n_layers - 1
+            ops.gemm_qkv(sa, lw["sw_qkv"], lw["b_qkv"], ws["qk"], ws["vt"], B, Tmax, Tp, D, H, P)
+            ops.mha_split(ws["qk"], ws["vt"], B, Tmax, Tp, H, self.attn_precision, out_split=ws["att"])
+            ops.gemm_split(ws["att"], lw["sw_o"], lw["b_o"], M, D, D, L.EPI_BIAS_RES_LN, P, resid=xa,
+                           gamma=lw["g1"], beta=lw["be1"], out=xb, out_split=sb)
+            ops.gemm_split(sb, lw["sw_1"], lw["b_1"], M, self.dim_feedforward, D, L.EPI_BIAS_RELU, P,
+                           out_split=ws["ff"])
+            ops.gemm_split(ws["ff"], lw["sw_2"], lw["b_2"], M, D, self.dim_feedforward, L.EPI_BIAS_RES_LN, P,
+                           resid=xb, gamma=lw["g2"], beta=lw["be2"], out=emb if last else xa, out_split=sa)
+        self._emb_split = (sa, ws["xproj"])
+        return emb, ilens, lens_dev, seq_off, B, Tmax
 
     @staticmethod
     def _draw_perm(ilens: List[int], Tmax: int, dev, perms=None) -> Tensor:
@@ -170,7 +225,8 @@ class TransformerEdaModel(nn.Module):
         label = ops.pad_pack(self._to_device_flat(list(ts), dev), seq_off, lens_dev, B, Tmax, S, -1.0)
         label = label.view(B, Tmax, S)
         perm = self._draw_perm(ilens, Tmax, dev)
-        att, probs, loss_att = self.eda.attractors(x, perm, lens_dev, ilens, B, Tmax, S + 1, n_spk_label=S)
+        att, probs, loss_att = self.eda.attractors(x, perm, lens_dev, ilens, B, Tmax, S + 1, n_spk_label=S,
+                                                   emb_split=self._emb_split)
         pred, _, _ = ops.posterior(x, att, B, Tmax, S, want_logits=True, want_post=False)
         loss_pit, min_idx, label_perm, _ = ops.pit_loss(pred, label, lens_dev)
         counts = ops.der_counters(pred, label_perm, lens_dev)
@@ -196,7 +252,8 @@ class TransformerEdaModel(nn.Module):
         uint8 decisions of bin/make_rttm.py:29 in ``self.last['labels']``."""
         x, ilens, lens_dev, _, B, Tmax = self._embed(src)
         perm = self._draw_perm(ilens, Tmax, x.device, perms)
-        att, probs, _ = self.eda.attractors(x, perm, lens_dev, ilens, B, Tmax, max_n_speakers)
+        att, probs, _ = self.eda.attractors(x, perm, lens_dev, ilens, B, Tmax, max_n_speakers,
+                                            emb_split=self._emb_split)
         n_att = max_n_speakers - 1
         _, post, labels = ops.posterior(x, att, B, Tmax, n_att,
                                         threshold=0.5 if activity_threshold is None else activity_threshold,

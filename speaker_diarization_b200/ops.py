@@ -113,3 +113,73 @@ def der_counters(pred: Tensor, label_perm: Tensor, lens: Tensor) -> Tensor:
     L.call("eda_der_counters", L.ptr(_f32(pred)), L.ptr(_f32(label_perm)), L.ptr(lens), B, T, S,
            L.ptr(counts), L.stream())
     return counts
+
+
+# ------------------------------------------------------- split-bf16 tensor-core pipeline ----
+class Split:
+    """A matrix held as a split-bf16 pair (x = hi + lo): two (rows, ld) bf16 CUDA tensors."""
+    __slots__ = ("hi", "lo")
+
+    def __init__(self, hi: Tensor, lo: Tensor):
+        assert hi.dtype == torch.bfloat16 and lo.dtype == torch.bfloat16 and hi.shape == lo.shape
+        assert hi.is_contiguous() and lo.is_contiguous() and hi.is_cuda
+        self.hi, self.lo = hi, lo
+
+    @classmethod
+    def empty(cls, rows: int, cols: int, device) -> "Split":
+        buf = torch.empty((2, rows, cols), dtype=torch.bfloat16, device=device)
+        return cls(buf[0], buf[1])
+
+    @property
+    def rows(self) -> int:
+        return self.hi.shape[0]
+
+    @property
+    def ld(self) -> int:
+        return self.hi.shape[1]
+
+    def float(self) -> Tensor:
+        return self.hi.float() + self.lo.float()
+
+
+def split_bf16(x: Tensor, ldk: int = 0, out: Optional[Split] = None) -> Split:
+    """fp32 (rows, K) -> Split (rows, ldk), zero padded; ldk defaults to K rounded up to 8."""
+    _f32(x)
+    rows, K = x.shape
+    ldk = ldk or (K + 7) // 8 * 8
+    out = out or Split.empty(rows, ldk, x.device)
+    L.call("eda_split_bf16", L.ptr(x), x.stride(0), rows, K, L.ptr(out.hi), L.ptr(out.lo), ldk, L.stream())
+    return out
+
+
+def pad_pack_split(flat: Tensor, seq_off: Tensor, lens: Tensor, B: int, Tmax: int, out: Split, pad: float) -> Split:
+    """flat (sum T_i, C) [row stride may exceed C] -> Split (B*Tmax, out.ld) padded with `pad`."""
+    assert flat.dtype == torch.float32 and flat.is_cuda and flat.stride(1) == 1
+    L.call("eda_pad_pack_split", flat.data_ptr(), flat.stride(0), L.ptr(seq_off), L.ptr(lens), B, Tmax,
+           flat.shape[1], float(pad), L.ptr(out.hi), L.ptr(out.lo), out.ld, L.stream())
+    return out
+
+
+def gemm_split(a: Split, w: Split, bias: Optional[Tensor], M: int, N: int, K: int, epilogue: int, prec: int,
+               resid: Optional[Tensor] = None, gamma: Optional[Tensor] = None, beta: Optional[Tensor] = None,
+               out: Optional[Tensor] = None, out_split: Optional[Split] = None) -> None:
+    """nn.Linear + fused epilogue on split operands; writes fp32 `out` and/or `out_split`."""
+    L.call("eda_gemm_split", L.ptr(a.hi), L.ptr(a.lo), a.ld, L.ptr(w.hi), L.ptr(w.lo), w.ld, L.ptr(bias),
+           L.ptr(resid), resid.stride(0) if resid is not None else 0, L.ptr(gamma), L.ptr(beta),
+           L.ptr(out), out.stride(0) if out is not None else 0,
+           L.ptr(out_split.hi) if out_split else None, L.ptr(out_split.lo) if out_split else None,
+           out_split.ld if out_split else 0, M, N, K, epilogue, prec, L.stream())
+
+
+def gemm_qkv(a: Split, w: Split, bias: Tensor, qk: Split, vt: Split, B: int, T: int, Tp: int, D: int,
+             n_heads: int, prec: int) -> None:
+    L.call("eda_gemm_qkv", L.ptr(a.hi), L.ptr(a.lo), a.ld, L.ptr(w.hi), L.ptr(w.lo), w.ld, L.ptr(bias),
+           L.ptr(qk.hi), L.ptr(qk.lo), qk.ld, L.ptr(vt.hi), L.ptr(vt.lo), B, T, Tp, D, n_heads, prec, L.stream())
+
+
+def mha_split(qk: Split, vt: Split, B: int, T: int, Tp: int, n_heads: int, prec: int,
+              out: Optional[Tensor] = None, out_split: Optional[Split] = None) -> None:
+    L.call("eda_mha_split", L.ptr(qk.hi), L.ptr(qk.lo), qk.ld, L.ptr(vt.hi), L.ptr(vt.lo), Tp, B, T, n_heads,
+           L.ptr(out), out.stride(0) if out is not None else 0,
+           L.ptr(out_split.hi) if out_split else None, L.ptr(out_split.lo) if out_split else None,
+           out_split.ld if out_split else 0, prec, L.stream())

@@ -156,6 +156,10 @@ int eda_lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* 
                         int B, int Tmax, int D, int n_dec,
                         float* attractors, float* hc_out, void* stream);
 
+/* Number of 8-CTA clusters of the recurrence kernel the device keeps resident at once; each
+ * advances 4 sequences, so batches above 4x this value take more than one wave.            */
+int eda_lstm_max_active_clusters(void);
+
 /* Existence head: probs[b,n] = sigmoid(attractors[b,n,:] . w + bias)
  * (encoder_decoder_attractor.py:50-54) and, when n_spk_label >= 0, the attractor loss of
  * models.py:350-371 (BCE-with-logits applied to the probabilities against

@@ -39,6 +39,7 @@ SIGNATURES = {
     "eda_gemm_qkv": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "eda_mha_split": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _i, _p, _p, _i, _i, _p]),
     "eda_lstm_attractors": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p]),
+    "eda_lstm_max_active_clusters": (_i, []),
     "eda_attractor_head": (_i, [_p, _p, _p, _i, _i, _i, _p, _i, _p, _p]),
     "eda_posterior": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p, _p]),
     "eda_pit_loss": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p]),

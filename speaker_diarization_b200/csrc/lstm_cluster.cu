@@ -3,15 +3,24 @@
 // Reference: encoder_decoder_attractor.py:36-40 (packed encoder LSTM over the shuffled
 // frames, decoder LSTM on zero inputs seeded with the encoder's final (h, c)).
 //
-// One cluster of 8 CTAs advances G sequences together.  CTA `c` of the cluster owns hidden
-// units [32c, 32c+32), i.e. the 128 gate rows {i,f,g,o} x 32 units of W_hh.  Those rows stay
-// RESIDENT IN REGISTERS for the whole sequence (128 rows x 256 k = 128 fp32 per thread at
-// 256 threads), so the per-step critical path is: broadcast-read h from shared memory ->
-// 128*G FFMA per thread -> combine the two k-halves through shared memory -> cell update ->
-// write the 32 new h values to all 8 CTAs through distributed shared memory -> one cluster
-// barrier.  The input projection emb.W_ih^T + b is hoisted out as a GEMM (eda_linear) and
-// the random frame shuffle (models.py:228-232) is applied as an index into it.
+// One cluster of 8 CTAs advances G = 4 sequences together.  CTA `c` owns hidden units
+// [32c, 32c+32), i.e. the 128 gate rows {i,f,g,o} x 32 units of W_hh, RESIDENT IN REGISTERS
+// for the whole sequence: thread (warp w, lane = rg*8 + kc) holds the 4 gate rows of unit
+// u = 4w + rg restricted to the k-slice {4(kc + 8i) + j : i < 8, j < 4} (128 fp32).
+// Per step:
+//   wait on the local mbarrier until all 8 CTAs' slices of h_t have landed in shared memory
+//   -> 8 conflict-free LDS.128 per sequence -> 256 packed FFMA2 (fma.rn.f32x2)
+//   -> warp-shuffle transpose-reduction over the 8 k-slices (16 SHFL: the 16 (gate, sequence)
+//      partial sums end up as 4 gates of ONE sequence per lane)
+//   -> cell update in registers -> the CTA's 32 x G new h values are staged in shared memory
+//      and pushed into the next h buffer of all 8 CTAs with ONE 512-byte cp.async.bulk per
+//      destination (distributed shared memory), whose byte count completes the consumer's
+//      mbarrier: no cluster-wide barrier in the loop, 8 barrier transactions per step.
+// The input projection emb.W_ih^T + b is hoisted out as a tensor-core GEMM and the random
+// frame shuffle (models.py:228-232) is applied as an index into it.
 #include <cooperative_groups.h>
+
+#include <algorithm>
 
 #include "common.cuh"
 
@@ -22,20 +31,70 @@ namespace eda {
 constexpr int kD = 256;       // hidden size
 constexpr int kCluster = 8;   // CTAs per cluster
 constexpr int kUnits = kD / kCluster;  // 32 hidden units per CTA
+// Sequences per cluster (template parameter kG): 4 when ceil(B/4) clusters fit the device at
+// once (15 on a B200), otherwise 5..8 so that the whole batch still runs as ONE wave.
 
-__device__ __forceinline__ void load_w_rows(float (&w)[128], const float* __restrict__ W, int cta,
-                                            int r_local, int kh) {
-  // local row r_local = gate*32 + unit  ->  global row gate*256 + 32*cta + unit
-  const int grow = (r_local >> 5) * kD + cta * kUnits + (r_local & 31);
-  const float4* src = reinterpret_cast<const float4*>(W + (size_t)grow * kD + kh * 128);
+__device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t map_rank(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+// local shared memory -> a peer CTA's shared memory, completing the peer's mbarrier
+__device__ __forceinline__ void bulk_push(uint32_t raddr, uint32_t laddr, uint32_t bytes, uint32_t rbar) {
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(raddr), "r"(laddr), "r"(bytes), "r"(rbar) : "memory");
+}
+__device__ __forceinline__ void bar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void bar_arm(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool bar_try(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, P;\n\t}"
+      : "=r"(ok) : "r"(s_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void bar_wait(uint64_t* bar, uint32_t parity) {
+  if (bar_try(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!bar_try(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) { __trap(); }   // protocol bug -> launch error, never a hang
+  }
+}
+// packed fp32x2 FMA (Blackwell FFMA2): d = a * b + c on both halves
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+  return (uint64_t)__float_as_uint(lo) | ((uint64_t)__float_as_uint(hi) << 32);
+}
+__device__ __forceinline__ float sum2(uint64_t v) {
+  return __uint_as_float((uint32_t)v) + __uint_as_float((uint32_t)(v >> 32));
+}
+
+// w2[gate][2*i + {0,1}] = packed (W[row][4(kc+8i)+0..1]), (W[row][4(kc+8i)+2..3])
+__device__ __forceinline__ void load_w(uint64_t (&w2)[4][16], const float* __restrict__ W, int cta, int u, int kc) {
 #pragma unroll
-  for (int i = 0; i < 32; ++i) {
-    float4 v = __ldg(src + i);
-    w[4 * i + 0] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+  for (int gate = 0; gate < 4; ++gate) {
+    const float4* src = reinterpret_cast<const float4*>(W + (size_t)(gate * kD + cta * kUnits + u) * kD);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 v = __ldg(src + kc + 8 * i);
+      w2[gate][2 * i] = pack2(v.x, v.y);
+      w2[gate][2 * i + 1] = pack2(v.z, v.w);
+    }
   }
 }
 
-template <int G>
+template <int kG>
 __global__ void __launch_bounds__(256, 1)
 lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__ perm,
                     const int32_t* __restrict__ lens, const int32_t* __restrict__ order,
@@ -46,137 +105,225 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
   const int cta = (int)cluster.block_rank();
   const int group = blockIdx.x / kCluster;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int kh = warp & 1;                    // which half of k this warp reduces
-  const int r_local = (warp >> 1) * 32 + lane;  // gate row (0..127) this thread accumulates
+  const int rg = lane >> 3, kc = lane & 7;
+  const int u = warp * 4 + rg;                         // local hidden unit of this lane
+  // sequence whose gates end up in this lane after the reduction: kG <= 4 leaves every sum in
+  // two lanes (kc, kc^1); kG > 4 uses all 8 k-slice lanes for 8 distinct sequences
+  const int seq = kG <= 4 ? ((kc >> 2) & 1) * 2 + ((kc >> 1) & 1) : kc;
+  const bool owner = kG <= 4 ? ((kc & 1) == 0 && seq < kG) : (kc < kG);   // lane that stores results
 
-  __shared__ __align__(16) float hs[2][G][kD];     // h_{t-1} of the G sequences, double buffered
-  __shared__ float part[2][G][128];                // k-half partial sums
-  __shared__ int s_seq[G], s_len[G];
+  // h_t double buffered, laid out [source CTA][sequence][unit] so that a CTA's slice is 512 B
+  __shared__ __align__(128) float hs[2][kCluster][kG][kUnits];
+  __shared__ __align__(128) float hstage[2][kG][kUnits];   // this CTA's new slice, double buffered
+  __shared__ __align__(8) uint64_t bars[2];
+  __shared__ int s_seq[kG], s_len[kG];
 
-  if (tid < G) {
-    int slot = group * G + tid;
+  if (tid < kG) {
+    const int slot = group * kG + tid;
     int b = -1, n = 0;
     if (slot < B) { b = order ? order[slot] : slot; n = lens[b]; }
     s_seq[tid] = b; s_len[tid] = n;
   }
-  for (int i = tid; i < 2 * G * kD; i += 256) (&hs[0][0][0])[i] = 0.f;
+  for (int i = tid; i < 2 * kG * kD; i += 256) (&hs[0][0][0][0])[i] = 0.f;
+  if (tid == 0) {
+    bar_init(&bars[0], 1); bar_init(&bars[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   __syncthreads();
   int max_len = 0;
 #pragma unroll
-  for (int g = 0; g < G; ++g) max_len = max(max_len, s_len[g]);
+  for (int g = 0; g < kG; ++g) max_len = max(max_len, s_len[g]);
+  const int n_total = max_len + n_dec;
+  constexpr uint32_t kStepBytes = kG * kD * 4;
+  if (tid == 0) {
+    if (n_total > 1) bar_arm(&bars[1], kStepBytes);    // h_1 (written during step 0)
+    if (n_total > 2) bar_arm(&bars[0], kStepBytes);    // h_2
+  }
 
-  float w[128];
-  load_w_rows(w, w_enc, cta, r_local, kh);
+  uint64_t w2[4][16];
+  load_w(w2, w_enc, cta, u, kc);
 
-  // cell-update role: thread (cg_ = tid / 32, unit = lane) for cg_ < G
-  const bool cell = warp < G;
-  const int my_b = cell ? s_seq[warp] : -1;
-  const int my_len = cell ? s_len[warp] : 0;
+  const int my_b = seq < kG ? s_seq[seq] : -1;
+  const int my_len = seq < kG ? s_len[seq] : 0;
   float c_state = 0.f, h_state = 0.f;
   float xg[4] = {0.f, 0.f, 0.f, 0.f};
   int p_next = 0;
-  const size_t col = (size_t)cta * kUnits + lane;
+  const size_t col = (size_t)cta * kUnits + u;
   auto load_x = [&](int p, float (&dst)[4]) {
     const float* row = xproj + ((size_t)my_b * Tmax + p) * (4 * kD) + col;
 #pragma unroll
     for (int x = 0; x < 4; ++x) dst[x] = __ldg(row + x * kD);
   };
-  if (cell && my_len > 0) {
+  if (my_len > 0) {   // (my_b >= 0 whenever my_len > 0)
     load_x(__ldg(perm + (size_t)my_b * Tmax), xg);
     if (my_len > 1) p_next = __ldg(perm + (size_t)my_b * Tmax + 1);
   }
-  cluster.sync();   // every CTA's hs is zeroed before anybody writes into it remotely
+  // thread r < 8 pushes this CTA's slice to rank r: remote slice / barrier addresses per buffer
+  uint32_t r_h0 = 0, r_h1 = 0, r_bar0 = 0, r_bar1 = 0;
+  if (tid < kCluster) {
+    r_h0 = map_rank(s_u32(&hs[0][cta][0][0]), tid); r_h1 = map_rank(s_u32(&hs[1][cta][0][0]), tid);
+    r_bar0 = map_rank(s_u32(&bars[0]), tid); r_bar1 = map_rank(s_u32(&bars[1]), tid);
+  }
+  cluster.sync();   // barriers initialised and h buffers zeroed everywhere before any remote write
 
-  for (int phase = 0; phase < 2; ++phase) {
-    const int n_steps = phase == 0 ? max_len : n_dec;
-    if (phase == 1) {
-      load_w_rows(w, w_dec, cta, r_local, kh);
-      if (cell) {
+  for (int gs = 0; gs < n_total; ++gs) {
+    const bool dec = gs >= max_len;
+    const int s = dec ? gs - max_len : gs;
+    const int cur = gs & 1;
+    if (gs == max_len) {              // switch to the decoder: new recurrent weights, bias-only input
+      load_w(w2, w_dec, cta, u, kc);
 #pragma unroll
-        for (int x = 0; x < 4; ++x) xg[x] = __ldg(dec_bias + x * kD + col);
-        if (hc_out && my_b >= 0) {
-          hc_out[((size_t)my_b * 2 + 0) * kD + col] = h_state;
-          hc_out[((size_t)my_b * 2 + 1) * kD + col] = c_state;
+      for (int x = 0; x < 4; ++x) xg[x] = __ldg(dec_bias + x * kD + col);
+      if (hc_out && my_b >= 0 && owner) {
+        hc_out[((size_t)my_b * 2 + 0) * kD + col] = h_state;
+        hc_out[((size_t)my_b * 2 + 1) * kD + col] = c_state;
+      }
+    }
+    // prefetch next step's input projection while the mat-vec runs
+    float xn[4] = {0.f, 0.f, 0.f, 0.f};
+    int p_next2 = 0;
+    if (!dec && s + 1 < my_len) {
+      load_x(p_next, xn);
+      if (s + 2 < my_len) p_next2 = __ldg(perm + (size_t)my_b * Tmax + s + 2);
+    }
+    if (gs > 0) {
+      bar_wait(&bars[cur], ((gs - 1) >> 1) & 1);       // all 8 slices of h_gs have landed
+      if (tid == 0 && gs + 2 < n_total) bar_arm(&bars[cur], kStepBytes);   // re-arm for h_{gs+2}
+    }
+    uint64_t acc[4][kG];
+#pragma unroll
+    for (int gate = 0; gate < 4; ++gate)
+#pragma unroll
+      for (int g = 0; g < kG; ++g) acc[gate][g] = 0ull;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+#pragma unroll
+      for (int g = 0; g < kG; ++g) {
+        const float4 hv = *reinterpret_cast<const float4*>(&hs[cur][i][g][4 * kc]);   // k = 32 i + 4 kc + j
+        const uint64_t h01 = pack2(hv.x, hv.y), h23 = pack2(hv.z, hv.w);
+#pragma unroll
+        for (int gate = 0; gate < 4; ++gate) {
+          acc[gate][g] = ffma2(w2[gate][2 * i], h01, acc[gate][g]);
+          acc[gate][g] = ffma2(w2[gate][2 * i + 1], h23, acc[gate][g]);
         }
       }
     }
-    for (int s = 0; s < n_steps; ++s) {
-      const int cur = (phase == 0 ? s : max_len + s) & 1;
-      // prefetch next step's input projection while the mat-vec runs
-      float xn[4] = {0.f, 0.f, 0.f, 0.f};
-      int p_next2 = 0;
-      if (phase == 0 && cell && s + 1 < my_len) {
-        load_x(p_next, xn);
-        if (s + 2 < my_len) p_next2 = __ldg(perm + (size_t)my_b * Tmax + s + 2);
+    // transpose-reduce over the 8 k-slices (lane bits 2,1,0): every round halves the set of
+    // sequences a lane keeps and adds the partner's partial sums for them
+    float v4[4];
+    if constexpr (kG <= 4) {
+      float v8[4][2];
+      {
+        const bool up = (kc & 4) != 0;                   // keeps sequences {2,3}
+#pragma unroll
+        for (int gate = 0; gate < 4; ++gate)
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const float lo = j < kG ? sum2(acc[gate][j]) : 0.f, hi = 2 + j < kG ? sum2(acc[gate][2 + j]) : 0.f;
+            v8[gate][j] = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, 4);
+          }
       }
-      float acc[G];
+      {
+        const bool up = (kc & 2) != 0;                   // keeps the odd sequence of its pair
 #pragma unroll
-      for (int g = 0; g < G; ++g) acc[g] = 0.f;
-#pragma unroll
-      for (int i = 0; i < 128; i += 4) {
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-          const float4 hv = *reinterpret_cast<const float4*>(&hs[cur][g][kh * 128 + i]);
-          acc[g] = fmaf(w[i + 0], hv.x, acc[g]);
-          acc[g] = fmaf(w[i + 1], hv.y, acc[g]);
-          acc[g] = fmaf(w[i + 2], hv.z, acc[g]);
-          acc[g] = fmaf(w[i + 3], hv.w, acc[g]);
+        for (int gate = 0; gate < 4; ++gate) {
+          const float keep = up ? v8[gate][1] : v8[gate][0];
+          const float give = up ? v8[gate][0] : v8[gate][1];
+          v4[gate] = keep + __shfl_xor_sync(0xffffffffu, give, 2);
         }
       }
 #pragma unroll
-      for (int g = 0; g < G; ++g) part[kh][g][r_local] = acc[g];
+      for (int gate = 0; gate < 4; ++gate) v4[gate] += __shfl_xor_sync(0xffffffffu, v4[gate], 1);
+    } else {
+      float va[4][4], vb[4][2];
+      {
+        const bool up = (kc & 4) != 0;                   // keeps sequences {4..7}
+#pragma unroll
+        for (int gate = 0; gate < 4; ++gate)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float lo = sum2(acc[gate][j]), hi = 4 + j < kG ? sum2(acc[gate][4 + j]) : 0.f;
+            va[gate][j] = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, 4);
+          }
+      }
+      {
+        const bool up = (kc & 2) != 0;
+#pragma unroll
+        for (int gate = 0; gate < 4; ++gate)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+            vb[gate][j] = (up ? va[gate][2 + j] : va[gate][j]) +
+                          __shfl_xor_sync(0xffffffffu, up ? va[gate][j] : va[gate][2 + j], 2);
+      }
+      {
+        const bool up = (kc & 1) != 0;
+#pragma unroll
+        for (int gate = 0; gate < 4; ++gate)
+          v4[gate] = (up ? vb[gate][1] : vb[gate][0]) + __shfl_xor_sync(0xffffffffu, up ? vb[gate][0] : vb[gate][1], 1);
+      }
+    }
+
+    const bool active = dec ? (my_b >= 0) : (s < my_len);
+    if (active) {
+      const float ig = sigmoidf_ref(v4[0] + xg[0]), fg = sigmoidf_ref(v4[1] + xg[1]);
+      const float gg = tanhf(v4[2] + xg[2]), og = sigmoidf_ref(v4[3] + xg[3]);
+      c_state = fg * c_state + ig * gg;
+      h_state = og * tanhf(c_state);
+      if (dec && owner) attractors[((size_t)my_b * n_dec + s) * kD + col] = h_state;
+    }
+    if (gs + 1 < n_total) {           // publish h (changed or not) into the next buffer of all 8 CTAs
+      if (owner) hstage[cur][seq][u] = h_state;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncthreads();
-      if (cell) {
-        const bool active = phase == 1 ? (my_b >= 0) : (s < my_len);
-        if (active) {
-          float gate[4];
+      if (tid < kCluster)
+        bulk_push(cur ? r_h0 : r_h1, s_u32(&hstage[cur][0][0]), kG * kUnits * 4, cur ? r_bar0 : r_bar1);
+    }
+    if (!dec) {
 #pragma unroll
-          for (int x = 0; x < 4; ++x)
-            gate[x] = (part[0][warp][x * 32 + lane] + part[1][warp][x * 32 + lane]) + xg[x];
-          const float ig = sigmoidf_ref(gate[0]), fg = sigmoidf_ref(gate[1]);
-          const float gg = tanhf(gate[2]), og = sigmoidf_ref(gate[3]);
-          c_state = fg * c_state + ig * gg;
-          h_state = og * tanhf(c_state);
-          if (phase == 1)
-            attractors[((size_t)my_b * n_dec + s) * kD + col] = h_state;
-        }
-        // publish h (changed or not) into the next buffer of all 8 CTAs
-        float* dst = &hs[cur ^ 1][warp][cta * kUnits + lane];
-#pragma unroll
-        for (int r = 0; r < kCluster; ++r) *cluster.map_shared_rank(dst, r) = h_state;
-        if (phase == 0) {
-#pragma unroll
-          for (int x = 0; x < 4; ++x) xg[x] = xn[x];
-          p_next = p_next2;
-        }
-      }
-      cluster.sync();
+      for (int x = 0; x < 4; ++x) xg[x] = xn[x];
+      p_next = p_next2;
     }
   }
+  cluster.sync();    // nobody exits while a peer may still be reading its own buffers' traffic
 }
 
-template <int G>
-static int launch_lstm(const float* xproj, const int32_t* perm, const int32_t* lens,
-                       const int32_t* order, const float* w_enc, const float* w_dec,
-                       const float* dec_bias, int B, int Tmax, int n_dec, float* attractors,
-                       float* hc_out, cudaStream_t st) {
-  const int groups = ceil_div(B, G);
-  cudaLaunchConfig_t cfg = {};
+template <int kG>
+static int launch_lstm(cudaLaunchConfig_t& cfg, const float* xproj, const int32_t* perm, const int32_t* lens,
+                       const int32_t* order, const float* w_enc, const float* w_dec, const float* dec_bias,
+                       int B, int Tmax, int n_dec, float* attractors, float* hc_out) {
+  EDA_CUDA(cudaLaunchKernelEx(&cfg, lstm_cluster_kernel<kG>, xproj, perm, lens, order, w_enc, w_dec,
+                              dec_bias, B, Tmax, n_dec, attractors, hc_out));
+  count_launch();
+  return EDA_OK;
+}
+
+static void lstm_launch_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attr, int groups, cudaStream_t st) {
+  cfg = cudaLaunchConfig_t{};
   cfg.gridDim = dim3(groups * kCluster);
   cfg.blockDim = dim3(256);
   cfg.dynamicSmemBytes = 0;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = kCluster;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  EDA_CUDA(cudaLaunchKernelEx(&cfg, lstm_cluster_kernel<G>, xproj, perm, lens, order, w_enc, w_dec,
-                              dec_bias, B, Tmax, n_dec, attractors, hc_out));
-  count_launch();
-  return EDA_OK;
+}
+
+// How many 8-CTA clusters of the recurrence kernel the device can keep resident at once
+// (each advances kG sequences): batches beyond kG * this run in more than one wave.
+int lstm_max_active_clusters() {
+  static int cached = -1;
+  if (cached < 0) {
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    lstm_launch_config(cfg, attr, 64, nullptr);
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, lstm_cluster_kernel<4>, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
+    cached = n;
+  }
+  return cached;
 }
 
 int lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens,
@@ -186,9 +333,22 @@ int lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens
   EDA_REQUIRE(D == kD, "eda_lstm_attractors: D must be 256 (got %d)", D);
   EDA_REQUIRE(B > 0 && Tmax > 0 && n_dec >= 0, "eda_lstm_attractors: bad sizes");
   EDA_REQUIRE(((uintptr_t)w_enc | (uintptr_t)w_dec) % 16 == 0, "eda_lstm_attractors: weights must be 16B aligned");
-  // 16 clusters of 8 fit a B200 (2 per GPC): prefer the lower-latency G=4 while it fills them.
-  if (B <= 64) return launch_lstm<4>(xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, st);
-  return launch_lstm<8>(xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, st);
+  // one wave if at all possible: the smallest G in 4..8 whose cluster count fits the device
+  const int fit = std::max(1, lstm_max_active_clusters());
+  int G = 4;
+  while (G < 8 && ceil_div(B, G) > fit) ++G;
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[1];
+  lstm_launch_config(cfg, attr, ceil_div(B, G), st);
+  switch (G) {
+    case 4: return launch_lstm<4>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out);
+    case 5: return launch_lstm<5>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out);
+    case 6: return launch_lstm<6>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out);
+    case 7: return launch_lstm<7>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out);
+    default: return launch_lstm<8>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out);
+  }
 }
 
 }  // namespace eda
+
+extern "C" int eda_lstm_max_active_clusters(void) { return eda::lstm_max_active_clusters(); }

@@ -73,7 +73,10 @@ def test_mha(dev, prec, B, T):
     assert (out.cpu() - ref).abs().max().item() < tol
 
 
-@pytest.mark.parametrize("lens,n_dec", [([40, 17, 1, 40, 33], 3), ([300] * 9, 15), ([5], 15), ([64, 0, 20], 4)])
+@pytest.mark.parametrize("lens,n_dec", [([40, 17, 1, 40, 33], 3), ([300] * 9, 15), ([5], 15), ([64, 0, 20], 4),
+                                        ([37 + (i * 7) % 23 for i in range(66)], 3),      # 5 sequences per cluster
+                                        ([20 + (i * 5) % 11 for i in range(117)], 2)])    # 8 per cluster
+
 def test_lstm_attractors(dev, lens, n_dec):
     from oracle.eend_eda_oracle import eda as oracle_eda
     from oracle.weights import EdaConfig, synth_state_dict

@@ -54,8 +54,11 @@ int64_t eda_frontend_num_frames(int64_t n_samples, int frame_shift);
 /* Pass 1: audio -> log10(max(|STFT|^2 . mel^T, 1e-10)) per frame, plus per-recording
  * per-bin sums (for the mean).  `audio` holds n_rec recordings back to back;
  * rec_sample_off / rec_frame_off are (n_rec+1) int64 prefix offsets (device).
- * logmel: (total_frames, n_mels) fp32.  colsum: (n_rec, n_mels) fp64, zeroed by the call. */
-int eda_frontend_logmel(const eda_frontend_plan* plan, const void* audio, int audio_is_f64,
+ * logmel: (total_frames, n_mels) fp32.  colsum: (n_rec, n_mels) fp64, zeroed by the call.
+ * audio_dtype: EDA_AUDIO_F32 / F64 (what soundfile hands the reference, kaldi_data.py:82) /
+ * I16 (the wav file's own PCM samples; converted as x / 32768 exactly like soundfile does). */
+enum { EDA_AUDIO_F32 = 0, EDA_AUDIO_F64 = 1, EDA_AUDIO_I16 = 2 };
+int eda_frontend_logmel(const eda_frontend_plan* plan, const void* audio, int audio_dtype,
                         const int64_t* rec_sample_off, const int64_t* rec_frame_off,
                         int n_rec, int64_t total_frames,
                         float* logmel, double* colsum, void* stream);

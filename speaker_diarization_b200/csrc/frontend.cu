@@ -25,6 +25,9 @@ struct eda_frontend_plan {
   float* d_melw;       // (n_mels, n_bins) dense Slaney filterbank, float32 like librosa
   int* d_mel_lo;       // (n_mels) first bin with a non-zero weight
   int* d_mel_hi;       // (n_mels) last bin with a non-zero weight
+  double* d_melw64;    // packed non-zero weights (as double), filter m at [mel_off[m], mel_off[m+1])
+  int* d_mel_off;      // (n_mels + 1)
+  int mel_nnz;
 };
 
 namespace eda {
@@ -60,6 +63,10 @@ static void mel_filterbank(int sr, int n_fft, int n_mels, std::vector<float>& w)
 }
 
 // ---- pass 1 ---------------------------------------------------------------------------
+__device__ __forceinline__ double audio_sample(const float* a, int64_t i) { return (double)__ldg(a + i); }
+__device__ __forceinline__ double audio_sample(const double* a, int64_t i) { return __ldg(a + i); }
+// 16-bit PCM, scaled the way soundfile hands it to the reference (x / 32768, exact in fp64)
+__device__ __forceinline__ double audio_sample(const int16_t* a, int64_t i) { return (double)__ldg(a + i) * (1.0 / 32768.0); }
 __device__ __forceinline__ double2 cmul(double2 a, double2 b) {
   return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
@@ -119,8 +126,8 @@ logmel_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_
     const int64_t s_start = (f - r_f0) * hop - M;
     for (int n = lane; n < M; n += 32) {
       const int64_t i0 = s_start + 2 * n, i1 = i0 + 1;
-      const double x0 = (i0 >= 0 && i0 < r_n) ? (double)audio[r_s0 + i0] : 0.0;
-      const double x1 = (i1 >= 0 && i1 < r_n) ? (double)audio[r_s0 + i1] : 0.0;
+      const double x0 = (i0 >= 0 && i0 < r_n) ? audio_sample(audio, r_s0 + i0) : 0.0;
+      const double x1 = (i1 >= 0 && i1 < r_n) ? audio_sample(audio, r_s0 + i1) : 0.0;
       bufA[n] = make_double2(x0 * s_win[2 * n], x1 * s_win[2 * n + 1]);
     }
     __syncwarp();
@@ -162,6 +169,178 @@ logmel_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_
       const float* wrow = s_melw + (size_t)lane * n_bins;
       for (int k = my_lo; k <= my_hi; ++k) acc += pw[k] * (double)wrow[k];
       const double v = log10(fmax(acc, 1e-10));
+      logmel[(size_t)f * n_mels + lane] = (float)v;
+      csum += v;
+    }
+    __syncwarp();
+  }
+  if (lane < n_mels) atomicAdd(colsum + (size_t)rec * n_mels + lane, csum);
+}
+
+// ---- pass 1, fast path (n_fft = 256 or 512) ---------------------------------------------
+// One warp per frame, the M = n_fft/2 packed complex points held in REGISTERS (R = M/32 per
+// lane): a size-R DIF FFT inside each lane, one twiddle, then a 32-point DIF FFT ACROSS the
+// lanes with xor-shuffles (no shared-memory round trips, no index arithmetic).  The spectrum
+// goes through shared memory once for the real-FFT untangle, which produces the power of bins
+// k and M-k together.  fp64 throughout, like the reference's numpy.
+struct cd { double x, y; };
+__device__ __forceinline__ cd cadd(cd a, cd b) { return {a.x + b.x, a.y + b.y}; }
+__device__ __forceinline__ cd csub(cd a, cd b) { return {a.x - b.x, a.y - b.y}; }
+__device__ __forceinline__ cd cmulw(cd a, cd w) { return {a.x * w.x - a.y * w.y, a.x * w.y + a.y * w.x}; }
+__device__ __forceinline__ cd cmul_mi(cd a) { return {a.y, -a.x}; }          // a * (-i)
+
+
+template <int R>
+__device__ __forceinline__ void fft_local(cd (&a)[R]) {      // DIF, output slot j holds Y[bitrev(j)]
+  constexpr double h = 0.70710678118654752440;
+  if constexpr (R == 8) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const cd u = a[i], v = a[i + 4];
+      a[i] = cadd(u, v);
+      const cd d = csub(u, v);
+      a[i + 4] = i == 0 ? d : i == 1 ? cd{(d.x + d.y) * h, (d.y - d.x) * h} : i == 2 ? cmul_mi(d)
+                                                                              : cd{(d.y - d.x) * h, -(d.x + d.y) * h};
+    }
+  }
+#pragma unroll
+  for (int base = 0; base < R; base += 4) {
+    const cd u0 = a[base], u1 = a[base + 1], v0 = a[base + 2], v1 = a[base + 3];
+    const cd s0 = cadd(u0, v0), s1 = cadd(u1, v1), d0 = csub(u0, v0), d1 = cmul_mi(csub(u1, v1));
+    a[base] = cadd(s0, s1); a[base + 1] = csub(s0, s1);
+    a[base + 2] = cadd(d0, d1); a[base + 3] = csub(d0, d1);
+  }
+}
+
+template <int R, typename AudioT>
+__global__ void __launch_bounds__(256)
+logmel_fast_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_sample_off,
+                   const int64_t* __restrict__ rec_frame_off, int n_rec, int64_t total_frames, int hop,
+                   int n_mels, const double* __restrict__ window, const double2* __restrict__ tw,
+                   const double* __restrict__ melw64, const int* __restrict__ mel_off,
+                   const int* __restrict__ mel_lo, int mel_nnz, float* __restrict__ logmel,
+                   double* __restrict__ colsum, int frames_per_warp) {
+  constexpr int M = 32 * R, NFFT = 2 * M, RB = R == 8 ? 3 : 2;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  // layout: [tw: M double2][melw: mel_nnz double (padded to even)][per-warp: M double2 + (M+2) double]
+  double2* s_tw = reinterpret_cast<double2*>(smem_raw);
+  double* s_melw = reinterpret_cast<double*>(s_tw + M);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char* wbase = smem_raw + (size_t)M * 16 + (size_t)((mel_nnz + 1) & ~1) * 8 + (size_t)warp * (M * 16 + (M + 2) * 8);
+  double2* zbuf = reinterpret_cast<double2*>(wbase);
+  double* pw = reinterpret_cast<double*>(wbase + M * 16);
+  for (int i = threadIdx.x; i < M; i += blockDim.x) s_tw[i] = tw[i];
+  for (int i = threadIdx.x; i < mel_nnz; i += blockDim.x) s_melw[i] = melw64[i];
+  __syncthreads();
+
+  // per-lane constants
+  auto wn = [&](int e) -> cd {                 // W_NFFT^e for 0 <= e < NFFT
+    const double2 t = s_tw[e & (M - 1)];
+    return e >= M ? cd{-t.x, -t.y} : cd{t.x, t.y};
+  };
+  double win0[R], win1[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) { win0[r] = window[2 * (lane + 32 * r)]; win1[r] = window[2 * (lane + 32 * r) + 1]; }
+  cd ltw[R];                                   // W_M^{lane * bitrev(j)}
+#pragma unroll
+  for (int j = 0; j < R; ++j) ltw[j] = wn(2 * lane * (int)(__brev((unsigned)j) >> (32 - RB)));
+  cd stw[4];                                   // cross-lane stages d = 16, 8, 4, 2: W_{2d}^{lane % d} on lower lanes
+  double sgn[5];
+#pragma unroll
+  for (int s = 0; s < 5; ++s) {
+    const int d = 16 >> s;
+    const bool lower = (lane & d) != 0;
+    sgn[s] = lower ? -1.0 : 1.0;
+    if (s < 4) stw[s] = lower ? wn((lane % d) * (NFFT / (2 * d))) : cd{1.0, 0.0};
+  }
+  const int k1 = (int)(__brev((unsigned)lane) >> 27);
+  const int my_off = lane < n_mels ? mel_off[lane] : 0, my_cnt = lane < n_mels ? mel_off[lane + 1] - my_off : 0;
+  const int my_lo = lane < n_mels ? mel_lo[lane] : 0;
+
+  const int64_t gwarp = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
+  const int64_t f_begin = gwarp * frames_per_warp;
+  const int64_t f_end = min(total_frames, f_begin + frames_per_warp);
+  if (f_begin >= f_end) return;
+  int rec = 0;
+  {
+    int lo = 0, hi = n_rec - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (rec_frame_off[mid] <= f_begin) lo = mid; else hi = mid - 1;
+    }
+    rec = lo;
+  }
+  double csum = 0.0;
+  int64_t r_f0 = rec_frame_off[rec], r_f1 = rec_frame_off[rec + 1];
+  int64_t r_s0 = rec_sample_off[rec], r_n = rec_sample_off[rec + 1] - r_s0;
+  for (int64_t f = f_begin; f < f_end; ++f) {
+    while (f >= r_f1) {   // crossed into the next recording (empty recordings are skipped)
+      if (lane < n_mels) atomicAdd(colsum + (size_t)rec * n_mels + lane, csum);
+      csum = 0.0;
+      ++rec;
+      r_f0 = rec_frame_off[rec]; r_f1 = rec_frame_off[rec + 1];
+      r_s0 = rec_sample_off[rec]; r_n = rec_sample_off[rec + 1] - r_s0;
+    }
+    // windowed frame packed as z[n] = x[2n] + i x[2n+1], n = lane + 32 r (center=True zero padding)
+    const int64_t s_start = (f - r_f0) * hop - M;
+    cd a[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int64_t i0 = s_start + 2 * (lane + 32 * r), i1 = i0 + 1;
+      const double x0 = (i0 >= 0 && i0 < r_n) ? audio_sample(audio, r_s0 + i0) : 0.0;
+      const double x1 = (i1 >= 0 && i1 < r_n) ? audio_sample(audio, r_s0 + i1) : 0.0;
+      a[r] = {x0 * win0[r], x1 * win1[r]};
+    }
+    fft_local<R>(a);
+#pragma unroll
+    for (int j = 1; j < R; ++j) a[j] = cmulw(a[j], ltw[j]);
+    // 32-point DIF across lanes: upper lane keeps own + partner, lower lane (partner - own) * w
+#pragma unroll
+    for (int s = 0; s < 5; ++s) {
+      const int d = 16 >> s;
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        const double px = __shfl_xor_sync(0xffffffffu, a[j].x, d), py = __shfl_xor_sync(0xffffffffu, a[j].y, d);
+        const cd t = {fma(a[j].x, sgn[s], px), fma(a[j].y, sgn[s], py)};
+        a[j] = s < 4 ? cmulw(t, stw[s]) : t;
+      }
+    }
+    // lane holds Z[R * bitrev5(lane) + bitrev(j)] in slot j: natural order through shared memory
+#pragma unroll
+    for (int j = 0; j < R; ++j)
+      zbuf[R * k1 + (int)(__brev((unsigned)j) >> (32 - RB))] = make_double2(a[j].x, a[j].y);
+    __syncwarp();
+    // real-FFT untangle: bins k and M-k from Z[k], Z[M-k]:  X[k] = (E + T)/2, X[M-k] = conj(E - T)/2,
+    // E = Z[k] + conj(Z[M-k]),  T = W^k * (-i) (Z[k] - conj(Z[M-k]))
+#pragma unroll
+    for (int jj = 0; jj < R / 2; ++jj) {
+      const int k = 1 + lane + 32 * jj;                // 1 .. M/2
+      const double2 zk = zbuf[k], zm = zbuf[M - k];
+      const cd E = {zk.x + zm.x, zk.y - zm.y};
+      const cd D = {zk.x - zm.x, zk.y + zm.y};
+      const double2 w = s_tw[k];
+      const cd T = cmulw(cmul_mi(D), cd{w.x, w.y});
+      const cd p = cadd(E, T), q = csub(E, T);
+      pw[k] = 0.25 * (p.x * p.x + p.y * p.y);
+      pw[M - k] = 0.25 * (q.x * q.x + q.y * q.y);      // k == M/2 writes the same value twice
+    }
+    if (lane == 0) {
+      const double2 z0 = zbuf[0];
+      pw[0] = (z0.x + z0.y) * (z0.x + z0.y);
+      pw[M] = (z0.x - z0.y) * (z0.x - z0.y);
+    }
+    __syncwarp();
+    if (lane < n_mels) {
+      double acc0 = 0.0, acc1 = 0.0;
+      const double* wrow = s_melw + my_off;
+      const double* prow = pw + my_lo;
+      int i = 0;
+      for (; i + 1 < my_cnt; i += 2) {
+        acc0 = fma(prow[i], wrow[i], acc0);
+        acc1 = fma(prow[i + 1], wrow[i + 1], acc1);
+      }
+      if (i < my_cnt) acc0 = fma(prow[i], wrow[i], acc0);
+      const double v = log10(fmax(acc0 + acc1, 1e-10));
       logmel[(size_t)f * n_mels + lane] = (float)v;
       csum += v;
     }
@@ -243,6 +422,18 @@ int eda_frontend_plan_create(int sample_rate, int frame_size, int frame_shift, i
       if (melw[(size_t)m * p->n_bins + k] != 0.f) { lo[m] = std::min(lo[m], k); hi[m] = k; }
     if (hi[m] < 0) lo[m] = 0;
   }
+  std::vector<double> w64;
+  std::vector<int> woff(n_mels + 1, 0);
+  for (int m = 0; m < n_mels; ++m) {
+    woff[m] = (int)w64.size();
+    for (int k = lo[m]; k <= hi[m]; ++k) w64.push_back((double)melw[(size_t)m * p->n_bins + k]);
+  }
+  woff[n_mels] = (int)w64.size();
+  p->mel_nnz = (int)w64.size();
+  EDA_CUDA(cudaMalloc(&p->d_melw64, sizeof(double) * std::max<size_t>(1, w64.size())));
+  EDA_CUDA(cudaMalloc(&p->d_mel_off, sizeof(int) * (n_mels + 1)));
+  EDA_CUDA(cudaMemcpy(p->d_melw64, w64.data(), sizeof(double) * w64.size(), cudaMemcpyHostToDevice));
+  EDA_CUDA(cudaMemcpy(p->d_mel_off, woff.data(), sizeof(int) * (n_mels + 1), cudaMemcpyHostToDevice));
   EDA_CUDA(cudaMalloc(&p->d_window, sizeof(double) * n_fft));
   EDA_CUDA(cudaMalloc(&p->d_tw, sizeof(double2) * (n_fft / 2)));
   EDA_CUDA(cudaMalloc(&p->d_melw, sizeof(float) * melw.size()));
@@ -256,6 +447,17 @@ int eda_frontend_plan_create(int sample_rate, int frame_size, int frame_shift, i
   const int smem = (int)logmel_smem(n_fft, n_mels);
   EDA_CUDA(cudaFuncSetAttribute(logmel_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   EDA_CUDA(cudaFuncSetAttribute(logmel_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  EDA_CUDA(cudaFuncSetAttribute(logmel_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  if (n_fft == 256 || n_fft == 512) {
+    const int M = n_fft / 2;
+    const int fsm = (int)((size_t)M * 16 + (size_t)((p->mel_nnz + 1) & ~1) * 8 + (size_t)8 * (M * 16 + (M + 2) * 8));
+    EDA_CUDA(cudaFuncSetAttribute(logmel_fast_kernel<4, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm));
+    EDA_CUDA(cudaFuncSetAttribute(logmel_fast_kernel<4, double>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm));
+    EDA_CUDA(cudaFuncSetAttribute(logmel_fast_kernel<4, int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm));
+    EDA_CUDA(cudaFuncSetAttribute(logmel_fast_kernel<8, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm));
+    EDA_CUDA(cudaFuncSetAttribute(logmel_fast_kernel<8, double>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm));
+    EDA_CUDA(cudaFuncSetAttribute(logmel_fast_kernel<8, int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm));
+  }
   *out = p;
   return EDA_OK;
 }
@@ -263,11 +465,12 @@ int eda_frontend_plan_create(int sample_rate, int frame_size, int frame_shift, i
 int eda_frontend_plan_destroy(eda_frontend_plan* p) {
   if (!p) return EDA_OK;
   cudaFree(p->d_window); cudaFree(p->d_tw); cudaFree(p->d_melw); cudaFree(p->d_mel_lo); cudaFree(p->d_mel_hi);
+  cudaFree(p->d_melw64); cudaFree(p->d_mel_off);
   delete p;
   return EDA_OK;
 }
 
-int eda_frontend_logmel(const eda_frontend_plan* p, const void* audio, int audio_is_f64,
+int eda_frontend_logmel(const eda_frontend_plan* p, const void* audio, int audio_dtype,
                         const int64_t* rec_sample_off, const int64_t* rec_frame_off, int n_rec,
                         int64_t total_frames, float* logmel, double* colsum, void* stream) {
   using namespace eda;
@@ -281,13 +484,30 @@ int eda_frontend_logmel(const eda_frontend_plan* p, const void* audio, int audio
   int fpw = (int)std::max<int64_t>(1, std::min<int64_t>(64, total_frames / target_warps));
   const int64_t n_warps = ceil_div<int64_t>(total_frames, fpw);
   const int blocks = (int)ceil_div<int64_t>(n_warps, 8);
+  EDA_REQUIRE(audio_dtype >= EDA_AUDIO_F32 && audio_dtype <= EDA_AUDIO_I16, "eda_frontend_logmel: unknown audio dtype %d", audio_dtype);
+  if (p->n_fft == 256 || p->n_fft == 512) {
+    // fast path: register-resident FFT, shuffles across lanes
+    const int M = p->n_fft / 2;
+    const size_t smem = (size_t)M * 16 + (size_t)((p->mel_nnz + 1) & ~1) * 8 + (size_t)8 * (M * 16 + (M + 2) * 8);
+#define EDA_FAST(R, T)                                                                                      \
+  logmel_fast_kernel<R, T><<<blocks, 256, smem, st>>>((const T*)audio, rec_sample_off, rec_frame_off, n_rec, \
+      total_frames, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw64, p->d_mel_off, p->d_mel_lo, \
+      p->mel_nnz, logmel, colsum, fpw)
+    if (p->n_fft == 256) {
+      if (audio_dtype == EDA_AUDIO_F64) EDA_FAST(4, double); else if (audio_dtype == EDA_AUDIO_I16) EDA_FAST(4, int16_t); else EDA_FAST(4, float);
+    } else {
+      if (audio_dtype == EDA_AUDIO_F64) EDA_FAST(8, double); else if (audio_dtype == EDA_AUDIO_I16) EDA_FAST(8, int16_t); else EDA_FAST(8, float);
+    }
+#undef EDA_FAST
+    EDA_LAUNCH_CHECK();
+    return EDA_OK;
+  }
   const size_t smem = logmel_smem(p->n_fft, p->n_mels);
-  if (audio_is_f64)
-    logmel_kernel<double><<<blocks, 256, smem, st>>>((const double*)audio, rec_sample_off, rec_frame_off, n_rec, total_frames,
-        p->n_fft, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw, p->d_mel_lo, p->d_mel_hi, logmel, colsum, fpw);
-  else
-    logmel_kernel<float><<<blocks, 256, smem, st>>>((const float*)audio, rec_sample_off, rec_frame_off, n_rec, total_frames,
-        p->n_fft, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw, p->d_mel_lo, p->d_mel_hi, logmel, colsum, fpw);
+#define EDA_GEN(T)                                                                                                \
+  logmel_kernel<T><<<blocks, 256, smem, st>>>((const T*)audio, rec_sample_off, rec_frame_off, n_rec, total_frames, \
+      p->n_fft, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw, p->d_mel_lo, p->d_mel_hi, logmel, colsum, fpw)
+  if (audio_dtype == EDA_AUDIO_F64) EDA_GEN(double); else if (audio_dtype == EDA_AUDIO_I16) EDA_GEN(int16_t); else EDA_GEN(float);
+#undef EDA_GEN
   EDA_LAUNCH_CHECK();
   return EDA_OK;
 }

@@ -55,7 +55,7 @@ __device__ __forceinline__ bool bar_try(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred P;\n\t"
-      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"   // bulk-copy bytes are visible on completion
       "selp.b32 %0, 1, 0, P;\n\t}"
       : "=r"(ok) : "r"(s_u32(bar)), "r"(parity) : "memory");
   return ok != 0;

@@ -25,6 +25,11 @@ from . import _lib as L
 
 Array = Union[np.ndarray, torch.Tensor]
 
+# audio sample types the kernels read directly (include/eda_b200.h: EDA_AUDIO_*).  int16 is the
+# wav file's own PCM: the kernel scales by 1/32768 exactly like soundfile does for the
+# reference (kaldi_data.py:82), so shipping int16 halves / quarters the host->device bytes.
+_AUDIO_DTYPES = {torch.float32: 0, torch.float64: 1, torch.int16: 2}
+
 
 def get_input_dim(frame_size: int, context_size: int, transform_type: str) -> int:
     """feature.py:10-21."""
@@ -73,12 +78,13 @@ class FrontEnd:
         ``counts`` giving each recording's sample count (no concatenation copy then)."""
         if counts is not None:
             flat = recs.reshape(-1)
-            is_f64 = flat.dtype == torch.float64
+            if flat.dtype not in _AUDIO_DTYPES:
+                flat = flat.float()
             audio = flat if flat.is_cuda else flat.to(self.device, non_blocking=True)
-            return (audio.contiguous(), is_f64) + self._offsets([int(c) for c in counts])
-        first = recs[0]
-        is_f64 = (first.dtype == np.float64) if isinstance(first, np.ndarray) else (first.dtype == torch.float64)
-        tdt = torch.float64 if is_f64 else torch.float32
+            return (audio.contiguous(), _AUDIO_DTYPES[flat.dtype]) + self._offsets([int(c) for c in counts])
+        first = torch.as_tensor(recs[0])
+        tdt = first.dtype if first.dtype in _AUDIO_DTYPES else torch.float32
+        is_f64 = _AUDIO_DTYPES[tdt]
         ns = [int(r.shape[0]) for r in recs]
         if isinstance(first, torch.Tensor) and first.is_cuda:
             audio = torch.cat([r.to(tdt) for r in recs]).contiguous()

@@ -174,3 +174,18 @@ def test_frontend_batch_of_ragged_recordings():
         assert tuple(o.shape) == want.shape
         if want.size:
             assert np.abs(o.cpu().numpy() - want).max() < 2e-5
+
+
+def test_frontend_int16_pcm_matches_soundfile_scaling():
+    """int16 PCM fed straight to the kernel == the float64 samples soundfile would hand the
+    reference (x / 32768), both 8 kHz (n_fft 256) and 16 kHz (n_fft 512) fast paths."""
+    from oracle import feature_oracle as fo
+    from speaker_diarization_b200 import feature
+    for rate, fs, hop in ((8000, 200, 80), (16000, 400, 160)):
+        x, _ = fo.synth_audio(rate * 3 + 17, rate, 2, 91, dtype=np.float64)
+        pcm = np.clip(np.round(x * 32768.0), -32768, 32767).astype(np.int16)
+        want = fo.frontend(pcm.astype(np.float64) / 32768.0, rate, fs, hop)
+        fe = feature.FrontEnd(rate, fs, hop, 7, 10)
+        got = fe.features([pcm])[0]
+        assert tuple(got.shape) == want.shape
+        assert np.abs(got.cpu().numpy() - want).max() < 2e-5

@@ -14,8 +14,9 @@
 //   warp 0      TMA producer   (SWIZZLE_128B K-major tiles {A_hi, A_lo, B_hi, B_lo}, 2 stages)
 //   warp 1      MMA issuer (one thread) + TMEM owner: 2 accumulator buffers x 256 columns,
 //               so the epilogue of tile i overlaps the MMAs of tile i+1
-//   warps 2-5   epilogue: tcgen05.ld -> bias / ReLU / residual + LayerNorm (row kept in TMEM
-//               between the statistics passes) -> smem transpose -> coalesced stores of the
+//   warps 2-9   epilogue (two warps per TMEM lane quadrant, 128 columns each): tcgen05.ld ->
+//               bias / ReLU / residual + LayerNorm (row held in the registers of two threads,
+//               statistics exchanged through smem) -> smem transpose -> coalesced stores of the
 //               fp32 and/or split-bf16 output; the QKV variant pre-scales q by 1/sqrt(dh) and
 //               stores v TRANSPOSED per (batch, head) for the attention kernel.
 #include <algorithm>
@@ -34,9 +35,12 @@ constexpr int GBM = 128, GBN = 256, GBK = 64, GSTAGES = 2;
 constexpr int G_A_TILE = GBM * GBK * 2;                  // 16 KB
 constexpr int G_B_TILE = GBN * GBK * 2;                  // 32 KB
 constexpr int G_STAGE = 2 * G_A_TILE + 2 * G_B_TILE;     // 96 KB
-constexpr int G_STG_LD = 36;                             // floats per staged row (32 + pad)
-constexpr int G_STG_BYTES = 4 * 32 * G_STG_LD * 4;       // 4 epilogue warps
-constexpr int G_SMEM = GSTAGES * G_STAGE + G_STG_BYTES + 256 + 1024;
+constexpr int G_EPI_WARPS = 8;
+constexpr int G_THREADS = 64 + 32 * G_EPI_WARPS;
+constexpr int G_STG_LD = 20;                             // floats per staged row (16 + pad): conflict-free float4
+constexpr int G_STG_BYTES = G_EPI_WARPS * 32 * G_STG_LD * 4;
+constexpr int G_LNX_BYTES = 2 * 2 * GBM * 4;             // LayerNorm partial sums [pass][column half][row]
+constexpr int G_SMEM = GSTAGES * G_STAGE + G_STG_BYTES + G_LNX_BYTES + 256 + 1024;
 
 enum { GEPI_QKV = 4 };
 
@@ -74,14 +78,15 @@ __global__ void split_bf16_kernel(const float* __restrict__ src, int ld, int row
 }
 
 template <int EPI>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(G_THREADS, 1)
 gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                   const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
                   const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* stg_all = reinterpret_cast<float*>(smem + GSTAGES * G_STAGE);
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + GSTAGES * G_STAGE + G_STG_BYTES);
+  float (*ln_x)[2][GBM] = reinterpret_cast<float (*)[2][GBM]>(smem + GSTAGES * G_STAGE + G_STG_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + GSTAGES * G_STAGE + G_STG_BYTES + G_LNX_BYTES);
   uint64_t* empty = full + GSTAGES;
   uint64_t* tfull = empty + GSTAGES;
   uint64_t* tempty = tfull + 2;
@@ -95,7 +100,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA_hi); tma_prefetch_desc(&tmA_lo); tma_prefetch_desc(&tmB_hi); tma_prefetch_desc(&tmB_lo);
     for (int s = 0; s < GSTAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], G_EPI_WARPS); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -157,80 +162,110 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
       }
     }
   } else {
-    // ===== epilogue: warps 2..5; warp w may touch TMEM lanes 32*(w%4) .. +31 =====
-    const int q = warp & 3;
-    float* stg = stg_all + q * 32 * G_STG_LD;
-    const int srow = lane >> 3, scol = (lane & 7) * 4;               // staged-copy role
+    // ===== epilogue: warps 2..9.  Warp w touches TMEM lanes 32*(w%4)..+31 (rows of the tile);
+    // the two warps of a lane quadrant split the 256 columns in halves of 128. =====
+    const int q = warp & 3, ch = (warp - 2) >> 2;
+    float* stg = stg_all + (warp - 2) * 32 * G_STG_LD;
+    const int frow = lane >> 2, fcol = (lane & 3) * 4;            // staged-copy role: 8 rows x 4 float4 per pass
     uint32_t lt = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
       const int m0 = (tile / n_tiles_n) * GBM, n_blk = tile % n_tiles_n, n0 = n_blk * GBN;
       const uint32_t ab = lt & 1;
+      const int rbase = m0 + q * 32;                              // first global row of this warp
+      // residual chunk c of this thread's row (RES_LN): 8 x 16 B, thread-per-row
+      auto load_resid = [&](int c, float4 (&dst)[8]) {
+        const int row = rbase + lane;
+        const float4* src = reinterpret_cast<const float4*>(p.resid + (size_t)row * p.ldr + ch * 128 + c * 32);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dst[j] = row < p.M ? __ldg(src + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+      };
+      float4 rp[8];
+      if constexpr (EPI == EDA_EPI_BIAS_RES_LN) load_resid(0, rp);   // in flight while the MMAs finish
       mbar_wait(&tfull[ab], (lt >> 1) & 1);
       tc_fence_after();
-      const uint32_t trow = tmem_base + ab * GBN + (uint32_t(q * 32) << 16);
+      const uint32_t trow = tmem_base + ab * GBN + ch * 128 + (uint32_t(q * 32) << 16);
 
-      // registers (thread = row) -> smem transpose -> coalesced row segments of fp32 / split bf16
-      auto store_chunk = [&](const float (&v)[32], int c, int col_base, bf16* out_hi, bf16* out_lo, int lds) {
+      // thread-per-row registers -> 32 x 16 smem block -> coalesced row segments (full 32 B sectors)
+      auto store_chunk = [&](const float (&v)[32], int gcol0, bf16* out_hi, bf16* out_lo, int lds) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<float4*>(&stg[lane * G_STG_LD + 4 * j]) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        __syncwarp();
+        for (int hf = 0; hf < 2; ++hf) {
 #pragma unroll
-        for (int it2 = 0; it2 < 8; ++it2) {
-          const int r = it2 * 4 + srow, grow = m0 + q * 32 + r, gcol = col_base + c * 32 + scol;
-          const float4 x = *reinterpret_cast<const float4*>(&stg[r * G_STG_LD + scol]);
-          if (grow < p.M && gcol < p.N) {
-            if (p.C && EPI != GEPI_QKV) {
-              float* dst = p.C + (size_t)grow * p.ldc + gcol;
-              if (gcol + 3 < p.N) *reinterpret_cast<float4*>(dst) = x;
-              else {
-                dst[0] = x.x;
-                if (gcol + 1 < p.N) dst[1] = x.y;
-                if (gcol + 2 < p.N) dst[2] = x.z;
+          for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<float4*>(&stg[lane * G_STG_LD + 4 * j]) =
+                make_float4(v[16 * hf + 4 * j], v[16 * hf + 4 * j + 1], v[16 * hf + 4 * j + 2], v[16 * hf + 4 * j + 3]);
+          __syncwarp();
+#pragma unroll
+          for (int it2 = 0; it2 < 4; ++it2) {
+            const int r = it2 * 8 + frow, grow = rbase + r, gcol = gcol0 + 16 * hf + fcol;
+            const float4 x = *reinterpret_cast<const float4*>(&stg[r * G_STG_LD + fcol]);
+            if (grow < p.M && gcol < p.N) {
+              if (p.C && EPI != GEPI_QKV) {
+                float* dst = p.C + (size_t)grow * p.ldc + gcol;
+                if (gcol + 3 < p.N) *reinterpret_cast<float4*>(dst) = x;
+                else {
+                  dst[0] = x.x;
+                  if (gcol + 1 < p.N) dst[1] = x.y;
+                  if (gcol + 2 < p.N) dst[2] = x.z;
+                }
+              }
+              if (out_hi) {      // split outputs require N % 4 == 0 (checked on the host)
+                __nv_bfloat162 h0, l0, h1, l1;
+                split2(x.x, x.y, h0, l0);
+                split2(x.z, x.w, h1, l1);
+                uint2 hv, lv;
+                hv.x = *reinterpret_cast<uint32_t*>(&h0); hv.y = *reinterpret_cast<uint32_t*>(&h1);
+                lv.x = *reinterpret_cast<uint32_t*>(&l0); lv.y = *reinterpret_cast<uint32_t*>(&l1);
+                *reinterpret_cast<uint2*>(out_hi + (size_t)grow * lds + gcol) = hv;
+                *reinterpret_cast<uint2*>(out_lo + (size_t)grow * lds + gcol) = lv;
               }
             }
-            if (out_hi) {      // split outputs require N % 4 == 0 (checked on the host)
-              __nv_bfloat162 h0, l0, h1, l1;
-              split2(x.x, x.y, h0, l0);
-              split2(x.z, x.w, h1, l1);
-              uint2 hv, lv;
-              hv.x = *reinterpret_cast<uint32_t*>(&h0); hv.y = *reinterpret_cast<uint32_t*>(&h1);
-              lv.x = *reinterpret_cast<uint32_t*>(&l0); lv.y = *reinterpret_cast<uint32_t*>(&l1);
-              *reinterpret_cast<uint2*>(out_hi + (size_t)grow * lds + gcol) = hv;
-              *reinterpret_cast<uint2*>(out_lo + (size_t)grow * lds + gcol) = lv;
-            }
           }
+          __syncwarp();
         }
-        __syncwarp();
+      };
+      // v[j] += vec[col0 + j] (bias-like row vector; 16 B loads when aligned, broadcast across lanes)
+      auto add_vec = [&](float (&v)[32], const float* vec, int col0) {
+        if (((uintptr_t)(vec + col0) & 15) == 0 && col0 + 32 <= p.N) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(vec + col0) + j);
+            v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += col0 + j < p.N ? __ldg(vec + col0 + j) : 0.f;
+        }
       };
 
       if constexpr (EPI == EDA_EPI_BIAS || EPI == EDA_EPI_BIAS_RELU) {
-        for (int c = 0; c < GBN / 32; ++c) {
-          if (n0 + c * 32 >= p.N) break;
+        for (int c = 0; c < 4; ++c) {
+          const int col0 = n0 + ch * 128 + c * 32;
+          if (col0 >= p.N) break;
           float v[32];
           tmem_ld32(trow + c * 32, v);
+          if (p.bias) add_vec(v, p.bias, col0);
+          if (EPI == EDA_EPI_BIAS_RELU) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int col = n0 + c * 32 + j;
-            v[j] += (p.bias && col < p.N) ? __ldg(p.bias + col) : 0.f;
-            if (EPI == EDA_EPI_BIAS_RELU) v[j] = fmaxf(v[j], 0.f);
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
           }
-          store_chunk(v, c, n0, p.Chi, p.Clo, p.lds);
+          store_chunk(v, col0, p.Chi, p.Clo, p.lds);
         }
       } else if constexpr (EPI == GEPI_QKV) {
         // n_blk 0: q (pre-scaled), 1: k -> split (M, 2*GBN); 2: v -> transposed per (b, h)
-        const int row = m0 + q * 32 + lane;
+        const int row = rbase + lane;
         const int b = row / p.T, t = row - b * p.T;
-        for (int c = 0; c < GBN / 32; ++c) {
+        const float sc = n_blk == 0 ? p.q_scale : 1.0f;
+        for (int c = 0; c < 4; ++c) {
+          const int cc = ch * 4 + c;                               // 32-column chunk within the 256-wide tile
           float v[32];
           tmem_ld32(trow + c * 32, v);
-          const float sc = n_blk == 0 ? p.q_scale : 1.0f;
+          add_vec(v, p.bias, n0 + cc * 32);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = (v[j] + __ldg(p.bias + n0 + c * 32 + j)) * sc;
+          for (int j = 0; j < 32; ++j) v[j] *= sc;
           if (n_blk < 2) {
-            store_chunk(v, c, n0, p.Chi, p.Clo, p.lds);
+            store_chunk(v, n0 + cc * 32, p.Chi, p.Clo, p.lds);
           } else if (row < p.M) {
-            const int h = c >> 1, d0 = (c & 1) * 32;
+            const int h = cc >> 1, d0 = (cc & 1) * 32;
             const size_t base = ((size_t)(b * p.H + h) * 64 + d0) * p.Tp + t;
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
@@ -241,54 +276,75 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
           }
         }
       } else {
-        // LayerNorm epilogues: N == 256 == GBN, the thread owns the whole row (kept in TMEM).
+        // LayerNorm epilogues: N == 256 == GBN.  A row is owned by TWO threads (column halves) and
+        // stays in TMEM between the passes; row statistics are exchanged through shared memory
+        // with a 64-thread named barrier per lane quadrant.  Two-pass variance like ATen.
+        // The residual is read thread-per-row (each 32 B sector is consumed by two back-to-back
+        // loads) and prefetched one 32-column chunk ahead so DRAM latency is off the critical path.
         float sum = 0.f;
-        for (int c = 0; c < GBN / 32; ++c) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int col0 = ch * 128 + c * 32;
           float v[32];
           tmem_ld32(trow + c * 32, v);
           if constexpr (EPI == EDA_EPI_BIAS_RES_LN) {
-            // coalesced read of the residual chunk, transposed through smem to thread-per-row
-#pragma unroll
-            for (int it2 = 0; it2 < 8; ++it2) {
-              const int r = it2 * 4 + srow, grow = m0 + q * 32 + r;
-              float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (grow < p.M) x = __ldg(reinterpret_cast<const float4*>(p.resid + (size_t)grow * p.ldr + c * 32 + scol));
-              *reinterpret_cast<float4*>(&stg[r * G_STG_LD + scol]) = x;
-            }
-            __syncwarp();
+            float4 rn[8];
+            if (c < 3) load_resid(c + 1, rn);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float4 x = *reinterpret_cast<const float4*>(&stg[lane * G_STG_LD + 4 * j]);
-              v[4 * j] += x.x; v[4 * j + 1] += x.y; v[4 * j + 2] += x.z; v[4 * j + 3] += x.w;
+              v[4 * j] += rp[j].x; v[4 * j + 1] += rp[j].y; v[4 * j + 2] += rp[j].z; v[4 * j + 3] += rp[j].w;
             }
-            __syncwarp();
-          }
+            if (c < 3) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) { v[j] += __ldg(p.bias + c * 32 + j); sum += v[j]; }
+              for (int j = 0; j < 8; ++j) rp[j] = rn[j];
+            }
+          }
+          add_vec(v, p.bias, col0);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) sum += v[j];
           tmem_st32(trow + c * 32, v);
         }
         tmem_wait_st();
-        const float mean = sum * (1.0f / GBN);
+        const int xr = q * 32 + lane;
+        ln_x[0][ch][xr] = sum;
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+        const float mean = (ln_x[0][0][xr] + ln_x[0][1][xr]) * (1.0f / GBN);
         float sq = 0.f;
-        for (int c = 0; c < GBN / 32; ++c) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
           float v[32];
           tmem_ld32(trow + c * 32, v);
 #pragma unroll
           for (int j = 0; j < 32; ++j) { const float d = v[j] - mean; sq = fmaf(d, d, sq); }
         }
-        const float rstd = 1.0f / sqrtf(sq * (1.0f / GBN) + 1e-5f);
-        for (int c = 0; c < GBN / 32; ++c) {
+        ln_x[1][ch][xr] = sq;
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+        const float rstd = 1.0f / sqrtf((ln_x[1][0][xr] + ln_x[1][1][xr]) * (1.0f / GBN) + 1e-5f);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int col0 = ch * 128 + c * 32;
           float v[32];
           tmem_ld32(trow + c * 32, v);
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            v[j] = (v[j] - mean) * rstd * __ldg(p.gamma + c * 32 + j) + __ldg(p.beta + c * 32 + j);
-          store_chunk(v, c, 0, p.Chi, p.Clo, p.lds);
+          for (int j = 0; j < 8; ++j) {
+            const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.gamma + col0) + j);
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.beta + col0) + j);
+            v[4 * j] = (v[4 * j] - mean) * rstd * g4.x + b4.x;
+            v[4 * j + 1] = (v[4 * j + 1] - mean) * rstd * g4.y + b4.y;
+            v[4 * j + 2] = (v[4 * j + 2] - mean) * rstd * g4.z + b4.z;
+            v[4 * j + 3] = (v[4 * j + 3] - mean) * rstd * g4.w + b4.w;
+          }
+          store_chunk(v, col0, p.Chi, p.Clo, p.lds);
         }
+        // (ln_x reuse is safe: a warp rewrites ln_x[k] only after the partner has passed the
+        //  barrier that follows its read of ln_x[k])
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[ab]);
+      {
+
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[ab]);
+      }
     }
   }
   tc_fence_before();
@@ -392,7 +448,7 @@ static int launch_gemm(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const C
     attr = true;
   }
   const int n_tiles = ceil_div(p.N, GBN) * ceil_div(p.M, GBM);
-  gemm_split_kernel<EPI><<<std::min(n_tiles, num_sms()), 192, G_SMEM, st>>>(a_hi, a_lo, b_hi, b_lo, p);
+  gemm_split_kernel<EPI><<<std::min(n_tiles, num_sms()), G_THREADS, G_SMEM, st>>>(a_hi, a_lo, b_hi, b_lo, p);
   EDA_LAUNCH_CHECK();
   return EDA_OK;
 }

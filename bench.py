@@ -41,6 +41,11 @@ def peaks():
         return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
 
 
+def pcm16(x: torch.Tensor) -> torch.Tensor:
+    """float [-1, 1) -> 16-bit PCM (what a wav file stores)."""
+    return (x * 32768.0).round().clamp_(-32768, 32767).to(torch.int16).contiguous()
+
+
 def synth_audio_batch(n_rec: int, seed: int) -> torch.Tensor:
     """(n_rec, SECONDS*RATE) float32 synthetic 2-speaker mixtures: gated, low-passed noise.
     Cheap vectorised stand-in for oracle.feature_oracle.synth_audio (same spirit: talk spurts
@@ -103,7 +108,8 @@ def cpu_reference(n_rec: int, steps: int, warmup: int, threads: int):
     torch.set_num_threads(threads)
     sd = synth_state_dict(EdaConfig(n_layers=LAYERS), 777)
     model = OracleEda(sd, n_heads=HEADS, library_lstm=True)
-    audio = synth_audio_batch(n_rec, 0).double().numpy()          # soundfile hands float64 (kaldi_data.py:82)
+    # soundfile hands the reference float64 = int16 PCM / 32768 (kaldi_data.py:82)
+    audio = (pcm16(synth_audio_batch(n_rec, 0)).double() / 32768.0).numpy()
     def step():
         feats = [torch.from_numpy(fo.frontend(a, RATE, FRAME, SHIFT, CTX, SUB)) for a in audio]
         return model.infer(feats, attractor_threshold=0.5, max_n_speakers=MAXSPK)
@@ -129,6 +135,7 @@ def run_ours(args):
     from oracle.weights import EdaConfig, synth_state_dict     # seeded weights only (not the oracle path)
     from speaker_diarization_b200 import _lib as L, feature
     from speaker_diarization_b200.eend_eda.models import TransformerEdaModel
+    from speaker_diarization_b200.pipeline import InferencePipeline
 
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -141,22 +148,23 @@ def run_ours(args):
     model.load_state_dict(synth_state_dict(EdaConfig(n_layers=LAYERS), 777))
     model = model.to(dev).eval()
     fe = feature.FrontEnd(RATE, FRAME, SHIFT, CTX, SUB, device=dev)
-    host_audio = [synth_audio_batch(B, 2 * rank + i).pin_memory() for i in range(2)]   # 2 x 102 MB
+    pipe = InferencePipeline(model, fe, max_n_speakers=MAXSPK, attractor_threshold=0.5, activity_threshold=0.5, depth=2)
+    # host audio = 16-bit PCM, the sample format of the wav files the reference reads (kaldi_data.py:59-83)
+    host_audio = [pcm16(synth_audio_batch(B, 2 * rank + i)).pin_memory() for i in range(2)]    # 2 x 51 MB
     dev_audio = [a.to(dev) for a in host_audio]
     ns = [SECONDS * RATE] * B
-    gather_buf = [torch.empty((B, T, MAXSPK - 1), device=dev) for _ in range(world)] if (world > 1 and rank == 0) else None
+    if world > 1:       # the path's one collective: result collection on rank 0
+        gather_buf = [torch.empty((B, T, MAXSPK - 1), device=dev) for _ in range(world)] if rank == 0 else None
+        pipe.gather = lambda post: dist.gather(post, gather_buf, dst=0)
 
-    def step(i, audio_list):
-        feats = fe.features(audio_list[i & 1], ld=352, counts=ns)
-        ys = model.infer(feats, attractor_threshold=0.5, max_n_speakers=MAXSPK, activity_threshold=0.5)
-        post = model.last["posteriors"]
-        if world > 1:                      # the path's one collective: result collection on rank 0
-            dist.gather(post, gather_buf, dst=0)
-        return ys, post
+    def run_steps(audio_list, n):
+        last = None
+        for last in pipe.run((audio_list[i & 1], ns) for i in range(n)):
+            pass
+        return last
 
     torch.manual_seed(1234 + rank)
-    for i in range(max(3, args.warmup)):
-        step(i, dev_audio)
+    run_steps(dev_audio, max(3, args.warmup))
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -165,10 +173,9 @@ def run_ours(args):
     n0 = L.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
-    ev0.record()
-    for i in range(args.steps):
-        step(i, dev_audio)
-    ev1.record()
+    ev0.record(pipe.s_compute)
+    run_steps(dev_audio, args.steps)
+    ev1.record(pipe.s_out)                 # the result stream trails the compute stream
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -180,31 +187,33 @@ def run_ours(args):
     value = world * B * T / (ms_step * 1e-3)
 
     # ---- end to end through the public API with HOST buffers (pinned), result read back ----
-    def e2e_step(i):
-        ys, post = step(i, host_audio)
-        return post.cpu() if (world == 1 or rank == 0) else None
-    for i in range(2):
-        e2e_step(i)
+    run_steps(host_audio, 2)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
-    for i in range(args.steps):
-        e2e_step(i)
+    res = run_steps(host_audio, args.steps)           # every step: H2D of its audio, D2H of its posteriors
+    assert res["posteriors"].shape == (B, T, MAXSPK - 1) and len(res["n_speakers"]) == B
     torch.cuda.synchronize()
     e2e_s = torch.tensor([(time.perf_counter() - t0) / args.steps], device=dev)
     if world > 1:
         dist.barrier()
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     clocks = sampler.stop()
-    h2d = B * SECONDS * RATE * 4 + B * T * 4 + 3 * (B + 1) * 8 + (2 * B + 1) * 8 + B * 4
-    d2h = B * T * (MAXSPK - 1) * 4 + B * MAXSPK * 4
+    h2d = B * SECONDS * RATE * 2 + B * T * 4 + 3 * (B + 1) * 8 + (2 * B + 1) * 8
+    d2h = B * T * (MAXSPK - 1) * 5 + B * MAXSPK * 4
+
+    def step(i, audio_list):
+        with torch.cuda.stream(pipe.s_compute):
+            feats, rows = fe.features_flat(audio_list[i & 1], ld=352, counts=ns)
+            return model.infer_device(feats, rows, MAXSPK, 0.5)
 
     out = None
     if rank == 0:
         # ---- roofline leg: per-entry-point device time of one instrumented step ------------
         L.PROFILE = {}
-        step(0, dev_audio)
+        with torch.cuda.stream(pipe.s_compute):
+            step(0, dev_audio)
         prof = L.profile_ms()
         L.PROFILE = None
         tot = sum(ms_ for v in prof.values() for ms_, _ in v)
@@ -255,7 +264,8 @@ def run_ours(args):
                                    f"({B} x {SECONDS}s @ {RATE} Hz audio through the front end), 2 speakers, per GPU",
                        "global_batch": world * B, "frames_per_step": world * B * T, "precision": precision,
                        "parallelism": f"dp{world} (recordings sharded, one NCCL gather of posteriors)",
-                       "l2": "two alternating 102 MB audio batches + 262 MB FFN intermediates per step exceed the 126 MB L2"},
+                       "l2": "two alternating 51 MB int16 audio batches + 524 MB of FFN intermediates per step exceed the 126 MB L2",
+                       "pipeline": "InferencePipeline depth 2: H2D / compute / D2H streams, host never waits on the batch just submitted"},
             "e2e": {"value": round(world * B * T / e2e_s.item(), 1), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,

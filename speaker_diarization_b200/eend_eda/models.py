@@ -59,6 +59,8 @@ class TransformerEdaModel(nn.Module):
         self.set_precision(precision or os.environ.get("EDA_B200_PRECISION", "fp32"))
         self._prep = None
         self._ws = {}
+        self._perm_ring = {}
+        self._emb_split = None
 
     def set_precision(self, name: str) -> None:
         """'fp32' (CUDA-core FFMA), 'bf16x3' (tcgen05, split-bf16 operands) or 'bf16'."""
@@ -144,20 +146,26 @@ class TransformerEdaModel(nn.Module):
         torch.cat([s.float() for s in seqs], dim=0, out=stage)
         return stage.to(dev, non_blocking=True)
 
-    def _embed(self, src: List[Tensor]):
-        """models.py:213-226 up to ``emb``; returns emb2d (B*Tmax, D) plus batch geometry."""
+    def _embed(self, src, ilens: Optional[List[int]] = None):
+        """models.py:213-226 up to ``emb``; returns emb2d (B*Tmax, D) plus batch geometry.
+        ``src`` is the reference's list of (T_i, F) tensors, or (with ``ilens``) ONE device
+        matrix holding the sequences back to back (row stride may exceed F)."""
         dev = self._device()
         self._check_mode()
         w = self._prepared()
-        ilens = [int(x.shape[0]) for x in src]
+        flat_in = ilens is not None
+        if not flat_in:
+            ilens = [int(x.shape[0]) for x in src]
         B, Tmax = len(ilens), max(ilens)
         off = np.zeros(B + 1, dtype=np.int64)
         np.cumsum(ilens, out=off[1:])
         meta = torch.from_numpy(np.concatenate([off, np.asarray(ilens, dtype=np.int64)])).to(dev, non_blocking=True)
         seq_off = meta[: B + 1]
         lens_dev = meta[B + 1:].to(torch.int32)
-        flat = self._to_device_flat(src, dev)
+        flat = src if flat_in else self._to_device_flat(src, dev)
         P = self.precision
+        if flat_in and P == L.PREC_FP32 and not flat.is_contiguous():
+            flat = flat.contiguous()
         if P != L.PREC_FP32:
             return self._embed_tc(flat, w, seq_off, lens_dev, ilens, B, Tmax, dev)
         self._emb_split = None
@@ -197,16 +205,27 @@ class TransformerEdaModel(nn.Module):
         self._emb_split = (sa, ws["xproj"])
         return emb, ilens, lens_dev, seq_off, B, Tmax
 
-    @staticmethod
-    def _draw_perm(ilens: List[int], Tmax: int, dev, perms=None) -> Tensor:
+    def _draw_perm(self, ilens: List[int], Tmax: int, dev, perms=None) -> Tensor:
         """models.py:229-232: one ``torch.randperm(ilen)`` per sequence from the global CPU
         generator, in batch order; shipped as an int32 (B, Tmax) index (identity beyond ilen).
         ``perms`` (extension): use these frame orders instead of drawing (callers that batch
         chunks out of order draw them first, in the reference's order)."""
-        perm = torch.arange(Tmax, dtype=torch.int32).repeat(len(ilens), 1).pin_memory()
+        # pinned staging buffers are recycled through a small ring (an event per buffer guards
+        # the asynchronous H2D copy that last read it)
+        B = len(ilens)
+        ring = self._perm_ring.setdefault((B, Tmax), [])
+        slot = next((r for r in ring if r[1].query()), None)
+        if slot is None:
+            slot = [torch.empty((B, Tmax), dtype=torch.int32, pin_memory=True), torch.cuda.Event()]
+            if len(ring) < 8:
+                ring.append(slot)
+        perm = slot[0]
+        perm[:] = torch.arange(Tmax, dtype=torch.int32)
         for i, n in enumerate(ilens):
             perm[i, :n] = (torch.randperm(n) if perms is None else perms[i]).to(torch.int32)
-        return perm.to(dev, non_blocking=True)
+        out = perm.to(dev, non_blocking=True)
+        slot[1].record(torch.cuda.current_stream(dev))
+        return out
 
     def forward_embedding(self, src: List[Tensor]):
         """Reference signature (models.py:213): (encoder_out_shuffled, emb, ilens)."""
@@ -243,6 +262,20 @@ class TransformerEdaModel(nn.Module):
         return loss, stats
 
     # ----------------------------------------------------------------------- infer -------
+    @torch.no_grad()
+    def infer_device(self, feats: Tensor, ilens: List[int], max_n_speakers=15, activity_threshold=0.5, perms=None):
+        """The device half of ``infer`` with NO host synchronisation: ``feats`` is one CUDA matrix
+        holding the sequences back to back (as ``FrontEnd.features_flat`` returns it).  Returns
+        (posteriors (B, Tmax, max_n_speakers-1), attractor existence probs (B, max_n_speakers),
+        uint8 activity labels) on the device; speaker counting / slicing is the caller's."""
+        x, ilens, lens_dev, _, B, Tmax = self._embed(feats, ilens)
+        perm = self._draw_perm(ilens, Tmax, x.device, perms)
+        att, probs, _ = self.eda.attractors(x, perm, lens_dev, ilens, B, Tmax, max_n_speakers,
+                                            emb_split=self._emb_split)
+        _, post, labels = ops.posterior(x, att, B, Tmax, max_n_speakers - 1, threshold=activity_threshold,
+                                        want_labels=True)
+        return post, probs, labels
+
     @torch.no_grad()
     def infer(self, src: List[Tensor], infer_num_speakers=None, max_n_speakers=15, attractor_threshold=0.5,
               activity_threshold: Optional[float] = None, perms=None):

@@ -56,6 +56,7 @@ class FrontEnd:
         if self.device.type != "cuda":
             raise L.EdaError("speaker_diarization_b200 has no CPU path")
         self._plan = C.c_void_p()
+        self._off_cache = {}
         with torch.cuda.device(self.device):
             L.call("eda_frontend_plan_create", sample_rate, frame_size, frame_shift, n_mels, C.byref(self._plan))
 
@@ -98,6 +99,15 @@ class FrontEnd:
         return (audio, is_f64) + self._offsets(ns)
 
     def _offsets(self, ns):
+        key = tuple(ns)
+        hit = self._off_cache.get(key)
+        if hit is None:
+            if len(self._off_cache) > 64:
+                self._off_cache.clear()
+            hit = self._off_cache[key] = self._offsets_uncached(ns)
+        return hit
+
+    def _offsets_uncached(self, ns):
         frames = [count_frames(n, self.frame_shift) for n in ns]
         rows = [(f + self.subsampling - 1) // self.subsampling for f in frames]
         off = np.zeros((3, len(ns) + 1), dtype=np.int64)
@@ -121,6 +131,16 @@ class FrontEnd:
     def features(self, recs, ld: int = 0, counts=None) -> List[torch.Tensor]:
         """The whole chain for a batch of recordings: list of (ceil(frames/sub), feat_dim)
         fp32 CUDA tensors (views into one buffer; row stride ``ld`` if given, e.g. 352)."""
+        feats, rows = self.features_flat(recs, ld, counts)
+        out, pos = [], 0
+        for r in rows:
+            out.append(feats[pos:pos + r])
+            pos += r
+        return out
+
+    def features_flat(self, recs, ld: int = 0, counts=None):
+        """Same, as ONE (sum rows, feat_dim) view (row stride ``ld``) plus the row count of each
+        recording -- the form ``TransformerEdaModel.infer_device`` consumes without a copy."""
         lm, colsum, (offs, frames, rows) = self.logmel(recs, counts)
         ld = ld or self.feat_dim
         total_rows = int(sum(rows))
@@ -129,11 +149,7 @@ class FrontEnd:
             L.call("eda_frontend_splice_subsample", self._plan, L.ptr(lm), L.ptr(colsum), L.ptr(offs[1]),
                    L.ptr(offs[2]), len(rows), total_rows, self.context_size, self.subsampling,
                    L.ptr(feats), ld, L.stream())
-        out, pos = [], 0
-        for r in rows:
-            out.append(feats[pos:pos + r, : self.feat_dim])
-            pos += r
-        return out
+        return feats[:, : self.feat_dim], rows
 
 
 _frontends = {}

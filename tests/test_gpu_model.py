@@ -189,3 +189,39 @@ def test_frontend_int16_pcm_matches_soundfile_scaling():
         got = fe.features([pcm])[0]
         assert tuple(got.shape) == want.shape
         assert np.abs(got.cpu().numpy() - want).max() < 2e-5
+
+
+def test_pipeline_matches_infer():
+    """InferencePipeline (3 streams, 2 batches in flight, int16 PCM from pinned host memory) ==
+    feature.extract + TransformerEdaModel.infer batch by batch with the same randperm stream."""
+    from oracle import feature_oracle as fo
+    from oracle.weights import EdaConfig, synth_state_dict
+    from speaker_diarization_b200 import feature
+    from speaker_diarization_b200.eend_eda.models import TransformerEdaModel
+    from speaker_diarization_b200.pipeline import InferencePipeline
+    cfg = EdaConfig(n_layers=2)
+    m = TransformerEdaModel(2, cfg.in_size, cfg.n_heads, cfg.n_units, cfg.n_layers, precision="bf16x3")
+    m.load_state_dict(synth_state_dict(cfg, 777))
+    m = m.cuda().eval()
+    fe = feature.FrontEnd(8000, 200, 80, 7, 10)
+    batches = []
+    for k in range(4):
+        n = 8000 * (4 + k)
+        pcm = np.stack([np.clip(np.round(fo.synth_audio(n, 8000, 2, 10 * k + i, dtype=np.float64)[0] * 32768), -32768, 32767)
+                        for i in range(3)]).astype(np.int16)
+        batches.append((torch.from_numpy(pcm).pin_memory(), [n] * 3))
+    torch.manual_seed(5)
+    want = []
+    for audio, counts in batches:
+        feats = fe.features([a for a in audio])
+        ys = m.infer(feats, attractor_threshold=0.5, activity_threshold=0.5)
+        want.append((m.last["posteriors"].cpu(), [int(y.shape[1]) for y in ys], m.last["labels"].cpu()))
+    torch.manual_seed(5)
+    pipe = InferencePipeline(m, fe, depth=2)
+    got = [dict(posteriors=r["posteriors"].clone(), n=r["n_speakers"], labels=r["labels"].clone(), lengths=r["lengths"])
+           for r in pipe.run(batches)]
+    assert len(got) == 4
+    for (wp, wn, wl), g in zip(want, got):
+        assert torch.equal(g["posteriors"], wp) and torch.equal(g["labels"], wl)
+        assert [min(x, 14) for x in g["n"]] == wn
+        assert g["lengths"] == [wp.shape[1]] * 3

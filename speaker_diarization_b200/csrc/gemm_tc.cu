@@ -16,8 +16,8 @@
 //               so the epilogue of tile i overlaps the MMAs of tile i+1
 //   warps 2-9   epilogue (two warps per TMEM lane quadrant, 128 columns each): tcgen05.ld ->
 //               bias / ReLU / residual + LayerNorm (row held in the registers of two threads,
-//               statistics exchanged through smem) -> smem transpose -> coalesced stores of the
-//               fp32 and/or split-bf16 output; the QKV variant pre-scales q by 1/sqrt(dh) and
+//               statistics exchanged through smem) -> thread-per-row 32-byte stores (STG.256, one full
+//               sector each) of the fp32 and/or split-bf16 output; the QKV variant pre-scales q by 1/sqrt(dh) and
 //               stores v TRANSPOSED per (batch, head) for the attention kernel.
 #include <algorithm>
 #include <mutex>
@@ -37,10 +37,8 @@ constexpr int G_B_TILE = GBN * GBK * 2;                  // 32 KB
 constexpr int G_STAGE = 2 * G_A_TILE + 2 * G_B_TILE;     // 96 KB
 constexpr int G_EPI_WARPS = 8;
 constexpr int G_THREADS = 64 + 32 * G_EPI_WARPS;
-constexpr int G_STG_LD = 20;                             // floats per staged row (16 + pad): conflict-free float4
-constexpr int G_STG_BYTES = G_EPI_WARPS * 32 * G_STG_LD * 4;
 constexpr int G_LNX_BYTES = 2 * 2 * GBM * 4;             // LayerNorm partial sums [pass][column half][row]
-constexpr int G_SMEM = GSTAGES * G_STAGE + G_STG_BYTES + G_LNX_BYTES + 256 + 1024;
+constexpr int G_SMEM = GSTAGES * G_STAGE + G_LNX_BYTES + 256 + 1024;
 
 enum { GEPI_QKV = 4 };
 
@@ -60,6 +58,18 @@ __device__ __forceinline__ void split2(float x0, float x1, __nv_bfloat162& hi, _
   hi = __halves2bfloat162(h0, h1);
   lo = __halves2bfloat162(__float2bfloat16_rn(x0 - __bfloat162float(h0)),
                           __float2bfloat16_rn(x1 - __bfloat162float(h1)));
+}
+
+// one 32-byte (full sector) global store
+__device__ __forceinline__ void st_global_v8(void* p, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                             uint32_t a4, uint32_t a5, uint32_t a6, uint32_t a7) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"l"(p), "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(a4), "r"(a5), "r"(a6), "r"(a7) : "memory");
+}
+
+__device__ __forceinline__ void ld_global_nc_v8(const float* p, float4& a, float4& b) {
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
 }
 
 // fp32 (rows x K, ld) -> hi, lo bf16 (rows x ldk), zero padded columns [K, ldk)
@@ -84,9 +94,8 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
                   const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  float* stg_all = reinterpret_cast<float*>(smem + GSTAGES * G_STAGE);
-  float (*ln_x)[2][GBM] = reinterpret_cast<float (*)[2][GBM]>(smem + GSTAGES * G_STAGE + G_STG_BYTES);
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + GSTAGES * G_STAGE + G_STG_BYTES + G_LNX_BYTES);
+  float (*ln_x)[2][GBM] = reinterpret_cast<float (*)[2][GBM]>(smem + GSTAGES * G_STAGE);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + GSTAGES * G_STAGE + G_LNX_BYTES);
   uint64_t* empty = full + GSTAGES;
   uint64_t* tfull = empty + GSTAGES;
   uint64_t* tempty = tfull + 2;
@@ -165,8 +174,6 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
     // ===== epilogue: warps 2..9.  Warp w touches TMEM lanes 32*(w%4)..+31 (rows of the tile);
     // the two warps of a lane quadrant split the 256 columns in halves of 128. =====
     const int q = warp & 3, ch = (warp - 2) >> 2;
-    float* stg = stg_all + (warp - 2) * 32 * G_STG_LD;
-    const int frow = lane >> 2, fcol = (lane & 3) * 4;            // staged-copy role: 8 rows x 4 float4 per pass
     uint32_t lt = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
       const int m0 = (tile / n_tiles_n) * GBM, n_blk = tile % n_tiles_n, n0 = n_blk * GBN;
@@ -175,9 +182,17 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
       // residual chunk c of this thread's row (RES_LN): 8 x 16 B, thread-per-row
       auto load_resid = [&](int c, float4 (&dst)[8]) {
         const int row = rbase + lane;
-        const float4* src = reinterpret_cast<const float4*>(p.resid + (size_t)row * p.ldr + ch * 128 + c * 32);
+        const float* src = p.resid + (size_t)row * p.ldr + ch * 128 + c * 32;
+        if (row >= p.M) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) dst[j] = row < p.M ? __ldg(src + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int j = 0; j < 8; ++j) dst[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else if (((uintptr_t)src & 31) == 0) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) ld_global_nc_v8(src + 8 * j, dst[2 * j], dst[2 * j + 1]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dst[j] = __ldg(reinterpret_cast<const float4*>(src) + j);
+        }
       };
       float4 rp[8];
       if constexpr (EPI == EDA_EPI_BIAS_RES_LN) load_resid(0, rp);   // in flight while the MMAs finish
@@ -185,42 +200,50 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
       tc_fence_after();
       const uint32_t trow = tmem_base + ab * GBN + ch * 128 + (uint32_t(q * 32) << 16);
 
-      // thread-per-row registers -> 32 x 16 smem block -> coalesced row segments (full 32 B sectors)
+      // thread-per-row stores straight from registers: 32 consecutive columns of one row are
+      // 128 B of fp32 / 64 B of bf16, written as 32-byte (full-sector) STG.256s
       auto store_chunk = [&](const float (&v)[32], int gcol0, bf16* out_hi, bf16* out_lo, int lds) {
+        const int grow = rbase + lane;
+        if (grow >= p.M || gcol0 >= p.N) return;
+        const bool whole = gcol0 + 32 <= p.N;
+        if (p.C && EPI != GEPI_QKV) {
+          float* dst = p.C + (size_t)grow * p.ldc + gcol0;
+          if (whole && ((uintptr_t)dst & 31) == 0) {
 #pragma unroll
-        for (int hf = 0; hf < 2; ++hf) {
+            for (int j = 0; j < 4; ++j)
+              st_global_v8(dst + 8 * j, __float_as_uint(v[8 * j]), __float_as_uint(v[8 * j + 1]),
+                           __float_as_uint(v[8 * j + 2]), __float_as_uint(v[8 * j + 3]), __float_as_uint(v[8 * j + 4]),
+                           __float_as_uint(v[8 * j + 5]), __float_as_uint(v[8 * j + 6]), __float_as_uint(v[8 * j + 7]));
+          } else {
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            *reinterpret_cast<float4*>(&stg[lane * G_STG_LD + 4 * j]) =
-                make_float4(v[16 * hf + 4 * j], v[16 * hf + 4 * j + 1], v[16 * hf + 4 * j + 2], v[16 * hf + 4 * j + 3]);
-          __syncwarp();
-#pragma unroll
-          for (int it2 = 0; it2 < 4; ++it2) {
-            const int r = it2 * 8 + frow, grow = rbase + r, gcol = gcol0 + 16 * hf + fcol;
-            const float4 x = *reinterpret_cast<const float4*>(&stg[r * G_STG_LD + fcol]);
-            if (grow < p.M && gcol < p.N) {
-              if (p.C && EPI != GEPI_QKV) {
-                float* dst = p.C + (size_t)grow * p.ldc + gcol;
-                if (gcol + 3 < p.N) *reinterpret_cast<float4*>(dst) = x;
-                else {
-                  dst[0] = x.x;
-                  if (gcol + 1 < p.N) dst[1] = x.y;
-                  if (gcol + 2 < p.N) dst[2] = x.z;
-                }
-              }
-              if (out_hi) {      // split outputs require N % 4 == 0 (checked on the host)
-                __nv_bfloat162 h0, l0, h1, l1;
-                split2(x.x, x.y, h0, l0);
-                split2(x.z, x.w, h1, l1);
-                uint2 hv, lv;
-                hv.x = *reinterpret_cast<uint32_t*>(&h0); hv.y = *reinterpret_cast<uint32_t*>(&h1);
-                lv.x = *reinterpret_cast<uint32_t*>(&l0); lv.y = *reinterpret_cast<uint32_t*>(&l1);
-                *reinterpret_cast<uint2*>(out_hi + (size_t)grow * lds + gcol) = hv;
-                *reinterpret_cast<uint2*>(out_lo + (size_t)grow * lds + gcol) = lv;
-              }
-            }
+            for (int j = 0; j < 32; ++j)
+              if (gcol0 + j < p.N) dst[j] = v[j];
           }
-          __syncwarp();
+        }
+        if (out_hi) {      // split outputs require N % 4 == 0 (checked on the host)
+          uint32_t h[16], l[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            __nv_bfloat162 h2, l2;
+            split2(v[2 * j], v[2 * j + 1], h2, l2);
+            h[j] = *reinterpret_cast<uint32_t*>(&h2);
+            l[j] = *reinterpret_cast<uint32_t*>(&l2);
+          }
+          bf16* dh = out_hi + (size_t)grow * lds + gcol0;
+          bf16* dl = out_lo + (size_t)grow * lds + gcol0;
+          if (whole && (((uintptr_t)dh | (uintptr_t)dl) & 31) == 0) {
+            st_global_v8(dh, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+            st_global_v8(dh + 16, h[8], h[9], h[10], h[11], h[12], h[13], h[14], h[15]);
+            st_global_v8(dl, l[0], l[1], l[2], l[3], l[4], l[5], l[6], l[7]);
+            st_global_v8(dl + 16, l[8], l[9], l[10], l[11], l[12], l[13], l[14], l[15]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (gcol0 + 2 * j < p.N) {
+                *reinterpret_cast<uint32_t*>(dh + 2 * j) = h[j];
+                *reinterpret_cast<uint32_t*>(dl + 2 * j) = l[j];
+              }
+          }
         }
       };
       // v[j] += vec[col0 + j] (bias-like row vector; 16 B loads when aligned, broadcast across lanes)

@@ -80,6 +80,11 @@ __device__ __forceinline__ float sum2(uint64_t v) {
   return __uint_as_float((uint32_t)v) + __uint_as_float((uint32_t)(v >> 32));
 }
 
+// Gate non-linearities on the MUFU pipe (ex2.approx + rcp.approx, ~3e-7 relative): they sit on
+// the per-step dependency chain, where libm's expf/tanhf cost several hundred cycles.
+__device__ __forceinline__ float fast_sigmoid(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float fast_tanh(float x) { return 1.f - __fdividef(2.f, 1.f + __expf(2.f * x)); }
+
 // w2[gate][2*i + {0,1}] = packed (W[row][4(kc+8i)+0..1]), (W[row][4(kc+8i)+2..3])
 __device__ __forceinline__ void load_w(uint64_t (&w2)[4][16], const float* __restrict__ W, int cta, int u, int kc) {
 #pragma unroll
@@ -265,10 +270,10 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
 
     const bool active = dec ? (my_b >= 0) : (s < my_len);
     if (active) {
-      const float ig = sigmoidf_ref(v4[0] + xg[0]), fg = sigmoidf_ref(v4[1] + xg[1]);
-      const float gg = tanhf(v4[2] + xg[2]), og = sigmoidf_ref(v4[3] + xg[3]);
+      const float ig = fast_sigmoid(v4[0] + xg[0]), fg = fast_sigmoid(v4[1] + xg[1]);
+      const float gg = fast_tanh(v4[2] + xg[2]), og = fast_sigmoid(v4[3] + xg[3]);
       c_state = fg * c_state + ig * gg;
-      h_state = og * tanhf(c_state);
+      h_state = og * fast_tanh(c_state);
       if (dec && owner) attractors[((size_t)my_b * n_dec + s) * kD + col] = h_state;
     }
     if (gs + 1 < n_total) {           // publish h (changed or not) into the next buffer of all 8 CTAs

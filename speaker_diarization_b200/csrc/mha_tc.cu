@@ -12,10 +12,11 @@
 //   warp 0     TMA producer: Q once, then K_j / V_j tiles (single stage each; two CTAs share an
 //              SM, so one CTA's softmax overlaps the other's MMAs)
 //   warp 1     MMA issuer (one thread) + TMEM owner (256 columns: S/P 0..127, O 128..191)
-//   warps 2-5  softmax: thread = query row.  S -> running max / sum, P = exp(S - m) split into
-//              bf16 hi/lo and written BACK INTO TMEM over S (A operand of P.V comes from
-//              TMEM), O rescaled in TMEM when the running max moves; final O / l -> split bf16
-//              (and/or fp32) through a shared-memory transpose.
+//   warps 2-5  softmax: thread = query row.  S -> running max / sum, P = exp(S - m) (MUFU ex2)
+//              split into bf16 hi/lo and written BACK INTO TMEM in place over the 32-column S
+//              chunk it was computed from (16 columns of packed hi pairs, 16 of lo pairs; the
+//              A operand of P.V comes from TMEM), O rescaled in TMEM when the running max
+//              moves; final O / l -> split bf16 (and/or fp32), thread-per-row 32-byte stores.
 #include <algorithm>
 
 #include "common.cuh"
@@ -36,7 +37,6 @@ constexpr int A_OFF_K = 2 * A_TILE16;                    // K_hi, K_lo
 constexpr int A_OFF_V = 4 * A_TILE16;                    // Vt_hi (2 chunks x 8 KB), Vt_lo
 constexpr int A_OFF_BAR = 6 * A_TILE16;
 constexpr int A_SMEM = 6 * A_TILE16 + 128 + 1024;
-constexpr int A_OST_LD = 68;                             // floats per staged output row
 constexpr uint32_t TM_S = 0, TM_O = 128;
 
 struct MhaParams {
@@ -69,6 +69,22 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
       "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
       ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
+}
+// two fp32 -> packed bf16 pair (a in the low half = element 2c), round to nearest even
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ void st_global_v8(void* p, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                             uint32_t a4, uint32_t a5, uint32_t a6, uint32_t a7) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"l"(p), "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(a4), "r"(a5), "r"(a6), "r"(a7) : "memory");
 }
 __device__ __forceinline__ uint32_t pack_bf16(bf16 a, bf16 b) {   // a -> low half (element 2c), b -> high
   __nv_bfloat162 v = __halves2bfloat162(a, b);
@@ -138,7 +154,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
       const uint64_t q_hi = smem_desc_sw128(sbase + A_OFF_Q), q_lo = smem_desc_sw128(sbase + A_OFF_Q + A_TILE16);
       const uint64_t k_hi = smem_desc_sw128(sbase + A_OFF_K), k_lo = smem_desc_sw128(sbase + A_OFF_K + A_TILE16);
       const uint32_t tS = tmem_base + TM_S, tO = tmem_base + TM_O;
-      const uint32_t tPhi = tS, tPlo = tS + 64;
+      const uint32_t tPhi = tS;
       mbar_wait(bar_q, 0);
       for (int j = 0; j < n_kt; ++j) {
         const uint32_t ph = j & 1;
@@ -162,10 +178,11 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
         for (int k = 0; k < ABN / 16; ++k) {
           const uint32_t voff = A_OFF_V + (k >> 2) * 8192 + (k & 3) * 32;
           const uint64_t v_hi = smem_desc_sw128(sbase + voff), v_lo = smem_desc_sw128(sbase + voff + A_TILE16);
-          umma_bf16_ts(tO, tPhi + k * 8, v_hi, idesc_o, (j | k) != 0);
+          const uint32_t pa = tPhi + (k >> 1) * 32 + (k & 1) * 8;    // hi pairs; lo pairs 16 columns on
+          umma_bf16_ts(tO, pa, v_hi, idesc_o, (j | k) != 0);
           if (x3) {
-            umma_bf16_ts(tO, tPhi + k * 8, v_lo, idesc_o, 1);
-            umma_bf16_ts(tO, tPlo + k * 8, v_hi, idesc_o, 1);
+            umma_bf16_ts(tO, pa, v_lo, idesc_o, 1);
+            umma_bf16_ts(tO, pa + 16, v_hi, idesc_o, 1);
           }
         }
         umma_commit(v_empty);
@@ -183,19 +200,25 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
       mbar_wait(bar_s, j & 1);
       tc_fence_after();
       const int n_valid = min(ABN, p.T - j * ABN);      // keys of this tile that exist
+      const bool whole = n_valid == ABN;                // (CTA-uniform) no masking needed
       // pass 1: row maximum
       float mx = -INFINITY;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         float v[32];
         tmem_ld32(tS + c * 32, v);
+        if (whole) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i < n_valid) ? v[i] : -INFINITY);
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, v[i]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i < n_valid) ? v[i] : -INFINITY);
+        }
       }
       const float m_new = fmaxf(m_cur, mx);             // finite: key 0 of every tile exists
       if (j > 0 && __any_sync(0xffffffffu, m_new > m_cur)) {
         // O *= exp(m_old - m_new): every earlier P.V has completed (bar_s was committed after it)
-        const float alpha = exp2f((m_cur - m_new) * kLog2e);
+        const float alpha = ex2_approx((m_cur - m_new) * kLog2e);
         l_sum *= alpha;
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
@@ -208,62 +231,84 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
       }
       m_cur = m_new;
       const float mb = m_new * kLog2e;
-      // pass 2: P = exp(S - m) -> split bf16, written over S (hi: cols 0..63, lo: cols 64..127)
-      uint32_t plo[4][16];
+      // pass 2: P = exp(S - m) -> split bf16, written IN PLACE over the 32 S columns it came from:
+      // packed hi pairs in the first 16 columns of the chunk, lo pairs in the last 16
+      float l0 = 0.f, l1 = 0.f;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         float v[32];
         tmem_ld32(tS + c * 32, v);
-        uint32_t phi[16];
+        float pk[32];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          float p0 = exp2f(fmaf(v[i], kLog2e, -mb)), p1 = exp2f(fmaf(v[i + 1], kLog2e, -mb));
-          if (c * 32 + i >= n_valid) p0 = 0.f;
-          if (c * 32 + i + 1 >= n_valid) p1 = 0.f;
-          l_sum += p0 + p1;
-          const bf16 h0 = __float2bfloat16_rn(p0), h1 = __float2bfloat16_rn(p1);
-          phi[i >> 1] = pack_bf16(h0, h1);
-          plo[c][i >> 1] = pack_bf16(__float2bfloat16_rn(p0 - __bfloat162float(h0)),
-                                     __float2bfloat16_rn(p1 - __bfloat162float(h1)));
+          float p0 = ex2_approx(fmaf(v[i], kLog2e, -mb)), p1 = ex2_approx(fmaf(v[i + 1], kLog2e, -mb));
+          if (!whole) {
+            if (c * 32 + i >= n_valid) p0 = 0.f;
+            if (c * 32 + i + 1 >= n_valid) p1 = 0.f;
+          }
+          l0 += p0; l1 += p1;
+          const uint32_t hi = pack_bf16x2(p0, p1);
+          pk[i >> 1] = __uint_as_float(hi);
+          pk[16 + (i >> 1)] = __uint_as_float(pack_bf16x2(p0 - __uint_as_float(hi << 16),
+                                                          p1 - __uint_as_float(hi & 0xffff0000u)));
         }
-        tmem_st16(tS + c * 16, phi);       // lands on S columns that were already consumed
+        tmem_st32(tS + c * 32, pk);
       }
-      if (x3) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) tmem_st16(tS + 64 + c * 16, plo[c]);
-      }
+      l_sum += l0 + l1;
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_p);
     }
-    // ---- epilogue: O / l -> smem (thread = row) -> coalesced row stores -------------------
+    // ---- epilogue: O / l, thread = row: 64 columns = 256 B fp32 / 128 B per bf16 half ------
     mbar_wait(bar_o, 0);
     tc_fence_after();
     const float inv = 1.0f / l_sum;
-    float* ost = reinterpret_cast<float*>(smem) + qd * 32 * A_OST_LD;     // Q/K tiles are dead now
+    const int q = q0 + qd * 32 + lane;
+    const size_t row = (size_t)b * p.T + q;
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
       float o[32];
       tmem_ld32(tO + c * 32, o);
+      if (q >= p.T) continue;
 #pragma unroll
-      for (int i = 0; i < 32; i += 4)
-        *reinterpret_cast<float4*>(&ost[lane * A_OST_LD + c * 32 + i]) =
-            make_float4(o[i] * inv, o[i + 1] * inv, o[i + 2] * inv, o[i + 3] * inv);
-    }
-    __syncwarp();
-    for (int r = 0; r < 32; ++r) {
-      const int q = q0 + qd * 32 + r;
-      if (q >= p.T) break;
-      const float2 x = *reinterpret_cast<const float2*>(&ost[r * A_OST_LD + 2 * lane]);
-      const size_t row = (size_t)b * p.T + q;
-      const int col = h * ADH + 2 * lane;
-      if (p.out) *reinterpret_cast<float2*>(p.out + row * p.ld_out + col) = x;
+      for (int i = 0; i < 32; ++i) o[i] *= inv;
+      const int col = h * ADH + c * 32;
+      if (p.out) {
+        float* dst = p.out + row * p.ld_out + col;
+        if (((uintptr_t)dst & 31) == 0) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 8)
+            st_global_v8(dst + i, __float_as_uint(o[i]), __float_as_uint(o[i + 1]), __float_as_uint(o[i + 2]),
+                         __float_as_uint(o[i + 3]), __float_as_uint(o[i + 4]), __float_as_uint(o[i + 5]),
+                         __float_as_uint(o[i + 6]), __float_as_uint(o[i + 7]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) *reinterpret_cast<float2*>(dst + i) = make_float2(o[i], o[i + 1]);
+        }
+      }
       if (p.out_hi) {
-        const bf16 h0 = __float2bfloat16_rn(x.x), h1 = __float2bfloat16_rn(x.y);
-        *reinterpret_cast<uint32_t*>(p.out_hi + row * p.ld_os + col) = pack_bf16(h0, h1);
-        *reinterpret_cast<uint32_t*>(p.out_lo + row * p.ld_os + col) =
-            pack_bf16(__float2bfloat16_rn(x.x - __bfloat162float(h0)), __float2bfloat16_rn(x.y - __bfloat162float(h1)));
+        uint32_t hh[16], ll[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          hh[i >> 1] = pack_bf16x2(o[i], o[i + 1]);
+          ll[i >> 1] = pack_bf16x2(o[i] - __uint_as_float(hh[i >> 1] << 16),
+                                   o[i + 1] - __uint_as_float(hh[i >> 1] & 0xffff0000u));
+        }
+        bf16* dh = p.out_hi + row * p.ld_os + col;
+        bf16* dl = p.out_lo + row * p.ld_os + col;
+        if ((((uintptr_t)dh | (uintptr_t)dl) & 31) == 0) {
+          st_global_v8(dh, hh[0], hh[1], hh[2], hh[3], hh[4], hh[5], hh[6], hh[7]);
+          st_global_v8(dh + 16, hh[8], hh[9], hh[10], hh[11], hh[12], hh[13], hh[14], hh[15]);
+          st_global_v8(dl, ll[0], ll[1], ll[2], ll[3], ll[4], ll[5], ll[6], ll[7]);
+          st_global_v8(dl + 16, ll[8], ll[9], ll[10], ll[11], ll[12], ll[13], ll[14], ll[15]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            *reinterpret_cast<uint32_t*>(dh + 2 * i) = hh[i];
+            *reinterpret_cast<uint32_t*>(dl + 2 * i) = ll[i];
+          }
+        }
       }
     }
     tc_fence_before();

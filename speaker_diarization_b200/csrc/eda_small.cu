@@ -71,42 +71,65 @@ int pad_pack_split(const float* src, int ld_src, const int64_t* seq_off, const i
 }
 
 // ---------------------------------------------------------- attractor head ----------
-// encoder_decoder_attractor.py:50-54 and models.py:350-371.  One CTA; warp per (b, n).
-__global__ void attractor_head_kernel(const float* __restrict__ att, const float* __restrict__ w,
-                                      const float* __restrict__ bias, int B, int n_dec, int D,
-                                      float* __restrict__ probs, int n_spk_label,
-                                      float* __restrict__ loss_att) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const int total = B * n_dec;
-  for (int i = warp; i < total; i += nwarps) {
-    const float* a = att + (size_t)i * D;
-    float s = 0.f;
+// encoder_decoder_attractor.py:50-54 and models.py:350-371.  Warp per (b, n) over the whole
+// grid; the attractor loss is a second one-CTA kernel (it needs every probability).
+__global__ void __launch_bounds__(256)
+attractor_head_kernel(const float* __restrict__ att, const float* __restrict__ w,
+                      const float* __restrict__ bias, int total, int D, float* __restrict__ probs) {
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (i >= total) return;
+  const float* a = att + (size_t)i * D;
+  float s = 0.f;
+  if (D % 4 == 0 && (((uintptr_t)a | (uintptr_t)w) & 15) == 0) {
+    const float4* a4 = reinterpret_cast<const float4*>(a);
+    const float4* w4 = reinterpret_cast<const float4*>(w);
+    for (int d = lane; d < D / 4; d += 32) {
+      const float4 x = __ldg(a4 + d), y = __ldg(w4 + d);
+      s = fmaf(x.x, y.x, s); s = fmaf(x.y, y.y, s); s = fmaf(x.z, y.z, s); s = fmaf(x.w, y.w, s);
+    }
+  } else {
     for (int d = lane; d < D; d += 32) s = fmaf(__ldg(a + d), __ldg(w + d), s);
-    s = warp_sum(s);
-    if (lane == 0) probs[i] = sigmoidf_ref(s + __ldg(bias));
   }
-  if (n_spk_label < 0 || loss_att == nullptr) return;
-  __syncthreads();
-  // BCE-with-logits on the PROBABILITIES (reference behaviour), fixed summation order.
-  if (threadIdx.x == 0) {
-    float total_loss = 0.f;
-    for (int b = 0; b < B; ++b) {
+  s = warp_sum(s);
+  if (lane == 0) probs[i] = sigmoidf_ref(s + __ldg(bias));
+}
+
+// BCE-with-logits on the PROBABILITIES (reference behaviour).  Row sums in parallel (thread = b,
+// n ascending), then ONE thread adds the rows in ascending b: a fixed summation order.
+__global__ void __launch_bounds__(1024)
+attractor_loss_kernel(const float* __restrict__ probs, int B, int n_dec, int n_spk_label,
+                      float* __restrict__ loss_att) {
+  __shared__ float rows[1024];
+  float total_loss = 0.f;
+  for (int b0 = 0; b0 < B; b0 += 1024) {
+    const int b = b0 + threadIdx.x;
+    if (b < B) {
       float row = 0.f;
       for (int n = 0; n < n_dec; ++n) {
         const float x = probs[b * n_dec + n], y = n < n_spk_label ? 1.f : 0.f;
         row += fmaxf(x, 0.f) - x * y + log1pf(expf(-fabsf(x)));
       }
-      total_loss += row / (float)n_dec;
+      rows[threadIdx.x] = row / (float)n_dec;
     }
-    loss_att[0] = total_loss / (float)B;
+    __syncthreads();
+    if (threadIdx.x == 0)
+      for (int j = 0; j < min(1024, B - b0); ++j) total_loss += rows[j];
+    __syncthreads();
   }
+  if (threadIdx.x == 0) loss_att[0] = total_loss / (float)B;
 }
 
 int attractor_head(const float* att, const float* w, const float* bias, int B, int n_dec, int D,
                    float* probs, int n_spk_label, float* loss_att, cudaStream_t st) {
   EDA_REQUIRE(B > 0 && n_dec > 0 && D > 0, "eda_attractor_head: bad sizes");
-  attractor_head_kernel<<<1, 1024, 0, st>>>(att, w, bias, B, n_dec, D, probs, n_spk_label, loss_att);
+  const int total = B * n_dec;
+  attractor_head_kernel<<<ceil_div(total, 8), 256, 0, st>>>(att, w, bias, total, D, probs);
   EDA_LAUNCH_CHECK();
+  if (n_spk_label >= 0 && loss_att != nullptr) {
+    attractor_loss_kernel<<<1, 1024, 0, st>>>(probs, B, n_dec, n_spk_label, loss_att);
+    EDA_LAUNCH_CHECK();
+  }
   return EDA_OK;
 }
 

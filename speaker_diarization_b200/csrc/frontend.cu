@@ -212,23 +212,28 @@ __device__ __forceinline__ void fft_local(cd (&a)[R]) {      // DIF, output slot
   }
 }
 
+constexpr int kLogmelGroup = 4;      // frames whose mel projection + log10 run together
+static size_t logmel_fast_smem(int M, int mel_nnz) {
+  return (size_t)M * 16 + (size_t)((mel_nnz + 1) & ~1) * 8 + (size_t)8 * (M * 16 + kLogmelGroup * (M + 2) * 8);
+}
+
 template <int R, typename AudioT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, R == 4 ? 2 : 1)
 logmel_fast_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_sample_off,
                    const int64_t* __restrict__ rec_frame_off, int n_rec, int64_t total_frames, int hop,
                    int n_mels, const double* __restrict__ window, const double2* __restrict__ tw,
                    const double* __restrict__ melw64, const int* __restrict__ mel_off,
                    const int* __restrict__ mel_lo, int mel_nnz, float* __restrict__ logmel,
                    double* __restrict__ colsum, int frames_per_warp) {
-  constexpr int M = 32 * R, NFFT = 2 * M, RB = R == 8 ? 3 : 2;
+  constexpr int M = 32 * R, NFFT = 2 * M, RB = R == 8 ? 3 : 2, FB = kLogmelGroup;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  // layout: [tw: M double2][melw: mel_nnz double (padded to even)][per-warp: M double2 + (M+2) double]
+  // layout: [tw: M double2][melw: mel_nnz double (padded to even)][per-warp: M double2 + FB x (M+2) double]
   double2* s_tw = reinterpret_cast<double2*>(smem_raw);
   double* s_melw = reinterpret_cast<double*>(s_tw + M);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned char* wbase = smem_raw + (size_t)M * 16 + (size_t)((mel_nnz + 1) & ~1) * 8 + (size_t)warp * (M * 16 + (M + 2) * 8);
+  unsigned char* wbase = smem_raw + (size_t)M * 16 + (size_t)((mel_nnz + 1) & ~1) * 8 + (size_t)warp * (M * 16 + FB * (M + 2) * 8);
   double2* zbuf = reinterpret_cast<double2*>(wbase);
-  double* pw = reinterpret_cast<double*>(wbase + M * 16);
+  double* pwg = reinterpret_cast<double*>(wbase + M * 16);     // power spectra of the frame group
   for (int i = threadIdx.x; i < M; i += blockDim.x) s_tw[i] = tw[i];
   for (int i = threadIdx.x; i < mel_nnz; i += blockDim.x) s_melw[i] = melw64[i];
   __syncthreads();
@@ -273,78 +278,104 @@ logmel_fast_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__
   double csum = 0.0;
   int64_t r_f0 = rec_frame_off[rec], r_f1 = rec_frame_off[rec + 1];
   int64_t r_s0 = rec_sample_off[rec], r_n = rec_sample_off[rec + 1] - r_s0;
-  for (int64_t f = f_begin; f < f_end; ++f) {
+  // raw samples of one frame, packed as z[n] = x[2n] + i x[2n+1], n = lane + 32 r (center=True zero padding)
+  double nx0[R], nx1[R];
+  auto load_raw = [&](int64_t ff) {
+    const int64_t s_start = (ff - r_f0) * hop - M;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int64_t i0 = s_start + 2 * (lane + 32 * r), i1 = i0 + 1;
+      nx0[r] = (i0 >= 0 && i0 < r_n) ? audio_sample(audio, r_s0 + i0) : 0.0;
+      nx1[r] = (i1 >= 0 && i1 < r_n) ? audio_sample(audio, r_s0 + i1) : 0.0;
+    }
+  };
+  bool have_next = false;                     // (warp-uniform) nx* already hold the next frame
+  int64_t f = f_begin;
+  while (f < f_end) {
     while (f >= r_f1) {   // crossed into the next recording (empty recordings are skipped)
       if (lane < n_mels) atomicAdd(colsum + (size_t)rec * n_mels + lane, csum);
       csum = 0.0;
       ++rec;
       r_f0 = rec_frame_off[rec]; r_f1 = rec_frame_off[rec + 1];
       r_s0 = rec_sample_off[rec]; r_n = rec_sample_off[rec + 1] - r_s0;
+      have_next = false;
     }
-    // windowed frame packed as z[n] = x[2n] + i x[2n+1], n = lane + 32 r (center=True zero padding)
-    const int64_t s_start = (f - r_f0) * hop - M;
-    cd a[R];
+    // a group of up to FB frames of ONE recording: FFTs one after the other, mel + log together
+    const int64_t f_lim = min(f_end, r_f1);
+    const int nfb = (int)min((int64_t)FB, f_lim - f);
+    for (int fb = 0; fb < nfb; ++fb) {
+      const int64_t ff = f + fb;
+      double* pw = pwg + fb * (M + 2);
+      if (!have_next) load_raw(ff);
+      cd a[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const int64_t i0 = s_start + 2 * (lane + 32 * r), i1 = i0 + 1;
-      const double x0 = (i0 >= 0 && i0 < r_n) ? audio_sample(audio, r_s0 + i0) : 0.0;
-      const double x1 = (i1 >= 0 && i1 < r_n) ? audio_sample(audio, r_s0 + i1) : 0.0;
-      a[r] = {x0 * win0[r], x1 * win1[r]};
-    }
-    fft_local<R>(a);
+      for (int r = 0; r < R; ++r) a[r] = {nx0[r] * win0[r], nx1[r] * win1[r]};
+      have_next = ff + 1 < f_lim;
+      if (have_next) load_raw(ff + 1);          // in flight while this frame's FFT runs
+      fft_local<R>(a);
 #pragma unroll
-    for (int j = 1; j < R; ++j) a[j] = cmulw(a[j], ltw[j]);
-    // 32-point DIF across lanes: upper lane keeps own + partner, lower lane (partner - own) * w
+      for (int j = 1; j < R; ++j) a[j] = cmulw(a[j], ltw[j]);
+      // 32-point DIF across lanes: upper lane keeps own + partner, lower lane (partner - own) * w
 #pragma unroll
-    for (int s = 0; s < 5; ++s) {
-      const int d = 16 >> s;
+      for (int s = 0; s < 5; ++s) {
+        const int d = 16 >> s;
 #pragma unroll
-      for (int j = 0; j < R; ++j) {
-        const double px = __shfl_xor_sync(0xffffffffu, a[j].x, d), py = __shfl_xor_sync(0xffffffffu, a[j].y, d);
-        const cd t = {fma(a[j].x, sgn[s], px), fma(a[j].y, sgn[s], py)};
-        a[j] = s < 4 ? cmulw(t, stw[s]) : t;
+        for (int j = 0; j < R; ++j) {
+          const double px = __shfl_xor_sync(0xffffffffu, a[j].x, d), py = __shfl_xor_sync(0xffffffffu, a[j].y, d);
+          const cd t = {fma(a[j].x, sgn[s], px), fma(a[j].y, sgn[s], py)};
+          a[j] = s < 4 ? cmulw(t, stw[s]) : t;
+        }
       }
-    }
-    // lane holds Z[R * bitrev5(lane) + bitrev(j)] in slot j: natural order through shared memory
+      // lane holds Z[R * bitrev5(lane) + bitrev(j)] in slot j: natural order through shared memory
+      __syncwarp();                               // previous frame's untangle has finished reading zbuf
 #pragma unroll
-    for (int j = 0; j < R; ++j)
-      zbuf[R * k1 + (int)(__brev((unsigned)j) >> (32 - RB))] = make_double2(a[j].x, a[j].y);
-    __syncwarp();
-    // real-FFT untangle: bins k and M-k from Z[k], Z[M-k]:  X[k] = (E + T)/2, X[M-k] = conj(E - T)/2,
-    // E = Z[k] + conj(Z[M-k]),  T = W^k * (-i) (Z[k] - conj(Z[M-k]))
+      for (int j = 0; j < R; ++j)
+        zbuf[R * k1 + (int)(__brev((unsigned)j) >> (32 - RB))] = make_double2(a[j].x, a[j].y);
+      __syncwarp();
+      // real-FFT untangle: bins k and M-k from Z[k], Z[M-k]:  X[k] = (E + T)/2, X[M-k] = conj(E - T)/2,
+      // E = Z[k] + conj(Z[M-k]),  T = W^k * (-i) (Z[k] - conj(Z[M-k]))
 #pragma unroll
-    for (int jj = 0; jj < R / 2; ++jj) {
-      const int k = 1 + lane + 32 * jj;                // 1 .. M/2
-      const double2 zk = zbuf[k], zm = zbuf[M - k];
-      const cd E = {zk.x + zm.x, zk.y - zm.y};
-      const cd D = {zk.x - zm.x, zk.y + zm.y};
-      const double2 w = s_tw[k];
-      const cd T = cmulw(cmul_mi(D), cd{w.x, w.y});
-      const cd p = cadd(E, T), q = csub(E, T);
-      pw[k] = 0.25 * (p.x * p.x + p.y * p.y);
-      pw[M - k] = 0.25 * (q.x * q.x + q.y * q.y);      // k == M/2 writes the same value twice
-    }
-    if (lane == 0) {
-      const double2 z0 = zbuf[0];
-      pw[0] = (z0.x + z0.y) * (z0.x + z0.y);
-      pw[M] = (z0.x - z0.y) * (z0.x - z0.y);
+      for (int jj = 0; jj < R / 2; ++jj) {
+        const int k = 1 + lane + 32 * jj;                // 1 .. M/2
+        const double2 zk = zbuf[k], zm = zbuf[M - k];
+        const cd E = {zk.x + zm.x, zk.y - zm.y};
+        const cd D = {zk.x - zm.x, zk.y + zm.y};
+        const double2 w = s_tw[k];
+        const cd T = cmulw(cmul_mi(D), cd{w.x, w.y});
+        const cd pp = cadd(E, T), q = csub(E, T);
+        pw[k] = 0.25 * (pp.x * pp.x + pp.y * pp.y);
+        pw[M - k] = 0.25 * (q.x * q.x + q.y * q.y);      // k == M/2 writes the same value twice
+      }
+      if (lane == 0) {
+        const double2 z0 = zbuf[0];
+        pw[0] = (z0.x + z0.y) * (z0.x + z0.y);
+        pw[M] = (z0.x - z0.y) * (z0.x - z0.y);
+      }
     }
     __syncwarp();
     if (lane < n_mels) {
-      double acc0 = 0.0, acc1 = 0.0;
+      // sparse mel rows: one weight load feeds the FB frames' independent accumulation chains
+      double acc[FB];
+#pragma unroll
+      for (int fb = 0; fb < FB; ++fb) acc[fb] = 0.0;
       const double* wrow = s_melw + my_off;
-      const double* prow = pw + my_lo;
-      int i = 0;
-      for (; i + 1 < my_cnt; i += 2) {
-        acc0 = fma(prow[i], wrow[i], acc0);
-        acc1 = fma(prow[i + 1], wrow[i + 1], acc1);
+      const double* prow = pwg + my_lo;
+      for (int i = 0; i < my_cnt; ++i) {
+        const double w = wrow[i];
+#pragma unroll
+        for (int fb = 0; fb < FB; ++fb) acc[fb] = fma(prow[fb * (M + 2) + i], w, acc[fb]);   // rows >= nfb: stale, unused
       }
-      if (i < my_cnt) acc0 = fma(prow[i], wrow[i], acc0);
-      const double v = log10(fmax(acc0 + acc1, 1e-10));
-      logmel[(size_t)f * n_mels + lane] = (float)v;
-      csum += v;
+#pragma unroll
+      for (int fb = 0; fb < FB; ++fb) {
+        if (fb < nfb) {
+          const double v = log10(fmax(acc[fb], 1e-10));
+          logmel[(size_t)(f + fb) * n_mels + lane] = (float)v;
+          csum += v;
+        }
+      }
     }
     __syncwarp();
+    f += nfb;
   }
   if (lane < n_mels) atomicAdd(colsum + (size_t)rec * n_mels + lane, csum);
 }
@@ -450,7 +481,7 @@ int eda_frontend_plan_create(int sample_rate, int frame_size, int frame_shift, i
   EDA_CUDA(cudaFuncSetAttribute(logmel_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   if (n_fft == 256 || n_fft == 512) {
     const int M = n_fft / 2;
-    const int fsm = (int)((size_t)M * 16 + (size_t)((p->mel_nnz + 1) & ~1) * 8 + (size_t)8 * (M * 16 + (M + 2) * 8));
+    const int fsm = (int)logmel_fast_smem(M, p->mel_nnz);
     EDA_CUDA(cudaFuncSetAttribute(logmel_fast_kernel<4, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm));
     EDA_CUDA(cudaFuncSetAttribute(logmel_fast_kernel<4, double>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm));
     EDA_CUDA(cudaFuncSetAttribute(logmel_fast_kernel<4, int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm));
@@ -488,7 +519,7 @@ int eda_frontend_logmel(const eda_frontend_plan* p, const void* audio, int audio
   if (p->n_fft == 256 || p->n_fft == 512) {
     // fast path: register-resident FFT, shuffles across lanes
     const int M = p->n_fft / 2;
-    const size_t smem = (size_t)M * 16 + (size_t)((p->mel_nnz + 1) & ~1) * 8 + (size_t)8 * (M * 16 + (M + 2) * 8);
+    const size_t smem = logmel_fast_smem(M, p->mel_nnz);
 #define EDA_FAST(R, T)                                                                                      \
   logmel_fast_kernel<R, T><<<blocks, 256, smem, st>>>((const T*)audio, rec_sample_off, rec_frame_off, n_rec, \
       total_frames, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw64, p->d_mel_off, p->d_mel_lo, \

@@ -11,7 +11,7 @@ def mk(r, c):
 shapes = [("qkv", 768, 256, "qkv"), ("out_proj", 256, 256, L.EPI_BIAS_RES_LN), ("ffn1", 2048, 256, L.EPI_BIAS_RELU),
           ("ffn2", 256, 2048, L.EPI_BIAS_RES_LN), ("xproj", 1024, 256, L.EPI_BIAS), ("in_lin", 256, 352, L.EPI_BIAS_LN)]
 B, T = M // 500, 500
-PREC = {"bf16x3": PREC, "bf16": L.PREC_BF16}[os.environ.get("PREC", "bf16x3")]
+PREC = {"bf16x3": L.PREC_BF16X3, "bf16": L.PREC_BF16}[os.environ.get("PREC", "bf16x3")]
 PASSES = 3 if PREC == L.PREC_BF16X3 else 1
 for name, N, K, epi in shapes:
     a, w = mk(M, K), mk(N, K)

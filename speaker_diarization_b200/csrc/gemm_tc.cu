@@ -31,14 +31,16 @@ namespace eda {
 using namespace tc;
 typedef __nv_bfloat16 bf16;
 
-constexpr int GBM = 128, GBN = 256, GBK = 64, GSTAGES = 2;
-constexpr int G_A_TILE = GBM * GBK * 2;                  // 16 KB
-constexpr int G_B_TILE = GBN * GBK * 2;                  // 32 KB
-constexpr int G_STAGE = 2 * G_A_TILE + 2 * G_B_TILE;     // 96 KB
+constexpr int GBM = 128, GBN = 256, GBK = 64, GSTAGES = 3;
+constexpr int G_A_TILE = GBM * GBK * 2;                  // 16 KB: this CTA's 128 rows of A
+constexpr int G_B_TILE = (GBN / 2) * GBK * 2;            // 16 KB: this CTA's HALF (128 rows) of the W tile
+constexpr int G_STAGE = 2 * G_A_TILE + 2 * G_B_TILE;     // 64 KB (hi + lo of both)
 constexpr int G_EPI_WARPS = 8;
 constexpr int G_THREADS = 64 + 32 * G_EPI_WARPS;
 constexpr int G_LNX_BYTES = 2 * 2 * GBM * 4;             // LayerNorm partial sums [pass][column half][row]
-constexpr int G_SMEM = GSTAGES * G_STAGE + G_LNX_BYTES + 256 + 1024;
+constexpr int G_VEC_MAX = 4096;                          // bias entries staged in smem (zero padded to a tile multiple)
+constexpr int G_VEC_BYTES = (G_VEC_MAX + 2 * GBN) * 4;   // bias + LayerNorm gamma, beta
+constexpr int G_SMEM = GSTAGES * G_STAGE + G_LNX_BYTES + G_VEC_BYTES + 256 + 1024;
 
 enum { GEPI_QKV = 4 };
 
@@ -67,6 +69,12 @@ __device__ __forceinline__ void st_global_v8(void* p, uint32_t a0, uint32_t a1, 
                ::"l"(p), "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(a4), "r"(a5), "r"(a6), "r"(a7) : "memory");
 }
 
+// two fp32 -> packed bf16 pair (a in the low half), round to nearest even
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
 __device__ __forceinline__ void ld_global_nc_v8(const float* p, float4& a, float4& b) {
   asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
@@ -95,58 +103,76 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float (*ln_x)[2][GBM] = reinterpret_cast<float (*)[2][GBM]>(smem + GSTAGES * G_STAGE);
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + GSTAGES * G_STAGE + G_LNX_BYTES);
+  // epilogue row vectors live in shared memory: global loads issued between the epilogue's
+  // stores queue up behind them in the LSU
+  float* s_bias = reinterpret_cast<float*>(smem + GSTAGES * G_STAGE + G_LNX_BYTES);
+  float* s_gamma = s_bias + G_VEC_MAX;
+  float* s_beta = s_gamma + GBN;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + GSTAGES * G_STAGE + G_LNX_BYTES + G_VEC_BYTES);
   uint64_t* empty = full + GSTAGES;
   uint64_t* tfull = empty + GSTAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_tiles_n = (p.N + GBN - 1) / GBN, n_tiles_m = (p.M + GBM - 1) / GBM;
-  const int n_tiles = n_tiles_n * n_tiles_m;
+  const uint32_t rank = cluster_ctarank();                     // 0 = leader (issues the MMAs of the pair)
+  const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+  const int n_tiles_n = (p.N + GBN - 1) / GBN, n_tiles_m = (p.M + 2 * GBM - 1) / (2 * GBM);
+  const int n_tiles = n_tiles_n * n_tiles_m;                   // 256 x 256 output tiles, one per CTA pair
   const int nkb = (p.Kp + GBK - 1) / GBK;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA_hi); tma_prefetch_desc(&tmA_lo); tma_prefetch_desc(&tmB_hi); tma_prefetch_desc(&tmB_lo);
     for (int s = 0; s < GSTAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], G_EPI_WARPS); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 2 * G_EPI_WARPS); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  if (warp == 1) tmem_alloc_pair(tmem_slot, 512);
+  const bool vec_smem = p.N <= G_VEC_MAX;
+  if (vec_smem) {
+    const int n_pad = n_tiles_n * GBN;
+    for (int i = threadIdx.x; i < n_pad; i += G_THREADS) s_bias[i] = (p.bias && i < p.N) ? __ldg(p.bias + i) : 0.f;
+    if (EPI == EDA_EPI_BIAS_LN || EPI == EDA_EPI_BIAS_RES_LN)
+      for (int i = threadIdx.x; i < GBN; i += G_THREADS) { s_gamma[i] = __ldg(p.gamma + i); s_beta[i] = __ldg(p.beta + i); }
+  }
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();              // both CTAs' barriers and TMEM exist before any cross-CTA signal
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer (both CTAs): own 128 rows of A, own half of the W tile; every byte of
+    // the pair is counted on the LEADER's full barrier =====
     if (lane == 0) {
-      const uint32_t stage_tx = p.passes == 3 ? G_STAGE : (G_A_TILE + G_B_TILE);
+      const uint32_t pair_tx = 2 * (p.passes == 3 ? G_STAGE : (G_A_TILE + G_B_TILE));
+      const uint32_t full_leader0 = map_to_rank(&full[0], 0);     // barriers are contiguous 8-byte objects
       uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int m0 = (tile / n_tiles_n) * GBM, n0 = (tile % n_tiles_n) * GBN;
+      for (int tile = pair; tile < n_tiles; tile += n_pairs) {
+        const int m0 = (tile / n_tiles_n) * 2 * GBM + (int)rank * GBM;
+        const int n0 = (tile % n_tiles_n) * GBN + (int)rank * (GBN / 2);
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int s = it % GSTAGES;
-          mbar_wait(&empty[s], ((it / GSTAGES) & 1) ^ 1);
+          mbar_wait(&empty[s], ((it / GSTAGES) & 1) ^ 1);      // the pair's MMAs have read this stage (multicast commit)
           uint8_t* st = smem + s * G_STAGE;
-          mbar_expect_tx(&full[s], stage_tx);
-          tma_load_2d(st, &tmA_hi, &full[s], kb * GBK, m0);
-          tma_load_2d(st + 2 * G_A_TILE, &tmB_hi, &full[s], kb * GBK, n0);
+          if (rank == 0) mbar_expect_tx(&full[s], pair_tx);
+          tma_load_2d_pair(st, &tmA_hi, (full_leader0 + 8 * s), kb * GBK, m0);
+          tma_load_2d_pair(st + 2 * G_A_TILE, &tmB_hi, (full_leader0 + 8 * s), kb * GBK, n0);
           if (p.passes == 3) {
-            tma_load_2d(st + G_A_TILE, &tmA_lo, &full[s], kb * GBK, m0);
-            tma_load_2d(st + 2 * G_A_TILE + G_B_TILE, &tmB_lo, &full[s], kb * GBK, n0);
+            tma_load_2d_pair(st + G_A_TILE, &tmA_lo, (full_leader0 + 8 * s), kb * GBK, m0);
+            tma_load_2d_pair(st + 2 * G_A_TILE + G_B_TILE, &tmB_lo, (full_leader0 + 8 * s), kb * GBK, n0);
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
-      const uint32_t idesc = idesc_bf16_f32(GBM, GBN);
+    // ===== MMA issuer: one thread of the LEADER CTA, cta_group::2, 256 x 256 x 16 per instruction =====
+    if (lane == 0 && rank == 0) {
+      const uint32_t idesc = idesc_bf16_f32(2 * GBM, GBN);
       uint32_t it = 0, lt = 0;
-      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
+      for (int tile = pair; tile < n_tiles; tile += n_pairs, ++lt) {
         const uint32_t ab = lt & 1;
-        mbar_wait(&tempty[ab], ((lt >> 1) & 1) ^ 1);       // epilogue has drained this accumulator
+        mbar_wait(&tempty[ab], ((lt >> 1) & 1) ^ 1);       // both CTAs' epilogues have drained this accumulator
         tc_fence_after();
         const uint32_t acc = tmem_base + ab * GBN;
         for (int kb = 0; kb < nkb; ++kb, ++it) {
@@ -159,15 +185,15 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
 #pragma unroll
           for (int k = 0; k < GBK / 16; ++k) {
             const uint64_t adv = uint64_t(k * 32 >> 4);          // +32 B per 16-element k-step
-            umma_bf16(acc, a_hi + adv, b_hi + adv, idesc, (kb | k) != 0);
+            umma_bf16_pair(acc, a_hi + adv, b_hi + adv, idesc, (kb | k) != 0);
             if (p.passes == 3) {
-              umma_bf16(acc, a_hi + adv, b_lo + adv, idesc, 1);
-              umma_bf16(acc, a_lo + adv, b_hi + adv, idesc, 1);
+              umma_bf16_pair(acc, a_hi + adv, b_lo + adv, idesc, 1);
+              umma_bf16_pair(acc, a_lo + adv, b_hi + adv, idesc, 1);
             }
           }
-          umma_commit(&empty[s]);        // frees this smem stage once the MMAs above have read it
+          umma_commit_pair(&empty[s]);   // frees this smem stage in BOTH CTAs once the MMAs above have read it
         }
-        umma_commit(&tfull[ab]);         // accumulator complete
+        umma_commit_pair(&tfull[ab]);    // accumulator halves complete in both CTAs
       }
     }
   } else {
@@ -175,8 +201,9 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
     // the two warps of a lane quadrant split the 256 columns in halves of 128. =====
     const int q = warp & 3, ch = (warp - 2) >> 2;
     uint32_t lt = 0;
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
-      const int m0 = (tile / n_tiles_n) * GBM, n_blk = tile % n_tiles_n, n0 = n_blk * GBN;
+    const uint32_t tempty_leader0 = map_to_rank(&tempty[0], 0);
+    for (int tile = pair; tile < n_tiles; tile += n_pairs, ++lt) {
+      const int m0 = (tile / n_tiles_n) * 2 * GBM + (int)rank * GBM, n_blk = tile % n_tiles_n, n0 = n_blk * GBN;
       const uint32_t ab = lt & 1;
       const int rbase = m0 + q * 32;                              // first global row of this warp
       // residual chunk c of this thread's row (RES_LN): 8 x 16 B, thread-per-row
@@ -224,10 +251,8 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
           uint32_t h[16], l[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            __nv_bfloat162 h2, l2;
-            split2(v[2 * j], v[2 * j + 1], h2, l2);
-            h[j] = *reinterpret_cast<uint32_t*>(&h2);
-            l[j] = *reinterpret_cast<uint32_t*>(&l2);
+            h[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+            l[j] = pack_bf16x2(v[2 * j] - __uint_as_float(h[j] << 16), v[2 * j + 1] - __uint_as_float(h[j] & 0xffff0000u));
           }
           bf16* dh = out_hi + (size_t)grow * lds + gcol0;
           bf16* dl = out_lo + (size_t)grow * lds + gcol0;
@@ -248,7 +273,14 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
       };
       // v[j] += vec[col0 + j] (bias-like row vector; 16 B loads when aligned, broadcast across lanes)
       auto add_vec = [&](float (&v)[32], const float* vec, int col0) {
-        if (((uintptr_t)(vec + col0) & 15) == 0 && col0 + 32 <= p.N) {
+        if (vec_smem) {            // (only ever called with vec == p.bias)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 b = *reinterpret_cast<const float4*>(s_bias + col0 + 4 * j);
+            v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+          }
+        } else if (vec == nullptr) {
+        } else if (((uintptr_t)(vec + col0) & 15) == 0 && col0 + 32 <= p.N) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const float4 b = __ldg(reinterpret_cast<const float4*>(vec + col0) + j);
@@ -266,7 +298,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
           if (col0 >= p.N) break;
           float v[32];
           tmem_ld32(trow + c * 32, v);
-          if (p.bias) add_vec(v, p.bias, col0);
+          add_vec(v, p.bias, col0);
           if (EPI == EDA_EPI_BIAS_RELU) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
@@ -350,8 +382,8 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
           tmem_ld32(trow + c * 32, v);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float4 g4 = __ldg(reinterpret_cast<const float4*>(p.gamma + col0) + j);
-            const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.beta + col0) + j);
+            const float4 g4 = *reinterpret_cast<const float4*>(s_gamma + col0 + 4 * j);
+            const float4 b4 = *reinterpret_cast<const float4*>(s_beta + col0 + 4 * j);
             v[4 * j] = (v[4 * j] - mean) * rstd * g4.x + b4.x;
             v[4 * j + 1] = (v[4 * j + 1] - mean) * rstd * g4.y + b4.y;
             v[4 * j + 2] = (v[4 * j + 2] - mean) * rstd * g4.z + b4.z;
@@ -366,15 +398,16 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
 
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[ab]);
+        if (lane == 0) mbar_arrive_cluster(tempty_leader0 + 8 * ab);
       }
     }
   }
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();              // the leader's MMAs touched the peer's smem and TMEM: leave together
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    tmem_dealloc_pair(tmem_base, 512);
   }
 }
 
@@ -470,9 +503,18 @@ static int launch_gemm(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const C
     EDA_CUDA(cudaFuncSetAttribute(gemm_split_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
     attr = true;
   }
-  const int n_tiles = ceil_div(p.N, GBN) * ceil_div(p.M, GBM);
-  gemm_split_kernel<EPI><<<std::min(n_tiles, num_sms()), G_THREADS, G_SMEM, st>>>(a_hi, a_lo, b_hi, b_lo, p);
-  EDA_LAUNCH_CHECK();
+  const int n_tiles = ceil_div(p.N, GBN) * ceil_div(p.M, 2 * GBM);      // one 256 x 256 tile per CTA pair
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attrs[1];
+  cfg.gridDim = dim3(2 * std::min(n_tiles, num_sms() / 2));
+  cfg.blockDim = dim3(G_THREADS);
+  cfg.dynamicSmemBytes = G_SMEM;
+  cfg.stream = st;
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = 2; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
+  cfg.attrs = attrs; cfg.numAttrs = 1;
+  EDA_CUDA(cudaLaunchKernelEx(&cfg, gemm_split_kernel<EPI>, a_hi, a_lo, b_hi, b_lo, p));
+  count_launch();
   return EDA_OK;
 }
 
@@ -496,8 +538,8 @@ int gemm_split(const void* a_hi, const void* a_lo, int lda, const void* w_hi, co
   int rc;
   if ((rc = make_tmap_bf16(&ta_hi, a_hi, p.M, K, lda, GBM)) != EDA_OK) return rc;
   if ((rc = make_tmap_bf16(&ta_lo, a_lo, p.M, K, lda, GBM)) != EDA_OK) return rc;
-  if ((rc = make_tmap_bf16(&tb_hi, w_hi, p.N, K, ldw, GBN)) != EDA_OK) return rc;
-  if ((rc = make_tmap_bf16(&tb_lo, w_lo, p.N, K, ldw, GBN)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16(&tb_hi, w_hi, p.N, K, ldw, GBN / 2)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16(&tb_lo, w_lo, p.N, K, ldw, GBN / 2)) != EDA_OK) return rc;
   switch (epi) {
     case EDA_EPI_BIAS: return launch_gemm<EDA_EPI_BIAS>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
     case EDA_EPI_BIAS_RELU: return launch_gemm<EDA_EPI_BIAS_RELU>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);

@@ -31,7 +31,12 @@ namespace eda {
 using namespace tc;
 typedef __nv_bfloat16 bf16;
 
-constexpr int GBM = 128, GBN = 256, GBK = 64, GSTAGES = 3;
+constexpr int GBM = 128, GBN = 256, GBK = 64;
+// Two shared-memory plans.  "Staged" (short K: the epilogue's stores dominate): 2 operand stages and
+// 8 KB per epilogue warp from which results leave through TMA stores.  "Direct" (long K): 3
+// operand stages, results stored straight from registers.
+constexpr int G_STAGES_STAGED = 2, G_STAGES_DIRECT = 3;
+constexpr int G_STG_WARP = 2 * 4096;                     // two 32-row x 128 B buffers per epilogue warp
 constexpr int G_A_TILE = GBM * GBK * 2;                  // 16 KB: this CTA's 128 rows of A
 constexpr int G_B_TILE = (GBN / 2) * GBK * 2;            // 16 KB: this CTA's HALF (128 rows) of the W tile
 constexpr int G_STAGE = 2 * G_A_TILE + 2 * G_B_TILE;     // 64 KB (hi + lo of both)
@@ -40,7 +45,9 @@ constexpr int G_THREADS = 64 + 32 * G_EPI_WARPS;
 constexpr int G_LNX_BYTES = 2 * 2 * GBM * 4;             // LayerNorm partial sums [pass][column half][row]
 constexpr int G_VEC_MAX = 4096;                          // bias entries staged in smem (zero padded to a tile multiple)
 constexpr int G_VEC_BYTES = (G_VEC_MAX + 2 * GBN) * 4;   // bias + LayerNorm gamma, beta
-constexpr int G_SMEM = GSTAGES * G_STAGE + G_LNX_BYTES + G_VEC_BYTES + 256 + 1024;
+constexpr int G_OPERAND_BYTES = G_STAGES_DIRECT * G_STAGE;    // == 2 stages + 8 staging buffers of 8 KB
+static_assert(G_STAGES_STAGED * G_STAGE + G_EPI_WARPS * G_STG_WARP == G_OPERAND_BYTES, "smem plans differ in size");
+constexpr int G_SMEM = G_OPERAND_BYTES + G_LNX_BYTES + G_VEC_BYTES + 256 + 1024;
 
 enum { GEPI_QKV = 4 };
 
@@ -95,20 +102,22 @@ __global__ void split_bf16_kernel(const float* __restrict__ src, int ld, int row
   }
 }
 
-template <int EPI>
+template <int EPI, bool ST>
 __global__ void __launch_bounds__(G_THREADS, 1)
 gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                   const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
-                  const GemmParams p) {
+                  const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC_hi,
+                  const __grid_constant__ CUtensorMap tmC_lo, const GemmParams p) {
+  constexpr int GSTAGES = ST ? G_STAGES_STAGED : G_STAGES_DIRECT;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  float (*ln_x)[2][GBM] = reinterpret_cast<float (*)[2][GBM]>(smem + GSTAGES * G_STAGE);
+  float (*ln_x)[2][GBM] = reinterpret_cast<float (*)[2][GBM]>(smem + G_OPERAND_BYTES);
   // epilogue row vectors live in shared memory: global loads issued between the epilogue's
   // stores queue up behind them in the LSU
-  float* s_bias = reinterpret_cast<float*>(smem + GSTAGES * G_STAGE + G_LNX_BYTES);
+  float* s_bias = reinterpret_cast<float*>(smem + G_OPERAND_BYTES + G_LNX_BYTES);
   float* s_gamma = s_bias + G_VEC_MAX;
   float* s_beta = s_gamma + GBN;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + GSTAGES * G_STAGE + G_LNX_BYTES + G_VEC_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + G_OPERAND_BYTES + G_LNX_BYTES + G_VEC_BYTES);
   uint64_t* empty = full + GSTAGES;
   uint64_t* tfull = empty + GSTAGES;
   uint64_t* tempty = tfull + 2;
@@ -123,6 +132,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA_hi); tma_prefetch_desc(&tmA_lo); tma_prefetch_desc(&tmB_hi); tma_prefetch_desc(&tmB_lo);
+    if (ST) { tma_prefetch_desc(&tmC); tma_prefetch_desc(&tmC_hi); tma_prefetch_desc(&tmC_lo); }
     for (int s = 0; s < GSTAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], 2 * G_EPI_WARPS); }
     fence_barrier_init();
@@ -201,6 +211,9 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
     // the two warps of a lane quadrant split the 256 columns in halves of 128. =====
     const int q = warp & 3, ch = (warp - 2) >> 2;
     uint32_t lt = 0;
+    // staged plan: this warp's two 4 KB buffers (32 rows x 128 B, SWIZZLE_128B like the tensor maps)
+    uint8_t* const stg = smem + G_STAGES_STAGED * G_STAGE + (warp - 2) * G_STG_WARP;
+    uint32_t n_stores = 0;
     const uint32_t tempty_leader0 = map_to_rank(&tempty[0], 0);
     for (int tile = pair; tile < n_tiles; tile += n_pairs, ++lt) {
       const int m0 = (tile / n_tiles_n) * 2 * GBM + (int)rank * GBM, n_blk = tile % n_tiles_n, n0 = n_blk * GBN;
@@ -271,6 +284,54 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
           }
         }
       };
+      // Staged plan: the lane's 32 words (128 B of its row) go to shared memory with eight
+      // conflict-free STS.128 (16 B units XOR-swizzled by row), then ONE TMA store writes the
+      // 32 x 128 B block; rows >= M and columns >= N are clipped by the tensor map.  One LSU
+      // wavefront per 128 B instead of one per 32 B sector for stores issued from registers, on
+      // the data pipe the tensor core's operand reads share.
+      auto tma_store_rows = [&](const uint32_t (&w)[32], const CUtensorMap* tm, int col_elem) {
+        if (rbase >= p.M) return;                                        // warp-uniform
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // buffer used two stores ago is free
+        __syncwarp();
+        uint8_t* buf = stg + (n_stores & 1) * 4096;
+        const uint32_t row_addr = smem_u32(buf) + lane * 128;
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};"
+                       ::"r"(row_addr + ((u ^ (lane & 7)) << 4)), "r"(w[4 * u]), "r"(w[4 * u + 1]), "r"(w[4 * u + 2]), "r"(w[4 * u + 3])
+                       : "memory");
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                       ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(buf)), "r"(col_elem), "r"(rbase) : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        ++n_stores;
+      };
+      // split result: chunk `half` (0/1) of a 64-column pair is packed into words [16 half, 16 half + 16)
+      auto pack_split = [&](const float (&v)[32], int half, uint32_t (&hi)[32], uint32_t (&lo)[32]) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const uint32_t h = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+          hi[16 * half + j] = h;
+          lo[16 * half + j] = pack_bf16x2(v[2 * j] - __uint_as_float(h << 16), v[2 * j + 1] - __uint_as_float(h & 0xffff0000u));
+        }
+      };
+      // one finished 32-column chunk (half 0/1 of a 64-column pair starting at gcol0 - 32 half)
+      auto emit_chunk = [&](float (&v)[32], int gcol0, int half, uint32_t (&hi)[32], uint32_t (&lo)[32],
+                            bf16* out_hi, bf16* out_lo, int lds) {
+        if constexpr (ST) {
+          if (out_hi) pack_split(v, half, hi, lo);
+          if (p.C && EPI != GEPI_QKV) tma_store_rows(reinterpret_cast<const uint32_t(&)[32]>(v), &tmC, gcol0);
+          if (out_hi && half == 1) {
+            tma_store_rows(hi, &tmC_hi, gcol0 - 32);
+            tma_store_rows(lo, &tmC_lo, gcol0 - 32);
+          }
+        } else {
+          store_chunk(v, gcol0, out_hi, out_lo, lds);
+        }
+      };
       // v[j] += vec[col0 + j] (bias-like row vector; 16 B loads when aligned, broadcast across lanes)
       auto add_vec = [&](float (&v)[32], const float* vec, int col0) {
         if (vec_smem) {            // (only ever called with vec == p.bias)
@@ -293,40 +354,50 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
       };
 
       if constexpr (EPI == EDA_EPI_BIAS || EPI == EDA_EPI_BIAS_RELU) {
-        for (int c = 0; c < 4; ++c) {
-          const int col0 = n0 + ch * 128 + c * 32;
-          if (col0 >= p.N) break;
-          float v[32];
-          tmem_ld32(trow + c * 32, v);
-          add_vec(v, p.bias, col0);
-          if (EPI == EDA_EPI_BIAS_RELU) {
+#pragma unroll 1
+        for (int cp = 0; cp < 2; ++cp) {                       // pairs of 32-column chunks
+          if (n0 + ch * 128 + cp * 64 >= p.N) break;
+          uint32_t hi[32], lo[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          for (int half = 0; half < 2; ++half) {
+            const int col0 = n0 + ch * 128 + cp * 64 + half * 32;
+            float v[32];
+            tmem_ld32(trow + cp * 64 + half * 32, v);
+            add_vec(v, p.bias, col0);
+            if (EPI == EDA_EPI_BIAS_RELU) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+            }
+            emit_chunk(v, col0, half, hi, lo, p.Chi, p.Clo, p.lds);
           }
-          store_chunk(v, col0, p.Chi, p.Clo, p.lds);
         }
       } else if constexpr (EPI == GEPI_QKV) {
         // n_blk 0: q (pre-scaled), 1: k -> split (M, 2*GBN); 2: v -> transposed per (b, h)
         const int row = rbase + lane;
         const int b = row / p.T, t = row - b * p.T;
         const float sc = n_blk == 0 ? p.q_scale : 1.0f;
-        for (int c = 0; c < 4; ++c) {
-          const int cc = ch * 4 + c;                               // 32-column chunk within the 256-wide tile
-          float v[32];
-          tmem_ld32(trow + c * 32, v);
-          add_vec(v, p.bias, n0 + cc * 32);
+#pragma unroll 1
+        for (int cp = 0; cp < 2; ++cp) {
+          uint32_t hi[32], lo[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] *= sc;
-          if (n_blk < 2) {
-            store_chunk(v, n0 + cc * 32, p.Chi, p.Clo, p.lds);
-          } else if (row < p.M) {
-            const int h = cc >> 1, d0 = (cc & 1) * 32;
-            const size_t base = ((size_t)(b * p.H + h) * 64 + d0) * p.Tp + t;
+          for (int half = 0; half < 2; ++half) {
+            const int cc = ch * 4 + cp * 2 + half;                   // 32-column chunk within the 256-wide tile
+            float v[32];
+            tmem_ld32(trow + (cp * 2 + half) * 32, v);
+            add_vec(v, p.bias, n0 + cc * 32);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const bf16 hv = __float2bfloat16_rn(v[j]);
-              p.vt_hi[base + (size_t)j * p.Tp] = hv;
-              p.vt_lo[base + (size_t)j * p.Tp] = __float2bfloat16_rn(v[j] - __bfloat162float(hv));
+            for (int j = 0; j < 32; ++j) v[j] *= sc;
+            if (n_blk < 2) {
+              emit_chunk(v, n0 + cc * 32, half, hi, lo, p.Chi, p.Clo, p.lds);
+            } else if (row < p.M) {
+              const int h = cc >> 1, d0 = (cc & 1) * 32;
+              const size_t base = ((size_t)(b * p.H + h) * 64 + d0) * p.Tp + t;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                const bf16 hv = __float2bfloat16_rn(v[j]);
+                p.vt_hi[base + (size_t)j * p.Tp] = hv;
+                p.vt_lo[base + (size_t)j * p.Tp] = __float2bfloat16_rn(v[j] - __bfloat162float(hv));
+              }
             }
           }
         }
@@ -375,21 +446,25 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         ln_x[1][ch][xr] = sq;
         asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
         const float rstd = 1.0f / sqrtf((ln_x[1][0][xr] + ln_x[1][1][xr]) * (1.0f / GBN) + 1e-5f);
+#pragma unroll 1
+        for (int cp = 0; cp < 2; ++cp) {
+          uint32_t hi[32], lo[32];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const int col0 = ch * 128 + c * 32;
-          float v[32];
-          tmem_ld32(trow + c * 32, v);
+          for (int half = 0; half < 2; ++half) {
+            const int col0 = ch * 128 + cp * 64 + half * 32;
+            float v[32];
+            tmem_ld32(trow + cp * 64 + half * 32, v);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 g4 = *reinterpret_cast<const float4*>(s_gamma + col0 + 4 * j);
-            const float4 b4 = *reinterpret_cast<const float4*>(s_beta + col0 + 4 * j);
-            v[4 * j] = (v[4 * j] - mean) * rstd * g4.x + b4.x;
-            v[4 * j + 1] = (v[4 * j + 1] - mean) * rstd * g4.y + b4.y;
-            v[4 * j + 2] = (v[4 * j + 2] - mean) * rstd * g4.z + b4.z;
-            v[4 * j + 3] = (v[4 * j + 3] - mean) * rstd * g4.w + b4.w;
+            for (int j = 0; j < 8; ++j) {
+              const float4 g4 = *reinterpret_cast<const float4*>(s_gamma + col0 + 4 * j);
+              const float4 b4 = *reinterpret_cast<const float4*>(s_beta + col0 + 4 * j);
+              v[4 * j] = (v[4 * j] - mean) * rstd * g4.x + b4.x;
+              v[4 * j + 1] = (v[4 * j + 1] - mean) * rstd * g4.y + b4.y;
+              v[4 * j + 2] = (v[4 * j + 2] - mean) * rstd * g4.z + b4.z;
+              v[4 * j + 3] = (v[4 * j + 3] - mean) * rstd * g4.w + b4.w;
+            }
+            emit_chunk(v, col0, half, hi, lo, p.Chi, p.Clo, p.lds);
           }
-          store_chunk(v, col0, p.Chi, p.Clo, p.lds);
         }
         // (ln_x reuse is safe: a warp rewrites ln_x[k] only after the partner has passed the
         //  barrier that follows its read of ln_x[k])
@@ -401,6 +476,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         if (lane == 0) mbar_arrive_cluster(tempty_leader0 + 8 * ab);
       }
     }
+    if (ST && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // staging smem outlives its readers
   }
   tc_fence_before();
   __syncthreads();
@@ -448,8 +524,8 @@ static std::mutex g_tmap_mu;
 
 // rank-3 view: dims (d0 inner, d1, d2), byte strides s1 (of d1) and s2 (of d2); box {64, b1, 1}
 static int make_tmap_impl(CUtensorMap* m, int rank, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2,
-                          uint64_t s1_bytes, uint64_t s2_bytes, uint32_t box_rows) {
-  const TmapKey key{ptr, d0, d1, d2, s1_bytes, s2_bytes, box_rows | (uint32_t(rank) << 16)};
+                          uint64_t s1_bytes, uint64_t s2_bytes, uint32_t box_rows, bool f32 = false) {
+  const TmapKey key{ptr, d0, d1, d2, s1_bytes, s2_bytes, box_rows | (uint32_t(rank) << 16) | (uint32_t(f32) << 20)};
   {
     std::lock_guard<std::mutex> g(g_tmap_mu);
     auto it = g_tmaps.find(key);
@@ -459,9 +535,9 @@ static int make_tmap_impl(CUtensorMap* m, int rank, const void* ptr, uint64_t d0
   if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return EDA_ECUDA; }
   cuuint64_t gdim[3] = {d0, d1, d2};
   cuuint64_t gstr[2] = {s1_bytes, s2_bytes};
-  cuuint32_t box[3] = {64, box_rows, 1};
+  cuuint32_t box[3] = {f32 ? 32u : 64u, box_rows, 1};          // 128 B inner extent either way
   cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), gdim, gstr, box, estr,
+  CUresult r = enc(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), gdim, gstr, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -482,6 +558,10 @@ int make_tmap_bf16_3d(CUtensorMap* m, const void* ptr, uint64_t d0, uint64_t d1,
 }
 
 // 2-D bf16 row-major (rows x cols, row stride ld elements) with a {64, box_rows} box
+// fp32 (rows x cols, row stride ld elements), box 32 columns x box_rows
+static int make_tmap_f32(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  return make_tmap_impl(m, 2, ptr, cols, rows, 1, ld * 4, 0, box_rows, true);
+}
 int make_tmap_bf16(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
   return make_tmap_impl(m, 2, ptr, cols, rows, 1, ld * 2, 0, box_rows);
 }
@@ -495,12 +575,13 @@ int split_bf16(const float* src, int ld, int rows, int K, void* hi, void* lo, in
   return EDA_OK;
 }
 
-template <int EPI>
-static int launch_gemm(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi, const CUtensorMap& b_lo,
-                       const GemmParams& p, cudaStream_t st) {
+template <int EPI, bool ST>
+static int launch_gemm2(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi, const CUtensorMap& b_lo,
+                        const CUtensorMap& c, const CUtensorMap& c_hi, const CUtensorMap& c_lo, const GemmParams& p,
+                        cudaStream_t st) {
   static bool attr = false;
   if (!attr) {
-    EDA_CUDA(cudaFuncSetAttribute(gemm_split_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
+    EDA_CUDA(cudaFuncSetAttribute(gemm_split_kernel<EPI, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
     attr = true;
   }
   const int n_tiles = ceil_div(p.N, GBN) * ceil_div(p.M, 2 * GBM);      // one 256 x 256 tile per CTA pair
@@ -513,9 +594,29 @@ static int launch_gemm(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const C
   attrs[0].id = cudaLaunchAttributeClusterDimension;
   attrs[0].val.clusterDim.x = 2; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
   cfg.attrs = attrs; cfg.numAttrs = 1;
-  EDA_CUDA(cudaLaunchKernelEx(&cfg, gemm_split_kernel<EPI>, a_hi, a_lo, b_hi, b_lo, p));
+  EDA_CUDA(cudaLaunchKernelEx(&cfg, gemm_split_kernel<EPI, ST>, a_hi, a_lo, b_hi, b_lo, c, c_hi, c_lo, p));
   count_launch();
   return EDA_OK;
+}
+
+// Short K (the stores dominate) -> staged plan with TMA stores, if the outputs can be described by
+// tensor maps (16 B aligned bases and row pitches); `n_split_cols` = logical width of the split output.
+template <int EPI>
+static int launch_gemm(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi, const CUtensorMap& b_lo,
+                       const GemmParams& p, int n_split_cols, cudaStream_t st) {
+  const bool c_out = p.C && EPI != GEPI_QKV;
+  bool staged = p.Kp <= 8 * GBK;
+  if (c_out && (((uintptr_t)p.C & 15) || (p.ldc & 3))) staged = false;
+  if (p.Chi && ((((uintptr_t)p.Chi | (uintptr_t)p.Clo) & 15) || (p.lds & 7))) staged = false;
+  if (!staged) return launch_gemm2<EPI, false>(a_hi, a_lo, b_hi, b_lo, a_hi, a_hi, a_hi, p, st);
+  CUtensorMap c = a_hi, c_hi = a_hi, c_lo = a_hi;        // placeholders for absent outputs (never dereferenced)
+  int rc;
+  if (c_out && (rc = make_tmap_f32(&c, p.C, p.M, p.N, p.ldc, 32)) != EDA_OK) return rc;
+  if (p.Chi) {
+    if ((rc = make_tmap_bf16(&c_hi, p.Chi, p.M, n_split_cols, p.lds, 32)) != EDA_OK) return rc;
+    if ((rc = make_tmap_bf16(&c_lo, p.Clo, p.M, n_split_cols, p.lds, 32)) != EDA_OK) return rc;
+  }
+  return launch_gemm2<EPI, true>(a_hi, a_lo, b_hi, b_lo, c, c_hi, c_lo, p, st);
 }
 
 // A: split (M x K, row stride lda elements), W: split (N x K, row stride ldw).
@@ -541,11 +642,11 @@ int gemm_split(const void* a_hi, const void* a_lo, int lda, const void* w_hi, co
   if ((rc = make_tmap_bf16(&tb_hi, w_hi, p.N, K, ldw, GBN / 2)) != EDA_OK) return rc;
   if ((rc = make_tmap_bf16(&tb_lo, w_lo, p.N, K, ldw, GBN / 2)) != EDA_OK) return rc;
   switch (epi) {
-    case EDA_EPI_BIAS: return launch_gemm<EDA_EPI_BIAS>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
-    case EDA_EPI_BIAS_RELU: return launch_gemm<EDA_EPI_BIAS_RELU>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
-    case EDA_EPI_BIAS_LN: return launch_gemm<EDA_EPI_BIAS_LN>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
-    case EDA_EPI_BIAS_RES_LN: return launch_gemm<EDA_EPI_BIAS_RES_LN>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
-    case GEPI_QKV: return launch_gemm<GEPI_QKV>(ta_hi, ta_lo, tb_hi, tb_lo, p, st);
+    case EDA_EPI_BIAS: return launch_gemm<EDA_EPI_BIAS>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
+    case EDA_EPI_BIAS_RELU: return launch_gemm<EDA_EPI_BIAS_RELU>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
+    case EDA_EPI_BIAS_LN: return launch_gemm<EDA_EPI_BIAS_LN>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
+    case EDA_EPI_BIAS_RES_LN: return launch_gemm<EDA_EPI_BIAS_RES_LN>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
+    case GEPI_QKV: return launch_gemm<GEPI_QKV>(ta_hi, ta_lo, tb_hi, tb_lo, p, 2 * GBN, st);
   }
   set_error("eda_gemm_split: unknown epilogue %d", epi);
   return EDA_EINVAL;

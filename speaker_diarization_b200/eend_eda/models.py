@@ -59,6 +59,7 @@ class TransformerEdaModel(nn.Module):
         self.set_precision(precision or os.environ.get("EDA_B200_PRECISION", "fp32"))
         self._prep = None
         self._ws = {}
+        self.workspace_slot = 0     # callers with several batches in flight on different streams use one slot each
         self._perm_ring = {}
         self._emb_split = None
 
@@ -108,10 +109,10 @@ class TransformerEdaModel(nn.Module):
     def _workspace(self, B: int, Tmax: int, dev):
         """Persistent per-shape buffers of the tensor-core pipeline (stable pointers keep the
         TMA descriptor cache of libeda_b200 warm)."""
-        key = (B, Tmax, str(dev))
+        key = (B, Tmax, str(dev), self.workspace_slot)
         ws = self._ws.get(key)
         if ws is None:
-            if len(self._ws) >= 4:
+            if len(self._ws) >= 8:
                 self._ws.clear()
             M, D, H = B * Tmax, self.n_units, self.n_heads
             Tp = _round_up(Tmax, 8)

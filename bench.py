@@ -148,7 +148,7 @@ def run_ours(args):
     model.load_state_dict(synth_state_dict(EdaConfig(n_layers=LAYERS), 777))
     model = model.to(dev).eval()
     fe = feature.FrontEnd(RATE, FRAME, SHIFT, CTX, SUB, device=dev)
-    pipe = InferencePipeline(model, fe, max_n_speakers=MAXSPK, attractor_threshold=0.5, activity_threshold=0.5, depth=2,
+    pipe = InferencePipeline(model, fe, max_n_speakers=MAXSPK, attractor_threshold=0.5, activity_threshold=0.5, depth=args.depth,
                              compute_streams=args.compute_streams)
     # host audio = 16-bit PCM, the sample format of the wav files the reference reads (kaldi_data.py:59-83)
     host_audio = [pcm16(synth_audio_batch(B, 2 * rank + i)).pin_memory() for i in range(2)]    # 2 x 51 MB
@@ -266,7 +266,7 @@ def run_ours(args):
                        "global_batch": world * B, "frames_per_step": world * B * T, "precision": precision,
                        "parallelism": f"dp{world} (recordings sharded, one NCCL gather of posteriors)",
                        "l2": "two alternating 51 MB int16 audio batches + 524 MB of FFN intermediates per step exceed the 126 MB L2",
-                       "pipeline": f"InferencePipeline depth 2: H2D / {args.compute_streams} alternating compute / D2H streams "
+                       "pipeline": f"InferencePipeline depth {args.depth}: H2D / {args.compute_streams} alternating compute / D2H streams "
                                    "(the next batch's front end fills the SMs the LSTM recurrence leaves idle), "
                                    "host never waits on the batch just submitted"},
             "e2e": {"value": round(world * B * T / e2e_s.item(), 1), "unit": UNIT, "h2d_bytes_per_step": h2d,
@@ -309,7 +309,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16x3", choices=["fp32", "bf16x3", "bf16"])
-    ap.add_argument("--compute-streams", type=int, default=2, help="compute streams the pipeline alternates batches over")
+    ap.add_argument("--depth", type=int, default=3, help="batches in flight in the pipeline")
+    ap.add_argument("--compute-streams", type=int, default=3, help="compute streams the pipeline alternates batches over")
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     out = run_reference(args) if args.impl == "reference" else run_ours(args)

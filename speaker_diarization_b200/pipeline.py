@@ -34,7 +34,7 @@ from . import _lib as L
 
 class InferencePipeline:
     def __init__(self, model, frontend, max_n_speakers: int = 15, attractor_threshold: float = 0.5,
-                 activity_threshold: float = 0.5, depth: int = 2, ld: int = 352, compute_streams: int = 2):
+                 activity_threshold: float = 0.5, depth: int = 3, ld: int = 352, compute_streams: int = 3):
         self.model, self.fe = model, frontend
         self.max_n_speakers, self.attractor_threshold = max_n_speakers, attractor_threshold
         self.activity_threshold, self.depth, self.ld = activity_threshold, max(1, depth), ld

@@ -31,6 +31,10 @@ T = SECONDS * RATE // SHIFT // SUB            # 500 model frames per recording
 METRIC, UNIT = "eend_eda_diarized_frames_per_sec", "frames/s"
 
 
+# DRAM traffic of the dominant kernel from the committed ncu capture (bytes per launch, bf16x3, configs[1])
+NCU_GEMM_DRAM_BYTES_PER_LAUNCH = 170.2e6
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -228,7 +232,10 @@ def run_ours(args):
         achieved = lin_fl / (lin_ms * 1e-3) / 1e12            # ALGORITHMIC flops (2*M*N*K) per second
         roof = dict(bound="tensor", kernel="gemm_split_kernel (eda_linear / eda_gemm_split / eda_gemm_qkv)",
                     achieved=round(achieved, 2), peak=pk["tf_sust"],
-                    unit="TFLOP/s", frac=round(achieved / pk["tf_sust"], 4), traffic=None,
+                    unit="TFLOP/s", frac=round(achieved / pk["tf_sust"], 4),
+                    traffic=NCU_GEMM_DRAM_BYTES_PER_LAUNCH if precision == "bf16x3" else None,
+                    traffic_source="dram__bytes_read.sum + dram__bytes_write.sum averaged over the step's 18 gemm_split_kernel "
+                                   "launches, ncu --set full (profiles/r01_ncu_step_v2.md)",
                     peak_source=pk["src"] + " (bf16 sustained)", issued_mma_factor=issued,
                     issued_tflops=round(issued * achieved, 2), tensor_pipe_frac_issued=round(issued * achieved / pk["tf_sust"], 4),
                     launches_per_step=len(gemm), avg_launch_ms=round(lin_ms / len(gemm), 4),

@@ -200,6 +200,18 @@ int eda_pit_loss_bwd(const float* pred, const float* label_perm, const int32_t* 
 int eda_der_counters(const float* pred, const float* label_perm, const int32_t* lens,
                      int B, int T, int S, int64_t* counts, void* stream);
 
+/* Post-processing to speaker segments (bin/make_rttm.py:29-35): a = T_hat > threshold (:29),
+ * scipy.signal.medfilt(a, (median, 1)) when median > 1 (:30-31; zero padded at the
+ * recording's ends, median odd), then per speaker the pairs of change points of the
+ * zero-padded column (:32-35).  Recordings are rows [rec_off[r], rec_off[r+1]) of ONE
+ * matrix with row stride ld: pass posteriors (post, fp32) or ready 0/1 decisions (labels,
+ * uint8), the other NULL.  n_spk_rec (optional, per recording): columns >= it yield nothing.
+ * segments (n_rec, n_spk, cap, 2) int32 = [start, end) frames in time order; counts
+ * (n_rec, n_spk) int32 = number of segments found (a value > cap means the tail was cut). */
+int eda_rttm_segments(const float* post, const uint8_t* labels, int ld, const int64_t* rec_off,
+                      int n_rec, const int32_t* n_spk_rec, int n_spk, float threshold, int median,
+                      int cap, int32_t* segments, int32_t* counts, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -115,6 +115,24 @@ def der_counters(pred: Tensor, label_perm: Tensor, lens: Tensor) -> Tensor:
     return counts
 
 
+def rttm_segments(src: Tensor, rec_off: Tensor, n_spk: int, threshold: float = 0.5, median: int = 1,
+                  cap: Optional[int] = None, n_spk_rec: Optional[Tensor] = None):
+    """bin/make_rttm.py:29-35 on the device.  ``src``: (rows, ld >= n_spk) fp32 posteriors or uint8
+    0/1 decisions, recordings stacked row-wise, ``rec_off`` int64 (n_rec + 1) row offsets.
+    Returns (segments (n_rec, n_spk, cap, 2) int32, counts (n_rec, n_spk) int32)."""
+    assert src.dim() == 2 and src.stride(1) == 1 and src.dtype in (torch.float32, torch.uint8)
+    n_rec = rec_off.numel() - 1
+    if cap is None:
+        cap = src.shape[0] // 2 + 1          # worst case: alternating frames
+    seg = torch.empty((n_rec, n_spk, cap, 2), dtype=torch.int32, device=src.device)
+    counts = torch.empty((n_rec, n_spk), dtype=torch.int32, device=src.device)
+    is_post = src.dtype == torch.float32
+    L.call("eda_rttm_segments", L.ptr(src) if is_post else None, None if is_post else L.ptr(src), src.stride(0),
+           L.ptr(rec_off), n_rec, L.ptr(n_spk_rec) if n_spk_rec is not None else None, n_spk, float(threshold),
+           int(median), int(cap), L.ptr(seg), L.ptr(counts), L.stream())
+    return seg, counts
+
+
 # ------------------------------------------------------- split-bf16 tensor-core pipeline ----
 class Split:
     """A matrix held as a split-bf16 pair (x = hi + lo): two (rows, ld) bf16 CUDA tensors."""

@@ -172,3 +172,40 @@ def test_pit_edge_cases(dev):
         assert idx.cpu().tolist() == idx_o.tolist(), (B, T, S)
         assert torch.equal(lab.cpu(), lab_o)
         assert abs(loss.item() - loss_o.item()) < 1e-5
+
+
+@pytest.mark.parametrize("lens,n_spk,median", [([7], 2, 1), ([1, 500, 33], 3, 1), ([500, 17, 2000], 4, 11),
+                                               ([64, 64], 1, 3), ([4097], 2, 5), ([3, 1, 2], 2, 7)])
+def test_rttm_segments_match_make_rttm(dev, lens, n_spk, median):
+    """eda_rttm_segments vs oracle/rttm_oracle.py (bin/make_rttm.py:29-35), bit-exact segment lists."""
+    import io
+    import numpy as np
+    from oracle import rttm_oracle as R
+    from speaker_diarization_b200 import rttm
+    g = torch.Generator().manual_seed(sum(lens) + n_spk + median)
+    recs = []
+    for n in lens:                      # smooth random posteriors so that segments have realistic lengths
+        x = torch.randn((n + 16, n_spk), generator=g).cumsum(0)
+        x = (x[16:] - x[:-16]) / 4.0
+        recs.append(torch.sigmoid(x).contiguous())
+    recs[0][0, 0] = 0.5                 # exactly at the threshold: strict '>'
+    want = [R.segments(r.numpy(), 0.5, median) for r in recs]
+    got = rttm.segments([r.to(dev) for r in recs], 0.5, median)
+    assert got == want
+    # uint8 decisions as input (the fused output of eda_posterior) give the same segments
+    got8 = rttm.segments([(r > 0.5).to(torch.uint8).to(dev) for r in recs], 0.5, median)
+    assert got8 == want
+    # RTTM text through the public helper
+    names = [f"rec{len(lens) - i}" for i in range(len(lens))]
+    wf = io.StringIO()
+    rttm.make_rttm(wf, names, [r.to(dev) for r in recs], 0.5, 80, 10, median, 8000)
+    assert wf.getvalue() == R.rttm_text(names, [r.numpy() for r in recs], 0.5, 80, 10, median, 8000)
+
+
+def test_rttm_ragged_speaker_counts(dev):
+    from oracle import rttm_oracle as R
+    from speaker_diarization_b200 import rttm
+    g = torch.Generator().manual_seed(5)
+    recs = [torch.rand((50, 3), generator=g), torch.rand((20, 1), generator=g), torch.rand((31, 2), generator=g)]
+    got = rttm.segments([r.to(dev) for r in recs], 0.6, 3)
+    assert got == [R.segments(r.numpy(), 0.6, 3) for r in recs]

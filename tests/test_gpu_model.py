@@ -225,3 +225,62 @@ def test_pipeline_matches_infer():
         assert torch.equal(g["posteriors"], wp) and torch.equal(g["labels"], wl)
         assert [min(x, 14) for x in g["n"]] == wn
         assert g["lengths"] == [wp.shape[1]] * 3
+
+
+def _full_size_model(n_layers, precision):
+    from oracle.weights import EdaConfig, synth_state_dict
+    from speaker_diarization_b200.eend_eda.models import TransformerEdaModel
+    cfg = EdaConfig(n_layers=n_layers)
+    m = TransformerEdaModel(2, cfg.in_size, cfg.n_heads, cfg.n_units, cfg.n_layers, precision=precision)
+    m.load_state_dict(synth_state_dict(cfg, 777))
+    return m.cuda().eval(), cfg
+
+
+def test_full_size_c2_batch_invariance():
+    """configs[1] at full size (64 x 500 frames, 4 layers) is too slow for the CPU oracle, so parity
+    rests on a size-independent property: a sequence's posteriors do not depend on what else is in
+    the batch.  The full batch must agree with single-sequence runs (same frame shuffle) to well
+    inside the parity bar, and the two precisions must agree with each other within it."""
+    from oracle.weights import synth_features
+    m, cfg = _full_size_model(4, "bf16x3")
+    lens = [500] * 64
+    src = [s.cuda() for s in synth_features(lens, cfg.in_size, 11)]
+    g = torch.Generator().manual_seed(3)
+    perms = [torch.randperm(n, generator=g) for n in lens]
+    m.infer(src, attractor_threshold=0.5, activity_threshold=0.5, perms=perms)
+    post, labels = m.last["posteriors"].clone(), m.last["labels"].clone()
+    for b in (0, 17, 63):
+        m.infer([src[b]], attractor_threshold=0.5, activity_threshold=0.5, perms=[perms[b]])
+        assert (m.last["posteriors"][0] - post[b]).abs().max().item() < 2e-5
+    m32, _ = _full_size_model(4, "fp32")
+    m32.infer(src, attractor_threshold=0.5, activity_threshold=0.5, perms=perms)
+    d = (m32.last["posteriors"] - post).abs()
+    assert d.max().item() < 1e-3
+    # thresholded labels may only differ where the posterior sits within the tolerance of 0.5
+    flip = m32.last["labels"] != labels
+    assert bool(((m32.last["posteriors"] - 0.5).abs()[flip] < 1e-3).all())
+
+
+def test_full_size_c4_long_form_chunks():
+    """configs[3]: a 30-minute recording = 9 chunks of 2000 frames, speaker count decided by the
+    attractor threshold.  Chunks in one batch == chunks one at a time (the reference's loop,
+    infer_eda.py:102-113), and ragged tails do not disturb the full chunks."""
+    from oracle.weights import synth_features
+    m, cfg = _full_size_model(4, "bf16x3")
+    lens = [2000] * 8 + [800]
+    src = [s.cuda() for s in synth_features(lens, cfg.in_size, 23)]
+    g = torch.Generator().manual_seed(9)
+    perms = [torch.randperm(n, generator=g) for n in lens]
+    ys = m.infer(src, attractor_threshold=0.5, perms=perms)
+    post = m.last["posteriors"].clone()
+    probs = m.last["probs"].clone()
+    for b in (0, 7):                 # full chunks: independent of the rest of the batch
+        y1 = m.infer([src[b]], attractor_threshold=0.5, perms=[perms[b]])
+        assert (m.last["posteriors"][0] - post[b]).abs().max().item() < 2e-5
+        assert (m.last["probs"][0] - probs[b]).abs().max().item() < 2e-5
+        assert y1[0].shape[1] == ys[b].shape[1]
+    # the 800-frame tail attends to its own -1 padding (no key-padding mask in the reference,
+    # models.py:223), so it depends on Tmax only: same result next to ONE full chunk
+    y2 = m.infer([src[3], src[8]], attractor_threshold=0.5, perms=[perms[3], perms[8]])
+    assert (m.last["posteriors"][1] - post[8]).abs().max().item() < 2e-5
+    assert y2[1].shape[1] == ys[8].shape[1]

@@ -200,6 +200,22 @@ int eda_pit_loss_bwd(const float* pred, const float* label_perm, const int32_t* 
 int eda_der_counters(const float* pred, const float* label_perm, const int32_t* lens,
                      int B, int T, int S, int64_t* counts, void* stream);
 
+/* Frame-level speaker labels from segment lists: the loop of feature.get_frame_labels
+ * (feature.py:228-245; identical at :310-330 in get_labeledSTFT) for a batch of chunks, with
+ * the row subsampling of feature.subsample (:122-127) folded in.  Segment s (seconds
+ * seg_st/seg_et, speaker column seg_spk, chunk seg_chunk) marks frames
+ * rint(st*rate/shift) .. rint(et*rate/shift) of chunk [chunk_start, chunk_end) using the
+ * reference's clipping rule (a segment covering the whole chunk is dropped, like there).
+ * chunk_frames = rows of the chunk's label matrix before subsampling; its kept rows
+ * (frames 0, sub, 2 sub, ...) start at row chunk_row_off[c] of out (total_rows x ld, int32
+ * or fp32 by out_f32; zeroed by the call).                                                */
+int eda_frame_labels(const double* seg_st, const double* seg_et, const int32_t* seg_spk,
+                     const int32_t* seg_chunk, int64_t n_seg, const int64_t* chunk_start,
+                     const int64_t* chunk_end, const int64_t* chunk_frames,
+                     const int64_t* chunk_row_off, int n_chunks, int64_t total_rows, int n_spk,
+                     double rate, int frame_shift, int subsampling, void* out, int ld, int out_f32,
+                     void* stream);
+
 /* Post-processing to speaker segments (bin/make_rttm.py:29-35): a = T_hat > threshold (:29),
  * scipy.signal.medfilt(a, (median, 1)) when median > 1 (:30-31; zero padded at the
  * recording's ends, median odd), then per speaker the pairs of change points of the

@@ -209,3 +209,41 @@ def test_rttm_ragged_speaker_counts(dev):
     recs = [torch.rand((50, 3), generator=g), torch.rand((20, 1), generator=g), torch.rand((31, 2), generator=g)]
     got = rttm.segments([r.to(dev) for r in recs], 0.6, 3)
     assert got == [R.segments(r.numpy(), 0.6, 3) for r in recs]
+
+
+@pytest.mark.parametrize("subsampling,dtype", [(1, torch.int32), (10, torch.float32), (7, torch.int32)])
+def test_frame_labels_match_reference_golden(dev, subsampling, dtype):
+    """eda_frame_labels vs outputs of the unmodified feature.get_frame_labels (tests/golden/labels.npz),
+    all chunks of all cases in ONE launch; subsampled rows = T[::subsampling] (feature.py:126)."""
+    import json, os
+    import numpy as np
+    from speaker_diarization_b200 import labels as LB
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "labels.npz"))
+    meta = json.loads(str(G["meta"]))
+    for name, m in meta.items():
+        if not isinstance(m, dict):
+            continue
+        segs = list(zip(G[f"{name}/st"].tolist(), G[f"{name}/et"].tolist(), G[f"{name}/spk"].tolist()))
+        want = [G[f"{name}/T{i}"] for i in range(len(m["ranges"]))]
+        starts = [r[0] for r in m["ranges"]]
+        ends = [w.shape[0] if r[1] is None else r[1] for r, w in zip(m["ranges"], want)]
+        out, rows = LB.frame_labels([segs] * len(want), starts, ends, [w.shape[0] for w in want], m["n_speakers"],
+                                    m["rate"], m["frame_shift"], subsampling, dtype, dev)
+        assert out.dtype == dtype
+        row = 0
+        for w, r in zip(want, rows):
+            assert r == w[::subsampling].shape[0]
+            assert np.array_equal(out[row:row + r].cpu().numpy().astype(np.int32), w[::subsampling]), name
+            row += r
+
+
+def test_frame_labels_edge_cases(dev):
+    from oracle import label_oracle as LO
+    from speaker_diarization_b200 import labels as LB
+    import numpy as np
+    # no segments at all; a chunk with zero frames; half-way rounding (0.005 s * 8000 / 80 = 0.5 -> 0, 1.5 -> 2)
+    out, rows = LB.frame_labels([[], [(0.005, 0.015, 1)], [(0.0, 9.0, 0)]], [0, 0, 100], [50, 50, 100], [50, 50, 0], 2,
+                                8000, 80, 1, torch.int32, dev)
+    assert rows == [50, 50, 0] and out.shape == (100, 2)
+    want = np.concatenate([LO.frame_labels([], 0, 50, 50, 2, 8000, 80), LO.frame_labels([(0.005, 0.015, 1)], 0, 50, 50, 2, 8000, 80)])
+    assert np.array_equal(out.cpu().numpy(), want) and want[50:53, 1].tolist() == [1, 1, 0]

@@ -59,6 +59,8 @@ class TransformerEdaModel(nn.Module):
         self.set_precision(precision or os.environ.get("EDA_B200_PRECISION", "fp32"))
         self._prep = None
         self._ws = {}
+        self._plist = None
+        self._arange = None
         self.workspace_slot = 0     # callers with several batches in flight on different streams use one slot each
         self._perm_ring = {}
         self._emb_split = None
@@ -78,7 +80,9 @@ class TransformerEdaModel(nn.Module):
 
     # ---------------------------------------------------------------- parameters --------
     def _prepared(self):
-        key = tuple((p.data_ptr(), p._version) for p in self.parameters())
+        if self._plist is None:                 # the Parameter objects are fixed after construction
+            self._plist = list(self.parameters())
+        key = tuple((p.data_ptr(), p._version) for p in self._plist)
         if self._prep is None or self._prep[0] != key:
             kpad = _round_up(self.in_size, 16)
             w = self.encoder.weight.detach()
@@ -221,9 +225,14 @@ class TransformerEdaModel(nn.Module):
             if len(ring) < 8:
                 ring.append(slot)
         perm = slot[0]
-        perm[:] = torch.arange(Tmax, dtype=torch.int32)
+        if self._arange is None or self._arange.numel() < Tmax:
+            self._arange = torch.arange(max(Tmax, 4096), dtype=torch.int32)
+        perm[:] = self._arange[:Tmax]
         for i, n in enumerate(ilens):
-            perm[i, :n] = (torch.randperm(n) if perms is None else perms[i]).to(torch.int32)
+            if perms is None:        # int32 output draws the same numbers from the generator as the int64 default
+                torch.randperm(n, out=perm[i, :n])
+            else:
+                perm[i, :n] = perms[i].to(torch.int32)
         out = perm.to(dev, non_blocking=True)
         slot[1].record(torch.cuda.current_stream(dev))
         return out

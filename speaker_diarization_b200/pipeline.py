@@ -77,7 +77,7 @@ class InferencePipeline:
                 s_compute.wait_stream(self.s_in)
         else:
             dev_audio = audio                     # list of recordings: FrontEnd stages them itself
-        with torch.cuda.stream(s_compute):
+        with torch.cuda.stream(s_compute), L.use_stream(s_compute):
             feats, rows = self.fe.features_flat(dev_audio, ld=self.ld, counts=counts)
             post, probs, labels = self.model.infer_device(feats, rows, self.max_n_speakers, self.activity_threshold)
             if self.gather is not None:
@@ -107,11 +107,9 @@ class InferencePipeline:
         """Block until the OLDEST submitted batch is on the host and return it."""
         slot, done, rows = self._pending.popleft()
         done.synchronize()
-        probs = slot["h_probs"].numpy()
-        n_spk = []
-        for b in range(probs.shape[0]):           # models.py:340-343
-            silence = np.where(probs[b] < self.attractor_threshold)[0]
-            n_spk.append(int(silence[0]) if silence.size else self.max_n_speakers - 1)
+        below = slot["h_probs"].numpy() < self.attractor_threshold          # models.py:340-343, all rows at once
+        first = below.argmax(axis=1)
+        n_spk = [int(f) if hit else self.max_n_speakers - 1 for f, hit in zip(first, below.any(axis=1))]
         return dict(posteriors=slot["h_post"], probs=slot["h_probs"], labels=slot["h_labels"],
                     n_speakers=n_spk, lengths=rows)
 

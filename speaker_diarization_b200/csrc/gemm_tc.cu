@@ -154,7 +154,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
   if (warp == 0) {
     // ===== TMA producer (both CTAs): own 128 rows of A, own half of the W tile; every byte of
     // the pair is counted on the LEADER's full barrier =====
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t pair_tx = 2 * (p.passes == 3 ? G_STAGE : (G_A_TILE + G_B_TILE));
       const uint32_t full_leader0 = map_to_rank(&full[0], 0);     // barriers are contiguous 8-byte objects
       uint32_t it = 0;
@@ -177,7 +177,9 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
     }
   } else if (warp == 1) {
     // ===== MMA issuer: one thread of the LEADER CTA, cta_group::2, 256 x 256 x 16 per instruction =====
-    if (lane == 0 && rank == 0) {
+    // (elect.sync, not lane == 0: ptxas then issues the uniform-datapath MMAs back to back
+    // instead of wrapping each one in an active-lane loop)
+    if (rank == 0 && elect_one()) {
       const uint32_t idesc = idesc_bf16_f32(2 * GBM, GBN);
       uint32_t it = 0, lt = 0;
       for (int tile = pair; tile < n_tiles; tile += n_pairs, ++lt) {
@@ -291,7 +293,8 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
       // the data pipe the tensor core's operand reads share.
       auto tma_store_rows = [&](const uint32_t (&w)[32], const CUtensorMap* tm, int col_elem) {
         if (rbase >= p.M) return;                                        // warp-uniform
-        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // buffer used two stores ago is free
+        // (elect.sync picks the same lane every time for a full mask, so the bulk groups stay with one thread)
+        if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // buffer used two stores ago is free
         __syncwarp();
         uint8_t* buf = stg + (n_stores & 1) * 4096;
         const uint32_t row_addr = smem_u32(buf) + lane * 128;
@@ -302,7 +305,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
                        : "memory");
         fence_proxy_async();
         __syncwarp();
-        if (lane == 0) {
+        if (elect_one()) {
           asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                        ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(buf)), "r"(col_elem), "r"(rbase) : "memory");
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -476,7 +479,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         if (lane == 0) mbar_arrive_cluster(tempty_leader0 + 8 * ab);
       }
     }
-    if (ST && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // staging smem outlives its readers
+    if (ST && elect_one()) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // staging smem outlives its readers
   }
   tc_fence_before();
   __syncthreads();

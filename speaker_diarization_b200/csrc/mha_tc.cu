@@ -2,16 +2,16 @@
 //
 // softmax(q k^T / sqrt(64)) v per (batch, head), NO mask: the reference attends to the
 // -1-padded frames too (models.py:223).  Flash-style: one CTA owns 128 queries of one (b, h)
-// and streams 128-key tiles.
+// and streams 64-key tiles.
 //
 // Operands are split-bf16 pairs written by the QKV GEMM epilogue: q (pre-scaled by 1/8) and k
 // as K-major rows of a (B*T, 512) matrix, v TRANSPOSED per (b, h) as (64, Tp) so that keys are
 // the contraction-major dimension of the second product.  Every product is three MMAs
 // (hi.hi + hi.lo + lo.hi), fp32 accumulation in TMEM.
 //
-//   warp 0     TMA producer: Q once, then K_j / V_j tiles (single stage each; two CTAs share an
-//              SM, so one CTA's softmax overlaps the other's MMAs)
-//   warp 1     MMA issuer (one thread) + TMEM owner (256 columns: S/P 0..127, O 128..191)
+//   warp 0     TMA producer: Q once, then K_j / V_j tiles (single stage each; three CTAs share an
+//              SM, so one CTA's softmax overlaps the others' MMAs)
+//   warp 1     MMA issuer (one thread) + TMEM owner (128 columns: S/P 0..63, O 64..127)
 //   warps 2-5  softmax: thread = query row.  S -> running max / sum, P = exp(S - m) (MUFU ex2)
 //              split into bf16 hi/lo and written BACK INTO TMEM in place over the 32-column S
 //              chunk it was computed from (16 columns of packed hi pairs, 16 of lo pairs; the
@@ -30,14 +30,25 @@ typedef __nv_bfloat16 bf16;
 int make_tmap_bf16_3d(CUtensorMap* m, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1_bytes,
                       uint64_t s2_bytes, uint32_t box_rows);
 
-constexpr int ABM = 128, ABN = 128, ADH = 64;
-constexpr int A_TILE16 = 128 * 64 * 2;                   // 16 KB: one 128-row x 64-col bf16 tile
+// 64-key tiles with TWO S/P buffers in TMEM: the MMA thread issues S(j+1) = Q.K(j+1)^T before it
+// waits for P(j), so the tensor core works on the next scores while the softmax warps turn the
+// current ones into P; per key tile the chain is max(softmax, MMA) instead of their sum.  (Three
+// CTAs per SM with one buffer each did not help: the per-tile latency chain was the limit.)
+constexpr int ABM = 128, ABN = 64, ADH = 64, A_CTAS_PER_SM = 2;
+constexpr int A_TILE16 = 128 * 64 * 2;                   // 16 KB: Q, 128 rows x 64 cols bf16
+constexpr int A_KTILE = ABN * 64 * 2;                    // 8 KB: K (ABN keys x 64 d) or Vt (64 d x ABN keys)
 constexpr int A_OFF_Q = 0;                               // Q_hi, Q_lo
 constexpr int A_OFF_K = 2 * A_TILE16;                    // K_hi, K_lo
-constexpr int A_OFF_V = 4 * A_TILE16;                    // Vt_hi (2 chunks x 8 KB), Vt_lo
-constexpr int A_OFF_BAR = 6 * A_TILE16;
-constexpr int A_SMEM = 6 * A_TILE16 + 128 + 1024;
-constexpr uint32_t TM_S = 0, TM_O = 128;
+constexpr int A_KV_STAGES = 2;                           // K / V rings: tile j+1 is in flight while j is used
+constexpr int A_KV_STAGE = 2 * A_KTILE;                  // hi + lo
+constexpr int A_OFF_V = A_OFF_K + A_KV_STAGES * A_KV_STAGE;          // Vt_hi, Vt_lo
+constexpr int A_OFF_BAR = A_OFF_V + A_KV_STAGES * A_KV_STAGE;
+constexpr int A_OFF_MX = A_OFF_BAR + 256;                 // row maxima exchanged between the two halves of a row
+constexpr int A_OFF_L = A_OFF_MX + 2 * 2 * 128 * 4;       // and their partial row sums, once at the end
+constexpr int A_SMEM = A_OFF_L + 2 * 128 * 4 + 1024;
+constexpr int A_THREADS = 320;                           // producer warp, MMA warp, 8 softmax warps
+constexpr uint32_t TM_S = 0, TM_O = 2 * ABN, A_TMEM_COLS = 256;        // S0 | S1 | O
+static_assert(ABN == 64, "the V tile is one 64-key box and P is written in 32-column chunks");
 
 struct MhaParams {
   int T, H, passes;
@@ -91,33 +102,61 @@ __device__ __forceinline__ uint32_t pack_bf16(bf16 a, bf16 b) {   // a -> low ha
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-__global__ void __launch_bounds__(192, 2)
+#ifdef EDA_MHA_TRACE
+// probe build only (scripts/mha_trace.py): clock64 stamps per CTA, 96 slots:
+//   [0] smid  [1] start  [2] end   MMA thread: [8+4j..] S issued, P ready, V ready, PV issued
+//   softmax warp 2: [48+2j] S ready, [49+2j] P arrived;  [80] O ready
+__device__ long long g_mha_trace[4096 * 96];
+#define MHA_STAMP(slot) g_mha_trace[(size_t)cta_lin * 96 + (slot)] = clock64()
+#else
+#define MHA_STAMP(slot)
+#endif
+
+__global__ void __launch_bounds__(A_THREADS, A_CTAS_PER_SM)
 mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant__ CUtensorMap tmQK_lo,
+              const __grid_constant__ CUtensorMap tmK_hi, const __grid_constant__ CUtensorMap tmK_lo,
               const __grid_constant__ CUtensorMap tmV_hi, const __grid_constant__ CUtensorMap tmV_lo,
               const MhaParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bar_q = reinterpret_cast<uint64_t*>(smem + A_OFF_BAR);
-  uint64_t* k_full = bar_q + 1;
-  uint64_t* k_empty = bar_q + 2;
-  uint64_t* v_full = bar_q + 3;
-  uint64_t* v_empty = bar_q + 4;
-  uint64_t* bar_s = bar_q + 5;
-  uint64_t* bar_p = bar_q + 6;
-  uint64_t* bar_o = bar_q + 7;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 8);
+  uint64_t* bar_s = bar_q + 1;        // [2]: S(j) complete in buffer j & 1
+  uint64_t* bar_p = bar_q + 3;        // [2]: P(j) written over it by the 8 softmax warps
+  uint64_t* bar_o = bar_q + 5;
+  uint64_t* bar_pv = bar_q + 6;       // P(j).V(j) has been accumulated into O
+  uint64_t* k_full = bar_q + 7;       // [A_KV_STAGES] each
+  uint64_t* k_empty = k_full + A_KV_STAGES;
+  uint64_t* v_full = k_empty + A_KV_STAGES;
+  uint64_t* v_empty = v_full + A_KV_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(v_empty + A_KV_STAGES);
+  float (*s_mx)[2][128] = reinterpret_cast<float (*)[2][128]>(smem + A_OFF_MX);     // [tile parity][half][row]
+  float (*s_l)[128] = reinterpret_cast<float (*)[128]>(smem + A_OFF_L);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * ABM, h = blockIdx.y, b = blockIdx.z;
   const int n_kt = (p.T + ABN - 1) / ABN;
+#ifdef EDA_MHA_TRACE
+  const int cta_lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  if (threadIdx.x == 0) {
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    g_mha_trace[(size_t)cta_lin * 96] = smid;
+    MHA_STAMP(1);
+  }
+#endif
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmQK_hi); tma_prefetch_desc(&tmQK_lo); tma_prefetch_desc(&tmV_hi); tma_prefetch_desc(&tmV_lo);
-    mbar_init(bar_q, 1); mbar_init(k_full, 1); mbar_init(k_empty, 1); mbar_init(v_full, 1); mbar_init(v_empty, 1);
-    mbar_init(bar_s, 1); mbar_init(bar_p, 4); mbar_init(bar_o, 1);
+    tma_prefetch_desc(&tmQK_hi); tma_prefetch_desc(&tmQK_lo); tma_prefetch_desc(&tmK_hi); tma_prefetch_desc(&tmK_lo);
+    tma_prefetch_desc(&tmV_hi); tma_prefetch_desc(&tmV_lo);
+    mbar_init(bar_q, 1);
+    for (int s = 0; s < A_KV_STAGES; ++s) {
+      mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); mbar_init(&v_full[s], 1); mbar_init(&v_empty[s], 1);
+    }
+    mbar_init(&bar_s[0], 1); mbar_init(&bar_s[1], 1); mbar_init(&bar_p[0], 8); mbar_init(&bar_p[1], 8);
+    mbar_init(bar_o, 1); mbar_init(bar_pv, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 256);
+  if (warp == 1) tmem_alloc(tmem_slot, A_TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -126,58 +165,69 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
 
   if (warp == 0) {
     // ===== TMA producer =====
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(bar_q, x3 ? 2 * A_TILE16 : A_TILE16);
       tma_load_3d(smem + A_OFF_Q, &tmQK_hi, bar_q, h * ADH, q0, b);
       if (x3) tma_load_3d(smem + A_OFF_Q + A_TILE16, &tmQK_lo, bar_q, h * ADH, q0, b);
       for (int j = 0; j < n_kt; ++j) {
-        const uint32_t ph = j & 1;
-        mbar_wait(k_empty, ph ^ 1);
-        mbar_expect_tx(k_full, x3 ? 2 * A_TILE16 : A_TILE16);
-        tma_load_3d(smem + A_OFF_K, &tmQK_hi, k_full, p.H * ADH + h * ADH, j * ABN, b);
-        if (x3) tma_load_3d(smem + A_OFF_K + A_TILE16, &tmQK_lo, k_full, p.H * ADH + h * ADH, j * ABN, b);
-        mbar_wait(v_empty, ph ^ 1);
-        mbar_expect_tx(v_full, x3 ? 2 * A_TILE16 : A_TILE16);
-        tma_load_3d(smem + A_OFF_V, &tmV_hi, v_full, j * ABN, 0, b * p.H + h);
-        tma_load_3d(smem + A_OFF_V + 8192, &tmV_hi, v_full, j * ABN + 64, 0, b * p.H + h);
-        if (x3) {
-          tma_load_3d(smem + A_OFF_V + A_TILE16, &tmV_lo, v_full, j * ABN, 0, b * p.H + h);
-          tma_load_3d(smem + A_OFF_V + A_TILE16 + 8192, &tmV_lo, v_full, j * ABN + 64, 0, b * p.H + h);
-        }
+        const int s = j % A_KV_STAGES;
+        const uint32_t ph = (j / A_KV_STAGES) & 1;
+        uint8_t* ks = smem + A_OFF_K + s * A_KV_STAGE;
+        uint8_t* vs = smem + A_OFF_V + s * A_KV_STAGE;
+        mbar_wait(&k_empty[s], ph ^ 1);
+        mbar_expect_tx(&k_full[s], x3 ? 2 * A_KTILE : A_KTILE);
+        tma_load_3d(ks, &tmK_hi, &k_full[s], p.H * ADH + h * ADH, j * ABN, b);
+        if (x3) tma_load_3d(ks + A_KTILE, &tmK_lo, &k_full[s], p.H * ADH + h * ADH, j * ABN, b);
+        mbar_wait(&v_empty[s], ph ^ 1);
+        mbar_expect_tx(&v_full[s], x3 ? 2 * A_KTILE : A_KTILE);
+        tma_load_3d(vs, &tmV_hi, &v_full[s], j * ABN, 0, b * p.H + h);
+        if (x3) tma_load_3d(vs + A_KTILE, &tmV_lo, &v_full[s], j * ABN, 0, b * p.H + h);
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
+    // ===== MMA issuer (one thread; elect.sync lets ptxas emit the uniform-datapath MMAs without a
+    // per-instruction active-lane loop, which a plain lane == 0 branch costs) =====
+    if (elect_one()) {
       const uint32_t idesc_s = idesc_bf16_f32(ABM, ABN), idesc_o = idesc_bf16_f32(ABM, ADH);
       const uint32_t sbase = smem_u32(smem);
       const uint64_t q_hi = smem_desc_sw128(sbase + A_OFF_Q), q_lo = smem_desc_sw128(sbase + A_OFF_Q + A_TILE16);
-      const uint64_t k_hi = smem_desc_sw128(sbase + A_OFF_K), k_lo = smem_desc_sw128(sbase + A_OFF_K + A_TILE16);
       const uint32_t tS = tmem_base + TM_S, tO = tmem_base + TM_O;
-      const uint32_t tPhi = tS;
-      mbar_wait(bar_q, 0);
-      for (int j = 0; j < n_kt; ++j) {
-        const uint32_t ph = j & 1;
-        mbar_wait(k_full, ph);
+      auto issue_s = [&](int j) {                  // S(j) = Q K(j)^T into buffer j & 1
+        const int s = j % A_KV_STAGES;
+        mbar_wait(&k_full[s], (j / A_KV_STAGES) & 1);
         tc_fence_after();
+        const uint64_t k_hi = smem_desc_sw128(sbase + A_OFF_K + s * A_KV_STAGE), k_lo = smem_desc_sw128(sbase + A_OFF_K + s * A_KV_STAGE + A_KTILE);
+        const uint32_t ts = tS + (j & 1) * ABN;
 #pragma unroll
         for (int k = 0; k < ADH / 16; ++k) {
           const uint64_t adv = uint64_t(k * 32 >> 4);
-          umma_bf16(tS, q_hi + adv, k_hi + adv, idesc_s, k != 0);
+          umma_bf16(ts, q_hi + adv, k_hi + adv, idesc_s, k != 0);
           if (x3) {
-            umma_bf16(tS, q_hi + adv, k_lo + adv, idesc_s, 1);
-            umma_bf16(tS, q_lo + adv, k_hi + adv, idesc_s, 1);
+            umma_bf16(ts, q_hi + adv, k_lo + adv, idesc_s, 1);
+            umma_bf16(ts, q_lo + adv, k_hi + adv, idesc_s, 1);
           }
         }
-        umma_commit(k_empty);
-        umma_commit(bar_s);
-        mbar_wait(bar_p, ph);          // P_j is in TMEM (over S), O has been rescaled if needed
-        mbar_wait(v_full, ph);
+        umma_commit(&k_empty[s]);
+        umma_commit(&bar_s[j & 1]);
+      };
+      mbar_wait(bar_q, 0);
+      issue_s(0);
+      for (int j = 0; j < n_kt; ++j) {
+        // S(j+1) overwrites the buffer P(j-1) lived in: P(j-1).V(j-1) was issued before it, and
+        // MMAs of one thread execute in issue order
+        if (j + 1 < n_kt) issue_s(j + 1);
+        MHA_STAMP(8 + 4 * j);
+        mbar_wait(&bar_p[j & 1], (j >> 1) & 1);     // P(j) is in TMEM (over S(j)), O rescaled if needed
+        MHA_STAMP(9 + 4 * j);
+        const int s = j % A_KV_STAGES;
+        mbar_wait(&v_full[s], (j / A_KV_STAGES) & 1);
+        MHA_STAMP(10 + 4 * j);
         tc_fence_after();
+        const uint32_t tPhi = tS + (j & 1) * ABN;
 #pragma unroll
         for (int k = 0; k < ABN / 16; ++k) {
-          const uint32_t voff = A_OFF_V + (k >> 2) * 8192 + (k & 3) * 32;
-          const uint64_t v_hi = smem_desc_sw128(sbase + voff), v_lo = smem_desc_sw128(sbase + voff + A_TILE16);
+          const uint32_t voff = A_OFF_V + s * A_KV_STAGE + k * 32;                    // 16 keys = 32 B along the key-major rows
+          const uint64_t v_hi = smem_desc_sw128(sbase + voff), v_lo = smem_desc_sw128(sbase + voff + A_KTILE);
           const uint32_t pa = tPhi + (k >> 1) * 32 + (k & 1) * 8;    // hi pairs; lo pairs 16 columns on
           umma_bf16_ts(tO, pa, v_hi, idesc_o, (j | k) != 0);
           if (x3) {
@@ -185,128 +235,147 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
             umma_bf16_ts(tO, pa + 16, v_hi, idesc_o, 1);
           }
         }
-        umma_commit(v_empty);
+        umma_commit(&v_empty[s]);
+        umma_commit(bar_pv);
         if (j == n_kt - 1) umma_commit(bar_o);
+        MHA_STAMP(11 + 4 * j);
       }
     }
   } else {
-    // ===== softmax + output: warps 2..5, thread = query row (TMEM lane) =====
-    const int qd = warp & 3;
+    // ===== softmax + output: warps 2..9.  Two threads per query row: warp w and w + 4 own the same
+    // 32 TMEM lanes (lane quarter = warp & 3) and one 32-key half of the tile each, so the row's
+    // exp / split chain is half as long and twice as many warps hide its latency.  The halves only
+    // share the row maximum (through shared memory, one 64-thread named barrier per tile).
+    const int qd = warp & 3, half = (warp - 2) >> 2;
+    const int row_in_tile = qd * 32 + lane;
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
-    const uint32_t tS = tmem_base + TM_S + lane_off, tO = tmem_base + TM_O + lane_off;
+    const uint32_t tS0 = tmem_base + TM_S + lane_off + half * 32, tO = tmem_base + TM_O + lane_off + half * 32;
     constexpr float kLog2e = 1.4426950408889634f;
-    float m_cur = -INFINITY, l_sum = 0.f;
+    // kLazy: the running reference maximum only moves when some row of the warp outgrows it by more
+    // than 2^kLazy; until then P = exp(S - m_ref) <= 2^kLazy, harmless in the fp32 accumulators, and
+    // O / l is unchanged by the common factor.  Saves the O read-modify-write of nearly every tile.
+    constexpr float kLazy = 8.0f;
+    float m_ref = -INFINITY, l_sum = 0.f;       // m_ref in log2 units (S * log2 e)
+    auto pair_sync = [&]() { asm volatile("bar.sync %0, 64;" ::"r"(1 + qd) : "memory"); };
     for (int j = 0; j < n_kt; ++j) {
-      mbar_wait(bar_s, j & 1);
+      const uint32_t tS = tS0 + (j & 1) * ABN;
+      mbar_wait(&bar_s[j & 1], (j >> 1) & 1);
+#ifdef EDA_MHA_TRACE
+      if (threadIdx.x == 64) MHA_STAMP(48 + 2 * j);
+#endif
       tc_fence_after();
-      const int n_valid = min(ABN, p.T - j * ABN);      // keys of this tile that exist
-      const bool whole = n_valid == ABN;                // (CTA-uniform) no masking needed
-      // pass 1: row maximum
-      float mx = -INFINITY;
+      const int n_valid = min(32, p.T - j * ABN - half * 32);     // keys of this half that exist (may be <= 0)
+      const bool whole = n_valid == 32;                           // warp-uniform
+      float v[32];                                                // the scores stay in registers: one TMEM read
+      tmem_ld32(tS, v);
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      if (whole) {
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float v[32];
-        tmem_ld32(tS + c * 32, v);
-        if (whole) {
+        for (int i = 0; i < 32; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], v[i]);
+      } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, v[i]);
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i < n_valid) ? v[i] : -INFINITY);
-        }
+        for (int i = 0; i < 32; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], i < n_valid ? v[i] : -INFINITY);
       }
-      const float m_new = fmaxf(m_cur, mx);             // finite: key 0 of every tile exists
-      if (j > 0 && __any_sync(0xffffffffu, m_new > m_cur)) {
-        // O *= exp(m_old - m_new): every earlier P.V has completed (bar_s was committed after it)
-        const float alpha = ex2_approx((m_cur - m_new) * kLog2e);
+      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * kLog2e;
+      s_mx[j & 1][half][row_in_tile] = mx;
+      pair_sync();
+      mx = fmaxf(mx, s_mx[j & 1][half ^ 1][row_in_tile]);         // finite: key 0 of every tile exists
+      if (j == 0) {
+        m_ref = mx;
+      } else if (__any_sync(0xffffffffu, mx > m_ref + kLazy)) {   // same rows, same verdict in both warps of the pair
+        // O *= 2^(m_old - m_new) on this half's 32 columns; P(j-1).V must have landed before O is touched
+        mbar_wait(bar_pv, (j - 1) & 1);
+        tc_fence_after();
+        const float m_new = fmaxf(m_ref, mx);
+        const float alpha = ex2_approx(m_ref - m_new);
         l_sum *= alpha;
+        m_ref = m_new;
+        float o[32];
+        tmem_ld32(tO, o);
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          float o[32];
-          tmem_ld32(tO + c * 32, o);
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] *= alpha;
-          tmem_st32(tO + c * 32, o);
-        }
+        for (int i = 0; i < 32; ++i) o[i] *= alpha;
+        tmem_st32(tO, o);
       }
-      m_cur = m_new;
-      const float mb = m_new * kLog2e;
-      // pass 2: P = exp(S - m) -> split bf16, written IN PLACE over the 32 S columns it came from:
+      // P = exp(S - m) -> split bf16, written IN PLACE over the 32 S columns it came from:
       // packed hi pairs in the first 16 columns of the chunk, lo pairs in the last 16
-      float l0 = 0.f, l1 = 0.f;
+      float l4[4] = {0.f, 0.f, 0.f, 0.f};
+      float pk[32];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float v[32];
-        tmem_ld32(tS + c * 32, v);
-        float pk[32];
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float p0 = ex2_approx(fmaf(v[i], kLog2e, -mb)), p1 = ex2_approx(fmaf(v[i + 1], kLog2e, -mb));
-          if (!whole) {
-            if (c * 32 + i >= n_valid) p0 = 0.f;
-            if (c * 32 + i + 1 >= n_valid) p1 = 0.f;
-          }
-          l0 += p0; l1 += p1;
-          const uint32_t hi = pack_bf16x2(p0, p1);
-          pk[i >> 1] = __uint_as_float(hi);
-          pk[16 + (i >> 1)] = __uint_as_float(pack_bf16x2(p0 - __uint_as_float(hi << 16),
-                                                          p1 - __uint_as_float(hi & 0xffff0000u)));
+      for (int i = 0; i < 32; i += 2) {
+        float p0 = ex2_approx(fmaf(v[i], kLog2e, -m_ref)), p1 = ex2_approx(fmaf(v[i + 1], kLog2e, -m_ref));
+        if (!whole) {
+          if (i >= n_valid) p0 = 0.f;
+          if (i + 1 >= n_valid) p1 = 0.f;
         }
-        tmem_st32(tS + c * 32, pk);
+        l4[i & 2] += p0; l4[(i & 2) + 1] += p1;
+        const uint32_t hi = pack_bf16x2(p0, p1);
+        pk[i >> 1] = __uint_as_float(hi);
+        pk[16 + (i >> 1)] = __uint_as_float(pack_bf16x2(p0 - __uint_as_float(hi << 16),
+                                                        p1 - __uint_as_float(hi & 0xffff0000u)));
       }
-      l_sum += l0 + l1;
+      tmem_st32(tS, pk);
+      l_sum += (l4[0] + l4[1]) + (l4[2] + l4[3]);
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_p);
+      if (lane == 0) mbar_arrive(&bar_p[j & 1]);
+#ifdef EDA_MHA_TRACE
+      if (threadIdx.x == 64) MHA_STAMP(49 + 2 * j);
+#endif
     }
-    // ---- epilogue: O / l, thread = row: 64 columns = 256 B fp32 / 128 B per bf16 half ------
+    // ---- epilogue: O / l; thread = (row, 32-column half): 128 B fp32 / 64 B per bf16 half -----
+    s_l[half][row_in_tile] = l_sum;
+    pair_sync();
+    l_sum += s_l[half ^ 1][row_in_tile];
     mbar_wait(bar_o, 0);
+#ifdef EDA_MHA_TRACE
+    if (threadIdx.x == 64) MHA_STAMP(80);
+#endif
     tc_fence_after();
     const float inv = 1.0f / l_sum;
-    const int q = q0 + qd * 32 + lane;
+    const int q = q0 + row_in_tile;
     const size_t row = (size_t)b * p.T + q;
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
+    {
       float o[32];
-      tmem_ld32(tO + c * 32, o);
-      if (q >= p.T) continue;
+      tmem_ld32(tO, o);
+      if (q < p.T) {
 #pragma unroll
-      for (int i = 0; i < 32; ++i) o[i] *= inv;
-      const int col = h * ADH + c * 32;
-      if (p.out) {
-        float* dst = p.out + row * p.ld_out + col;
-        if (((uintptr_t)dst & 31) == 0) {
+        for (int i = 0; i < 32; ++i) o[i] *= inv;
+        const int col = h * ADH + half * 32;
+        if (p.out) {
+          float* dst = p.out + row * p.ld_out + col;
+          if (((uintptr_t)dst & 31) == 0) {
 #pragma unroll
-          for (int i = 0; i < 32; i += 8)
-            st_global_v8(dst + i, __float_as_uint(o[i]), __float_as_uint(o[i + 1]), __float_as_uint(o[i + 2]),
-                         __float_as_uint(o[i + 3]), __float_as_uint(o[i + 4]), __float_as_uint(o[i + 5]),
-                         __float_as_uint(o[i + 6]), __float_as_uint(o[i + 7]));
-        } else {
+            for (int i = 0; i < 32; i += 8)
+              st_global_v8(dst + i, __float_as_uint(o[i]), __float_as_uint(o[i + 1]), __float_as_uint(o[i + 2]),
+                           __float_as_uint(o[i + 3]), __float_as_uint(o[i + 4]), __float_as_uint(o[i + 5]),
+                           __float_as_uint(o[i + 6]), __float_as_uint(o[i + 7]));
+          } else {
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) *reinterpret_cast<float2*>(dst + i) = make_float2(o[i], o[i + 1]);
+            for (int i = 0; i < 32; i += 2) *reinterpret_cast<float2*>(dst + i) = make_float2(o[i], o[i + 1]);
+          }
         }
-      }
-      if (p.out_hi) {
-        uint32_t hh[16], ll[16];
+        if (p.out_hi) {
+          uint32_t hh[16], ll[16];
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          hh[i >> 1] = pack_bf16x2(o[i], o[i + 1]);
-          ll[i >> 1] = pack_bf16x2(o[i] - __uint_as_float(hh[i >> 1] << 16),
-                                   o[i + 1] - __uint_as_float(hh[i >> 1] & 0xffff0000u));
-        }
-        bf16* dh = p.out_hi + row * p.ld_os + col;
-        bf16* dl = p.out_lo + row * p.ld_os + col;
-        if ((((uintptr_t)dh | (uintptr_t)dl) & 31) == 0) {
-          st_global_v8(dh, hh[0], hh[1], hh[2], hh[3], hh[4], hh[5], hh[6], hh[7]);
-          st_global_v8(dh + 16, hh[8], hh[9], hh[10], hh[11], hh[12], hh[13], hh[14], hh[15]);
-          st_global_v8(dl, ll[0], ll[1], ll[2], ll[3], ll[4], ll[5], ll[6], ll[7]);
-          st_global_v8(dl + 16, ll[8], ll[9], ll[10], ll[11], ll[12], ll[13], ll[14], ll[15]);
-        } else {
+          for (int i = 0; i < 32; i += 2) {
+            hh[i >> 1] = pack_bf16x2(o[i], o[i + 1]);
+            ll[i >> 1] = pack_bf16x2(o[i] - __uint_as_float(hh[i >> 1] << 16),
+                                     o[i + 1] - __uint_as_float(hh[i >> 1] & 0xffff0000u));
+          }
+          bf16* dh = p.out_hi + row * p.ld_os + col;
+          bf16* dl = p.out_lo + row * p.ld_os + col;
+          if ((((uintptr_t)dh | (uintptr_t)dl) & 31) == 0) {
+            st_global_v8(dh, hh[0], hh[1], hh[2], hh[3], hh[4], hh[5], hh[6], hh[7]);
+            st_global_v8(dh + 16, hh[8], hh[9], hh[10], hh[11], hh[12], hh[13], hh[14], hh[15]);
+            st_global_v8(dl, ll[0], ll[1], ll[2], ll[3], ll[4], ll[5], ll[6], ll[7]);
+            st_global_v8(dl + 16, ll[8], ll[9], ll[10], ll[11], ll[12], ll[13], ll[14], ll[15]);
+          } else {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            *reinterpret_cast<uint32_t*>(dh + 2 * i) = hh[i];
-            *reinterpret_cast<uint32_t*>(dl + 2 * i) = ll[i];
+            for (int i = 0; i < 16; ++i) {
+              *reinterpret_cast<uint32_t*>(dh + 2 * i) = hh[i];
+              *reinterpret_cast<uint32_t*>(dl + 2 * i) = ll[i];
+            }
           }
         }
       }
@@ -316,8 +385,11 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 256);
+    tmem_dealloc(tmem_base, A_TMEM_COLS);
   }
+#ifdef EDA_MHA_TRACE
+  if (threadIdx.x == 0) MHA_STAMP(2);
+#endif
 }
 
 // ------------------------------------------------------------------------- host ---------
@@ -336,18 +408,20 @@ int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi
     EDA_CUDA(cudaFuncSetAttribute(mha_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, A_SMEM));
     attr = true;
   }
-  CUtensorMap tq_hi, tq_lo, tv_hi, tv_lo;
+  CUtensorMap tq_hi, tq_lo, tk_hi, tk_lo, tv_hi, tv_lo;
   int rc;
   const uint64_t row_b = (uint64_t)ld_qk * 2;
   if ((rc = make_tmap_bf16_3d(&tq_hi, qk_hi, 2 * H * ADH, T, B, row_b, row_b * T, 128)) != EDA_OK) return rc;
   if ((rc = make_tmap_bf16_3d(&tq_lo, qk_lo, 2 * H * ADH, T, B, row_b, row_b * T, 128)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16_3d(&tk_hi, qk_hi, 2 * H * ADH, T, B, row_b, row_b * T, ABN)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16_3d(&tk_lo, qk_lo, 2 * H * ADH, T, B, row_b, row_b * T, ABN)) != EDA_OK) return rc;
   if ((rc = make_tmap_bf16_3d(&tv_hi, vt_hi, T, ADH, (uint64_t)B * H, (uint64_t)Tp * 2, (uint64_t)Tp * 2 * ADH, 64)) != EDA_OK) return rc;
   if ((rc = make_tmap_bf16_3d(&tv_lo, vt_lo, T, ADH, (uint64_t)B * H, (uint64_t)Tp * 2, (uint64_t)Tp * 2 * ADH, 64)) != EDA_OK) return rc;
   MhaParams p = {};
   p.T = T; p.H = H; p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
   p.out = out; p.ld_out = ld_out; p.out_hi = (bf16*)out_hi; p.out_lo = (bf16*)out_lo; p.ld_os = ld_os;
   dim3 grid(ceil_div(T, ABM), H, B);
-  mha_tc_kernel<<<grid, 192, A_SMEM, st>>>(tq_hi, tq_lo, tv_hi, tv_lo, p);
+  mha_tc_kernel<<<grid, A_THREADS, A_SMEM, st>>>(tq_hi, tq_lo, tk_hi, tk_lo, tv_hi, tv_lo, p);
   EDA_LAUNCH_CHECK();
   return EDA_OK;
 }
@@ -404,3 +478,9 @@ extern "C" int eda_mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, co
   return eda::mha_split(qk_hi, qk_lo, ld_qk, vt_hi, vt_lo, Tp, B, T, n_heads, out, ld_out, out_hi, out_lo, ld_os,
                         prec, (cudaStream_t)stream);
 }
+
+#ifdef EDA_MHA_TRACE
+extern "C" int eda_mha_trace_read(long long* host, int n_cta) {
+  return (int)cudaMemcpyFromSymbol(host, eda::g_mha_trace, (size_t)n_cta * 96 * sizeof(long long));
+}
+#endif

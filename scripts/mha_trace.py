@@ -48,12 +48,14 @@ def main():
                                None, 0, out_hi.data_ptr(), out_lo.data_ptr(), D, 1, None)
         assert rc == 0
     torch.cuda.synchronize()
-    n_cta = 4 * H * B
+    n_cta = min(4 * H * B, 2 * torch.cuda.get_device_properties(0).multi_processor_count)
     buf = np.zeros((n_cta, 96), dtype=np.int64)
     lib.eda_mha_trace_read.argtypes = [p, C.c_int]
     assert lib.eda_mha_trace_read(buf.ctypes.data, n_cta) == 0
     life = buf[:, 2] - buf[:, 1]
-    print("CTA lifetime cycles: mean %.0f  min %d  max %d" % (life.mean(), life.min(), life.max()))
+    print("CTA lifetime cycles: mean %.0f  min %d  max %d ; items per CTA %d..%d ; cycles per item %.0f" % (
+        life.mean(), life.min(), life.max(), buf[:, 3].min(), buf[:, 3].max(), (life / buf[:, 3]).mean()))
+    print("(per-tile stamps below are each CTA's FIRST item)")
     nk = 8
     mma = buf[:, 8:8 + 4 * nk].reshape(n_cta, nk, 4)
     sm = buf[:, 48:48 + 2 * nk].reshape(n_cta, nk, 2)

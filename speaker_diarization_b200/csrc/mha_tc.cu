@@ -51,7 +51,7 @@ constexpr uint32_t TM_S = 0, TM_O = 2 * ABN, A_TMEM_COLS = 256;        // S0 | S
 static_assert(ABN == 64, "the V tile is one 64-key box and P is written in 32-column chunks");
 
 struct MhaParams {
-  int T, H, passes;
+  int T, H, B, passes;
   float* out; int ld_out;                 // optional fp32 (B*T, H*64)
   bf16* out_hi; bf16* out_lo; int ld_os;  // optional split
 };
@@ -103,15 +103,20 @@ __device__ __forceinline__ uint32_t pack_bf16(bf16 a, bf16 b) {   // a -> low ha
 }
 
 #ifdef EDA_MHA_TRACE
-// probe build only (scripts/mha_trace.py): clock64 stamps per CTA, 96 slots:
-//   [0] smid  [1] start  [2] end   MMA thread: [8+4j..] S issued, P ready, V ready, PV issued
+// probe build only (scripts/mha_trace.py): clock64 stamps of each CTA's FIRST work item, 96 slots:
+//   [0] smid  [1] start  [2] end  [3] items done   MMA thread: [8+4j..] S issued, P ready, V ready, PV issued
 //   softmax warp 2: [48+2j] S ready, [49+2j] P arrived;  [80] O ready
 __device__ long long g_mha_trace[4096 * 96];
-#define MHA_STAMP(slot) g_mha_trace[(size_t)cta_lin * 96 + (slot)] = clock64()
+#define MHA_STAMP(slot) do { if (it == 0) g_mha_trace[(size_t)blockIdx.x * 96 + (slot)] = clock64(); } while (0)
 #else
 #define MHA_STAMP(slot)
 #endif
 
+// Persistent: A_CTAS_PER_SM CTAs per SM, each walking the (batch, head, query tile) items
+// blockIdx.x, blockIdx.x + gridDim.x, ...  Barriers, the TMEM allocation and the K/V rings live
+// across items: the producer prefetches the next item's Q and first K/V tiles while the current
+// item's last tiles and epilogue run, so an item costs its key tiles and nothing else (a CTA per
+// item spent a quarter of its life in launch latency, setup and waiting for its first loads).
 __global__ void __launch_bounds__(A_THREADS, A_CTAS_PER_SM)
 mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant__ CUtensorMap tmQK_lo,
               const __grid_constant__ CUtensorMap tmK_hi, const __grid_constant__ CUtensorMap tmK_lo,
@@ -119,12 +124,14 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
               const MhaParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bar_q = reinterpret_cast<uint64_t*>(smem + A_OFF_BAR);
-  uint64_t* bar_s = bar_q + 1;        // [2]: S(j) complete in buffer j & 1
-  uint64_t* bar_p = bar_q + 3;        // [2]: P(j) written over it by the 8 softmax warps
-  uint64_t* bar_o = bar_q + 5;
-  uint64_t* bar_pv = bar_q + 6;       // P(j).V(j) has been accumulated into O
-  uint64_t* k_full = bar_q + 7;       // [A_KV_STAGES] each
+  uint64_t* bar_q = reinterpret_cast<uint64_t*>(smem + A_OFF_BAR);     // Q of the item has landed
+  uint64_t* bar_s = bar_q + 1;        // [2]: S(g) complete in buffer g & 1   (g = key tiles since kernel start)
+  uint64_t* bar_p = bar_q + 3;        // [2]: P(g) written over it by the 8 softmax warps
+  uint64_t* bar_o = bar_q + 5;        // O of the item is complete
+  uint64_t* bar_pv = bar_q + 6;       // P(g).V(g) has been accumulated into O
+  uint64_t* q_empty = bar_q + 7;      // the item's S MMAs have all read Q
+  uint64_t* o_free = bar_q + 8;       // the item's epilogue has read O out of TMEM
+  uint64_t* k_full = bar_q + 9;       // [A_KV_STAGES] each
   uint64_t* k_empty = k_full + A_KV_STAGES;
   uint64_t* v_full = k_empty + A_KV_STAGES;
   uint64_t* v_empty = v_full + A_KV_STAGES;
@@ -133,22 +140,21 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
   float (*s_l)[128] = reinterpret_cast<float (*)[128]>(smem + A_OFF_L);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * ABM, h = blockIdx.y, b = blockIdx.z;
-  const int n_kt = (p.T + ABN - 1) / ABN;
+  const int n_kt = (p.T + ABN - 1) / ABN, n_qt = (p.T + ABM - 1) / ABM;
+  const int n_items = n_qt * p.H * p.B;
 #ifdef EDA_MHA_TRACE
-  const int cta_lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
   if (threadIdx.x == 0) {
     uint32_t smid;
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    g_mha_trace[(size_t)cta_lin * 96] = smid;
-    MHA_STAMP(1);
+    g_mha_trace[(size_t)blockIdx.x * 96] = smid;
+    g_mha_trace[(size_t)blockIdx.x * 96 + 1] = clock64();
   }
 #endif
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQK_hi); tma_prefetch_desc(&tmQK_lo); tma_prefetch_desc(&tmK_hi); tma_prefetch_desc(&tmK_lo);
     tma_prefetch_desc(&tmV_hi); tma_prefetch_desc(&tmV_lo);
-    mbar_init(bar_q, 1);
+    mbar_init(bar_q, 1); mbar_init(q_empty, 1); mbar_init(o_free, 8);
     for (int s = 0; s < A_KV_STAGES; ++s) {
       mbar_init(&k_full[s], 1); mbar_init(&k_empty[s], 1); mbar_init(&v_full[s], 1); mbar_init(&v_empty[s], 1);
     }
@@ -166,22 +172,28 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
   if (warp == 0) {
     // ===== TMA producer =====
     if (elect_one()) {
-      mbar_expect_tx(bar_q, x3 ? 2 * A_TILE16 : A_TILE16);
-      tma_load_3d(smem + A_OFF_Q, &tmQK_hi, bar_q, h * ADH, q0, b);
-      if (x3) tma_load_3d(smem + A_OFF_Q + A_TILE16, &tmQK_lo, bar_q, h * ADH, q0, b);
-      for (int j = 0; j < n_kt; ++j) {
-        const int s = j % A_KV_STAGES;
-        const uint32_t ph = (j / A_KV_STAGES) & 1;
-        uint8_t* ks = smem + A_OFF_K + s * A_KV_STAGE;
-        uint8_t* vs = smem + A_OFF_V + s * A_KV_STAGE;
-        mbar_wait(&k_empty[s], ph ^ 1);
-        mbar_expect_tx(&k_full[s], x3 ? 2 * A_KTILE : A_KTILE);
-        tma_load_3d(ks, &tmK_hi, &k_full[s], p.H * ADH + h * ADH, j * ABN, b);
-        if (x3) tma_load_3d(ks + A_KTILE, &tmK_lo, &k_full[s], p.H * ADH + h * ADH, j * ABN, b);
-        mbar_wait(&v_empty[s], ph ^ 1);
-        mbar_expect_tx(&v_full[s], x3 ? 2 * A_KTILE : A_KTILE);
-        tma_load_3d(vs, &tmV_hi, &v_full[s], j * ABN, 0, b * p.H + h);
-        if (x3) tma_load_3d(vs + A_KTILE, &tmV_lo, &v_full[s], j * ABN, 0, b * p.H + h);
+      uint32_t g = 0;
+      int it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+        const int q0 = (item % n_qt) * ABM, h = (item / n_qt) % p.H, b = item / (n_qt * p.H);
+        mbar_wait(q_empty, (it & 1) ^ 1);
+        mbar_expect_tx(bar_q, x3 ? 2 * A_TILE16 : A_TILE16);
+        tma_load_3d(smem + A_OFF_Q, &tmQK_hi, bar_q, h * ADH, q0, b);
+        if (x3) tma_load_3d(smem + A_OFF_Q + A_TILE16, &tmQK_lo, bar_q, h * ADH, q0, b);
+        for (int j = 0; j < n_kt; ++j, ++g) {
+          const int s = g % A_KV_STAGES;
+          const uint32_t ph = (g / A_KV_STAGES) & 1;
+          uint8_t* ks = smem + A_OFF_K + s * A_KV_STAGE;
+          uint8_t* vs = smem + A_OFF_V + s * A_KV_STAGE;
+          mbar_wait(&k_empty[s], ph ^ 1);
+          mbar_expect_tx(&k_full[s], x3 ? 2 * A_KTILE : A_KTILE);
+          tma_load_3d(ks, &tmK_hi, &k_full[s], p.H * ADH + h * ADH, j * ABN, b);
+          if (x3) tma_load_3d(ks + A_KTILE, &tmK_lo, &k_full[s], p.H * ADH + h * ADH, j * ABN, b);
+          mbar_wait(&v_empty[s], ph ^ 1);
+          mbar_expect_tx(&v_full[s], x3 ? 2 * A_KTILE : A_KTILE);
+          tma_load_3d(vs, &tmV_hi, &v_full[s], j * ABN, 0, b * p.H + h);
+          if (x3) tma_load_3d(vs + A_KTILE, &tmV_lo, &v_full[s], j * ABN, 0, b * p.H + h);
+        }
       }
     }
   } else if (warp == 1) {
@@ -192,12 +204,13 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
       const uint32_t sbase = smem_u32(smem);
       const uint64_t q_hi = smem_desc_sw128(sbase + A_OFF_Q), q_lo = smem_desc_sw128(sbase + A_OFF_Q + A_TILE16);
       const uint32_t tS = tmem_base + TM_S, tO = tmem_base + TM_O;
-      auto issue_s = [&](int j) {                  // S(j) = Q K(j)^T into buffer j & 1
-        const int s = j % A_KV_STAGES;
-        mbar_wait(&k_full[s], (j / A_KV_STAGES) & 1);
+      uint32_t gs = 0, gp = 0;                     // key tiles whose S / P.V has been issued
+      auto issue_s = [&]() {                       // S(gs) = Q K^T into buffer gs & 1
+        const int s = gs % A_KV_STAGES;
+        mbar_wait(&k_full[s], (gs / A_KV_STAGES) & 1);
         tc_fence_after();
         const uint64_t k_hi = smem_desc_sw128(sbase + A_OFF_K + s * A_KV_STAGE), k_lo = smem_desc_sw128(sbase + A_OFF_K + s * A_KV_STAGE + A_KTILE);
-        const uint32_t ts = tS + (j & 1) * ABN;
+        const uint32_t ts = tS + (gs & 1) * ABN;
 #pragma unroll
         for (int k = 0; k < ADH / 16; ++k) {
           const uint64_t adv = uint64_t(k * 32 >> 4);
@@ -208,37 +221,43 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
           }
         }
         umma_commit(&k_empty[s]);
-        umma_commit(&bar_s[j & 1]);
+        umma_commit(&bar_s[gs & 1]);
+        ++gs;
       };
-      mbar_wait(bar_q, 0);
-      issue_s(0);
-      for (int j = 0; j < n_kt; ++j) {
-        // S(j+1) overwrites the buffer P(j-1) lived in: P(j-1).V(j-1) was issued before it, and
-        // MMAs of one thread execute in issue order
-        if (j + 1 < n_kt) issue_s(j + 1);
-        MHA_STAMP(8 + 4 * j);
-        mbar_wait(&bar_p[j & 1], (j >> 1) & 1);     // P(j) is in TMEM (over S(j)), O rescaled if needed
-        MHA_STAMP(9 + 4 * j);
-        const int s = j % A_KV_STAGES;
-        mbar_wait(&v_full[s], (j / A_KV_STAGES) & 1);
-        MHA_STAMP(10 + 4 * j);
-        tc_fence_after();
-        const uint32_t tPhi = tS + (j & 1) * ABN;
+      int it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+        mbar_wait(bar_q, it & 1);
+        issue_s();
+        for (int j = 0; j < n_kt; ++j, ++gp) {
+          // S(g+1) overwrites the buffer P(g-1) lived in: P(g-1).V(g-1) was issued before it, and
+          // MMAs of one thread execute in issue order
+          if (j + 1 < n_kt) issue_s();
+          else umma_commit(q_empty);                     // every S of the item is issued: Q may be replaced once they finish
+          MHA_STAMP(8 + 4 * j);
+          mbar_wait(&bar_p[gp & 1], (gp >> 1) & 1);     // P(g) is in TMEM (over S(g)), O rescaled if needed
+          MHA_STAMP(9 + 4 * j);
+          const int s = gp % A_KV_STAGES;
+          mbar_wait(&v_full[s], (gp / A_KV_STAGES) & 1);
+          if (j == 0) mbar_wait(o_free, (it & 1) ^ 1);   // the previous item's O has been read out
+          MHA_STAMP(10 + 4 * j);
+          tc_fence_after();
+          const uint32_t tPhi = tS + (gp & 1) * ABN;
 #pragma unroll
-        for (int k = 0; k < ABN / 16; ++k) {
-          const uint32_t voff = A_OFF_V + s * A_KV_STAGE + k * 32;                    // 16 keys = 32 B along the key-major rows
-          const uint64_t v_hi = smem_desc_sw128(sbase + voff), v_lo = smem_desc_sw128(sbase + voff + A_KTILE);
-          const uint32_t pa = tPhi + (k >> 1) * 32 + (k & 1) * 8;    // hi pairs; lo pairs 16 columns on
-          umma_bf16_ts(tO, pa, v_hi, idesc_o, (j | k) != 0);
-          if (x3) {
-            umma_bf16_ts(tO, pa, v_lo, idesc_o, 1);
-            umma_bf16_ts(tO, pa + 16, v_hi, idesc_o, 1);
+          for (int k = 0; k < ABN / 16; ++k) {
+            const uint32_t voff = A_OFF_V + s * A_KV_STAGE + k * 32;                    // 16 keys = 32 B along the key-major rows
+            const uint64_t v_hi = smem_desc_sw128(sbase + voff), v_lo = smem_desc_sw128(sbase + voff + A_KTILE);
+            const uint32_t pa = tPhi + (k >> 1) * 32 + (k & 1) * 8;    // hi pairs; lo pairs 16 columns on
+            umma_bf16_ts(tO, pa, v_hi, idesc_o, (j | k) != 0);
+            if (x3) {
+              umma_bf16_ts(tO, pa, v_lo, idesc_o, 1);
+              umma_bf16_ts(tO, pa + 16, v_hi, idesc_o, 1);
+            }
           }
+          umma_commit(&v_empty[s]);
+          umma_commit(bar_pv);
+          if (j == n_kt - 1) umma_commit(bar_o);
+          MHA_STAMP(11 + 4 * j);
         }
-        umma_commit(&v_empty[s]);
-        umma_commit(bar_pv);
-        if (j == n_kt - 1) umma_commit(bar_o);
-        MHA_STAMP(11 + 4 * j);
       }
     }
   } else {
@@ -255,11 +274,15 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
     // than 2^kLazy; until then P = exp(S - m_ref) <= 2^kLazy, harmless in the fp32 accumulators, and
     // O / l is unchanged by the common factor.  Saves the O read-modify-write of nearly every tile.
     constexpr float kLazy = 8.0f;
-    float m_ref = -INFINITY, l_sum = 0.f;       // m_ref in log2 units (S * log2 e)
     auto pair_sync = [&]() { asm volatile("bar.sync %0, 64;" ::"r"(1 + qd) : "memory"); };
-    for (int j = 0; j < n_kt; ++j) {
-      const uint32_t tS = tS0 + (j & 1) * ABN;
-      mbar_wait(&bar_s[j & 1], (j >> 1) & 1);
+    uint32_t g = 0;                             // key tiles since kernel start (buffer / phase bookkeeping)
+    int it = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+    const int q0 = (item % n_qt) * ABM, h = (item / n_qt) % p.H, b = item / (n_qt * p.H);
+    float m_ref = -INFINITY, l_sum = 0.f;       // m_ref in log2 units (S * log2 e)
+    for (int j = 0; j < n_kt; ++j, ++g) {
+      const uint32_t tS = tS0 + (g & 1) * ABN;
+      mbar_wait(&bar_s[g & 1], (g >> 1) & 1);
 #ifdef EDA_MHA_TRACE
       if (threadIdx.x == 64) MHA_STAMP(48 + 2 * j);
 #endif
@@ -277,14 +300,14 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
         for (int i = 0; i < 32; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], i < n_valid ? v[i] : -INFINITY);
       }
       float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * kLog2e;
-      s_mx[j & 1][half][row_in_tile] = mx;
+      s_mx[g & 1][half][row_in_tile] = mx;
       pair_sync();
-      mx = fmaxf(mx, s_mx[j & 1][half ^ 1][row_in_tile]);         // finite: key 0 of every tile exists
+      mx = fmaxf(mx, s_mx[g & 1][half ^ 1][row_in_tile]);         // finite: key 0 of every tile exists
       if (j == 0) {
         m_ref = mx;
       } else if (__any_sync(0xffffffffu, mx > m_ref + kLazy)) {   // same rows, same verdict in both warps of the pair
         // O *= 2^(m_old - m_new) on this half's 32 columns; P(j-1).V must have landed before O is touched
-        mbar_wait(bar_pv, (j - 1) & 1);
+        mbar_wait(bar_pv, (g - 1) & 1);
         tc_fence_after();
         const float m_new = fmaxf(m_ref, mx);
         const float alpha = ex2_approx(m_ref - m_new);
@@ -318,7 +341,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bar_p[j & 1]);
+      if (lane == 0) mbar_arrive(&bar_p[g & 1]);
 #ifdef EDA_MHA_TRACE
       if (threadIdx.x == 64) MHA_STAMP(49 + 2 * j);
 #endif
@@ -327,7 +350,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
     s_l[half][row_in_tile] = l_sum;
     pair_sync();
     l_sum += s_l[half ^ 1][row_in_tile];
-    mbar_wait(bar_o, 0);
+    mbar_wait(bar_o, it & 1);
 #ifdef EDA_MHA_TRACE
     if (threadIdx.x == 64) MHA_STAMP(80);
 #endif
@@ -338,6 +361,9 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
     {
       float o[32];
       tmem_ld32(tO, o);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(o_free);          // the next item's first P.V may overwrite O
       if (q < p.T) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) o[i] *= inv;
@@ -380,6 +406,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
         }
       }
     }
+    }   // items
     tc_fence_before();
   }
   __syncthreads();
@@ -388,7 +415,10 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
     tmem_dealloc(tmem_base, A_TMEM_COLS);
   }
 #ifdef EDA_MHA_TRACE
-  if (threadIdx.x == 0) MHA_STAMP(2);
+  if (threadIdx.x == 0) {
+    g_mha_trace[(size_t)blockIdx.x * 96 + 2] = clock64();
+    g_mha_trace[(size_t)blockIdx.x * 96 + 3] = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  }
 #endif
 }
 
@@ -401,7 +431,6 @@ int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi
   EDA_REQUIRE(out || (out_hi && out_lo), "eda_mha_split: no output requested");
   EDA_REQUIRE(!out || (ld_out % 2 == 0 && (uintptr_t)out % 8 == 0), "eda_mha_split: fp32 output misaligned");
   EDA_REQUIRE(!out_hi || (ld_os % 2 == 0), "eda_mha_split: split output stride must be even");
-  EDA_REQUIRE(B <= 65535 && H <= 65535, "eda_mha_split: B / n_heads too large for the grid");
   EDA_REQUIRE(prec == EDA_PREC_BF16X3 || prec == EDA_PREC_BF16, "eda_mha_split: precision must be BF16X3 or BF16");
   static bool attr = false;
   if (!attr) {
@@ -418,9 +447,11 @@ int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi
   if ((rc = make_tmap_bf16_3d(&tv_hi, vt_hi, T, ADH, (uint64_t)B * H, (uint64_t)Tp * 2, (uint64_t)Tp * 2 * ADH, 64)) != EDA_OK) return rc;
   if ((rc = make_tmap_bf16_3d(&tv_lo, vt_lo, T, ADH, (uint64_t)B * H, (uint64_t)Tp * 2, (uint64_t)Tp * 2 * ADH, 64)) != EDA_OK) return rc;
   MhaParams p = {};
-  p.T = T; p.H = H; p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
+  p.T = T; p.H = H; p.B = B; p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
   p.out = out; p.ld_out = ld_out; p.out_hi = (bf16*)out_hi; p.out_lo = (bf16*)out_lo; p.ld_os = ld_os;
-  dim3 grid(ceil_div(T, ABM), H, B);
+  const int64_t n_items = (int64_t)ceil_div(T, ABM) * H * B;
+  EDA_REQUIRE(n_items < (int64_t(1) << 31), "eda_mha_split: too many (batch, head, query tile) items");
+  const int grid = (int)std::min<int64_t>(n_items, (int64_t)A_CTAS_PER_SM * num_sms());
   mha_tc_kernel<<<grid, A_THREADS, A_SMEM, st>>>(tq_hi, tq_lo, tk_hi, tk_lo, tv_hi, tv_lo, p);
   EDA_LAUNCH_CHECK();
   return EDA_OK;

@@ -240,3 +240,54 @@ class OracleEda:
         return loss, stats
 
     __call__ = forward
+
+
+# ---------------------------------------------------------------- training step
+def forward_backward(state_dict: Dict[str, Tensor], src: Sequence[Tensor], ts: Sequence[Tensor],
+                     n_heads: int = 4, diar_weight: float = 1.0, attractor_weight: float = 1.0,
+                     library_lstm: bool = True):
+    """R/models.py:236-263 followed by ``loss.backward()`` (R/train_eda.py:182-190), dropout-free.
+
+    Returns (loss, {state_dict key: gradient}).  The random frame shuffle is drawn from the global
+    generator exactly like ``forward``; the PIT permutation is chosen without gradient
+    (R/models.py:401-403 picks ``min`` over the per-permutation losses, so only the winning
+    permutation carries gradient)."""
+    sd = {k: v.detach().float().cpu().clone().requires_grad_(True) for k, v in state_dict.items()}
+    padded, lens = pad_batch(src, -1.0)
+    with torch.enable_grad():
+        emb = encode(padded, sd, n_heads)
+        perms = draw_shuffle(lens)
+        label, _ = pad_batch(ts, -1.0)
+        S = label.shape[2]
+        att, probs = eda(emb, lens, perms, S + 1, sd, library_lstm)
+        pred = emb @ att[:, :-1].transpose(1, 2)
+        l_att = attractor_loss(probs, S)
+        l_pit, idx, _, lab = pit_loss(pred, label, lens)
+        loss = diar_weight * l_pit + attractor_weight * l_att
+        loss.backward()
+    grads = {k: (v.grad if v.grad is not None else torch.zeros_like(v)).detach() for k, v in sd.items()}
+    return loss.detach(), grads, dict(emb=emb.detach(), pred=pred.detach(), min_idx=idx, label_permute=lab,
+                                      attractors=att.detach(), probs=probs.detach())
+
+
+def noam_lr(step: int, d_model: int, warmup: int, factor: float = 1.0) -> float:
+    """R/lr_scheduler.py:6-33 (NoamScheduler): factor * d_model^-0.5 * min(step^-0.5, step * warmup^-1.5)."""
+    step = max(step, 1)
+    return factor * d_model ** (-0.5) * min(step ** (-0.5), step * warmup ** (-1.5))
+
+
+def adam_step(params: Dict[str, Tensor], grads: Dict[str, Tensor], state: Dict[str, Tensor], step: int,
+              lr: float, betas=(0.9, 0.98), eps: float = 1e-9):
+    """torch.optim.Adam as R/train_eda.py:131 configures it for 'noam' (betas (0.9, 0.98), eps 1e-9),
+    restated; ``step`` counts from 1.  (The reference's clip_grad_value_ at R/train_eda.py:194-199
+    runs AFTER optimizer.zero_grad(), i.e. on empty gradients: it never changes an update.)"""
+    b1, b2 = betas
+    for k, p in params.items():
+        g = grads[k]
+        m = state.setdefault("m." + k, torch.zeros_like(p))
+        v = state.setdefault("v." + k, torch.zeros_like(p))
+        m.mul_(b1).add_(g, alpha=1 - b1)
+        v.mul_(b2).addcmul_(g, g, value=1 - b2)
+        denom = (v.sqrt() / (1 - b2 ** step) ** 0.5).add_(eps)
+        p.addcdiv_(m, denom, value=-lr / (1 - b1 ** step))
+    return params

@@ -87,7 +87,10 @@ enum {
   EDA_EPI_BIAS = 0,        /* C = A.W^T + bias                                   */
   EDA_EPI_BIAS_RELU = 1,   /* C = relu(A.W^T + bias)          (linear1, models.py:193) */
   EDA_EPI_BIAS_LN = 2,     /* C = LN(A.W^T + bias)            (encoder+encoder_norm, models.py:220-221) */
-  EDA_EPI_BIAS_RES_LN = 3  /* C = LN(resid + A.W^T + bias)    (post-LN residual blocks) */
+  EDA_EPI_BIAS_RES_LN = 3, /* C = LN(resid + A.W^T + bias)    (post-LN residual blocks) */
+  /* 4 is internal (the QKV scatter of eda_gemm_qkv) */
+  EDA_EPI_BIAS_RES = 5,    /* C = resid + A.W^T + bias        (backward: gradient joins of the residual stream) */
+  EDA_EPI_RELU_MASK = 6    /* C = (A.W^T) where mask > 0 else 0   (backward of linear1's ReLU)   */
 };
 enum { EDA_PREC_FP32 = 0, EDA_PREC_BF16X3 = 1, EDA_PREC_BF16 = 2 };
 
@@ -227,6 +230,101 @@ int eda_frame_labels(const double* seg_st, const double* seg_et, const int32_t* 
 int eda_rttm_segments(const float* post, const uint8_t* labels, int ld, const int64_t* rec_off,
                       int n_rec, const int32_t* n_spk_rec, int n_spk, float threshold, int median,
                       int cap, int32_t* segments, int32_t* counts, void* stream);
+
+/* ============================================================== training step ==========
+ * Backward pass + optimiser of the reference's training loop (train_eda.py:182-192:
+ * loss, stats = model(y, t); loss.backward(); optimizer.step(); scheduler.step()), SURVEY 8f n1.
+ * Forward entry points with a "_train" suffix are the inference ones plus the few saved
+ * quantities the backward kernels need.  Gradient GEMMs run on the same tcgen05 kernel as the
+ * forward (prec = EDA_PREC_BF16X3 or EDA_PREC_BF16).                                         */
+
+/* eda_gemm_split with a LayerNorm epilogue that also stores rstd (M) = 1/sqrt(var + eps) per row. */
+int eda_gemm_split_train(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
+                         const float* bias, const float* resid, int ldr, const float* ln_gamma, const float* ln_beta,
+                         float* C, int ldc, void* c_hi, void* c_lo, int ldcs, float* rstd_out, int M, int N, int K,
+                         int epilogue, int prec, void* stream);
+
+/* Input gradient of nn.Linear: dX (M, K_in) = dY (M, N_out) . W, with W handed over TRANSPOSED
+ * (wt = W^T, (K_in, N_out) row-major split pair, so the contraction index is contiguous).
+ * Optional fusions: + resid (fp32 (M, K_in): the other branch of a residual join; K_in == 256)
+ * or zeroing where relu_mask_hi (bf16 (M, K_in), the forward activation) is <= 0.
+ * Outputs: fp32 dX and/or split dx_hi/dx_lo.                                                   */
+int eda_gemm_dgrad(const void* dy_hi, const void* dy_lo, int ld_dy, const void* wt_hi, const void* wt_lo, int ldw,
+                   const float* resid, int ldr, const void* relu_mask_hi, int ldm, float* dX, int ldx,
+                   void* dx_hi, void* dx_lo, int ldxs, int M, int K_in, int N_out, int prec, void* stream);
+
+/* Weight gradient of nn.Linear: dW (N_out, K_in) (+)= dY^T (N_out, M) . X (M, K_in).  Both operands
+ * are read as they lie in HBM (row = sample) through MN-major shared-memory descriptors; the
+ * reduction over M is cut into slices whose partial results live in `workspace`
+ * (>= N_out * round_up(K_in, 4) * 4 bytes; more lets more CTA pairs work) and are added in
+ * slice order.                                                                                 */
+int eda_gemm_wgrad(const void* dy_hi, const void* dy_lo, int ld_dy, const void* x_hi, const void* x_lo, int ld_x,
+                   int M, int N_out, int K_in, float* dW, int ld_dw, void* workspace, int64_t workspace_bytes,
+                   int accumulate, int prec, void* stream);
+
+/* nn.LayerNorm(256) backward from the forward OUTPUT y (xhat = (y - beta) / gamma; gamma != 0)
+ * and the saved rstd: dx fp32 and/or split; dgamma, dbeta and (optional) the column sums of dx
+ * (= bias gradient of the Linear feeding the norm).  workspace >= 592 * 3 KB.                   */
+int eda_ln_bwd(const float* dy, int ld_dy, const float* y, int ld_y, const float* gamma, const float* beta,
+               const float* rstd, int M, int D, float* dx, int ld_dx, void* dx_hi, void* dx_lo, int ld_dxs,
+               float* dgamma, float* dbeta, float* dcolsum, void* workspace, int64_t workspace_bytes, int accumulate,
+               void* stream);
+
+/* out (N) (+)= column sums of a split matrix (M, N): bias gradients.  workspace >= 296 * N * 4 B. */
+int eda_colsum_split(const void* hi, const void* lo, int M, int N, int ld, float* out, void* workspace,
+                     int64_t workspace_bytes, int accumulate, void* stream);
+
+/* eda_mha_split that also stores lse (B*n_heads, T): log2-domain log-sum-exp of every score row. */
+int eda_mha_split_train(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
+                        int Tp, int B, int T, int n_heads, void* out_hi, void* out_lo, int ld_os, float* lse,
+                        int prec, void* stream);
+/* delta (B*T, 4) = rowsum over each head's 64 columns of dO * O (both split pairs, D == 256). */
+int eda_mha_delta(const void* do_hi, const void* do_lo, int ld_do, const void* o_hi, const void* o_lo, int ld_o,
+                  int M, int D, float* delta, void* stream);
+/* Attention backward on the layouts eda_gemm_qkv wrote.  dk, dv are written as split pairs into
+ * columns [D, 2D) and [2D, 3D) of dqkv (B*T, ld_dqkv); dq' (w.r.t. the pre-scaled q) is
+ * accumulated in dq_acc (B*T, D) fp32 (zeroed by the call) - follow with
+ * eda_scale_split(dq_acc, 1/8) into columns [0, D) of dqkv.                                      */
+int eda_mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
+                const void* do_hi, const void* do_lo, int ld_do, const float* lse, const float* delta, int B,
+                int T, int n_heads, float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, int prec,
+                void* stream);
+/* (hi, lo) = split(src * scale): fp32 (rows, cols) -> split pair with row stride ld_s.           */
+int eda_scale_split(const float* src, int ld, int rows, int cols, float scale, void* hi, void* lo, int ld_s, void* stream);
+
+/* eda_lstm_attractors that keeps, per step, the activated gates and cell state and (split bf16)
+ * the hidden state BEFORE the step: encoder gates/c rows are b*Tmax + step, hprev rows are
+ * b*Tmax + perm[step] (frame order); decoder rows are b*n_dec + step.  hc_out is required.      */
+int eda_lstm_attractors_train(const float* xproj, const int32_t* perm, const int32_t* lens, const int32_t* order,
+                              const float* w_hh_enc, const float* w_hh_dec, const float* dec_bias, int B, int Tmax,
+                              int D, int n_dec, float* attractors, float* hc_out, float* gates, float* c,
+                              void* hprev_hi, void* hprev_lo, float* dec_gates, float* dec_c, void* dec_hprev_hi,
+                              void* dec_hprev_lo, void* stream);
+/* BPTT through decoder and encoder from dattractors (B, n_dec, D).  Writes the gradient w.r.t.
+ * the gate pre-activations as split pairs: dxproj (B*Tmax, 4D) in FRAME order (rows of padded
+ * frames are zero), ddec (B*n_dec, 4D).  The caller turns them into weight / input gradients
+ * with eda_gemm_wgrad / eda_gemm_dgrad / eda_colsum_split.                                       */
+int eda_lstm_attractors_bwd(const int32_t* perm, const int32_t* lens, const int32_t* order,
+                            const float* w_hh_enc, const float* w_hh_dec, const float* gates, const float* c,
+                            const float* dec_gates, const float* dec_c, const float* hc, const float* dattractors,
+                            int B, int Tmax, int D, int n_dec, void* dxproj_hi, void* dxproj_lo,
+                            void* ddec_hi, void* ddec_lo, void* stream);
+
+/* Backward of eda_posterior's logits: demb (B*Tmax, ld_demb) written; dattractors
+ * (B, att_stride_rows, D) accumulated with atomics (zero or pre-fill it first).  n_att <= 8.     */
+int eda_posterior_bwd(const float* dpred, const float* emb, int ld_emb, const float* attractors, int att_stride_rows,
+                      int B, int Tmax, int D, int n_att, float* demb, int ld_demb, float* dattractors, void* stream);
+/* Backward of eda_attractor_head + the attractor loss scaled by `scale`: dattractors += ...,
+ * dw (D) and dbias (1) written (or accumulated).                                                 */
+int eda_attractor_head_bwd(const float* attractors, const float* probs, const float* w, int B, int n_dec, int D,
+                           int n_spk_label, float scale, float* dattractors, float* dw, float* dbias, int accumulate,
+                           void* stream);
+
+/* x *= *scale_dev (the upstream gradient of the loss, kept on the device).                       */
+int eda_scale_dev(const float* scale_dev, float* x, int64_t n, void* stream);
+/* torch.optim.Adam (train_eda.py:131) on flat buffers; `step` counts from 1.                     */
+int eda_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                  float beta1, float beta2, float eps, int step, void* stream);
 
 #ifdef __cplusplus
 }

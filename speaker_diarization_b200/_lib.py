@@ -15,6 +15,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libeda_b200.so")
 
 EPI_BIAS, EPI_BIAS_RELU, EPI_BIAS_LN, EPI_BIAS_RES_LN = 0, 1, 2, 3
+EPI_BIAS_RES, EPI_RELU_MASK = 5, 6
 PREC_FP32, PREC_BF16X3, PREC_BF16 = 0, 1, 2
 PRECISIONS = {"fp32": PREC_FP32, "bf16x3": PREC_BF16X3, "bf16": PREC_BF16}
 
@@ -47,6 +48,22 @@ SIGNATURES = {
     "eda_der_counters": (_i, [_p, _p, _p, _i, _i, _i, _p, _p]),
     "eda_frame_labels": (_i, [_p, _p, _p, _p, _i64, _p, _p, _p, _p, _i, _i64, _i, C.c_double, _i, _i, _p, _i, _i, _p]),
     "eda_rttm_segments": (_i, [_p, _p, _i, _p, _i, _p, _i, _f, _i, _i, _p, _p, _p]),
+    # ---- training step
+    "eda_gemm_split_train": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p]),
+    "eda_gemm_dgrad": (_i, [_p, _p, _i, _p, _p, _i, _p, _i, _p, _i, _p, _i, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "eda_gemm_wgrad": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i64, _i, _i, _p]),
+    "eda_ln_bwd": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _i, _p, _i, _p, _p, _i, _p, _p, _p, _p, _i64, _i, _p]),
+    "eda_colsum_split": (_i, [_p, _p, _i, _i, _i, _p, _p, _i64, _i, _p]),
+    "eda_mha_split_train": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _p, _i, _p, _i, _p]),
+    "eda_mha_delta": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _p, _p]),
+    "eda_mha_bwd": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _i, _i, _i, _p, _p, _p, _i, _i, _p]),
+    "eda_scale_split": (_i, [_p, _i, _i, _i, _f, _p, _p, _i, _p]),
+    "eda_lstm_attractors_train": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "eda_lstm_attractors_bwd": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p]),
+    "eda_posterior_bwd": (_i, [_p, _p, _i, _p, _i, _i, _i, _i, _i, _p, _i, _p, _p]),
+    "eda_attractor_head_bwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _i, _p]),
+    "eda_scale_dev": (_i, [_p, _p, _i64, _p]),
+    "eda_adam_step": (_i, [_p, _p, _p, _p, _i64, _f, _f, _f, _f, _i, _p]),
 }
 
 _lib = None

@@ -49,7 +49,7 @@ constexpr int G_OPERAND_BYTES = G_STAGES_DIRECT * G_STAGE;    // == 2 stages + 8
 static_assert(G_STAGES_STAGED * G_STAGE + G_EPI_WARPS * G_STG_WARP == G_OPERAND_BYTES, "smem plans differ in size");
 constexpr int G_SMEM = G_OPERAND_BYTES + G_LNX_BYTES + G_VEC_BYTES + 256 + 1024;
 
-enum { GEPI_QKV = 4 };
+enum { GEPI_QKV = 4 };     // (EDA_EPI_BIAS_RES = 5 and EDA_EPI_RELU_MASK = 6 are public, eda_b200.h)
 
 struct GemmParams {
   const float* bias;
@@ -60,6 +60,11 @@ struct GemmParams {
   int M, N, Kp, passes;
   // QKV variant: rows are (b, t) with t < T; v goes to vt[(b*H + h)*64 + d][t], row stride Tp
   bf16* vt_hi; bf16* vt_lo; int T, Tp, H; float q_scale;
+  float* rstd_out;                         // LayerNorm epilogues (training): 1/sqrt(var + eps) per row, optional
+  const bf16* mask; int ldm;               // EDA_EPI_RELU_MASK: result is zeroed where mask <= 0
+  // weight-gradient form (WG): C[i,j] = sum_r A[r,i] B[r,j] over Kp rows, both operands MN-major;
+  // the reduction is cut into `ksplit` slices whose fp32 partial results are `c_slice` elements apart
+  int ksplit; long long c_slice;
 };
 
 __device__ __forceinline__ void split2(float x0, float x1, __nv_bfloat162& hi, __nv_bfloat162& lo) {
@@ -102,7 +107,7 @@ __global__ void split_bf16_kernel(const float* __restrict__ src, int ld, int row
   }
 }
 
-template <int EPI, bool ST>
+template <int EPI, bool ST, bool WG>
 __global__ void __launch_bounds__(G_THREADS, 1)
 gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                   const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
@@ -127,8 +132,10 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
   const uint32_t rank = cluster_ctarank();                     // 0 = leader (issues the MMAs of the pair)
   const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const int n_tiles_n = (p.N + GBN - 1) / GBN, n_tiles_m = (p.M + 2 * GBM - 1) / (2 * GBM);
-  const int n_tiles = n_tiles_n * n_tiles_m;                   // 256 x 256 output tiles, one per CTA pair
-  const int nkb = (p.Kp + GBK - 1) / GBK;
+  const int n_mn = n_tiles_n * n_tiles_m;                      // 256 x 256 output tiles, one per CTA pair
+  const int nkb_all = (p.Kp + GBK - 1) / GBK;
+  const int nkb_slice = WG ? (nkb_all + p.ksplit - 1) / p.ksplit : nkb_all;
+  const int n_tiles = WG ? n_mn * p.ksplit : n_mn;             // (WG: every reduction slice of a tile is a work item)
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA_hi); tma_prefetch_desc(&tmA_lo); tma_prefetch_desc(&tmB_hi); tma_prefetch_desc(&tmB_lo);
@@ -159,18 +166,34 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
       const uint32_t full_leader0 = map_to_rank(&full[0], 0);     // barriers are contiguous 8-byte objects
       uint32_t it = 0;
       for (int tile = pair; tile < n_tiles; tile += n_pairs) {
-        const int m0 = (tile / n_tiles_n) * 2 * GBM + (int)rank * GBM;
-        const int n0 = (tile % n_tiles_n) * GBN + (int)rank * (GBN / 2);
-        for (int kb = 0; kb < nkb; ++kb, ++it) {
+        const int mn = WG ? tile % n_mn : tile, ks = WG ? tile / n_mn : 0;
+        const int m0 = (mn / n_tiles_n) * 2 * GBM + (int)rank * GBM;
+        const int n0 = (mn % n_tiles_n) * GBN + (int)rank * (GBN / 2);
+        const int kb0 = ks * nkb_slice, kb1 = min(nkb_all, kb0 + nkb_slice);
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
           const int s = it % GSTAGES;
           mbar_wait(&empty[s], ((it / GSTAGES) & 1) ^ 1);      // the pair's MMAs have read this stage (multicast commit)
           uint8_t* st = smem + s * G_STAGE;
           if (rank == 0) mbar_expect_tx(&full[s], pair_tx);
-          tma_load_2d_pair(st, &tmA_hi, (full_leader0 + 8 * s), kb * GBK, m0);
-          tma_load_2d_pair(st + 2 * G_A_TILE, &tmB_hi, (full_leader0 + 8 * s), kb * GBK, n0);
-          if (p.passes == 3) {
-            tma_load_2d_pair(st + G_A_TILE, &tmA_lo, (full_leader0 + 8 * s), kb * GBK, m0);
-            tma_load_2d_pair(st + 2 * G_A_TILE + G_B_TILE, &tmB_lo, (full_leader0 + 8 * s), kb * GBK, n0);
+          const uint32_t fb = full_leader0 + 8 * s;
+          if constexpr (WG) {
+            // MN-major operands: a tile is two boxes of 64 (output index, contiguous in HBM) x 64 reduction rows
+#pragma unroll
+            for (int blk = 0; blk < 2; ++blk) {
+              tma_load_2d_pair(st + blk * 8192, &tmA_hi, fb, m0 + blk * 64, kb * GBK);
+              tma_load_2d_pair(st + 2 * G_A_TILE + blk * 8192, &tmB_hi, fb, n0 + blk * 64, kb * GBK);
+              if (p.passes == 3) {
+                tma_load_2d_pair(st + G_A_TILE + blk * 8192, &tmA_lo, fb, m0 + blk * 64, kb * GBK);
+                tma_load_2d_pair(st + 2 * G_A_TILE + G_B_TILE + blk * 8192, &tmB_lo, fb, n0 + blk * 64, kb * GBK);
+              }
+            }
+          } else {
+            tma_load_2d_pair(st, &tmA_hi, fb, kb * GBK, m0);
+            tma_load_2d_pair(st + 2 * G_A_TILE, &tmB_hi, fb, kb * GBK, n0);
+            if (p.passes == 3) {
+              tma_load_2d_pair(st + G_A_TILE, &tmA_lo, fb, kb * GBK, m0);
+              tma_load_2d_pair(st + 2 * G_A_TILE + G_B_TILE, &tmB_lo, fb, kb * GBK, n0);
+            }
           }
         }
       }
@@ -180,24 +203,29 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
     // (elect.sync, not lane == 0: ptxas then issues the uniform-datapath MMAs back to back
     // instead of wrapping each one in an active-lane loop)
     if (rank == 0 && elect_one()) {
-      const uint32_t idesc = idesc_bf16_f32(2 * GBM, GBN);
+      const uint32_t idesc = idesc_bf16_f32(2 * GBM, GBN) | (WG ? ((1u << 15) | (1u << 16)) : 0u);   // WG: A and B MN-major
       uint32_t it = 0, lt = 0;
       for (int tile = pair; tile < n_tiles; tile += n_pairs, ++lt) {
         const uint32_t ab = lt & 1;
         mbar_wait(&tempty[ab], ((lt >> 1) & 1) ^ 1);       // both CTAs' epilogues have drained this accumulator
         tc_fence_after();
         const uint32_t acc = tmem_base + ab * GBN;
-        for (int kb = 0; kb < nkb; ++kb, ++it) {
+        const int ks = WG ? tile / n_mn : 0;
+        const int kb0 = ks * nkb_slice, kb1 = min(nkb_all, kb0 + nkb_slice);
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
           const int s = it % GSTAGES;
           mbar_wait(&full[s], (it / GSTAGES) & 1);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + s * G_STAGE);
-          const uint64_t a_hi = smem_desc_sw128(sa), a_lo = smem_desc_sw128(sa + G_A_TILE);
-          const uint64_t b_hi = smem_desc_sw128(sa + 2 * G_A_TILE), b_lo = smem_desc_sw128(sa + 2 * G_A_TILE + G_B_TILE);
+          const uint64_t a_hi = WG ? smem_desc_sw128_mn(sa) : smem_desc_sw128(sa);
+          const uint64_t a_lo = WG ? smem_desc_sw128_mn(sa + G_A_TILE) : smem_desc_sw128(sa + G_A_TILE);
+          const uint64_t b_hi = WG ? smem_desc_sw128_mn(sa + 2 * G_A_TILE) : smem_desc_sw128(sa + 2 * G_A_TILE);
+          const uint64_t b_lo = WG ? smem_desc_sw128_mn(sa + 2 * G_A_TILE + G_B_TILE) : smem_desc_sw128(sa + 2 * G_A_TILE + G_B_TILE);
 #pragma unroll
           for (int k = 0; k < GBK / 16; ++k) {
-            const uint64_t adv = uint64_t(k * 32 >> 4);          // +32 B per 16-element k-step
-            umma_bf16_pair(acc, a_hi + adv, b_hi + adv, idesc, (kb | k) != 0);
+            // K-major: +32 B per 16-element k-step; MN-major: 16 reduction rows of 128 B = +2048 B
+            const uint64_t adv = uint64_t((WG ? k * 2048 : k * 32) >> 4);
+            umma_bf16_pair(acc, a_hi + adv, b_hi + adv, idesc, ((kb - kb0) | k) != 0);
             if (p.passes == 3) {
               umma_bf16_pair(acc, a_hi + adv, b_lo + adv, idesc, 1);
               umma_bf16_pair(acc, a_lo + adv, b_hi + adv, idesc, 1);
@@ -218,7 +246,9 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
     uint32_t n_stores = 0;
     const uint32_t tempty_leader0 = map_to_rank(&tempty[0], 0);
     for (int tile = pair; tile < n_tiles; tile += n_pairs, ++lt) {
-      const int m0 = (tile / n_tiles_n) * 2 * GBM + (int)rank * GBM, n_blk = tile % n_tiles_n, n0 = n_blk * GBN;
+      const int mn = WG ? tile % n_mn : tile;
+      const int m0 = (mn / n_tiles_n) * 2 * GBM + (int)rank * GBM, n_blk = mn % n_tiles_n, n0 = n_blk * GBN;
+      float* const Cout = WG ? p.C + (size_t)(tile / n_mn) * p.c_slice : p.C;
       const uint32_t ab = lt & 1;
       const int rbase = m0 + q * 32;                              // first global row of this warp
       // residual chunk c of this thread's row (RES_LN): 8 x 16 B, thread-per-row
@@ -237,7 +267,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         }
       };
       float4 rp[8];
-      if constexpr (EPI == EDA_EPI_BIAS_RES_LN) load_resid(0, rp);   // in flight while the MMAs finish
+      if constexpr (EPI == EDA_EPI_BIAS_RES_LN || EPI == EDA_EPI_BIAS_RES) load_resid(0, rp);   // in flight while the MMAs finish
       mbar_wait(&tfull[ab], (lt >> 1) & 1);
       tc_fence_after();
       const uint32_t trow = tmem_base + ab * GBN + ch * 128 + (uint32_t(q * 32) << 16);
@@ -249,7 +279,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         if (grow >= p.M || gcol0 >= p.N) return;
         const bool whole = gcol0 + 32 <= p.N;
         if (p.C && EPI != GEPI_QKV) {
-          float* dst = p.C + (size_t)grow * p.ldc + gcol0;
+          float* dst = Cout + (size_t)grow * p.ldc + gcol0;
           if (whole && ((uintptr_t)dst & 31) == 0) {
 #pragma unroll
             for (int j = 0; j < 4; ++j)
@@ -356,7 +386,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         }
       };
 
-      if constexpr (EPI == EDA_EPI_BIAS || EPI == EDA_EPI_BIAS_RELU) {
+      if constexpr (EPI == EDA_EPI_BIAS || EPI == EDA_EPI_BIAS_RELU || EPI == EDA_EPI_RELU_MASK) {
 #pragma unroll 1
         for (int cp = 0; cp < 2; ++cp) {                       // pairs of 32-column chunks
           if (n0 + ch * 128 + cp * 64 >= p.N) break;
@@ -370,6 +400,24 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
             if (EPI == EDA_EPI_BIAS_RELU) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+            }
+            if constexpr (EPI == EDA_EPI_RELU_MASK) {
+              // ReLU backward: keep the gradient where the forward activation (its bf16 hi part) was > 0
+              const int row = rbase + lane;
+              if (row < p.M && col0 + 32 <= p.N) {
+                const uint4* mp = reinterpret_cast<const uint4*>(p.mask + (size_t)row * p.ldm + col0);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  const uint4 mv = __ldg(mp + u);
+                  const uint32_t w[4] = {mv.x, mv.y, mv.z, mv.w};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    // positive bf16: sign bit clear and magnitude non-zero
+                    if (!((w[e] & 0x7fffu) != 0 && !(w[e] & 0x8000u))) v[8 * u + 2 * e] = 0.f;
+                    if (!((w[e] & 0x7fff0000u) != 0 && !(w[e] & 0x80000000u))) v[8 * u + 2 * e + 1] = 0.f;
+                  }
+                }
+              }
             }
             emit_chunk(v, col0, half, hi, lo, p.Chi, p.Clo, p.lds);
           }
@@ -410,13 +458,16 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         // with a 64-thread named barrier per lane quadrant.  Two-pass variance like ATen.
         // The residual is read thread-per-row (each 32 B sector is consumed by two back-to-back
         // loads) and prefetched one 32-column chunk ahead so DRAM latency is off the critical path.
+        constexpr bool kLN = EPI != EDA_EPI_BIAS_RES;       // BIAS_RES: residual add only, rows leave after one pass
+        constexpr bool kRes = EPI == EDA_EPI_BIAS_RES_LN || EPI == EDA_EPI_BIAS_RES;
         float sum = 0.f;
+        uint32_t rhi[32], rlo[32];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           const int col0 = ch * 128 + c * 32;
           float v[32];
           tmem_ld32(trow + c * 32, v);
-          if constexpr (EPI == EDA_EPI_BIAS_RES_LN) {
+          if constexpr (kRes) {
             float4 rn[8];
             if (c < 3) load_resid(c + 1, rn);
 #pragma unroll
@@ -429,10 +480,15 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
             }
           }
           add_vec(v, p.bias, col0);
+          if constexpr (!kLN) {
+            emit_chunk(v, col0, c & 1, rhi, rlo, p.Chi, p.Clo, p.lds);
+          } else {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) sum += v[j];
-          tmem_st32(trow + c * 32, v);
+            for (int j = 0; j < 32; ++j) sum += v[j];
+            tmem_st32(trow + c * 32, v);
+          }
         }
+        if constexpr (kLN) {
         tmem_wait_st();
         const int xr = q * 32 + lane;
         ln_x[0][ch][xr] = sum;
@@ -449,6 +505,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         ln_x[1][ch][xr] = sq;
         asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
         const float rstd = 1.0f / sqrtf((ln_x[1][0][xr] + ln_x[1][1][xr]) * (1.0f / GBN) + 1e-5f);
+        if (p.rstd_out && ch == 0 && rbase + lane < p.M) p.rstd_out[rbase + lane] = rstd;
 #pragma unroll 1
         for (int cp = 0; cp < 2; ++cp) {
           uint32_t hi[32], lo[32];
@@ -471,6 +528,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         }
         // (ln_x reuse is safe: a warp rewrites ln_x[k] only after the partner has passed the
         //  barrier that follows its read of ln_x[k])
+        }   // kLN
       }
       {
 
@@ -578,16 +636,16 @@ int split_bf16(const float* src, int ld, int rows, int K, void* hi, void* lo, in
   return EDA_OK;
 }
 
-template <int EPI, bool ST>
+template <int EPI, bool ST, bool WG = false>
 static int launch_gemm2(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi, const CUtensorMap& b_lo,
                         const CUtensorMap& c, const CUtensorMap& c_hi, const CUtensorMap& c_lo, const GemmParams& p,
                         cudaStream_t st) {
   static bool attr = false;
   if (!attr) {
-    EDA_CUDA(cudaFuncSetAttribute(gemm_split_kernel<EPI, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
+    EDA_CUDA(cudaFuncSetAttribute(gemm_split_kernel<EPI, ST, WG>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
     attr = true;
   }
-  const int n_tiles = ceil_div(p.N, GBN) * ceil_div(p.M, 2 * GBM);      // one 256 x 256 tile per CTA pair
+  const int n_tiles = ceil_div(p.N, GBN) * ceil_div(p.M, 2 * GBM) * (WG ? p.ksplit : 1);   // one 256 x 256 tile per CTA pair
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attrs[1];
   cfg.gridDim = dim3(2 * std::min(n_tiles, num_sms() / 2));
@@ -597,7 +655,7 @@ static int launch_gemm2(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const 
   attrs[0].id = cudaLaunchAttributeClusterDimension;
   attrs[0].val.clusterDim.x = 2; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
   cfg.attrs = attrs; cfg.numAttrs = 1;
-  EDA_CUDA(cudaLaunchKernelEx(&cfg, gemm_split_kernel<EPI, ST>, a_hi, a_lo, b_hi, b_lo, c, c_hi, c_lo, p));
+  EDA_CUDA(cudaLaunchKernelEx(&cfg, gemm_split_kernel<EPI, ST, WG>, a_hi, a_lo, b_hi, b_lo, c, c_hi, c_lo, p));
   count_launch();
   return EDA_OK;
 }
@@ -632,10 +690,11 @@ int gemm_split(const void* a_hi, const void* a_lo, int lda, const void* w_hi, co
   if (p.C) EDA_REQUIRE(p.ldc % 4 == 0 && (uintptr_t)p.C % 16 == 0, "eda_gemm_split: C must be 16B aligned with ldc %% 4 == 0");
   if (p.Chi) EDA_REQUIRE(p.Clo && p.lds % 4 == 0 && p.N % 4 == 0 && ((uintptr_t)p.Chi | (uintptr_t)p.Clo) % 8 == 0, "eda_gemm_split: split output needs N %% 4 == 0, lds %% 4 == 0, 8B alignment");
   const bool ln = epi == EDA_EPI_BIAS_LN || epi == EDA_EPI_BIAS_RES_LN;
-  if (ln) {
-    EDA_REQUIRE(p.N == 256 && p.gamma && p.beta && p.bias, "eda_gemm_split: LayerNorm epilogues need N == 256, bias, gamma, beta");
-    EDA_REQUIRE(epi != EDA_EPI_BIAS_RES_LN || (p.resid && p.ldr % 4 == 0 && (uintptr_t)p.resid % 16 == 0), "eda_gemm_split: residual missing/misaligned");
-  }
+  if (ln) EDA_REQUIRE(p.N == 256 && p.gamma && p.beta && p.bias, "eda_gemm_split: LayerNorm epilogues need N == 256, bias, gamma, beta");
+  if (epi == EDA_EPI_BIAS_RES_LN || epi == EDA_EPI_BIAS_RES)
+    EDA_REQUIRE(p.N == 256 && p.resid && p.ldr % 4 == 0 && (uintptr_t)p.resid % 16 == 0, "eda_gemm_split: residual epilogues need N == 256 and an aligned residual");
+  if (epi == EDA_EPI_RELU_MASK)
+    EDA_REQUIRE(p.mask && p.ldm % 8 == 0 && (uintptr_t)p.mask % 16 == 0 && p.N % 32 == 0, "eda_gemm_split: mask must be 16B aligned, ldm %% 8 == 0, N %% 32 == 0");
   p.Kp = K;
   p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
   CUtensorMap ta_hi, ta_lo, tb_hi, tb_lo;
@@ -650,9 +709,58 @@ int gemm_split(const void* a_hi, const void* a_lo, int lda, const void* w_hi, co
     case EDA_EPI_BIAS_LN: return launch_gemm<EDA_EPI_BIAS_LN>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
     case EDA_EPI_BIAS_RES_LN: return launch_gemm<EDA_EPI_BIAS_RES_LN>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
     case GEPI_QKV: return launch_gemm<GEPI_QKV>(ta_hi, ta_lo, tb_hi, tb_lo, p, 2 * GBN, st);
+    case EDA_EPI_BIAS_RES: return launch_gemm<EDA_EPI_BIAS_RES>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
+    case EDA_EPI_RELU_MASK: return launch_gemm<EDA_EPI_RELU_MASK>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
   }
   set_error("eda_gemm_split: unknown epilogue %d", epi);
   return EDA_EINVAL;
+}
+
+// ---- weight gradient: dW (N_out x K_in) = dY^T X, reduction over the M rows ------------------
+// out[i] = (accumulate ? out[i] : 0) + sum_s part[s][i] in slice order (deterministic)
+__global__ void splitk_reduce_kernel(const float* __restrict__ part, int ksplit, long long slice, int rows, int cols,
+                                     int ld_part, float* __restrict__ out, int ld_out, int accumulate) {
+  const long long n = (long long)rows * cols;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols), c = (int)(i % cols);
+    float acc = accumulate ? out[(size_t)r * ld_out + c] : 0.f;
+    for (int s = 0; s < ksplit; ++s) acc += part[(size_t)s * slice + (size_t)r * ld_part + c];
+    out[(size_t)r * ld_out + c] = acc;
+  }
+}
+
+int gemm_wgrad(const void* dy_hi, const void* dy_lo, int ld_dy, const void* x_hi, const void* x_lo, int ld_x,
+               int M, int N_out, int K_in, float* dW, int ld_dw, float* work, size_t work_bytes, int accumulate,
+               int prec, cudaStream_t st) {
+  EDA_REQUIRE(dy_hi && dy_lo && x_hi && x_lo && dW && work && M > 0 && N_out > 0 && K_in > 0, "eda_gemm_wgrad: bad arguments");
+  EDA_REQUIRE(ld_dy % 8 == 0 && ld_x % 8 == 0, "eda_gemm_wgrad: operand row strides must be multiples of 8 elements");
+  EDA_REQUIRE(((uintptr_t)dy_hi | (uintptr_t)dy_lo | (uintptr_t)x_hi | (uintptr_t)x_lo) % 16 == 0, "eda_gemm_wgrad: operands must be 16B aligned");
+  EDA_REQUIRE(prec == EDA_PREC_BF16X3 || prec == EDA_PREC_BF16, "eda_gemm_wgrad: precision must be BF16X3 or BF16");
+  const int ldp = (K_in + 3) / 4 * 4;
+  const int n_mn = ceil_div(K_in, GBN) * ceil_div(N_out, 2 * GBM);
+  const int nkb = ceil_div(M, GBK);
+  const size_t slice = (size_t)N_out * ldp;
+  int want = std::max(1, (num_sms() / 2) / n_mn);
+  want = (int)std::min<size_t>(want, work_bytes / (slice * sizeof(float)));
+  EDA_REQUIRE(want >= 1, "eda_gemm_wgrad: workspace smaller than one %d x %d fp32 slice", N_out, ldp);
+  const int nkb_slice = ceil_div(nkb, std::min(want, nkb));
+  GemmParams p = {};
+  p.C = work; p.ldc = ldp; p.M = N_out; p.N = K_in; p.Kp = M;
+  p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
+  p.ksplit = ceil_div(nkb, nkb_slice);              // every slice owns at least one k-block
+  p.c_slice = (long long)slice;
+  CUtensorMap ta_hi, ta_lo, tb_hi, tb_lo;
+  int rc;
+  if ((rc = make_tmap_bf16(&ta_hi, dy_hi, M, N_out, ld_dy, 64)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16(&ta_lo, dy_lo, M, N_out, ld_dy, 64)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16(&tb_hi, x_hi, M, K_in, ld_x, 64)) != EDA_OK) return rc;
+  if ((rc = make_tmap_bf16(&tb_lo, x_lo, M, K_in, ld_x, 64)) != EDA_OK) return rc;
+  if ((rc = launch_gemm2<EDA_EPI_BIAS, false, true>(ta_hi, ta_lo, tb_hi, tb_lo, ta_hi, ta_hi, ta_hi, p, st)) != EDA_OK) return rc;
+  const long long n = (long long)N_out * K_in;
+  splitk_reduce_kernel<<<(int)std::min<long long>(ceil_div<long long>(n, 256), num_sms() * 8), 256, 0, st>>>(
+      work, p.ksplit, (long long)slice, N_out, K_in, ldp, dW, ld_dw, accumulate);
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
 }
 
 // grow-only scratch for eda_linear's on-the-fly operand split (stream-ordered reuse)
@@ -703,6 +811,38 @@ int eda_gemm_split(const void* a_hi, const void* a_lo, int lda, const void* w_hi
   p.bias = bias; p.resid = resid; p.ldr = ldr; p.gamma = ln_gamma; p.beta = ln_beta;
   p.C = C; p.ldc = ldc; p.Chi = (eda::bf16*)c_hi; p.Clo = (eda::bf16*)c_lo; p.lds = ldcs; p.M = M; p.N = N;
   return eda::gemm_split(a_hi, a_lo, lda, w_hi, w_lo, ldw, p, K, epilogue, prec, (cudaStream_t)stream);
+}
+
+int eda_gemm_split_train(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
+                         const float* bias, const float* resid, int ldr, const float* ln_gamma, const float* ln_beta,
+                         float* C, int ldc, void* c_hi, void* c_lo, int ldcs, float* rstd_out, int M, int N, int K,
+                         int epilogue, int prec, void* stream) {
+  EDA_REQUIRE(epilogue == EDA_EPI_BIAS_LN || epilogue == EDA_EPI_BIAS_RES_LN, "eda_gemm_split_train: LayerNorm epilogues only");
+  EDA_REQUIRE(C || c_hi, "eda_gemm_split_train: no output requested");
+  eda::GemmParams p = {};
+  p.bias = bias; p.resid = resid; p.ldr = ldr; p.gamma = ln_gamma; p.beta = ln_beta;
+  p.C = C; p.ldc = ldc; p.Chi = (eda::bf16*)c_hi; p.Clo = (eda::bf16*)c_lo; p.lds = ldcs; p.M = M; p.N = N;
+  p.rstd_out = rstd_out;
+  return eda::gemm_split(a_hi, a_lo, lda, w_hi, w_lo, ldw, p, K, epilogue, prec, (cudaStream_t)stream);
+}
+
+int eda_gemm_dgrad(const void* dy_hi, const void* dy_lo, int ld_dy, const void* wt_hi, const void* wt_lo, int ldw,
+                   const float* resid, int ldr, const void* relu_mask_hi, int ldm, float* dX, int ldx,
+                   void* dx_hi, void* dx_lo, int ldxs, int M, int K_in, int N_out, int prec, void* stream) {
+  EDA_REQUIRE(dX || dx_hi, "eda_gemm_dgrad: no output requested");
+  EDA_REQUIRE(!(resid && relu_mask_hi), "eda_gemm_dgrad: residual and ReLU mask are mutually exclusive");
+  eda::GemmParams p = {};
+  p.resid = resid; p.ldr = ldr; p.mask = (const eda::bf16*)relu_mask_hi; p.ldm = ldm;
+  p.C = dX; p.ldc = ldx; p.Chi = (eda::bf16*)dx_hi; p.Clo = (eda::bf16*)dx_lo; p.lds = ldxs; p.M = M; p.N = K_in;
+  const int epi = resid ? EDA_EPI_BIAS_RES : relu_mask_hi ? EDA_EPI_RELU_MASK : EDA_EPI_BIAS;
+  return eda::gemm_split(dy_hi, dy_lo, ld_dy, wt_hi, wt_lo, ldw, p, N_out, epi, prec, (cudaStream_t)stream);
+}
+
+int eda_gemm_wgrad(const void* dy_hi, const void* dy_lo, int ld_dy, const void* x_hi, const void* x_lo, int ld_x,
+                   int M, int N_out, int K_in, float* dW, int ld_dw, void* workspace, int64_t workspace_bytes,
+                   int accumulate, int prec, void* stream) {
+  return eda::gemm_wgrad(dy_hi, dy_lo, ld_dy, x_hi, x_lo, ld_x, M, N_out, K_in, dW, ld_dw, (float*)workspace,
+                         (size_t)workspace_bytes, accumulate, prec, (cudaStream_t)stream);
 }
 
 int eda_gemm_qkv(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,

@@ -22,6 +22,8 @@
 
 #include <algorithm>
 
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace cg = cooperative_groups;
@@ -99,13 +101,28 @@ __device__ __forceinline__ void load_w(uint64_t (&w2)[4][16], const float* __res
   }
 }
 
+// What the training step keeps of the forward recurrence for its backward pass (all optional:
+// gates == nullptr means inference).  Encoder rows are indexed by STEP (b * Tmax + s) except hprev,
+// which sits at the frame's own row b * Tmax + perm[s] so that dW_hh = dxproj^T . hprev is one GEMM
+// with dxproj in frame order; decoder rows are b * n_dec + s.
+struct LstmSave {
+  float* gates;            // (B*Tmax, 4*D) activated i, f, g, o
+  float* c;                // (B*Tmax, D)   cell state after the step
+  __nv_bfloat16* hprev_hi; // (B*Tmax, D)   hidden state BEFORE the step, split bf16
+  __nv_bfloat16* hprev_lo;
+  float* dec_gates;        // (B*n_dec, 4*D)
+  float* dec_c;            // (B*n_dec, D)
+  __nv_bfloat16* dec_hprev_hi;  // (B*n_dec, D)
+  __nv_bfloat16* dec_hprev_lo;
+};
+
 template <int kG>
 __global__ void __launch_bounds__(256, 1)
 lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__ perm,
                     const int32_t* __restrict__ lens, const int32_t* __restrict__ order,
                     const float* __restrict__ w_enc, const float* __restrict__ w_dec,
                     const float* __restrict__ dec_bias, int B, int Tmax, int n_dec,
-                    float* __restrict__ attractors, float* __restrict__ hc_out) {
+                    float* __restrict__ attractors, float* __restrict__ hc_out, const LstmSave sv) {
   cg::cluster_group cluster = cg::this_cluster();
   const int cta = (int)cluster.block_rank();
   const int group = blockIdx.x / kCluster;
@@ -152,7 +169,7 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
   const int my_len = seq < kG ? s_len[seq] : 0;
   float c_state = 0.f, h_state = 0.f;
   float xg[4] = {0.f, 0.f, 0.f, 0.f};
-  int p_next = 0;
+  int p_next = 0, p_cur = 0;
   const size_t col = (size_t)cta * kUnits + u;
   auto load_x = [&](int p, float (&dst)[4]) {
     const float* row = xproj + ((size_t)my_b * Tmax + p) * (4 * kD) + col;
@@ -160,7 +177,8 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
     for (int x = 0; x < 4; ++x) dst[x] = __ldg(row + x * kD);
   };
   if (my_len > 0) {   // (my_b >= 0 whenever my_len > 0)
-    load_x(__ldg(perm + (size_t)my_b * Tmax), xg);
+    p_cur = __ldg(perm + (size_t)my_b * Tmax);
+    load_x(p_cur, xg);
     if (my_len > 1) p_next = __ldg(perm + (size_t)my_b * Tmax + 1);
   }
   // thread r < 8 pushes this CTA's slice to rank r: remote slice / barrier addresses per buffer
@@ -272,8 +290,18 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
     if (active) {
       const float ig = fast_sigmoid(v4[0] + xg[0]), fg = fast_sigmoid(v4[1] + xg[1]);
       const float gg = fast_tanh(v4[2] + xg[2]), og = fast_sigmoid(v4[3] + xg[3]);
+      if (sv.gates != nullptr && owner) {        // training: keep what the backward recurrence needs
+        const size_t row = dec ? (size_t)my_b * n_dec + s : (size_t)my_b * Tmax + s;
+        float* gsv = (dec ? sv.dec_gates : sv.gates) + row * (4 * kD) + col;
+        gsv[0] = ig; gsv[kD] = fg; gsv[2 * kD] = gg; gsv[3 * kD] = og;
+        const size_t hrow = dec ? row : (size_t)my_b * Tmax + p_cur;
+        const __nv_bfloat16 hh = __float2bfloat16_rn(h_state);
+        (dec ? sv.dec_hprev_hi : sv.hprev_hi)[hrow * kD + col] = hh;
+        (dec ? sv.dec_hprev_lo : sv.hprev_lo)[hrow * kD + col] = __float2bfloat16_rn(h_state - __bfloat162float(hh));
+      }
       c_state = fg * c_state + ig * gg;
       h_state = og * fast_tanh(c_state);
+      if (sv.gates != nullptr && owner) (dec ? sv.dec_c : sv.c)[(dec ? (size_t)my_b * n_dec + s : (size_t)my_b * Tmax + s) * kD + col] = c_state;
       if (dec && owner) attractors[((size_t)my_b * n_dec + s) * kD + col] = h_state;
     }
     if (gs + 1 < n_total) {           // publish h (changed or not) into the next buffer of all 8 CTAs
@@ -286,6 +314,7 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
     if (!dec) {
 #pragma unroll
       for (int x = 0; x < 4; ++x) xg[x] = xn[x];
+      p_cur = p_next;
       p_next = p_next2;
     }
   }
@@ -295,9 +324,9 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
 template <int kG>
 static int launch_lstm(cudaLaunchConfig_t& cfg, const float* xproj, const int32_t* perm, const int32_t* lens,
                        const int32_t* order, const float* w_enc, const float* w_dec, const float* dec_bias,
-                       int B, int Tmax, int n_dec, float* attractors, float* hc_out) {
+                       int B, int Tmax, int n_dec, float* attractors, float* hc_out, const LstmSave& sv) {
   EDA_CUDA(cudaLaunchKernelEx(&cfg, lstm_cluster_kernel<kG>, xproj, perm, lens, order, w_enc, w_dec,
-                              dec_bias, B, Tmax, n_dec, attractors, hc_out));
+                              dec_bias, B, Tmax, n_dec, attractors, hc_out, sv));
   count_launch();
   return EDA_OK;
 }
@@ -334,11 +363,14 @@ int lstm_max_active_clusters() {
 int lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens,
                     const int32_t* order, const float* w_enc, const float* w_dec,
                     const float* dec_bias, int B, int Tmax, int D, int n_dec, float* attractors,
-                    float* hc_out, cudaStream_t st) {
+                    float* hc_out, const LstmSave& sv, cudaStream_t st) {
   EDA_REQUIRE(D == kD, "eda_lstm_attractors: D must be 256 (got %d)", D);
   EDA_REQUIRE(B > 0 && Tmax > 0 && n_dec >= 0, "eda_lstm_attractors: bad sizes");
   EDA_REQUIRE(((uintptr_t)w_enc | (uintptr_t)w_dec) % 16 == 0, "eda_lstm_attractors: weights must be 16B aligned");
   // one wave if at all possible: the smallest G in 4..8 whose cluster count fits the device
+  if (sv.gates != nullptr)
+    EDA_REQUIRE(sv.c && sv.hprev_hi && sv.hprev_lo && sv.dec_gates && sv.dec_c && sv.dec_hprev_hi && sv.dec_hprev_lo && hc_out,
+                "eda_lstm_attractors_train: every save buffer (and hc_out) is required");
   const int fit = std::max(1, lstm_max_active_clusters());
   int G = 4;
   while (G < 8 && ceil_div(B, G) > fit) ++G;
@@ -346,14 +378,254 @@ int lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens
   cudaLaunchAttribute attr[1];
   lstm_launch_config(cfg, attr, ceil_div(B, G), st);
   switch (G) {
-    case 4: return launch_lstm<4>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out);
-    case 5: return launch_lstm<5>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out);
-    case 6: return launch_lstm<6>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out);
-    case 7: return launch_lstm<7>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out);
-    default: return launch_lstm<8>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out);
+    case 4: return launch_lstm<4>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv);
+    case 5: return launch_lstm<5>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv);
+    case 6: return launch_lstm<6>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv);
+    case 7: return launch_lstm<7>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv);
+    default: return launch_lstm<8>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv);
+  }
+}
+
+// ===================================================================== backward recurrence =====
+// BPTT through the decoder and encoder LSTMs, same cluster shape as the forward:
+// CTA c owns hidden units [32c, 32c+32).  Walking the steps backwards, per step
+//   wait until all 8 CTAs' gate gradients of the LATER step have landed (mbarrier + DSMEM bulk
+//   pushes, 4 x the forward's volume: 128 gate rows per CTA and sequence)
+//   -> dh[own 32 units] += W_hh[:, own units]^T . dgates  (the 1024 x 32 column slice of W_hh is
+//      register resident: thread (unit u, slice kc) holds rows {gate*256 + 32i + 4kc + j}; packed
+//      FFMA2, butterfly reduction over the 8 slice lanes)
+//   -> lane kc == sequence finishes the cell backward from the saved activated gates / cell states
+//   -> its 4 gate gradients go to HBM as the split-bf16 operand of the weight / input gradient
+//      GEMMs (frame order, row b*Tmax + perm[s]) and to the peers for the next (earlier) step.
+struct LstmBwd {
+  const int32_t* perm; const int32_t* lens; const int32_t* order;
+  const float* w_enc; const float* w_dec;
+  const float* gates; const float* c; const float* dec_gates; const float* dec_c; const float* hc;
+  const float* datt;                         // (B, n_dec, D) gradient w.r.t. the attractors
+  __nv_bfloat16* dxp_hi; __nv_bfloat16* dxp_lo;     // (B*Tmax, 4D) d loss / d (gate pre-activations), frame order
+  __nv_bfloat16* ddec_hi; __nv_bfloat16* ddec_lo;   // (B*n_dec, 4D)
+  int B, Tmax, n_dec;
+};
+
+// wt[i][gate][0..1] = packed W[gate*256 + 32 i + 4 kc + {0,1 | 2,3}][32 cta + u]
+__device__ __forceinline__ void load_wt(uint64_t (&wt)[8][4][2], const float* __restrict__ W, int cta, int u, int kc) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int gate = 0; gate < 4; ++gate) {
+      const float* src = W + (size_t)(gate * kD + 32 * i + 4 * kc) * kD + cta * kUnits + u;
+      wt[i][gate][0] = pack2(__ldg(src), __ldg(src + kD));
+      wt[i][gate][1] = pack2(__ldg(src + 2 * kD), __ldg(src + 3 * kD));
+    }
+}
+
+template <int kG>
+__global__ void __launch_bounds__(256, 1)
+lstm_bwd_cluster_kernel(const LstmBwd P) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const int cta = (int)cluster.block_rank();
+  const int group = blockIdx.x / kCluster;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int rg = lane >> 3, kc = lane & 7;
+  const int u = warp * 4 + rg;
+  const int seq = kc;
+  const bool owner = kc < kG;
+
+  extern __shared__ __align__(128) uint8_t lsm_raw[];
+  // gate gradients of one step, [buffer][source CTA][sequence][gate][unit]: a CTA's slice is kG*512 B
+  float (*dg)[kCluster][kG][4][kUnits] = reinterpret_cast<float (*)[kCluster][kG][4][kUnits]>(lsm_raw);
+  float (*stage)[kG][4][kUnits] = reinterpret_cast<float (*)[kG][4][kUnits]>(lsm_raw + 2 * kCluster * kG * 512);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(lsm_raw + 2 * kCluster * kG * 512 + 2 * kG * 512);
+  int* s_seq = reinterpret_cast<int*>(bars + 2);
+  int* s_len = s_seq + 8;
+
+  if (tid < kG) {
+    const int slot = group * kG + tid;
+    int b = -1, n = 0;
+    if (slot < P.B) { b = P.order ? P.order[slot] : slot; n = P.lens[b]; }
+    s_seq[tid] = b; s_len[tid] = n;
+  }
+  if (tid == 0) {
+    bar_init(&bars[0], 1); bar_init(&bars[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  int max_len = 0;
+#pragma unroll
+  for (int g = 0; g < kG; ++g) max_len = max(max_len, s_len[g]);
+  const int n_dec = P.n_dec, Tmax = P.Tmax;
+  const int n_total = max_len + n_dec;
+  constexpr uint32_t kStepBytes = kCluster * kG * 512;
+  if (tid == 0) {
+    if (n_total > 1) bar_arm(&bars[1], kStepBytes);
+    if (n_total > 2) bar_arm(&bars[0], kStepBytes);
+  }
+  uint64_t wt[8][4][2];
+  load_wt(wt, n_dec > 0 ? P.w_dec : P.w_enc, cta, u, kc);
+
+  const int my_b = owner ? s_seq[seq] : -1;
+  const int my_len = owner ? s_len[seq] : 0;
+  const size_t col = (size_t)cta * kUnits + u;
+  float carry_dh = 0.f, carry_dc = 0.f;
+
+  // saved activations of one step for this lane's (sequence, unit)
+  struct StepIn { float g[4], c, cp, da; int p; };
+  auto load_step = [&](int gs, StepIn& o) {
+    o.g[0] = o.g[1] = o.g[2] = o.g[3] = o.c = o.cp = o.da = 0.f; o.p = 0;
+    if (my_b < 0 || gs < 0) return;
+    const bool dec = gs >= max_len;
+    const int s = dec ? gs - max_len : gs;
+    if (dec) {
+      const size_t row = (size_t)my_b * n_dec + s;
+      const float* gp = P.dec_gates + row * (4 * kD) + col;
+#pragma unroll
+      for (int x = 0; x < 4; ++x) o.g[x] = __ldg(gp + x * kD);
+      o.c = __ldg(P.dec_c + row * kD + col);
+      o.cp = s > 0 ? __ldg(P.dec_c + (row - 1) * kD + col) : __ldg(P.hc + ((size_t)my_b * 2 + 1) * kD + col);
+      o.da = __ldg(P.datt + row * kD + col);
+    } else if (s < my_len) {
+      const size_t row = (size_t)my_b * Tmax + s;
+      const float* gp = P.gates + row * (4 * kD) + col;
+#pragma unroll
+      for (int x = 0; x < 4; ++x) o.g[x] = __ldg(gp + x * kD);
+      o.c = __ldg(P.c + row * kD + col);
+      o.cp = s > 0 ? __ldg(P.c + (row - 1) * kD + col) : 0.f;
+      o.p = __ldg(P.perm + row);
+    }
+  };
+  StepIn cur_in;
+  load_step(n_total - 1, cur_in);
+
+  uint32_t r_d0 = 0, r_d1 = 0, r_bar0 = 0, r_bar1 = 0;
+  if (tid < kCluster) {
+    r_d0 = map_rank(s_u32(&dg[0][cta][0][0][0]), tid); r_d1 = map_rank(s_u32(&dg[1][cta][0][0][0]), tid);
+    r_bar0 = map_rank(s_u32(&bars[0]), tid); r_bar1 = map_rank(s_u32(&bars[1]), tid);
+  }
+  cluster.sync();
+
+  for (int r = 0; r < n_total; ++r) {
+    const int gs = n_total - 1 - r;
+    const bool dec = gs >= max_len;
+    const int s = dec ? gs - max_len : gs;
+    const int cur = r & 1;
+    StepIn nxt;
+    load_step(gs - 1, nxt);                 // in flight under the mat-vec
+    if (r > 0) {
+      if (n_dec > 0 && gs + 1 == max_len - 1) load_wt(wt, P.w_enc, cta, u, kc);   // the later step is an encoder step from here on
+      bar_wait(&bars[cur], ((r - 1) >> 1) & 1);
+      if (tid == 0 && r + 2 < n_total) bar_arm(&bars[cur], kStepBytes);
+      uint64_t acc[kG];
+#pragma unroll
+      for (int g = 0; g < kG; ++g) acc[g] = 0ull;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int g = 0; g < kG; ++g)
+#pragma unroll
+          for (int gate = 0; gate < 4; ++gate) {
+            const float4 dv = *reinterpret_cast<const float4*>(&dg[cur][i][g][gate][4 * kc]);
+            acc[g] = ffma2(wt[i][gate][0], pack2(dv.x, dv.y), acc[g]);
+            acc[g] = ffma2(wt[i][gate][1], pack2(dv.z, dv.w), acc[g]);
+          }
+      float rsum = 0.f;
+#pragma unroll
+      for (int g = 0; g < kG; ++g) {
+        float v = sum2(acc[g]);
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        if (kc == g) rsum = v;
+      }
+      carry_dh += rsum;
+    }
+    if (owner) {
+      const bool active = my_b >= 0 && (dec || s < my_len);
+      float d4[4] = {0.f, 0.f, 0.f, 0.f};
+      if (active) {
+        const float ig = cur_in.g[0], fg = cur_in.g[1], gg = cur_in.g[2], og = cur_in.g[3];
+        const float dh = carry_dh + cur_in.da;
+        const float tc = fast_tanh(cur_in.c);
+        const float dc = carry_dc + dh * og * (1.f - tc * tc);
+        d4[0] = dc * gg * ig * (1.f - ig);
+        d4[1] = dc * cur_in.cp * fg * (1.f - fg);
+        d4[2] = dc * ig * (1.f - gg * gg);
+        d4[3] = dh * tc * og * (1.f - og);
+        carry_dc = dc * fg;
+        carry_dh = 0.f;
+        const size_t row = dec ? (size_t)my_b * n_dec + s : (size_t)my_b * Tmax + cur_in.p;
+        __nv_bfloat16* oh = (dec ? P.ddec_hi : P.dxp_hi) + row * (4 * kD) + col;
+        __nv_bfloat16* ol = (dec ? P.ddec_lo : P.dxp_lo) + row * (4 * kD) + col;
+#pragma unroll
+        for (int x = 0; x < 4; ++x) {
+          const __nv_bfloat16 hv = __float2bfloat16_rn(d4[x]);
+          oh[x * kD] = hv;
+          ol[x * kD] = __float2bfloat16_rn(d4[x] - __bfloat162float(hv));
+        }
+      }
+      if (r + 1 < n_total) {
+#pragma unroll
+        for (int x = 0; x < 4; ++x) stage[cur][seq][x][u] = d4[x];
+      }
+    }
+    if (r + 1 < n_total) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncthreads();
+      if (tid < kCluster)
+        bulk_push(cur ? r_d0 : r_d1, s_u32(&stage[cur][0][0][0]), kG * 512, cur ? r_bar0 : r_bar1);
+    }
+    cur_in = nxt;
+  }
+  cluster.sync();
+}
+
+template <int kG>
+static int launch_lstm_bwd(cudaLaunchConfig_t& cfg, const LstmBwd& P) {
+  const int smem = 2 * kCluster * kG * 512 + 2 * kG * 512 + 16 + 64 + 128;
+  static bool attr = false;
+  if (!attr) {
+    EDA_CUDA(cudaFuncSetAttribute(lstm_bwd_cluster_kernel<kG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr = true;
+  }
+  cfg.dynamicSmemBytes = smem;
+  EDA_CUDA(cudaLaunchKernelEx(&cfg, lstm_bwd_cluster_kernel<kG>, P));
+  count_launch();
+  return EDA_OK;
+}
+
+int lstm_attractors_bwd(const LstmBwd& P, cudaStream_t st) {
+  EDA_REQUIRE(P.perm && P.lens && P.w_enc && P.w_dec && P.gates && P.c && P.dec_gates && P.dec_c && P.hc && P.datt &&
+              P.dxp_hi && P.dxp_lo && P.ddec_hi && P.ddec_lo, "eda_lstm_attractors_bwd: null argument");
+  EDA_REQUIRE(P.B > 0 && P.Tmax > 0 && P.n_dec >= 1, "eda_lstm_attractors_bwd: bad sizes");
+  // rows of padded frames (and of sequences that stop early) carry no gradient
+  EDA_CUDA(cudaMemsetAsync(P.dxp_hi, 0, (size_t)P.B * P.Tmax * 4 * kD * sizeof(__nv_bfloat16), st));
+  EDA_CUDA(cudaMemsetAsync(P.dxp_lo, 0, (size_t)P.B * P.Tmax * 4 * kD * sizeof(__nv_bfloat16), st));
+  const int fit = std::max(1, lstm_max_active_clusters());
+  int G = 4;
+  while (G < 8 && ceil_div(P.B, G) > fit) ++G;
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[1];
+  lstm_launch_config(cfg, attr, ceil_div(P.B, G), st);
+  switch (G) {
+    case 4: return launch_lstm_bwd<4>(cfg, P);
+    case 5: return launch_lstm_bwd<5>(cfg, P);
+    case 6: return launch_lstm_bwd<6>(cfg, P);
+    case 7: return launch_lstm_bwd<7>(cfg, P);
+    default: return launch_lstm_bwd<8>(cfg, P);
   }
 }
 
 }  // namespace eda
 
 extern "C" int eda_lstm_max_active_clusters(void) { return eda::lstm_max_active_clusters(); }
+
+extern "C" int eda_lstm_attractors_bwd(const int32_t* perm, const int32_t* lens, const int32_t* order,
+                                       const float* w_hh_enc, const float* w_hh_dec, const float* gates, const float* c,
+                                       const float* dec_gates, const float* dec_c, const float* hc, const float* dattractors,
+                                       int B, int Tmax, int D, int n_dec, void* dxproj_hi, void* dxproj_lo,
+                                       void* ddec_hi, void* ddec_lo, void* stream) {
+  EDA_REQUIRE(D == eda::kD, "eda_lstm_attractors_bwd: D must be 256 (got %d)", D);
+  eda::LstmBwd P = {perm, lens, order, w_hh_enc, w_hh_dec, gates, c, dec_gates, dec_c, hc, dattractors,
+                    (__nv_bfloat16*)dxproj_hi, (__nv_bfloat16*)dxproj_lo, (__nv_bfloat16*)ddec_hi, (__nv_bfloat16*)ddec_lo,
+                    B, Tmax, n_dec};
+  return eda::lstm_attractors_bwd(P, (cudaStream_t)stream);
+}

@@ -54,6 +54,7 @@ struct MhaParams {
   int T, H, B, passes;
   float* out; int ld_out;                 // optional fp32 (B*T, H*64)
   bf16* out_hi; bf16* out_lo; int ld_os;  // optional split
+  float* lse;                             // optional (training): (B*H, T) log2-domain log-sum-exp of each score row
 };
 
 // D[tmem] (+)= A[tmem] * B[smem desc]
@@ -350,6 +351,8 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
     s_l[half][row_in_tile] = l_sum;
     pair_sync();
     l_sum += s_l[half ^ 1][row_in_tile];
+    if (p.lse && half == 0 && q0 + row_in_tile < p.T)      // softmax row = exp2(S log2e - lse): what the backward pass rebuilds P from
+      p.lse[((size_t)b * p.H + h) * p.T + q0 + row_in_tile] = m_ref + log2f(l_sum);
     mbar_wait(bar_o, it & 1);
 #ifdef EDA_MHA_TRACE
     if (threadIdx.x == 64) MHA_STAMP(80);
@@ -425,7 +428,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
 // ------------------------------------------------------------------------- host ---------
 int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
               int B, int T, int H, float* out, int ld_out, void* out_hi, void* out_lo, int ld_os, int prec,
-              cudaStream_t st) {
+              cudaStream_t st, float* lse = nullptr) {
   EDA_REQUIRE(qk_hi && qk_lo && vt_hi && vt_lo && B > 0 && T > 0 && H > 0, "eda_mha_split: bad arguments");
   EDA_REQUIRE(ld_qk >= 2 * H * ADH && ld_qk % 8 == 0 && Tp >= T && Tp % 8 == 0, "eda_mha_split: ld_qk / Tp must be multiples of 8 and large enough");
   EDA_REQUIRE(out || (out_hi && out_lo), "eda_mha_split: no output requested");
@@ -449,6 +452,7 @@ int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi
   MhaParams p = {};
   p.T = T; p.H = H; p.B = B; p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
   p.out = out; p.ld_out = ld_out; p.out_hi = (bf16*)out_hi; p.out_lo = (bf16*)out_lo; p.ld_os = ld_os;
+  p.lse = lse;
   const int64_t n_items = (int64_t)ceil_div(T, ABM) * H * B;
   EDA_REQUIRE(n_items < (int64_t(1) << 31), "eda_mha_split: too many (batch, head, query tile) items");
   const int grid = (int)std::min<int64_t>(n_items, (int64_t)A_CTAS_PER_SM * num_sms());
@@ -508,6 +512,14 @@ extern "C" int eda_mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, co
                              int ld_os, int prec, void* stream) {
   return eda::mha_split(qk_hi, qk_lo, ld_qk, vt_hi, vt_lo, Tp, B, T, n_heads, out, ld_out, out_hi, out_lo, ld_os,
                         prec, (cudaStream_t)stream);
+}
+
+extern "C" int eda_mha_split_train(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
+                                   int Tp, int B, int T, int n_heads, void* out_hi, void* out_lo, int ld_os, float* lse,
+                                   int prec, void* stream) {
+  EDA_REQUIRE(lse && out_hi && out_lo, "eda_mha_split_train: null argument");
+  return eda::mha_split(qk_hi, qk_lo, ld_qk, vt_hi, vt_lo, Tp, B, T, n_heads, nullptr, 0, out_hi, out_lo, ld_os, prec,
+                        (cudaStream_t)stream, lse);
 }
 
 #ifdef EDA_MHA_TRACE

@@ -167,6 +167,21 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
   return d;
 }
 
+// MN-major SWIZZLE_128B operand tile: the MN index is contiguous in memory (64 elements = one 128 B
+// row per reduction index k), 8-k groups are SBO = 1024 B apart, the next 64 MN elements start
+// LBO = 8192 B further (a {64, 64} TMA box per 64 MN elements).  Canonical layout
+// ((8,8,m),(8,k)) : ((1,8,LBO),(64,SBO)) in bf16 elements; needs a_major / b_major = 1 in the
+// instruction descriptor.
+__device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t saddr, uint32_t lbo_bytes = 8192) {
+  uint64_t d = 0;
+  d |= uint64_t((saddr & 0x3FFFF) >> 4);
+  d |= uint64_t(lbo_bytes >> 4) << 16;
+  d |= uint64_t(1024 >> 4) << 32;
+  d |= uint64_t(1) << 46;
+  d |= uint64_t(2) << 61;
+  return d;
+}
+
 // 32 lanes x 32 columns of fp32: thread i of the warp gets row (lane base + i), 32 columns.
 // (issue only: the registers are valid after tmem_wait_ld())
 __device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, float (&v)[32]) {

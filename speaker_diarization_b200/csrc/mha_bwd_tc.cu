@@ -252,13 +252,13 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
     }
     // dK, dV of this key tile (complete: the last bar_dq covers every MMA issued before it)
     const int key = k0 + r;
+    float ok[32], ov[32];
+    tmem_ld32(tmem_base + TM_DK + lane_off + half * 32, ok);    // warp-collective loads: before the row guard
+    tmem_ld32(tmem_base + TM_DV + lane_off + half * 32, ov);
+    __syncwarp();
     if (key < p.T) {
       const size_t row = (size_t)b * p.T + key;
-#pragma unroll 1
-      for (int which = 0; which < 2; ++which) {
-        float o[32];
-        tmem_ld32(tmem_base + (which ? TM_DV : TM_DK) + lane_off + half * 32, o);
-        const int col = (which ? p.dv_col0 : p.dk_col0) + h * BDH + half * 32;
+      auto put = [&](const float (&o)[32], int col) {
         uint32_t hh[16], ll[16];
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
@@ -272,7 +272,9 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
           dh[u] = make_uint4(hh[4 * u], hh[4 * u + 1], hh[4 * u + 2], hh[4 * u + 3]);
           dl4[u] = make_uint4(ll[4 * u], ll[4 * u + 1], ll[4 * u + 2], ll[4 * u + 3]);
         }
-      }
+      };
+      put(ok, p.dk_col0 + h * BDH + half * 32);
+      put(ov, p.dv_col0 + h * BDH + half * 32);
     }
     tc_fence_before();
   }

@@ -11,9 +11,12 @@ and default initialisation for free); no arithmetic goes through them.  Everythi
 path runs in the hand-written sm_100a kernels of libeda_b200.so via ``..ops``.  There is
 no CPU path: the model must live on a CUDA device.
 
-Not covered (reference features outside BASELINE.json's north_star): autograd through the
-kernels (``forward`` returns a loss tensor without ``grad_fn``), train-mode
-dropout > 0, ``has_pos=True`` (never enabled by the reference drivers, train_eda.py:81).
+Training: in ``train()`` mode with gradients enabled and a tensor-core precision,
+``forward`` returns a loss with a ``grad_fn`` whose backward runs the hand-written backward kernels
+(``training.py``); in ``eval()`` mode or under ``no_grad`` it is the inference-cost forward.
+
+Not covered: train-mode dropout > 0 (build with ``dropout=0`` to train), ``has_pos=True`` (never
+enabled by the reference drivers, train_eda.py:81), gradients under ``precision='fp32'``.
 """
 from __future__ import annotations
 
@@ -247,7 +250,15 @@ class TransformerEdaModel(nn.Module):
 
     # --------------------------------------------------------------------- forward -------
     def forward(self, src: List[Tensor], ts: List[Tensor], has_mask=False, activation=None):
-        """models.py:236-295: (loss, stats).  ``loss`` is a 0-d CUDA tensor (no grad_fn)."""
+        """models.py:236-295: (loss, stats).  ``loss`` is a 0-d CUDA tensor; it carries a ``grad_fn``
+        in train() mode with gradients enabled (tensor-core precisions; one backward per forward)."""
+        if self.training and torch.is_grad_enabled() and self.precision != L.PREC_FP32:
+            from .training import EdaLossFn
+            if self._plist is None:
+                self._plist = list(self.parameters())
+            loss = EdaLossFn.apply(self, list(src), list(ts), *self._plist)
+            loss_att, loss_pit, counts = self._train_extras
+            return loss, self._stats(loss, loss_att, loss_pit, counts, int(ts[0].shape[1]))
         x, ilens, lens_dev, seq_off, B, Tmax = self._embed(src)
         dev = x.device
         S = int(ts[0].shape[1])
@@ -260,16 +271,20 @@ class TransformerEdaModel(nn.Module):
         loss_pit, min_idx, label_perm, _ = ops.pit_loss(pred, label, lens_dev)
         counts = ops.der_counters(pred, label_perm, lens_dev)
         loss = (self.diar_weight * loss_pit + self.attractor_weight * loss_att).reshape(())
+        self.last = dict(emb=x.view(B, Tmax, -1), attractors=att, probs=probs, pred=pred,
+                         min_idx=min_idx, label_permute=label_perm, counts=counts)
+        return loss, self._stats(loss, loss_att, loss_pit, counts, S)
+
+    @staticmethod
+    def _stats(loss, loss_att, loss_pit, counts, S):
+        """models.py:274-294 from the nine DER counters."""
         c = counts.tolist()                       # the step's single device->host sync
         correct, num_frames = c[0] / S, float(c[1])
         sp_sc, sp_ms, sp_fa, spk_sc, spk_ms, spk_fa, spk_er = (float(v) for v in c[2:])
-        stats = dict(
+        return dict(
             loss=loss.detach(), loss_att=loss_att.reshape(()).detach(), loss_pit=loss_pit.reshape(()).detach(),
             sad_mr=sp_ms / sp_sc, sad_fr=sp_fa / sp_sc, mi=spk_ms / spk_sc, fa=spk_fa / spk_sc,
             cf=spk_er / spk_sc, acc=correct / num_frames, der=(spk_ms + spk_fa + spk_er) / spk_sc)
-        self.last = dict(emb=x.view(B, Tmax, -1), attractors=att, probs=probs, pred=pred,
-                         min_idx=min_idx, label_permute=label_perm, counts=counts)
-        return loss, stats
 
     # ----------------------------------------------------------------------- infer -------
     @torch.no_grad()

@@ -319,7 +319,14 @@ def main():
     ap.add_argument("--depth", type=int, default=3, help="batches in flight in the pipeline")
     ap.add_argument("--compute-streams", type=int, default=3, help="compute streams the pipeline alternates batches over")
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--workload", default="infer", choices=["infer", "train"],
+                    help="infer = configs[1] (the headline metric); train = configs[4] training step (bench_train.py)")
     args = ap.parse_args()
+    if args.workload == "train":
+        import bench_train
+        argv = ["--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--impl", args.impl,
+                "--precision", args.precision if args.precision != "fp32" else "bf16x3"] + (["--skip-cpu"] if args.skip_cpu else [])
+        return bench_train.main(argv)
     out = run_reference(args) if args.impl == "reference" else run_ours(args)
     if out is not None:
         print(json.dumps(out), flush=True)

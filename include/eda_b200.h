@@ -270,7 +270,8 @@ int eda_ln_bwd(const float* dy, int ld_dy, const float* y, int ld_y, const float
                float* dgamma, float* dbeta, float* dcolsum, void* workspace, int64_t workspace_bytes, int accumulate,
                void* stream);
 
-/* out (N) (+)= column sums of a split matrix (M, N): bias gradients.  workspace >= 296 * N * 4 B. */
+/* out (N) (+)= column sums of a split matrix (M, N): bias gradients.  N % 8 == 0, N <= 2048;
+ * workspace >= 592 * N * 4 B.                                                                    */
 int eda_colsum_split(const void* hi, const void* lo, int M, int N, int ld, float* out, void* workspace,
                      int64_t workspace_bytes, int accumulate, void* stream);
 

@@ -24,17 +24,30 @@ __device__ __forceinline__ void split_store2(bf16* hi, bf16* lo, float x0, float
                                                               __float2bfloat16_rn(x1 - __bfloat162float(h1)));
 }
 
-// out_k[j] = sum over CTAs of part[cta][k][j], ascending cta (k-th of n_vec vectors of length n)
-__global__ void partial_finish_kernel(const float* __restrict__ part, int n_cta, int n_vec, int n,
-                                      float* out0, float* out1, float* out2, int accumulate) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_vec * n) return;
-  const int k = i / n, j = i % n;
-  float* out = k == 0 ? out0 : k == 1 ? out1 : out2;
-  if (!out) return;
-  float acc = accumulate ? out[j] : 0.f;
-  for (int c = 0; c < n_cta; ++c) acc += part[((size_t)c * n_vec + k) * n + j];
-  out[j] = acc;
+// out_k[j] = sum over CTAs of part[cta][k][j] (k-th of n_vec vectors of length n).  A block owns 32
+// columns; its 8 warps each add every 8th partial (coalesced 128 B reads), then the 8 sums are
+// added in warp order: a fixed summation tree, whatever the launch geometry.
+__global__ void __launch_bounds__(256)
+partial_finish_kernel(const float* __restrict__ part, int n_cta, int n_vec, int n,
+                      float* out0, float* out1, float* out2, int accumulate) {
+  __shared__ float red[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int i = blockIdx.x * 32 + lane;
+  float acc = 0.f;
+  if (i < n_vec * n)
+    for (int c = warp; c < n_cta; c += 8) acc += part[(size_t)c * n_vec * n + i];
+  red[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && i < n_vec * n) {
+    const int k = i / n, j = i % n;
+    float* out = k == 0 ? out0 : k == 1 ? out1 : out2;
+    if (out) {
+      float t = accumulate ? out[j] : 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += red[w][lane];
+      out[j] = t;
+    }
+  }
 }
 
 // ------------------------------------------------------------------ LayerNorm backward ------
@@ -120,42 +133,68 @@ int ln_bwd(const float* dy, int ld_dy, const float* y, int ld_y, const float* ga
   EDA_REQUIRE(work_bytes >= (size_t)n_cta * 768 * sizeof(float), "eda_ln_bwd: workspace too small (%d CTAs x 3 KB)", n_cta);
   ln_bwd_kernel<<<n_cta, 256, 0, st>>>(dy, ld_dy, y, ld_y, gamma, beta, rstd, M, dx, ld_dx, (bf16*)dx_hi, (bf16*)dx_lo, ld_s, work);
   EDA_LAUNCH_CHECK();
-  partial_finish_kernel<<<3, 256, 0, st>>>(work, n_cta, 3, 256, dgamma, dbeta, dcolsum, accumulate);
+  partial_finish_kernel<<<ceil_div(3 * 256, 32), 256, 0, st>>>(work, n_cta, 3, 256, dgamma, dbeta, dcolsum, accumulate);
   EDA_LAUNCH_CHECK();
   return EDA_OK;
 }
 
 // ------------------------------------------------------------------ column sums (bias grads) ---
-// out[j] = sum_rows (hi + lo)[row][j]; N <= 2048, N % 2 == 0.  Thread = column pair of a 512-column chunk.
-constexpr int CS_CTAS = 296;
+// out[j] = sum_rows (hi + lo)[row][j]; N % 8 == 0, N <= 2048.  A thread owns 8 columns (16 B of hi,
+// 16 B of lo per row); the 256 threads of a CTA cover 2048 / N rows per pass, four passes in flight.
+constexpr int CS_CTAS = 592;
 __global__ void __launch_bounds__(256)
 colsum_split_kernel(const bf16* __restrict__ hi, const bf16* __restrict__ lo, int M, int N, int ld, float* __restrict__ part) {
-  const int rows_per = ceil_div(M, (int)gridDim.x);
-  const int r0 = blockIdx.x * rows_per, r1 = min(M, r0 + rows_per);
-  for (int cbase = 0; cbase < N; cbase += 512) {
-    const int c = cbase + 2 * threadIdx.x;
-    float a0 = 0.f, a1 = 0.f;
-    if (c < N) {
-      for (int r = r0; r < r1; ++r) {
-        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(hi + (size_t)r * ld + c);
-        const __nv_bfloat162 l = *reinterpret_cast<const __nv_bfloat162*>(lo + (size_t)r * ld + c);
-        a0 += __bfloat162float(h.x) + __bfloat162float(l.x);
-        a1 += __bfloat162float(h.y) + __bfloat162float(l.y);
+  __shared__ float red[256][9];
+  const int tpr = N / 8;                          // threads per row
+  const int rpp = 256 / tpr;                      // rows per pass
+  const int sub = threadIdx.x / tpr, c8 = (threadIdx.x % tpr) * 8;
+  float acc[8] = {};
+  if (sub < rpp) {
+    const int stride = gridDim.x * rpp;
+    auto add = [&](const uint4& a, const uint4& b) {
+      const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        acc[2 * j] += __uint_as_float(aw[j] << 16) + __uint_as_float(bw[j] << 16);
+        acc[2 * j + 1] += __uint_as_float(aw[j] & 0xffff0000u) + __uint_as_float(bw[j] & 0xffff0000u);
       }
-      part[(size_t)blockIdx.x * N + c] = a0;
-      part[(size_t)blockIdx.x * N + c + 1] = a1;
+    };
+    int r = blockIdx.x * rpp + sub;
+    for (; r + 3 * stride < M; r += 4 * stride) {
+      uint4 a[4], b[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        a[k] = __ldg(reinterpret_cast<const uint4*>(hi + (size_t)(r + k * stride) * ld + c8));
+        b[k] = __ldg(reinterpret_cast<const uint4*>(lo + (size_t)(r + k * stride) * ld + c8));
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) add(a[k], b[k]);
+    }
+    for (; r < M; r += stride)
+      add(__ldg(reinterpret_cast<const uint4*>(hi + (size_t)r * ld + c8)), __ldg(reinterpret_cast<const uint4*>(lo + (size_t)r * ld + c8)));
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.x][j] = acc[j];
+  __syncthreads();
+  if (threadIdx.x < tpr) {                        // add the row groups in order
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float t = 0.f;
+      for (int g = 0; g < rpp; ++g) t += red[g * tpr + threadIdx.x][j];
+      part[(size_t)blockIdx.x * N + c8 + j] = t;
     }
   }
 }
 
 int colsum_split(const void* hi, const void* lo, int M, int N, int ld, float* out, float* work, size_t work_bytes,
                  int accumulate, cudaStream_t st) {
-  EDA_REQUIRE(hi && lo && out && work && M > 0 && N > 0 && N % 2 == 0 && ld % 2 == 0, "eda_colsum_split: bad arguments");
-  const int n_cta = std::min(CS_CTAS, M);
+  EDA_REQUIRE(hi && lo && out && work && M > 0 && N > 0 && N % 8 == 0 && N <= 2048 && ld % 8 == 0, "eda_colsum_split: bad arguments (N %% 8 == 0, N <= 2048, ld %% 8 == 0)");
+  EDA_REQUIRE(((uintptr_t)hi | (uintptr_t)lo) % 16 == 0, "eda_colsum_split: operands must be 16B aligned");
+  const int n_cta = std::min(CS_CTAS, ceil_div(M, std::max(1, 256 / (N / 8))));
   EDA_REQUIRE(work_bytes >= (size_t)n_cta * N * sizeof(float), "eda_colsum_split: workspace too small");
   colsum_split_kernel<<<n_cta, 256, 0, st>>>((const bf16*)hi, (const bf16*)lo, M, N, ld, work);
   EDA_LAUNCH_CHECK();
-  partial_finish_kernel<<<ceil_div(N, 256), 256, 0, st>>>(work, n_cta, 1, N, out, nullptr, nullptr, accumulate);
+  partial_finish_kernel<<<ceil_div(N, 32), 256, 0, st>>>(work, n_cta, 1, N, out, nullptr, nullptr, accumulate);
   EDA_LAUNCH_CHECK();
   return EDA_OK;
 }

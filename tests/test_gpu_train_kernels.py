@@ -118,9 +118,12 @@ def test_colsum_and_scale_split(dev):
     g = torch.Generator().manual_seed(5)
     x = torch.randn((3001, 2048), generator=g)
     out = torch.empty((2048,), device=dev)
-    work = torch.empty(4 << 20, dtype=torch.uint8, device=dev)
+    work = torch.empty(8 << 20, dtype=torch.uint8, device=dev)
     OT.colsum_split(_split(x, dev), 3001, 2048, out, work)
     assert rel_err(out.cpu(), x.double().sum(0).float()) < 1e-5
+    out2 = torch.empty((768,), device=dev)
+    OT.colsum_split(_split(x[:, :768].contiguous(), dev), 3001, 768, out2, work)
+    assert rel_err(out2.cpu(), x[:, :768].double().sum(0).float()) < 1e-5
     dst = ops.Split.empty(3001, 768, dev)
     OT.scale_split(x[:, :256].contiguous().to(dev), 0.125, dst, cols=256)
     assert rel_err(dst.float()[:, :256].cpu(), x[:, :256] * 0.125) < 1e-5

@@ -52,13 +52,9 @@ class TransformerEdaModel(nn.Module):
         self.n_units, self.n_layers, self.has_pos = n_units, n_layers, has_pos
         self.dim_feedforward, self.dropout_p = dim_feedforward, dropout
         self.src_mask = None
-        self.encoder = nn.Linear(in_size, n_units)
-        self.encoder_norm = nn.LayerNorm(n_units)
-        layer = TransformerEncoderLayer(n_units, n_heads, dim_feedforward, dropout, batch_first=True)
-        self.transformer_encoder = TransformerEncoder(layer, n_layers, enable_nested_tensor=False)
+        self._build_modules(in_size, n_units, n_heads, n_layers, dim_feedforward, dropout)
         self.eda = LstmEncoderDedecoderAttractor(input_size=n_units, num_layers=1, dropout=0.1)
         self.diar_weight, self.attractor_weight = diar_weight, attractor_weight
-        self.init_weights()
         self.set_precision(precision or os.environ.get("EDA_B200_PRECISION", "fp32"))
         self._prep = None
         self._ws = {}
@@ -67,6 +63,25 @@ class TransformerEdaModel(nn.Module):
         self.workspace_slot = 0     # callers with several batches in flight on different streams use one slot each
         self._perm_ring = {}
         self._emb_split = None
+
+    # state_dict names of the input projection, its LayerNorm and the encoder stack (models.py:185-193)
+    NAMES = dict(in_linear="encoder", in_norm="encoder_norm", stack="transformer_encoder")
+
+    def _build_modules(self, in_size, n_units, n_heads, n_layers, dim_feedforward, dropout):
+        self.encoder = nn.Linear(in_size, n_units)
+        self.encoder_norm = nn.LayerNorm(n_units)
+        layer = TransformerEncoderLayer(n_units, n_heads, dim_feedforward, dropout, batch_first=True)
+        self.transformer_encoder = TransformerEncoder(layer, n_layers, enable_nested_tensor=False)
+        self.init_weights()
+
+    def _in_linear(self) -> nn.Linear:
+        return getattr(self, self.NAMES["in_linear"])
+
+    def _in_norm(self) -> nn.LayerNorm:
+        return getattr(self, self.NAMES["in_norm"])
+
+    def _stack(self) -> TransformerEncoder:
+        return getattr(self, self.NAMES["stack"])
 
     def set_precision(self, name: str) -> None:
         """'fp32' (CUDA-core FFMA), 'bf16x3' (tcgen05, split-bf16 operands) or 'bf16'."""
@@ -88,11 +103,11 @@ class TransformerEdaModel(nn.Module):
         key = tuple((p.data_ptr(), p._version) for p in self._plist)
         if self._prep is None or self._prep[0] != key:
             kpad = _round_up(self.in_size, 16)
-            w = self.encoder.weight.detach()
+            w = self._in_linear().weight.detach()
             w_in = torch.zeros((self.n_units, kpad), dtype=torch.float32, device=w.device)
             w_in[:, : self.in_size] = w
             layers = []
-            for lyr in self.transformer_encoder.layers:
+            for lyr in self._stack().layers:
                 g = lambda t: t.detach().contiguous()
                 layers.append(dict(
                     w_qkv=g(lyr.self_attn.in_proj_weight), b_qkv=g(lyr.self_attn.in_proj_bias),
@@ -101,9 +116,9 @@ class TransformerEdaModel(nn.Module):
                     w_2=g(lyr.linear2.weight), b_2=g(lyr.linear2.bias),
                     g1=g(lyr.norm1.weight), be1=g(lyr.norm1.bias),
                     g2=g(lyr.norm2.weight), be2=g(lyr.norm2.bias)))
-            prep = dict(kpad=kpad, w_in=w_in, b_in=self.encoder.bias.detach().contiguous(),
-                        g_in=self.encoder_norm.weight.detach().contiguous(),
-                        be_in=self.encoder_norm.bias.detach().contiguous(), layers=layers)
+            prep = dict(kpad=kpad, w_in=w_in, b_in=self._in_linear().bias.detach().contiguous(),
+                        g_in=self._in_norm().weight.detach().contiguous(),
+                        be_in=self._in_norm().bias.detach().contiguous(), layers=layers)
             if w.is_cuda:
                 # split-bf16 copies of the weight matrices for the tensor-core pipeline (made once)
                 prep["ws_in"] = ops.split_bf16(w_in)
@@ -133,7 +148,7 @@ class TransformerEdaModel(nn.Module):
         return ws
 
     def _device(self) -> torch.device:
-        dev = self.encoder.weight.device
+        dev = self._in_linear().weight.device
         if dev.type != "cuda":
             raise L.EdaError("speaker_diarization_b200 has no CPU path: call .cuda() on the model first")
         return dev
@@ -369,3 +384,41 @@ class TransformerEdaModel(nn.Module):
         c = ops.der_counters(pred.detach().float().contiguous().to(dev),
                              label.detach().float().contiguous().to(dev), lens_dev).tolist()
         return (c[0] / label.size(2), float(c[1]), *(float(v) for v in c[2:]))
+
+
+class EendEdaModel(TransformerEdaModel):
+    """Drop-in for the reference's second model class (models.py:465-700) with
+    ``encoder_type="transformer"``: the same arithmetic as ``TransformerEdaModel`` under the
+    ``state_dict`` names ``linear`` / ``linear_norm`` / ``encoder`` (models.py:487,488,497), default
+    PyTorch initialisation of the input projection (no ``init_weights``), and ``infer`` keeping the
+    FIRST ``infer_num_speakers`` columns (models.py:644) instead of the most probable ones.
+    ``encoder_type="conformer"`` (torchaudio Conformer, models.py:498-502) is not built."""
+
+    NAMES = dict(in_linear="linear", in_norm="linear_norm", stack="encoder")
+
+    def __init__(self, n_speakers, in_size, n_heads, n_units, n_layers, dim_feedforward=2048, dropout=0.5,
+                 diar_weight: float = 1.0, attractor_weight: float = 1.0, encoder_type="transformer", eda_type="lstm",
+                 precision: Optional[str] = None):
+        if encoder_type != "transformer":
+            raise NotImplementedError(f"encoder_type not support {encoder_type}!!! (only 'transformer' has CUDA kernels; "
+                                      "the Conformer variant is SURVEY 8f n4)")
+        if eda_type != "lstm":
+            raise NotImplementedError(f"eda_type not support {eda_type}!!!")      # models.py:507 raises the same
+        super().__init__(n_speakers, in_size, n_heads, n_units, n_layers, dim_feedforward, dropout, False,
+                         diar_weight, attractor_weight, precision)
+        self.encoder_type, self.eda_type = encoder_type, eda_type
+
+    def _build_modules(self, in_size, n_units, n_heads, n_layers, dim_feedforward, dropout):
+        self.linear = nn.Linear(in_size, n_units)
+        self.linear_norm = nn.LayerNorm(n_units)
+        layer = TransformerEncoderLayer(n_units, n_heads, dim_feedforward, dropout, batch_first=True)
+        self.encoder = TransformerEncoder(layer, n_layers, enable_nested_tensor=False)
+
+    @torch.no_grad()
+    def infer(self, src: List[Tensor], infer_num_speakers=None, max_n_speakers=15, attractor_threshold=0.5,
+              activity_threshold: Optional[float] = None, perms=None):
+        """models.py:601-652."""
+        if infer_num_speakers is None:
+            return super().infer(src, None, max_n_speakers, attractor_threshold, activity_threshold, perms)
+        ys = super().infer(src, None, max_n_speakers, -1.0, activity_threshold, perms)     # all columns, one pass
+        return [y[:, :infer_num_speakers] for y in ys]

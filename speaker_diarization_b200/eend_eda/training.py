@@ -28,6 +28,7 @@ import torch
 from .. import _lib as L
 from .. import ops
 from .. import ops_train as OT
+from ..sharding import allreduce_mean_
 
 Tensor = torch.Tensor
 
@@ -192,7 +193,7 @@ def backward_train(model, saved: dict) -> Tensor:
     g_f, g_s = ws["g_f"], ws["g_s"]
     for i in range(model.n_layers - 1, -1, -1):
         lw, a = w["layers"][i], ws["layers"][i]
-        pre = f"transformer_encoder.layers.{i}."
+        pre = f"{model.NAMES['stack']}.layers.{i}."
         # norm2 / linear2 / ReLU / linear1
         OT.ln_bwd(dy, ws["x_f"][i + 1], lw["g2"], lw["be2"], a["rstd2"], work, G[pre + "norm2.weight"],
                   G[pre + "norm2.bias"], G[pre + "linear2.bias"], dx=g_f, dx_split=g_s)
@@ -214,9 +215,10 @@ def backward_train(model, saved: dict) -> Tensor:
         OT.gemm_wgrad(ws["dqkv"], ws["x_s"][i], M, 3 * D, D, G[pre + "self_attn.in_proj_weight"], work, P)
         OT.gemm_dgrad(ws["dqkv"], lw["wt_qkv"], M, D, 3 * D, P, resid=g_f, out=dy)
     # encoder_norm / encoder (input projection)
-    OT.ln_bwd(dy, ws["x_f"][0], w["g_in"], w["be_in"], ws["rstd0"], work, G["encoder_norm.weight"],
-              G["encoder_norm.bias"], G["encoder.bias"], dx_split=g_s)
-    OT.gemm_wgrad(g_s, ws["xin"], M, D, model.in_size, G["encoder.weight"], work, P)
+    lin, nrm = model.NAMES["in_linear"], model.NAMES["in_norm"]
+    OT.ln_bwd(dy, ws["x_f"][0], w["g_in"], w["be_in"], ws["rstd0"], work, G[nrm + ".weight"],
+              G[nrm + ".bias"], G[lin + ".bias"], dx_split=g_s)
+    OT.gemm_wgrad(g_s, ws["xin"], M, D, model.in_size, G[lin + ".weight"], work, P)
     return gflat
 
 
@@ -292,11 +294,7 @@ class NoamAdam:
         self.flat_g.zero_()
 
     def step(self) -> None:
-        if self.group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
-            ws = torch.distributed.get_world_size(self.group)
-            if ws > 1:
-                torch.distributed.all_reduce(self.flat_g, group=self.group)
-                self.flat_g.mul_(1.0 / ws)
+        allreduce_mean_(self.flat_g, self.group)
         self.t += 1
         OT.adam_step(self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0], self.betas[1],
                      self.eps, self.t)

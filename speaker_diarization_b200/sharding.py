@@ -76,3 +76,20 @@ def gather_posteriors(local: Dict[int, torch.Tensor], n_cols: int, dst: int = 0,
             out[i] = flats[r][pos:pos + t * s].reshape(t, s).clone()
             pos += t * s
     return out
+
+
+def allreduce_mean_(flat: torch.Tensor, group=None) -> torch.Tensor:
+    """Data-parallel training (train.py's DDP wrapper averages gradients over ranks): ONE all-reduce of
+    the whole flat gradient buffer, in place, then the mean.  No-op without an initialised group."""
+    if not (dist.is_available() and dist.is_initialized()):
+        return flat
+    world = dist.get_world_size(group)
+    if world > 1:
+        dist.all_reduce(flat, group=group)
+        flat.mul_(1.0 / world)
+    return flat
+
+
+def shard_batch(n_items: int, rank: int, world_size: int) -> List[int]:
+    """Indices of a mini-batch's sequences this rank trains on (strided, like DistributedSampler)."""
+    return list(range(rank, n_items, world_size))

@@ -35,6 +35,27 @@ def test_library_exports_every_declared_symbol():
     assert _lib.load().eda_abi_version() == 1
 
 
+def test_ctypes_table_matches_header_argument_counts():
+    """Every prototype in the header has as many parameters as its ctypes signature."""
+    from speaker_diarization_b200 import _lib
+    text = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "eda_b200.h")).read(), flags=re.S)
+    seen = 0
+    for m in re.finditer(r"\b(eda_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", text, flags=re.S):
+        name, args = m.group(1), m.group(2).strip()
+        n = 0 if args in ("void", "") else len(args.split(","))
+        assert n == len(_lib.SIGNATURES[name][1]), (name, n, len(_lib.SIGNATURES[name][1]))
+        seen += 1
+    assert seen == len(_lib.SIGNATURES)
+
+
+def test_noam_schedule_matches_reference_formula():
+    """lr_scheduler.py:29-33 with last_epoch = number of scheduler.step() calls so far."""
+    from speaker_diarization_b200.eend_eda.training import noam_lr
+    assert noam_lr(0, 256, 25000) == noam_lr(1, 256, 25000) == 256 ** -0.5 * 25000 ** -1.5
+    assert abs(noam_lr(25000, 256, 25000) - 256 ** -0.5 * 25000 ** -0.5) < 1e-15
+    assert noam_lr(100000, 256, 25000) == 256 ** -0.5 * 100000 ** -0.5
+
+
 def test_host_helpers_without_gpu():
     from speaker_diarization_b200 import feature
     # feature.py:186-193 frame counting incl. the dropped last frame when n % shift == 0

@@ -284,3 +284,29 @@ def test_full_size_c4_long_form_chunks():
     y2 = m.infer([src[3], src[8]], attractor_threshold=0.5, perms=[perms[3], perms[8]])
     assert (m.last["posteriors"][1] - post[8]).abs().max().item() < 2e-5
     assert y2[1].shape[1] == ys[8].shape[1]
+
+
+def test_eend_eda_model_transformer_variant(dev, manifest):
+    """The reference's second class EendEdaModel(encoder_type='transformer') (models.py:465-700):
+    same kernels under its own state_dict names; infer keeps the FIRST n columns (models.py:644)."""
+    from oracle.make_golden_eend import rename
+    from oracle.weights import EdaConfig, synth_features, synth_labels, synth_state_dict
+    from speaker_diarization_b200.eend_eda.models import EendEdaModel
+    case = manifest["cases"]["eendeda_l2"]
+    g = load_golden("eendeda_l2")
+    cfg = EdaConfig(n_layers=case["n_layers"], n_speakers=case["n_speakers"])
+    m = EendEdaModel(case["n_speakers"], cfg.in_size, cfg.n_heads, cfg.n_units, cfg.n_layers, precision="bf16x3")
+    m.load_state_dict(rename(synth_state_dict(cfg, case["weight_seed"])), strict=True)
+    m = m.to(dev).eval()
+    src = synth_features(case["lengths"], cfg.in_size, case["data_seed"])
+    ts = synth_labels(case["lengths"], case["n_speakers"], case["data_seed"])
+    torch.manual_seed(1000 + case["data_seed"])
+    for b, y in enumerate(m.infer(src, infer_num_speakers=2)):
+        assert (y.cpu().numpy() - g[f"post2_{b}"]).__abs__().max() < 1e-3
+    torch.manual_seed(1000 + case["data_seed"])
+    assert [y.shape[1] for y in m.infer(src, attractor_threshold=0.5)] == g["nspk_thr05"].tolist()
+    torch.manual_seed(2000 + case["data_seed"])
+    loss, stats = m(src, ts)
+    assert abs(loss.item() - float(g["loss"])) < 1e-3 and abs(stats["der"] - float(g["der"])) < 1e-3
+    with pytest.raises(NotImplementedError):
+        EendEdaModel(2, cfg.in_size, 4, 256, 2, encoder_type="conformer")

@@ -7,7 +7,8 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from speaker_diarization_b200.sharding import gather_posteriors, gen_chunk_indices, shard_recordings
+from speaker_diarization_b200.sharding import (allreduce_mean_, gather_posteriors, gen_chunk_indices, shard_batch,
+                                               shard_recordings)
 
 
 def test_chunk_indices_match_reference_generator():
@@ -64,3 +65,33 @@ def test_gather_posteriors_world2_gloo():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert res == [True, True]
+
+
+def _grad_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g = torch.Generator().manual_seed(7)
+        per_seq = torch.randn((6, 1000), generator=g)                 # one "gradient" per sequence of the batch
+        mine = shard_batch(6, rank, world)
+        flat = per_seq[mine].mean(0)                                  # this rank's mini-batch mean
+        allreduce_mean_(flat)
+        q.put(bool(torch.allclose(flat, per_seq.mean(0), atol=1e-6)) and mine == list(range(rank, 6, world)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_training_gradient_allreduce_world2_gloo():
+    """The training step's one collective (NoamAdam.step): mean of the flat gradient over ranks."""
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_grad_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res == [True, True]
+    assert torch.equal(allreduce_mean_(torch.ones(3)), torch.ones(3))     # no process group: untouched

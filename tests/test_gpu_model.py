@@ -286,7 +286,8 @@ def test_full_size_c4_long_form_chunks():
     assert y2[1].shape[1] == ys[8].shape[1]
 
 
-def test_eend_eda_model_transformer_variant(dev, manifest):
+def test_eend_eda_model_transformer_variant(manifest):
+    dev = torch.device("cuda:0")
     """The reference's second class EendEdaModel(encoder_type='transformer') (models.py:465-700):
     same kernels under its own state_dict names; infer keeps the FIRST n columns (models.py:644)."""
     from oracle.make_golden_eend import rename

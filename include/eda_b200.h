@@ -90,7 +90,10 @@ enum {
   EDA_EPI_BIAS_RES_LN = 3, /* C = LN(resid + A.W^T + bias)    (post-LN residual blocks) */
   /* 4 is internal (the QKV scatter of eda_gemm_qkv) */
   EDA_EPI_BIAS_RES = 5,    /* C = resid + A.W^T + bias        (backward: gradient joins of the residual stream) */
-  EDA_EPI_RELU_MASK = 6    /* C = (A.W^T) where mask > 0 else 0   (backward of linear1's ReLU)   */
+  EDA_EPI_RELU_MASK = 6,   /* C = (A.W^T) where mask > 0 else 0   (backward of linear1's ReLU)   */
+  EDA_EPI_BIAS_SILU = 7,   /* C = silu(A.W^T + bias)          (Conformer feed-forward, torchaudio conformer.py) */
+  EDA_EPI_BIAS_GLU = 8     /* C (M, N/2) = a * sigmoid(g)     (Conformer conv module; weight rows interleaved in
+                              32-row blocks a0..31, g0..31, a32..63, ... by the caller)            */
 };
 enum { EDA_PREC_FP32 = 0, EDA_PREC_BF16X3 = 1, EDA_PREC_BF16 = 2 };
 

@@ -49,7 +49,7 @@ constexpr int G_OPERAND_BYTES = G_STAGES_DIRECT * G_STAGE;    // == 2 stages + 8
 static_assert(G_STAGES_STAGED * G_STAGE + G_EPI_WARPS * G_STG_WARP == G_OPERAND_BYTES, "smem plans differ in size");
 constexpr int G_SMEM = G_OPERAND_BYTES + G_LNX_BYTES + G_VEC_BYTES + 256 + 1024;
 
-enum { GEPI_QKV = 4 };     // (EDA_EPI_BIAS_RES = 5 and EDA_EPI_RELU_MASK = 6 are public, eda_b200.h)
+enum { GEPI_QKV = 4 };     // (EDA_EPI_BIAS_RES = 5 ... EDA_EPI_BIAS_GLU = 8 are public, eda_b200.h)
 
 struct GemmParams {
   const float* bias;
@@ -60,6 +60,7 @@ struct GemmParams {
   int M, N, Kp, passes;
   // QKV variant: rows are (b, t) with t < T; v goes to vt[(b*H + h)*64 + d][t], row stride Tp
   bf16* vt_hi; bf16* vt_lo; int T, Tp, H; float q_scale;
+  float out_scale;                         // residual epilogues: C = (A.W^T + bias) * out_scale + resid (0 means 1)
   float* rstd_out;                         // LayerNorm epilogues (training): 1/sqrt(var + eps) per row, optional
   const bf16* mask; int ldm;               // EDA_EPI_RELU_MASK: result is zeroed where mask <= 0
   // weight-gradient form (WG): C[i,j] = sum_r A[r,i] B[r,j] over Kp rows, both operands MN-major;
@@ -386,7 +387,32 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         }
       };
 
-      if constexpr (EPI == EDA_EPI_BIAS || EPI == EDA_EPI_BIAS_RELU || EPI == EDA_EPI_RELU_MASK) {
+      if constexpr (EPI == EDA_EPI_BIAS_GLU) {
+        // nn.GLU over channel pairs (c, c + N/2): the host interleaves the weight rows in blocks of 32
+        // (a-block, gate-block), so both halves of a pair sit in ONE thread's consecutive 32-column
+        // chunks; output (M, N/2) fp32, column = 32 * (pair index) + j.
+#pragma unroll 1
+        for (int cp = 0; cp < 2; ++cp) {
+          const int colp = n0 + ch * 128 + cp * 64;
+          if (colp >= p.N) break;
+          float a[32], g[32];
+          tmem_ld32(trow + cp * 64, a);
+          tmem_ld32(trow + cp * 64 + 32, g);
+          add_vec(a, p.bias, colp);
+          add_vec(g, p.bias, colp + 32);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) a[j] = a[j] * __fdividef(1.f, 1.f + __expf(-g[j]));
+          const int grow = rbase + lane;
+          if (grow < p.M) {
+            float* dst = Cout + (size_t)grow * p.ldc + colp / 2;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              st_global_v8(dst + 8 * j, __float_as_uint(a[8 * j]), __float_as_uint(a[8 * j + 1]), __float_as_uint(a[8 * j + 2]),
+                           __float_as_uint(a[8 * j + 3]), __float_as_uint(a[8 * j + 4]), __float_as_uint(a[8 * j + 5]),
+                           __float_as_uint(a[8 * j + 6]), __float_as_uint(a[8 * j + 7]));
+          }
+        }
+      } else if constexpr (EPI == EDA_EPI_BIAS || EPI == EDA_EPI_BIAS_RELU || EPI == EDA_EPI_RELU_MASK || EPI == EDA_EPI_BIAS_SILU) {
 #pragma unroll 1
         for (int cp = 0; cp < 2; ++cp) {                       // pairs of 32-column chunks
           if (n0 + ch * 128 + cp * 64 >= p.N) break;
@@ -400,6 +426,10 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
             if (EPI == EDA_EPI_BIAS_RELU) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+            }
+            if (EPI == EDA_EPI_BIAS_SILU) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = v[j] * __fdividef(1.f, 1.f + __expf(-v[j]));
             }
             if constexpr (EPI == EDA_EPI_RELU_MASK) {
               // ReLU backward: keep the gradient where the forward activation (its bf16 hi part) was > 0
@@ -467,6 +497,12 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
           const int col0 = ch * 128 + c * 32;
           float v[32];
           tmem_ld32(trow + c * 32, v);
+          const bool scaled = p.out_scale != 0.f;      // (warp-uniform) Conformer half-step residuals
+          if (scaled) {
+            add_vec(v, p.bias, col0);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] *= p.out_scale;
+          }
           if constexpr (kRes) {
             float4 rn[8];
             if (c < 3) load_resid(c + 1, rn);
@@ -479,7 +515,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
               for (int j = 0; j < 8; ++j) rp[j] = rn[j];
             }
           }
-          add_vec(v, p.bias, col0);
+          if (!scaled) add_vec(v, p.bias, col0);
           if constexpr (!kLN) {
             emit_chunk(v, col0, c & 1, rhi, rlo, p.Chi, p.Clo, p.lds);
           } else {
@@ -711,6 +747,11 @@ int gemm_split(const void* a_hi, const void* a_lo, int lda, const void* w_hi, co
     case GEPI_QKV: return launch_gemm<GEPI_QKV>(ta_hi, ta_lo, tb_hi, tb_lo, p, 2 * GBN, st);
     case EDA_EPI_BIAS_RES: return launch_gemm<EDA_EPI_BIAS_RES>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
     case EDA_EPI_RELU_MASK: return launch_gemm<EDA_EPI_RELU_MASK>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
+    case EDA_EPI_BIAS_SILU: return launch_gemm<EDA_EPI_BIAS_SILU>(ta_hi, ta_lo, tb_hi, tb_lo, p, p.N, st);
+    case EDA_EPI_BIAS_GLU: {
+      EDA_REQUIRE(p.C && !p.Chi && p.N % 64 == 0 && p.ldc % 8 == 0 && (uintptr_t)p.C % 32 == 0, "eda_gemm_split_ex: GLU needs an fp32 output (32B aligned, ldc %% 8 == 0) and N %% 64 == 0");
+      return launch_gemm2<EDA_EPI_BIAS_GLU, false>(ta_hi, ta_lo, tb_hi, tb_lo, ta_hi, ta_hi, ta_hi, p, st);
+    }
   }
   set_error("eda_gemm_split: unknown epilogue %d", epi);
   return EDA_EINVAL;
@@ -810,6 +851,20 @@ int eda_gemm_split(const void* a_hi, const void* a_lo, int lda, const void* w_hi
   eda::GemmParams p = {};
   p.bias = bias; p.resid = resid; p.ldr = ldr; p.gamma = ln_gamma; p.beta = ln_beta;
   p.C = C; p.ldc = ldc; p.Chi = (eda::bf16*)c_hi; p.Clo = (eda::bf16*)c_lo; p.lds = ldcs; p.M = M; p.N = N;
+  return eda::gemm_split(a_hi, a_lo, lda, w_hi, w_lo, ldw, p, K, epilogue, prec, (cudaStream_t)stream);
+}
+
+int eda_gemm_split_ex(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
+                      const float* bias, const float* resid, int ldr, const float* ln_gamma, const float* ln_beta,
+                      float* C, int ldc, void* c_hi, void* c_lo, int ldcs, float out_scale, int M, int N, int K,
+                      int epilogue, int prec, void* stream) {
+  EDA_REQUIRE((epilogue >= EDA_EPI_BIAS && epilogue <= EDA_EPI_BIAS_RES_LN) || epilogue == EDA_EPI_BIAS_RES ||
+              epilogue == EDA_EPI_BIAS_SILU || epilogue == EDA_EPI_BIAS_GLU, "eda_gemm_split_ex: unknown epilogue %d", epilogue);
+  EDA_REQUIRE(C || c_hi, "eda_gemm_split_ex: no output requested");
+  eda::GemmParams p = {};
+  p.bias = bias; p.resid = resid; p.ldr = ldr; p.gamma = ln_gamma; p.beta = ln_beta;
+  p.C = C; p.ldc = ldc; p.Chi = (eda::bf16*)c_hi; p.Clo = (eda::bf16*)c_lo; p.lds = ldcs; p.M = M; p.N = N;
+  p.out_scale = (out_scale == 1.0f) ? 0.f : out_scale;
   return eda::gemm_split(a_hi, a_lo, lda, w_hi, w_lo, ldw, p, K, epilogue, prec, (cudaStream_t)stream);
 }
 

@@ -330,6 +330,30 @@ int eda_scale_dev(const float* scale_dev, float* x, int64_t n, void* stream);
 int eda_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                   float beta1, float beta2, float eps, int step, void* stream);
 
+/* ================================================= Conformer encoder variant ===
+ * EendEdaModel(encoder_type="conformer") (models.py:498-502, 525-528): torchaudio.models.Conformer
+ * layers = half-step SiLU feed-forward, pre-LN self-attention with key_padding_mask, convolution
+ * module (pointwise -> GLU -> depthwise k=31 -> BatchNorm1d -> SiLU -> pointwise), half-step
+ * feed-forward, final LayerNorm.  GEMMs run through eda_gemm_split_ex; inference (eval) only.   */
+
+/* eda_gemm_split with the extra epilogues EDA_EPI_BIAS_RES / _SILU / _GLU and a scale on the GEMM term
+ * of the residual epilogues: C = (A.W^T + bias) * out_scale + resid (then LayerNorm for RES_LN). */
+int eda_gemm_split_ex(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
+                      const float* bias, const float* resid, int ldr, const float* ln_gamma, const float* ln_beta,
+                      float* C, int ldc, void* c_hi, void* c_lo, int ldcs, float out_scale, int M, int N, int K,
+                      int epilogue, int prec, void* stream);
+/* nn.LayerNorm(256) on fp32 rows -> fp32 `out` (may be NULL) and/or the split pair of the next GEMM. */
+int eda_layernorm_split(const float* x, int ld, const float* gamma, const float* beta, int M, int D, float* out, int ld_out,
+                        void* out_hi, void* out_lo, int ld_s, void* stream);
+/* Depthwise Conv1d(256, 256, 31, padding 15, groups 256) + BatchNorm1d(eval) + SiLU on (B*T, 256) rows;
+ * scale[c] = bn_w / sqrt(running_var + eps), shift[c] = (conv_bias - running_mean) * scale + bn_b. */
+int eda_dwconv_bn_silu(const float* x, int ld, const float* w, const float* scale, const float* shift, int B, int T, int C,
+                       int K, void* out_hi, void* out_lo, int ld_s, void* stream);
+/* eda_mha_split with nn.MultiheadAttention's key_padding_mask: keys t >= key_lens[b] do not take part. */
+int eda_mha_split_masked(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
+                         int Tp, int B, int T, int n_heads, const int32_t* key_lens, void* out_hi, void* out_lo,
+                         int ld_os, int prec, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

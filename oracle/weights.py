@@ -119,3 +119,58 @@ def synth_labels(lengths, n_speakers: int, seed: int, p_active: float = 0.3, sil
                 state = bool(torch.rand((), generator=g) < (p_active if not state else 0.5))
         out.append(lab)
     return out
+
+
+def synth_conformer_state_dict(n_layers: int, seed: int, template=None):
+    """Seeded "trained-like" weights with the key set of EendEdaModel(encoder_type="conformer")
+    (models.py:487-502 + torchaudio ConformerLayer): every tensor gets its own draw; LayerNorm / BatchNorm affine
+    terms near (1, 0), running_var in [0.5, 1.5], running_mean ~ N(0, 0.1).  ``template`` (a state_dict of the real
+    class, build container only) fixes key order and shapes; without it the shapes are derived here."""
+    D, FF, F_IN, K = 256, 2048, 345, 31
+    shapes = OrderedDict()
+    shapes["linear.weight"], shapes["linear.bias"] = (D, F_IN), (D,)
+    shapes["linear_norm.weight"], shapes["linear_norm.bias"] = (D,), (D,)
+    for l in range(n_layers):
+        p = f"encoder.conformer_layers.{l}."
+        for f in ("ffn1", "ffn2"):
+            shapes[p + f + ".sequential.0.weight"], shapes[p + f + ".sequential.0.bias"] = (D,), (D,)
+            shapes[p + f + ".sequential.1.weight"], shapes[p + f + ".sequential.1.bias"] = (FF, D), (FF,)
+            shapes[p + f + ".sequential.4.weight"], shapes[p + f + ".sequential.4.bias"] = (D, FF), (D,)
+        shapes[p + "self_attn_layer_norm.weight"], shapes[p + "self_attn_layer_norm.bias"] = (D,), (D,)
+        shapes[p + "self_attn.in_proj_weight"], shapes[p + "self_attn.in_proj_bias"] = (3 * D, D), (3 * D,)
+        shapes[p + "self_attn.out_proj.weight"], shapes[p + "self_attn.out_proj.bias"] = (D, D), (D,)
+        c = p + "conv_module."
+        shapes[c + "layer_norm.weight"], shapes[c + "layer_norm.bias"] = (D,), (D,)
+        shapes[c + "sequential.0.weight"], shapes[c + "sequential.0.bias"] = (2 * D, D, 1), (2 * D,)
+        shapes[c + "sequential.2.weight"], shapes[c + "sequential.2.bias"] = (D, 1, K), (D,)
+        shapes[c + "sequential.3.weight"], shapes[c + "sequential.3.bias"] = (D,), (D,)
+        shapes[c + "sequential.3.running_mean"], shapes[c + "sequential.3.running_var"] = (D,), (D,)
+        shapes[c + "sequential.3.num_batches_tracked"] = ()
+        shapes[c + "sequential.5.weight"], shapes[c + "sequential.5.bias"] = (D, D, 1), (D,)
+        shapes[p + "final_layer_norm.weight"], shapes[p + "final_layer_norm.bias"] = (D,), (D,)
+    k = 1.0 / math.sqrt(D)
+    for m in ("encoder", "decoder"):
+        for n, s in (("weight_ih_l0", (4 * D, D)), ("weight_hh_l0", (4 * D, D)), ("bias_ih_l0", (4 * D,)), ("bias_hh_l0", (4 * D,))):
+            shapes[f"eda.{m}.{n}"] = s
+    shapes["eda.linear.weight"], shapes["eda.linear.bias"] = (1, D), (1,)
+    if template is not None:
+        assert {kk: tuple(v.shape) for kk, v in template.items()} == dict(shapes), "conformer key set / shapes differ"
+    g = torch.Generator(device="cpu")
+    g.manual_seed(0xC0F00000 + int(seed))
+    sd = OrderedDict()
+    for key, shape in shapes.items():
+        if key.endswith("num_batches_tracked"):
+            sd[key] = torch.tensor(100, dtype=torch.long)
+        elif key.endswith("running_var"):
+            sd[key] = 0.5 + torch.rand(shape, generator=g)
+        elif key.endswith("running_mean"):
+            sd[key] = torch.randn(shape, generator=g) * 0.1
+        elif key.endswith("norm.weight") or key.endswith("sequential.0.weight") and len(shape) == 1 or key.endswith("sequential.3.weight"):
+            sd[key] = 1.0 + torch.randn(shape, generator=g) * 0.1
+        elif len(shape) == 1:
+            sd[key] = torch.randn(shape, generator=g) * 0.05
+        else:
+            fan_in = shape[1] * (shape[2] if len(shape) == 3 else 1)
+            sd[key] = (torch.rand(shape, generator=g) * 2.0 - 1.0) / math.sqrt(fan_in)
+        sd[key] = sd[key].contiguous()
+    return sd

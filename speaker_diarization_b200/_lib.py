@@ -15,7 +15,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libeda_b200.so")
 
 EPI_BIAS, EPI_BIAS_RELU, EPI_BIAS_LN, EPI_BIAS_RES_LN = 0, 1, 2, 3
-EPI_BIAS_RES, EPI_RELU_MASK = 5, 6
+EPI_BIAS_RES, EPI_RELU_MASK, EPI_BIAS_SILU, EPI_BIAS_GLU = 5, 6, 7, 8
 PREC_FP32, PREC_BF16X3, PREC_BF16 = 0, 1, 2
 PRECISIONS = {"fp32": PREC_FP32, "bf16x3": PREC_BF16X3, "bf16": PREC_BF16}
 
@@ -64,6 +64,11 @@ SIGNATURES = {
     "eda_attractor_head_bwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _i, _p]),
     "eda_scale_dev": (_i, [_p, _p, _i64, _p]),
     "eda_adam_step": (_i, [_p, _p, _p, _p, _i64, _f, _f, _f, _f, _i, _p]),
+    # ---- Conformer variant
+    "eda_gemm_split_ex": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _f, _i, _i, _i, _i, _i, _p]),
+    "eda_layernorm_split": (_i, [_p, _i, _p, _p, _i, _i, _p, _i, _p, _p, _i, _p]),
+    "eda_dwconv_bn_silu": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _i, _p, _p, _i, _p]),
+    "eda_mha_split_masked": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _p, _p, _i, _i, _p]),
 }
 
 _lib = None

@@ -55,6 +55,7 @@ struct MhaParams {
   float* out; int ld_out;                 // optional fp32 (B*T, H*64)
   bf16* out_hi; bf16* out_lo; int ld_os;  // optional split
   float* lse;                             // optional (training): (B*H, T) log2-domain log-sum-exp of each score row
+  const int32_t* klens;                   // optional key_padding_mask (Conformer): keys t >= klens[b] are masked out
 };
 
 // D[tmem] (+)= A[tmem] * B[smem desc]
@@ -141,8 +142,11 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
   float (*s_l)[128] = reinterpret_cast<float (*)[128]>(smem + A_OFF_L);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_kt = (p.T + ABN - 1) / ABN, n_qt = (p.T + ABM - 1) / ABM;
+  const int n_kt_all = (p.T + ABN - 1) / ABN, n_qt = (p.T + ABM - 1) / ABM;
   const int n_items = n_qt * p.H * p.B;
+  // keys of batch entry b that take part (all T without a mask) and the 64-key tiles they span
+  auto keys_of = [&](int b) { return p.klens ? min(p.T, max(1, __ldg(p.klens + b))) : p.T; };
+  auto kt_of = [&](int b) { return p.klens ? (keys_of(b) + ABN - 1) / ABN : n_kt_all; };
 #ifdef EDA_MHA_TRACE
   if (threadIdx.x == 0) {
     uint32_t smid;
@@ -177,6 +181,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
       int it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
         const int q0 = (item % n_qt) * ABM, h = (item / n_qt) % p.H, b = item / (n_qt * p.H);
+        const int n_kt = kt_of(b);
         mbar_wait(q_empty, (it & 1) ^ 1);
         mbar_expect_tx(bar_q, x3 ? 2 * A_TILE16 : A_TILE16);
         tma_load_3d(smem + A_OFF_Q, &tmQK_hi, bar_q, h * ADH, q0, b);
@@ -227,6 +232,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
       };
       int it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+        const int n_kt = kt_of(item / (n_qt * p.H));
         mbar_wait(bar_q, it & 1);
         issue_s();
         for (int j = 0; j < n_kt; ++j, ++gp) {
@@ -280,6 +286,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
     int it = 0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
     const int q0 = (item % n_qt) * ABM, h = (item / n_qt) % p.H, b = item / (n_qt * p.H);
+    const int n_kt = kt_of(b), n_keys = keys_of(b);
     float m_ref = -INFINITY, l_sum = 0.f;       // m_ref in log2 units (S * log2 e)
     for (int j = 0; j < n_kt; ++j, ++g) {
       const uint32_t tS = tS0 + (g & 1) * ABN;
@@ -288,7 +295,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
       if (threadIdx.x == 64) MHA_STAMP(48 + 2 * j);
 #endif
       tc_fence_after();
-      const int n_valid = min(32, p.T - j * ABN - half * 32);     // keys of this half that exist (may be <= 0)
+      const int n_valid = min(32, n_keys - j * ABN - half * 32);  // keys of this half that exist (may be <= 0)
       const bool whole = n_valid == 32;                           // warp-uniform
       float v[32];                                                // the scores stay in registers: one TMEM read
       tmem_ld32(tS, v);
@@ -428,7 +435,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
 // ------------------------------------------------------------------------- host ---------
 int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
               int B, int T, int H, float* out, int ld_out, void* out_hi, void* out_lo, int ld_os, int prec,
-              cudaStream_t st, float* lse = nullptr) {
+              cudaStream_t st, float* lse = nullptr, const int32_t* klens = nullptr) {
   EDA_REQUIRE(qk_hi && qk_lo && vt_hi && vt_lo && B > 0 && T > 0 && H > 0, "eda_mha_split: bad arguments");
   EDA_REQUIRE(ld_qk >= 2 * H * ADH && ld_qk % 8 == 0 && Tp >= T && Tp % 8 == 0, "eda_mha_split: ld_qk / Tp must be multiples of 8 and large enough");
   EDA_REQUIRE(out || (out_hi && out_lo), "eda_mha_split: no output requested");
@@ -452,7 +459,7 @@ int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi
   MhaParams p = {};
   p.T = T; p.H = H; p.B = B; p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
   p.out = out; p.ld_out = ld_out; p.out_hi = (bf16*)out_hi; p.out_lo = (bf16*)out_lo; p.ld_os = ld_os;
-  p.lse = lse;
+  p.lse = lse; p.klens = klens;
   const int64_t n_items = (int64_t)ceil_div(T, ABM) * H * B;
   EDA_REQUIRE(n_items < (int64_t(1) << 31), "eda_mha_split: too many (batch, head, query tile) items");
   const int grid = (int)std::min<int64_t>(n_items, (int64_t)A_CTAS_PER_SM * num_sms());
@@ -520,6 +527,14 @@ extern "C" int eda_mha_split_train(const void* qk_hi, const void* qk_lo, int ld_
   EDA_REQUIRE(lse && out_hi && out_lo, "eda_mha_split_train: null argument");
   return eda::mha_split(qk_hi, qk_lo, ld_qk, vt_hi, vt_lo, Tp, B, T, n_heads, nullptr, 0, out_hi, out_lo, ld_os, prec,
                         (cudaStream_t)stream, lse);
+}
+
+extern "C" int eda_mha_split_masked(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
+                                    int Tp, int B, int T, int n_heads, const int32_t* key_lens, void* out_hi, void* out_lo,
+                                    int ld_os, int prec, void* stream) {
+  EDA_REQUIRE(key_lens && out_hi && out_lo, "eda_mha_split_masked: null argument");
+  return eda::mha_split(qk_hi, qk_lo, ld_qk, vt_hi, vt_lo, Tp, B, T, n_heads, nullptr, 0, out_hi, out_lo, ld_os, prec,
+                        (cudaStream_t)stream, nullptr, key_lens);
 }
 
 #ifdef EDA_MHA_TRACE

@@ -387,32 +387,158 @@ class TransformerEdaModel(nn.Module):
 
 
 class EendEdaModel(TransformerEdaModel):
-    """Drop-in for the reference's second model class (models.py:465-700) with
-    ``encoder_type="transformer"``: the same arithmetic as ``TransformerEdaModel`` under the
-    ``state_dict`` names ``linear`` / ``linear_norm`` / ``encoder`` (models.py:487,488,497), default
-    PyTorch initialisation of the input projection (no ``init_weights``), and ``infer`` keeping the
-    FIRST ``infer_num_speakers`` columns (models.py:644) instead of the most probable ones.
-    ``encoder_type="conformer"`` (torchaudio Conformer, models.py:498-502) is not built."""
+    """Drop-in for the reference's second model class (models.py:465-700): ``state_dict`` names
+    ``linear`` / ``linear_norm`` / ``encoder`` (models.py:487,488,497-501), default PyTorch
+    initialisation of the input projection (no ``init_weights``), ``infer`` keeping the FIRST
+    ``infer_num_speakers`` columns (models.py:644) instead of the most probable ones.
+
+    ``encoder_type="transformer"``: the arithmetic of ``TransformerEdaModel`` (training included).
+    ``encoder_type="conformer"``: ``torchaudio.models.Conformer`` layers with the
+    sequence lengths as key_padding_mask (models.py:525-528) on the tensor-core kernels; inference /
+    eval-mode ``forward`` only (BatchNorm uses its running statistics), precision 'bf16x3' or 'bf16'."""
 
     NAMES = dict(in_linear="linear", in_norm="linear_norm", stack="encoder")
 
     def __init__(self, n_speakers, in_size, n_heads, n_units, n_layers, dim_feedforward=2048, dropout=0.5,
                  diar_weight: float = 1.0, attractor_weight: float = 1.0, encoder_type="transformer", eda_type="lstm",
                  precision: Optional[str] = None):
-        if encoder_type != "transformer":
-            raise NotImplementedError(f"encoder_type not support {encoder_type}!!! (only 'transformer' has CUDA kernels; "
-                                      "the Conformer variant is SURVEY 8f n4)")
+        if encoder_type not in ("transformer", "conformer"):
+            raise NotImplementedError(f"encoder_type not support {encoder_type}!!!")     # models.py:503
         if eda_type != "lstm":
-            raise NotImplementedError(f"eda_type not support {eda_type}!!!")      # models.py:507 raises the same
+            raise NotImplementedError(f"eda_type not support {eda_type}!!!")             # models.py:509
+        object.__setattr__(self, "encoder_type", encoder_type)       # _build_modules runs inside super().__init__
         super().__init__(n_speakers, in_size, n_heads, n_units, n_layers, dim_feedforward, dropout, False,
                          diar_weight, attractor_weight, precision)
-        self.encoder_type, self.eda_type = encoder_type, eda_type
+        self.eda_type = eda_type
 
     def _build_modules(self, in_size, n_units, n_heads, n_layers, dim_feedforward, dropout):
         self.linear = nn.Linear(in_size, n_units)
         self.linear_norm = nn.LayerNorm(n_units)
-        layer = TransformerEncoderLayer(n_units, n_heads, dim_feedforward, dropout, batch_first=True)
-        self.encoder = TransformerEncoder(layer, n_layers, enable_nested_tensor=False)
+        if self.encoder_type == "transformer":
+            layer = TransformerEncoderLayer(n_units, n_heads, dim_feedforward, dropout, batch_first=True)
+            self.encoder = TransformerEncoder(layer, n_layers, enable_nested_tensor=False)
+        else:
+            from torchaudio.models import Conformer      # parameter container only (models.py:501)
+            self.encoder = Conformer(input_dim=n_units, num_heads=n_heads, ffn_dim=dim_feedforward,
+                                     num_layers=n_layers, depthwise_conv_kernel_size=31)
+
+    # ------------------------------------------------------------- Conformer encoder --------
+    def _prepared(self):
+        if self.encoder_type == "transformer":
+            return super()._prepared()
+        if self._plist is None:
+            self._plist = list(self.parameters()) + list(self.buffers())
+        key = tuple((p.data_ptr(), p._version) for p in self._plist)
+        if self._prep is None or self._prep[0] != key:
+            g = lambda t: t.detach().float().contiguous()
+            sp = lambda t: ops.split_bf16(g(t))
+            kpad = _round_up(self.in_size, 16)
+            w = g(self.linear.weight)
+            w_in = torch.zeros((self.n_units, kpad), dtype=torch.float32, device=w.device)
+            w_in[:, : self.in_size] = w
+            D = self.n_units
+            layers = []
+            for lyr in self.encoder.conformer_layers:
+                d = {}
+                for name, ffn in (("f1", lyr.ffn1), ("f2", lyr.ffn2)):
+                    q = ffn.sequential
+                    d[name] = dict(g=g(q[0].weight), be=g(q[0].bias), w1=sp(q[1].weight), b1=g(q[1].bias),
+                                   w2=sp(q[4].weight), b2=g(q[4].bias))
+                d["att"] = dict(g=g(lyr.self_attn_layer_norm.weight), be=g(lyr.self_attn_layer_norm.bias),
+                                w_qkv=sp(lyr.self_attn.in_proj_weight), b_qkv=g(lyr.self_attn.in_proj_bias),
+                                w_o=sp(lyr.self_attn.out_proj.weight), b_o=g(lyr.self_attn.out_proj.bias))
+                cm = lyr.conv_module
+                q = cm.sequential
+                # GLU pairs channel c with c + D: interleave the pointwise rows in blocks of 32 (a-block, gate-block)
+                # so that a pair lands in one thread of the GEMM epilogue (EDA_EPI_BIAS_GLU)
+                idx = torch.arange(D, device=w.device).view(D // 32, 32)
+                order = torch.stack([idx, idx + D], dim=1).reshape(-1)
+                bn = q[3]
+                scale = g(bn.weight) / torch.sqrt(g(bn.running_var) + bn.eps)
+                d["conv"] = dict(g=g(cm.layer_norm.weight), be=g(cm.layer_norm.bias),
+                                 w_pw1=sp(g(q[0].weight).view(2 * D, D)[order]), b_pw1=g(q[0].bias)[order].contiguous(),
+                                 w_dw=g(q[2].weight).view(D, -1).contiguous(), scale=scale.contiguous(),
+                                 shift=((g(q[2].bias) - g(bn.running_mean)) * scale + g(bn.bias)).contiguous(),
+                                 w_pw2=sp(g(q[5].weight).view(D, D)), b_pw2=g(q[5].bias))
+                d["fin"] = dict(g=g(lyr.final_layer_norm.weight), be=g(lyr.final_layer_norm.bias))
+                layers.append(d)
+            prep = dict(kpad=kpad, ws_in=ops.split_bf16(w_in), b_in=g(self.linear.bias), g_in=g(self.linear_norm.weight),
+                        be_in=g(self.linear_norm.bias), layers=layers)
+            self._prep = (key, prep)
+        return self._prep[1]
+
+    def _embed(self, src, ilens: Optional[List[int]] = None):
+        if self.encoder_type == "transformer":
+            return super()._embed(src, ilens)
+        dev = self._device()
+        if self.training:
+            raise NotImplementedError("the Conformer variant runs in eval() mode only (no backward kernels, BatchNorm "
+                                      "uses its running statistics)")
+        P = self.precision
+        if P == L.PREC_FP32:
+            raise NotImplementedError("the Conformer variant runs on the tensor-core pipeline: precision 'bf16x3' or 'bf16'")
+        w = self._prepared()
+        flat_in = ilens is not None
+        if not flat_in:
+            ilens = [int(x.shape[0]) for x in src]
+        B, Tmax = len(ilens), max(ilens)
+        off = np.zeros(B + 1, dtype=np.int64)
+        np.cumsum(ilens, out=off[1:])
+        meta = torch.from_numpy(np.concatenate([off, np.asarray(ilens, dtype=np.int64)])).to(dev, non_blocking=True)
+        seq_off, lens_dev = meta[: B + 1], meta[B + 1:].to(torch.int32)
+        flat = src if flat_in else self._to_device_flat(src, dev)
+        M, D, H, FF = B * Tmax, self.n_units, self.n_heads, self.dim_feedforward
+        key = ("conformer", B, Tmax, str(dev), self.workspace_slot)
+        ws = self._ws.get(key)
+        if ws is None:
+            Tp = _round_up(Tmax, 8)
+            f32 = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
+            ws = dict(Tp=Tp, xin=ops.Split.empty(M, w["kpad"], dev), xa=f32(M, D), xb=f32(M, D), glu=f32(M, D),
+                      sa=ops.Split.empty(M, D, dev), sb=ops.Split.empty(M, D, dev), ff=ops.Split.empty(M, FF, dev),
+                      qk=ops.Split.empty(M, 2 * D, dev), vt=ops.Split.empty(B * H * (D // H), Tp, dev),
+                      att=ops.Split.empty(M, D, dev), emb_s=ops.Split.empty(M, D, dev), xproj=f32(M, 4 * D))
+            self._ws[key] = ws
+        Tp, xa, xb, sa, sb, ff = ws["Tp"], ws["xa"], ws["xb"], ws["sa"], ws["sb"], ws["ff"]
+        ops.pad_pack_split(flat, seq_off, lens_dev, B, Tmax, ws["xin"], -1.0)
+        ops.gemm_split(ws["xin"], w["ws_in"], w["b_in"], M, D, ws["xin"].ld, L.EPI_BIAS_LN, P, gamma=w["g_in"],
+                       beta=w["be_in"], out=xa)
+        emb = torch.empty((M, D), dtype=torch.float32, device=dev)
+        n_layers = len(w["layers"])
+        for i, lw in enumerate(w["layers"]):
+            f1, at, cv, f2, fin = lw["f1"], lw["att"], lw["conv"], lw["f2"], lw["fin"]
+            # x = 0.5 * ffn1(x) + x
+            ops.layernorm_split(xa, f1["g"], f1["be"], out_split=sa)
+            ops.gemm_split_ex(sa, f1["w1"], f1["b1"], M, FF, D, L.EPI_BIAS_SILU, P, out_split=ff)
+            ops.gemm_split_ex(ff, f1["w2"], f1["b2"], M, D, FF, L.EPI_BIAS_RES, P, resid=xa, out=xb, out_scale=0.5)
+            # x = self_attn(LN(x), key_padding_mask) + x
+            ops.layernorm_split(xb, at["g"], at["be"], out_split=sa)
+            ops.gemm_qkv(sa, at["w_qkv"], at["b_qkv"], ws["qk"], ws["vt"], B, Tmax, Tp, D, H, P)
+            ops.mha_split_masked(ws["qk"], ws["vt"], B, Tmax, Tp, H, lens_dev, self.attn_precision, ws["att"])
+            ops.gemm_split_ex(ws["att"], at["w_o"], at["b_o"], M, D, D, L.EPI_BIAS_RES, P, resid=xb, out=xa)
+            # x = x + conv_module(x)
+            ops.layernorm_split(xa, cv["g"], cv["be"], out_split=sa)
+            ops.gemm_split_ex(sa, cv["w_pw1"], cv["b_pw1"], M, 2 * D, D, L.EPI_BIAS_GLU, P, out=ws["glu"])
+            ops.dwconv_bn_silu(ws["glu"], cv["w_dw"], cv["scale"], cv["shift"], B, Tmax, sb)
+            ops.gemm_split_ex(sb, cv["w_pw2"], cv["b_pw2"], M, D, D, L.EPI_BIAS_RES, P, resid=xa, out=xb)
+            # x = final_layer_norm(0.5 * ffn2(x) + x)
+            ops.layernorm_split(xb, f2["g"], f2["be"], out_split=sa)
+            ops.gemm_split_ex(sa, f2["w1"], f2["b1"], M, FF, D, L.EPI_BIAS_SILU, P, out_split=ff)
+            last = i == n_layers - 1
+            ops.gemm_split_ex(ff, f2["w2"], f2["b2"], M, D, FF, L.EPI_BIAS_RES_LN, P, resid=xb, gamma=fin["g"],
+                              beta=fin["be"], out=emb if last else xa, out_split=ws["emb_s"] if last else None,
+                              out_scale=0.5)
+        if n_layers == 0:
+            emb.copy_(xa)
+            ops.split_bf16(emb, out=ws["emb_s"])
+        self._emb_split = (ws["emb_s"], ws["xproj"])
+        return emb, ilens, lens_dev, seq_off, B, Tmax
+
+    def forward(self, src: List[Tensor], ts: List[Tensor], has_mask=False, activation=None):
+        """models.py:563-599."""
+        if self.encoder_type == "conformer" and self.training:
+            raise NotImplementedError("the Conformer variant has no backward kernels: call .eval() (as the reference's dev "
+                                      "loop does, train_eda.py:205)")
+        return super().forward(src, ts, has_mask, activation)
 
     @torch.no_grad()
     def infer(self, src: List[Tensor], infer_num_speakers=None, max_n_speakers=15, attractor_threshold=0.5,

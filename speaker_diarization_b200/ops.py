@@ -201,3 +201,38 @@ def mha_split(qk: Split, vt: Split, B: int, T: int, Tp: int, n_heads: int, prec:
            L.ptr(out), out.stride(0) if out is not None else 0,
            L.ptr(out_split.hi) if out_split else None, L.ptr(out_split.lo) if out_split else None,
            out_split.ld if out_split else 0, prec, L.stream())
+
+
+# ------------------------------------------------------------------ Conformer variant --------
+def gemm_split_ex(a: Split, w: Split, bias: Optional[Tensor], M: int, N: int, K: int, epilogue: int, prec: int,
+                  resid: Optional[Tensor] = None, gamma: Optional[Tensor] = None, beta: Optional[Tensor] = None,
+                  out: Optional[Tensor] = None, out_split: Optional[Split] = None, out_scale: float = 1.0) -> None:
+    """gemm_split + the SiLU / GLU / residual epilogues and a scale on the GEMM term of the residual ones."""
+    L.call("eda_gemm_split_ex", L.ptr(a.hi), L.ptr(a.lo), a.ld, L.ptr(w.hi), L.ptr(w.lo), w.ld, L.ptr(bias),
+           L.ptr(resid), resid.stride(0) if resid is not None else 0, L.ptr(gamma), L.ptr(beta),
+           L.ptr(out), out.stride(0) if out is not None else 0,
+           L.ptr(out_split.hi) if out_split else None, L.ptr(out_split.lo) if out_split else None,
+           out_split.ld if out_split else 0, float(out_scale), M, N, K, epilogue, prec, L.stream())
+
+
+def layernorm_split(x: Tensor, gamma: Tensor, beta: Tensor, out_split: Optional[Split] = None,
+                    out: Optional[Tensor] = None) -> None:
+    M, D = x.shape
+    L.call("eda_layernorm_split", L.ptr(_f32(x)), x.stride(0), L.ptr(gamma), L.ptr(beta), M, D,
+           L.ptr(out), out.stride(0) if out is not None else 0,
+           L.ptr(out_split.hi) if out_split else None, L.ptr(out_split.lo) if out_split else None,
+           out_split.ld if out_split else 0, L.stream())
+
+
+def dwconv_bn_silu(x: Tensor, w: Tensor, scale: Tensor, shift: Tensor, B: int, T: int, out_split: Split) -> None:
+    """x (B*T, 256) fp32 -> silu(scale * depthwise_conv31(x) + shift) as a split pair."""
+    C, K = w.shape
+    L.call("eda_dwconv_bn_silu", L.ptr(_f32(x)), x.stride(0), L.ptr(_f32(w)), L.ptr(scale), L.ptr(shift), B, T, C, K,
+           L.ptr(out_split.hi), L.ptr(out_split.lo), out_split.ld, L.stream())
+
+
+def mha_split_masked(qk: Split, vt: Split, B: int, T: int, Tp: int, n_heads: int, key_lens: Tensor, prec: int,
+                     out_split: Split) -> None:
+    assert key_lens.dtype == torch.int32
+    L.call("eda_mha_split_masked", L.ptr(qk.hi), L.ptr(qk.lo), qk.ld, L.ptr(vt.hi), L.ptr(vt.lo), Tp, B, T, n_heads,
+           L.ptr(key_lens), L.ptr(out_split.hi), L.ptr(out_split.lo), out_split.ld, prec, L.stream())

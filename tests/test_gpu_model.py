@@ -310,4 +310,4 @@ def test_eend_eda_model_transformer_variant(manifest):
     loss, stats = m(src, ts)
     assert abs(loss.item() - float(g["loss"])) < 1e-3 and abs(stats["der"] - float(g["der"])) < 1e-3
     with pytest.raises(NotImplementedError):
-        EendEdaModel(2, cfg.in_size, 4, 256, 2, encoder_type="conformer")
+        EendEdaModel(2, cfg.in_size, 4, 256, 2, encoder_type="rnn")          # models.py:503

@@ -241,19 +241,30 @@ int eda_rttm_segments(const float* post, const uint8_t* labels, int ld, const in
  * quantities the backward kernels need.  Gradient GEMMs run on the same tcgen05 kernel as the
  * forward (prec = EDA_PREC_BF16X3 or EDA_PREC_BF16).                                         */
 
-/* eda_gemm_split with a LayerNorm epilogue that also stores rstd (M) = 1/sqrt(var + eps) per row. */
+/* Dropout (nn.TransformerEncoderLayer in train() mode: on the attention weights, after out_proj, after the
+ * ReLU, after linear2) is a counter-based Philox4x32-7 function of (seed, site, row, column): element
+ * (row, col) is kept iff word (col & 3) of philox(key = seed, counter = (col >> 2, row, site, 0)) >= p * 2^32,
+ * kept values are multiplied by 1 / (1 - p).  The forward epilogues and the backward kernels evaluate the
+ * same function, so no mask is stored; eda_dropout_mask writes one out (tests).  For the attention weights
+ * row = (b * n_heads + h) * T + query, col = key.                                                          */
+int eda_dropout_mask(float p_drop, uint64_t seed, int site, int64_t rows, int cols, uint8_t* keep, void* stream);
+
+/* eda_gemm_split for model.train(): LayerNorm epilogues also store rstd (M) = 1/sqrt(var + eps) per row
+ * (rstd_out may be NULL); p_drop > 0 applies dropout to relu(A.W^T + bias) (EDA_EPI_BIAS_RELU) or to
+ * A.W^T + bias before the residual is added (EDA_EPI_BIAS_RES_LN).                                          */
 int eda_gemm_split_train(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
                          const float* bias, const float* resid, int ldr, const float* ln_gamma, const float* ln_beta,
-                         float* C, int ldc, void* c_hi, void* c_lo, int ldcs, float* rstd_out, int M, int N, int K,
-                         int epilogue, int prec, void* stream);
+                         float* C, int ldc, void* c_hi, void* c_lo, int ldcs, float* rstd_out, float p_drop,
+                         uint64_t seed, int site, int M, int N, int K, int epilogue, int prec, void* stream);
 
 /* Input gradient of nn.Linear: dX (M, K_in) = dY (M, N_out) . W, with W handed over TRANSPOSED
  * (wt = W^T, (K_in, N_out) row-major split pair, so the contraction index is contiguous).
  * Optional fusions: + resid (fp32 (M, K_in): the other branch of a residual join; K_in == 256)
- * or zeroing where relu_mask_hi (bf16 (M, K_in), the forward activation) is <= 0.
+ * or zeroing where relu_mask_hi (bf16 (M, K_in), the forward activation) is <= 0, kept values times
+ * mask_scale (1 / (1 - p) when the activation went through dropout).
  * Outputs: fp32 dX and/or split dx_hi/dx_lo.                                                   */
 int eda_gemm_dgrad(const void* dy_hi, const void* dy_lo, int ld_dy, const void* wt_hi, const void* wt_lo, int ldw,
-                   const float* resid, int ldr, const void* relu_mask_hi, int ldm, float* dX, int ldx,
+                   const float* resid, int ldr, const void* relu_mask_hi, int ldm, float mask_scale, float* dX, int ldx,
                    void* dx_hi, void* dx_lo, int ldxs, int M, int K_in, int N_out, int prec, void* stream);
 
 /* Weight gradient of nn.Linear: dW (N_out, K_in) (+)= dY^T (N_out, M) . X (M, K_in).  Both operands
@@ -267,11 +278,13 @@ int eda_gemm_wgrad(const void* dy_hi, const void* dy_lo, int ld_dy, const void* 
 
 /* nn.LayerNorm(256) backward from the forward OUTPUT y (xhat = (y - beta) / gamma; gamma != 0)
  * and the saved rstd: dx fp32 and/or split; dgamma, dbeta and (optional) the column sums of dx
- * (= bias gradient of the Linear feeding the norm).  workspace >= 592 * 3 KB.                   */
+ * (= bias gradient of the Linear feeding the norm).  workspace >= 592 * 3 KB.  With p_drop > 0 the
+ * split output and the column sums carry the forward's dropout mask of `site` (the Linear branch),
+ * the fp32 dx (residual branch) does not.                                                         */
 int eda_ln_bwd(const float* dy, int ld_dy, const float* y, int ld_y, const float* gamma, const float* beta,
                const float* rstd, int M, int D, float* dx, int ld_dx, void* dx_hi, void* dx_lo, int ld_dxs,
                float* dgamma, float* dbeta, float* dcolsum, void* workspace, int64_t workspace_bytes, int accumulate,
-               void* stream);
+               float p_drop, uint64_t seed, int site, void* stream);
 
 /* out (N) (+)= column sums of a split matrix (M, N): bias gradients.  N % 8 == 0, N <= 2048;
  * workspace >= 592 * N * 4 B.                                                                    */
@@ -281,7 +294,7 @@ int eda_colsum_split(const void* hi, const void* lo, int M, int N, int ld, float
 /* eda_mha_split that also stores lse (B*n_heads, T): log2-domain log-sum-exp of every score row. */
 int eda_mha_split_train(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
                         int Tp, int B, int T, int n_heads, void* out_hi, void* out_lo, int ld_os, float* lse,
-                        int prec, void* stream);
+                        float p_drop, uint64_t seed, int site, int prec, void* stream);
 /* delta (B*T, 4) = rowsum over each head's 64 columns of dO * O (both split pairs, D == 256). */
 int eda_mha_delta(const void* do_hi, const void* do_lo, int ld_do, const void* o_hi, const void* o_lo, int ld_o,
                   int M, int D, float* delta, void* stream);
@@ -291,8 +304,8 @@ int eda_mha_delta(const void* do_hi, const void* do_lo, int ld_do, const void* o
  * eda_scale_split(dq_acc, 1/8) into columns [0, D) of dqkv.                                      */
 int eda_mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
                 const void* do_hi, const void* do_lo, int ld_do, const float* lse, const float* delta, int B,
-                int T, int n_heads, float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, int prec,
-                void* stream);
+                int T, int n_heads, float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, float p_drop,
+                uint64_t seed, int site, int prec, void* stream);
 /* (hi, lo) = split(src * scale): fp32 (rows, cols) -> split pair with row stride ld_s.           */
 int eda_scale_split(const float* src, int ld, int rows, int cols, float scale, void* hi, void* lo, int ld_s, void* stream);
 

@@ -34,20 +34,27 @@ def pad_batch(seqs: Sequence[Tensor], value: float = -1.0) -> Tuple[Tensor, List
     return out, lens
 
 
-def encoder_layer(x: Tensor, sd: Dict[str, Tensor], prefix: str, n_heads: int) -> Tensor:
+def encoder_layer(x: Tensor, sd: Dict[str, Tensor], prefix: str, n_heads: int, drop=None) -> Tensor:
     """One ``nn.TransformerEncoderLayer`` as the reference configures it
     (R/models.py:193: post-LN, ReLU, eps 1e-5, batch_first, no masks at all — padded
-    frames are attended to like any other, models.py:223)."""
+    frames are attended to like any other, models.py:223).
+
+    ``drop`` = (p, (keep_attn (B,H,T,T), keep_out (B,T,D), keep_ffn (B,T,FF), keep_ffn2 (B,T,D))) restates
+    train()-mode dropout with EXPLICIT keep masks at the layer's four sites (attention weights inside
+    nn.MultiheadAttention, dropout1, the dropout after the activation, dropout2); kept values are
+    divided by 1 - p like ``F.dropout``."""
     B, T, D = x.shape
     dh = D // n_heads
+    dz = (lambda t, m: t * m.to(t.dtype) / (1.0 - drop[0])) if drop is not None else (lambda t, m: t)
+    km = drop[1] if drop is not None else (None, None, None, None)
     qkv = F.linear(x, sd[prefix + "self_attn.in_proj_weight"], sd[prefix + "self_attn.in_proj_bias"])
     q, k, v = (t.reshape(B, T, n_heads, dh).transpose(1, 2) for t in qkv.split(D, dim=-1))
-    att = torch.softmax((q @ k.transpose(-1, -2)) * (dh ** -0.5), dim=-1) @ v
+    att = dz(torch.softmax((q @ k.transpose(-1, -2)) * (dh ** -0.5), dim=-1), km[0]) @ v
     att = att.transpose(1, 2).reshape(B, T, D)
-    att = F.linear(att, sd[prefix + "self_attn.out_proj.weight"], sd[prefix + "self_attn.out_proj.bias"])
+    att = dz(F.linear(att, sd[prefix + "self_attn.out_proj.weight"], sd[prefix + "self_attn.out_proj.bias"]), km[1])
     x = F.layer_norm(x + att, (D,), sd[prefix + "norm1.weight"], sd[prefix + "norm1.bias"], 1e-5)
-    ff = F.linear(x, sd[prefix + "linear1.weight"], sd[prefix + "linear1.bias"]).relu_()
-    ff = F.linear(ff, sd[prefix + "linear2.weight"], sd[prefix + "linear2.bias"])
+    ff = dz(F.linear(x, sd[prefix + "linear1.weight"], sd[prefix + "linear1.bias"]).relu(), km[2])
+    ff = dz(F.linear(ff, sd[prefix + "linear2.weight"], sd[prefix + "linear2.bias"]), km[3])
     return F.layer_norm(x + ff, (D,), sd[prefix + "norm2.weight"], sd[prefix + "norm2.bias"], 1e-5)
 
 
@@ -58,13 +65,15 @@ def n_layers_of(sd: Dict[str, Tensor]) -> int:
     return n
 
 
-def encode(padded: Tensor, sd: Dict[str, Tensor], n_heads: int) -> Tensor:
-    """R/models.py:220-223 — Linear → LayerNorm → L encoder layers (has_pos=False)."""
+def encode(padded: Tensor, sd: Dict[str, Tensor], n_heads: int, drop=None) -> Tensor:
+    """R/models.py:220-223 — Linear → LayerNorm → L encoder layers (has_pos=False).
+    ``drop`` = (p, [per-layer keep-mask 4-tuples]) for train()-mode dropout with explicit masks."""
     D = sd["encoder.weight"].shape[0]
     x = F.linear(padded, sd["encoder.weight"], sd["encoder.bias"])
     x = F.layer_norm(x, (D,), sd["encoder_norm.weight"], sd["encoder_norm.bias"], 1e-5)
     for l in range(n_layers_of(sd)):
-        x = encoder_layer(x, sd, f"transformer_encoder.layers.{l}.", n_heads)
+        x = encoder_layer(x, sd, f"transformer_encoder.layers.{l}.", n_heads,
+                          None if drop is None else (drop[0], drop[1][l]))
     return x
 
 
@@ -245,7 +254,7 @@ class OracleEda:
 # ---------------------------------------------------------------- training step
 def forward_backward(state_dict: Dict[str, Tensor], src: Sequence[Tensor], ts: Sequence[Tensor],
                      n_heads: int = 4, diar_weight: float = 1.0, attractor_weight: float = 1.0,
-                     library_lstm: bool = True):
+                     library_lstm: bool = True, drop=None):
     """R/models.py:236-263 followed by ``loss.backward()`` (R/train_eda.py:182-190), dropout-free.
 
     Returns (loss, {state_dict key: gradient}).  The random frame shuffle is drawn from the global
@@ -255,7 +264,7 @@ def forward_backward(state_dict: Dict[str, Tensor], src: Sequence[Tensor], ts: S
     sd = {k: v.detach().float().cpu().clone().requires_grad_(True) for k, v in state_dict.items()}
     padded, lens = pad_batch(src, -1.0)
     with torch.enable_grad():
-        emb = encode(padded, sd, n_heads)
+        emb = encode(padded, sd, n_heads, drop)        # drop = (p, per-layer explicit keep masks) or None
         perms = draw_shuffle(lens)
         label, _ = pad_batch(ts, -1.0)
         S = label.shape[2]

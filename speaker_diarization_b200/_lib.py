@@ -19,7 +19,7 @@ EPI_BIAS_RES, EPI_RELU_MASK, EPI_BIAS_SILU, EPI_BIAS_GLU = 5, 6, 7, 8
 PREC_FP32, PREC_BF16X3, PREC_BF16 = 0, 1, 2
 PRECISIONS = {"fp32": PREC_FP32, "bf16x3": PREC_BF16X3, "bf16": PREC_BF16}
 
-_p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
+_p, _i, _i64, _f, _u64 = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint64
 
 # name -> (restype, argtypes); must list every symbol include/eda_b200.h declares
 SIGNATURES = {
@@ -49,14 +49,15 @@ SIGNATURES = {
     "eda_frame_labels": (_i, [_p, _p, _p, _p, _i64, _p, _p, _p, _p, _i, _i64, _i, C.c_double, _i, _i, _p, _i, _i, _p]),
     "eda_rttm_segments": (_i, [_p, _p, _i, _p, _i, _p, _i, _f, _i, _i, _p, _p, _p]),
     # ---- training step
-    "eda_gemm_split_train": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p]),
-    "eda_gemm_dgrad": (_i, [_p, _p, _i, _p, _p, _i, _p, _i, _p, _i, _p, _i, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "eda_dropout_mask": (_i, [_f, _u64, _i, _i64, _i, _p, _p]),
+    "eda_gemm_split_train": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _p, _f, _u64, _i, _i, _i, _i, _i, _i, _p]),
+    "eda_gemm_dgrad": (_i, [_p, _p, _i, _p, _p, _i, _p, _i, _p, _i, _f, _p, _i, _p, _p, _i, _i, _i, _i, _i, _p]),
     "eda_gemm_wgrad": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i64, _i, _i, _p]),
-    "eda_ln_bwd": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _i, _p, _i, _p, _p, _i, _p, _p, _p, _p, _i64, _i, _p]),
+    "eda_ln_bwd": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _i, _p, _i, _p, _p, _i, _p, _p, _p, _p, _i64, _i, _f, _u64, _i, _p]),
     "eda_colsum_split": (_i, [_p, _p, _i, _i, _i, _p, _p, _i64, _i, _p]),
-    "eda_mha_split_train": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _p, _i, _p, _i, _p]),
+    "eda_mha_split_train": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _p, _i, _p, _f, _u64, _i, _i, _p]),
     "eda_mha_delta": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _p, _p]),
-    "eda_mha_bwd": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _i, _i, _i, _p, _p, _p, _i, _i, _p]),
+    "eda_mha_bwd": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _i, _i, _i, _p, _p, _p, _i, _f, _u64, _i, _i, _p]),
     "eda_scale_split": (_i, [_p, _i, _i, _i, _f, _p, _p, _i, _p]),
     "eda_lstm_attractors_train": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "eda_lstm_attractors_bwd": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p]),

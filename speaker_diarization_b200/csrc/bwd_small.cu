@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(256)
 ln_bwd_kernel(const float* __restrict__ dy, int ld_dy, const float* __restrict__ y, int ld_y,
               const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ rstd,
               int M, float* __restrict__ dx, int ld_dx, bf16* __restrict__ dx_hi, bf16* __restrict__ dx_lo, int ld_s,
-              float* __restrict__ part) {
+              float* __restrict__ part, const DropoutCfg drop) {
   __shared__ float red[8][3][256];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c0 = lane * 4, c1 = 128 + lane * 4;
@@ -92,14 +92,21 @@ ln_bwd_kernel(const float* __restrict__ dy, int ld_dy, const float* __restrict__
     const float rs = __ldg(rstd + row);
     float o[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      o[j] = rs * (a[j] - s1 - xh[j] * s2);
-      a_cs[j] += o[j];
-    }
-    if (dx) {
+    for (int j = 0; j < 8; ++j) o[j] = rs * (a[j] - s1 - xh[j] * s2);
+    if (dx) {        // the residual branch sees the undropped gradient
       *reinterpret_cast<float4*>(dx + (size_t)row * ld_dx + c0) = make_float4(o[0], o[1], o[2], o[3]);
       *reinterpret_cast<float4*>(dx + (size_t)row * ld_dx + c1) = make_float4(o[4], o[5], o[6], o[7]);
     }
+    if (drop.thresh) {   // the Linear branch went through dropout in the forward: same mask, same scale
+      const uint32_t k0 = dropout_keep4(drop, (uint32_t)row, (uint32_t)lane), k1 = dropout_keep4(drop, (uint32_t)row, 32u + lane);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        o[j] = (k0 >> j) & 1u ? o[j] * drop.scale : 0.f;
+        o[4 + j] = (k1 >> j) & 1u ? o[4 + j] * drop.scale : 0.f;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a_cs[j] += o[j];
     if (dx_hi) {
       split_store2(dx_hi + (size_t)row * ld_s + c0, dx_lo + (size_t)row * ld_s + c0, o[0], o[1]);
       split_store2(dx_hi + (size_t)row * ld_s + c0 + 2, dx_lo + (size_t)row * ld_s + c0 + 2, o[2], o[3]);
@@ -123,7 +130,8 @@ ln_bwd_kernel(const float* __restrict__ dy, int ld_dy, const float* __restrict__
 
 int ln_bwd(const float* dy, int ld_dy, const float* y, int ld_y, const float* gamma, const float* beta,
            const float* rstd, int M, int D, float* dx, int ld_dx, void* dx_hi, void* dx_lo, int ld_s,
-           float* dgamma, float* dbeta, float* dcolsum, float* work, size_t work_bytes, int accumulate, cudaStream_t st) {
+           float* dgamma, float* dbeta, float* dcolsum, float* work, size_t work_bytes, int accumulate,
+           const DropoutCfg& drop, cudaStream_t st) {
   EDA_REQUIRE(D == 256, "eda_ln_bwd: D must be 256 (got %d)", D);
   EDA_REQUIRE(dy && y && gamma && beta && rstd && work && M > 0 && (dx || dx_hi), "eda_ln_bwd: bad arguments");
   EDA_REQUIRE(ld_dy % 4 == 0 && ld_y % 4 == 0 && ((uintptr_t)dy | (uintptr_t)y | (uintptr_t)gamma | (uintptr_t)beta) % 16 == 0, "eda_ln_bwd: inputs must be 16B aligned");
@@ -131,7 +139,7 @@ int ln_bwd(const float* dy, int ld_dy, const float* y, int ld_y, const float* ga
   EDA_REQUIRE(!dx_hi || (dx_lo && ld_s % 2 == 0), "eda_ln_bwd: split output needs both halves");
   const int n_cta = std::min(LNB_CTAS, ceil_div(M, 8));
   EDA_REQUIRE(work_bytes >= (size_t)n_cta * 768 * sizeof(float), "eda_ln_bwd: workspace too small (%d CTAs x 3 KB)", n_cta);
-  ln_bwd_kernel<<<n_cta, 256, 0, st>>>(dy, ld_dy, y, ld_y, gamma, beta, rstd, M, dx, ld_dx, (bf16*)dx_hi, (bf16*)dx_lo, ld_s, work);
+  ln_bwd_kernel<<<n_cta, 256, 0, st>>>(dy, ld_dy, y, ld_y, gamma, beta, rstd, M, dx, ld_dx, (bf16*)dx_hi, (bf16*)dx_lo, ld_s, work, drop);
   EDA_LAUNCH_CHECK();
   partial_finish_kernel<<<ceil_div(3 * 256, 32), 256, 0, st>>>(work, n_cta, 3, 256, dgamma, dbeta, dcolsum, accumulate);
   EDA_LAUNCH_CHECK();
@@ -362,6 +370,26 @@ int scale_split(const float* src, int ld, int rows, int cols, float scale, void*
   return EDA_OK;
 }
 
+// keep[row][col] of one dropout site (test / debugging aid: the kernels never materialise a mask)
+__global__ void dropout_mask_kernel(const DropoutCfg d, int64_t rows, int cols, uint8_t* __restrict__ keep) {
+  const int64_t n = rows * (int64_t)(cols / 4);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / (cols / 4);
+    const int g = (int)(i % (cols / 4));
+    const uint32_t k = d.thresh ? dropout_keep4(d, (uint32_t)r, (uint32_t)g) : 0xfu;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) keep[r * cols + 4 * g + e] = (k >> e) & 1u;
+  }
+}
+
+int dropout_mask(float p, uint64_t seed, int site, int64_t rows, int cols, uint8_t* keep, cudaStream_t st) {
+  EDA_REQUIRE(keep && rows > 0 && cols > 0 && cols % 4 == 0 && p >= 0.f && p < 1.f, "eda_dropout_mask: bad arguments (cols %% 4 == 0)");
+  const int64_t n = rows * (int64_t)(cols / 4);
+  dropout_mask_kernel<<<(int)std::min<int64_t>(ceil_div<int64_t>(n, 256), num_sms() * 16), 256, 0, st>>>(make_dropout(p, seed, site), rows, cols, keep);
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
+}
+
 // ------------------------------------------------------------ gradient scaling, Adam ---------
 __global__ void scale_dev_kernel(const float* __restrict__ scale, float* __restrict__ x, int64_t n) {
   const float s = __ldg(scale);
@@ -407,9 +435,15 @@ extern "C" {
 int eda_ln_bwd(const float* dy, int ld_dy, const float* y, int ld_y, const float* gamma, const float* beta,
                const float* rstd, int M, int D, float* dx, int ld_dx, void* dx_hi, void* dx_lo, int ld_dxs,
                float* dgamma, float* dbeta, float* dcolsum, void* workspace, int64_t workspace_bytes, int accumulate,
-               void* stream) {
+               float p_drop, uint64_t seed, int site, void* stream) {
+  EDA_REQUIRE(p_drop >= 0.f && p_drop < 1.f, "eda_ln_bwd: bad dropout probability");
   return eda::ln_bwd(dy, ld_dy, y, ld_y, gamma, beta, rstd, M, D, dx, ld_dx, dx_hi, dx_lo, ld_dxs, dgamma, dbeta,
-                     dcolsum, (float*)workspace, (size_t)workspace_bytes, accumulate, (cudaStream_t)stream);
+                     dcolsum, (float*)workspace, (size_t)workspace_bytes, accumulate, eda::make_dropout(p_drop, seed, site),
+                     (cudaStream_t)stream);
+}
+
+int eda_dropout_mask(float p_drop, uint64_t seed, int site, int64_t rows, int cols, uint8_t* keep, void* stream) {
+  return eda::dropout_mask(p_drop, seed, site, rows, cols, keep, (cudaStream_t)stream);
 }
 
 int eda_colsum_split(const void* hi, const void* lo, int M, int N, int ld, float* out, void* workspace,

@@ -68,6 +68,38 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// ---- dropout (training step): counter-based Philox4x32-7, the same function in the forward
+// epilogues, the backward kernels and eda_dropout_mask (tests), so a mask is never stored.
+// Element (row, col) of site `site` keeps its value iff word (col & 3) of
+// philox(key = seed, counter = (col >> 2, row, site, 0)) >= thresh = p * 2^32.
+struct DropoutCfg {
+  uint32_t thresh;       // 0 = dropout off
+  uint32_t seed_lo, seed_hi, site;
+  float scale;           // 1 / (1 - p)
+};
+__host__ __device__ inline DropoutCfg make_dropout(float p, uint64_t seed, int site) {
+  DropoutCfg d;
+  d.thresh = p > 0.f ? (uint32_t)((double)p * 4294967296.0) : 0u;
+  d.seed_lo = (uint32_t)seed; d.seed_hi = (uint32_t)(seed >> 32); d.site = (uint32_t)site;
+  d.scale = p > 0.f ? 1.0f / (1.0f - p) : 1.0f;
+  return d;
+}
+__device__ __forceinline__ uint4 philox4x32_7(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 7; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    c0 = hi1 ^ c1 ^ k0; c1 = lo1; c2 = hi0 ^ c3 ^ k1; c3 = lo0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+// keep-bits of the 4 elements (row, 4 * colgroup .. + 3): bit j set = element kept
+__device__ __forceinline__ uint32_t dropout_keep4(const DropoutCfg& d, uint32_t row, uint32_t colgroup) {
+  const uint4 r = philox4x32_7(colgroup, row, d.site, 0u, d.seed_lo, d.seed_hi);
+  return (r.x >= d.thresh ? 1u : 0u) | (r.y >= d.thresh ? 2u : 0u) | (r.z >= d.thresh ? 4u : 0u) | (r.w >= d.thresh ? 8u : 0u);
+}
+
 // sigmoid the way ATen's CPU/GPU kernels define it: 1 / (1 + exp(-x)), fp32.
 __device__ __forceinline__ float sigmoidf_ref(float x) { return 1.0f / (1.0f + expf(-x)); }
 

@@ -61,6 +61,9 @@ struct GemmParams {
   // QKV variant: rows are (b, t) with t < T; v goes to vt[(b*H + h)*64 + d][t], row stride Tp
   bf16* vt_hi; bf16* vt_lo; int T, Tp, H; float q_scale;
   float out_scale;                         // residual epilogues: C = (A.W^T + bias) * out_scale + resid (0 means 1)
+  DropoutCfg drop;                         // training: dropout on relu(A.W^T + bias) (BIAS_RELU) or on A.W^T + bias before
+                                           // the residual is added (BIAS_RES_LN); thresh == 0 = off
+  float mask_scale;                        // EDA_EPI_RELU_MASK: kept gradients are multiplied by this (0 means 1)
   float* rstd_out;                         // LayerNorm epilogues (training): 1/sqrt(var + eps) per row, optional
   const bf16* mask; int ldm;               // EDA_EPI_RELU_MASK: result is zeroed where mask <= 0
   // weight-gradient form (WG): C[i,j] = sum_r A[r,i] B[r,j] over Kp rows, both operands MN-major;
@@ -73,6 +76,16 @@ __device__ __forceinline__ void split2(float x0, float x1, __nv_bfloat162& hi, _
   hi = __halves2bfloat162(h0, h1);
   lo = __halves2bfloat162(__float2bfloat16_rn(x0 - __bfloat162float(h0)),
                           __float2bfloat16_rn(x1 - __bfloat162float(h1)));
+}
+
+// dropout on 32 consecutive columns col0.. of one row (8 Philox calls)
+__device__ __forceinline__ void apply_dropout32(float (&v)[32], const DropoutCfg& d, int row, int col0) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t keep = dropout_keep4(d, (uint32_t)row, (uint32_t)(col0 >> 2) + j);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) v[4 * j + e] = (keep >> e) & 1u ? v[4 * j + e] * d.scale : 0.f;
+  }
 }
 
 // one 32-byte (full sector) global store
@@ -108,7 +121,9 @@ __global__ void split_bf16_kernel(const float* __restrict__ src, int ld, int row
   }
 }
 
-template <int EPI, bool ST, bool WG>
+// EX: the launch uses the rarely needed epilogue extras (out_scale, dropout); they are compiled out of the
+// plain instantiations so the inference kernels keep their register budget.
+template <int EPI, bool ST, bool WG, bool EX>
 __global__ void __launch_bounds__(G_THREADS, 1)
 gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                   const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
@@ -249,7 +264,6 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
     for (int tile = pair; tile < n_tiles; tile += n_pairs, ++lt) {
       const int mn = WG ? tile % n_mn : tile;
       const int m0 = (mn / n_tiles_n) * 2 * GBM + (int)rank * GBM, n_blk = mn % n_tiles_n, n0 = n_blk * GBN;
-      float* const Cout = WG ? p.C + (size_t)(tile / n_mn) * p.c_slice : p.C;
       const uint32_t ab = lt & 1;
       const int rbase = m0 + q * 32;                              // first global row of this warp
       // residual chunk c of this thread's row (RES_LN): 8 x 16 B, thread-per-row
@@ -280,7 +294,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         if (grow >= p.M || gcol0 >= p.N) return;
         const bool whole = gcol0 + 32 <= p.N;
         if (p.C && EPI != GEPI_QKV) {
-          float* dst = Cout + (size_t)grow * p.ldc + gcol0;
+          float* dst = (WG ? p.C + (size_t)(tile / n_mn) * p.c_slice : p.C) + (size_t)grow * p.ldc + gcol0;
           if (whole && ((uintptr_t)dst & 31) == 0) {
 #pragma unroll
             for (int j = 0; j < 4; ++j)
@@ -404,7 +418,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
           for (int j = 0; j < 32; ++j) a[j] = a[j] * __fdividef(1.f, 1.f + __expf(-g[j]));
           const int grow = rbase + lane;
           if (grow < p.M) {
-            float* dst = Cout + (size_t)grow * p.ldc + colp / 2;
+            float* dst = p.C + (size_t)grow * p.ldc + colp / 2;
 #pragma unroll
             for (int j = 0; j < 4; ++j)
               st_global_v8(dst + 8 * j, __float_as_uint(a[8 * j]), __float_as_uint(a[8 * j + 1]), __float_as_uint(a[8 * j + 2]),
@@ -426,6 +440,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
             if (EPI == EDA_EPI_BIAS_RELU) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+              if (EX && p.drop.thresh) apply_dropout32(v, p.drop, rbase + lane, col0);
             }
             if (EPI == EDA_EPI_BIAS_SILU) {
 #pragma unroll
@@ -447,6 +462,10 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
                     if (!((w[e] & 0x7fff0000u) != 0 && !(w[e] & 0x80000000u))) v[8 * u + 2 * e + 1] = 0.f;
                   }
                 }
+              }
+              if (p.mask_scale != 0.f) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] *= p.mask_scale;
               }
             }
             emit_chunk(v, col0, half, hi, lo, p.Chi, p.Clo, p.lds);
@@ -497,11 +516,15 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
           const int col0 = ch * 128 + c * 32;
           float v[32];
           tmem_ld32(trow + c * 32, v);
-          const bool scaled = p.out_scale != 0.f;      // (warp-uniform) Conformer half-step residuals
+          // (warp-uniform) Conformer half-step residuals / training dropout act on A.W^T + bias BEFORE the residual
+          const bool scaled = EX && (p.out_scale != 0.f || p.drop.thresh != 0);
           if (scaled) {
             add_vec(v, p.bias, col0);
+            if (p.out_scale != 0.f) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] *= p.out_scale;
+              for (int j = 0; j < 32; ++j) v[j] *= p.out_scale;
+            }
+            if (p.drop.thresh) apply_dropout32(v, p.drop, rbase + lane, col0);
           }
           if constexpr (kRes) {
             float4 rn[8];
@@ -541,7 +564,7 @@ gemm_split_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_const
         ln_x[1][ch][xr] = sq;
         asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
         const float rstd = 1.0f / sqrtf((ln_x[1][0][xr] + ln_x[1][1][xr]) * (1.0f / GBN) + 1e-5f);
-        if (p.rstd_out && ch == 0 && rbase + lane < p.M) p.rstd_out[rbase + lane] = rstd;
+        if (EX && p.rstd_out && ch == 0 && rbase + lane < p.M) p.rstd_out[rbase + lane] = rstd;
 #pragma unroll 1
         for (int cp = 0; cp < 2; ++cp) {
           uint32_t hi[32], lo[32];
@@ -672,13 +695,13 @@ int split_bf16(const float* src, int ld, int rows, int K, void* hi, void* lo, in
   return EDA_OK;
 }
 
-template <int EPI, bool ST, bool WG = false>
+template <int EPI, bool ST, bool WG = false, bool EX = false>
 static int launch_gemm2(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi, const CUtensorMap& b_lo,
                         const CUtensorMap& c, const CUtensorMap& c_hi, const CUtensorMap& c_lo, const GemmParams& p,
                         cudaStream_t st) {
   static bool attr = false;
   if (!attr) {
-    EDA_CUDA(cudaFuncSetAttribute(gemm_split_kernel<EPI, ST, WG>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
+    EDA_CUDA(cudaFuncSetAttribute(gemm_split_kernel<EPI, ST, WG, EX>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
     attr = true;
   }
   const int n_tiles = ceil_div(p.N, GBN) * ceil_div(p.M, 2 * GBM) * (WG ? p.ksplit : 1);   // one 256 x 256 tile per CTA pair
@@ -691,7 +714,7 @@ static int launch_gemm2(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const 
   attrs[0].id = cudaLaunchAttributeClusterDimension;
   attrs[0].val.clusterDim.x = 2; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
   cfg.attrs = attrs; cfg.numAttrs = 1;
-  EDA_CUDA(cudaLaunchKernelEx(&cfg, gemm_split_kernel<EPI, ST, WG>, a_hi, a_lo, b_hi, b_lo, c, c_hi, c_lo, p));
+  EDA_CUDA(cudaLaunchKernelEx(&cfg, gemm_split_kernel<EPI, ST, WG, EX>, a_hi, a_lo, b_hi, b_lo, c, c_hi, c_lo, p));
   count_launch();
   return EDA_OK;
 }
@@ -705,7 +728,13 @@ static int launch_gemm(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const C
   bool staged = p.Kp <= 8 * GBK;
   if (c_out && (((uintptr_t)p.C & 15) || (p.ldc & 3))) staged = false;
   if (p.Chi && ((((uintptr_t)p.Chi | (uintptr_t)p.Clo) & 15) || (p.lds & 7))) staged = false;
-  if (!staged) return launch_gemm2<EPI, false>(a_hi, a_lo, b_hi, b_lo, a_hi, a_hi, a_hi, p, st);
+  // the extras exist for the epilogues that can use them (ReLU dropout, residual scale / dropout)
+  constexpr bool kCanEx = EPI == EDA_EPI_BIAS_RELU || EPI == EDA_EPI_BIAS_RES_LN || EPI == EDA_EPI_BIAS_RES || EPI == EDA_EPI_BIAS_LN;
+  const bool ex = kCanEx && (p.out_scale != 0.f || p.drop.thresh != 0 || p.rstd_out != nullptr);
+  if (!staged) {
+    if constexpr (kCanEx) { if (ex) return launch_gemm2<EPI, false, false, true>(a_hi, a_lo, b_hi, b_lo, a_hi, a_hi, a_hi, p, st); }
+    return launch_gemm2<EPI, false>(a_hi, a_lo, b_hi, b_lo, a_hi, a_hi, a_hi, p, st);
+  }
   CUtensorMap c = a_hi, c_hi = a_hi, c_lo = a_hi;        // placeholders for absent outputs (never dereferenced)
   int rc;
   if (c_out && (rc = make_tmap_f32(&c, p.C, p.M, p.N, p.ldc, 32)) != EDA_OK) return rc;
@@ -713,6 +742,7 @@ static int launch_gemm(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const C
     if ((rc = make_tmap_bf16(&c_hi, p.Chi, p.M, n_split_cols, p.lds, 32)) != EDA_OK) return rc;
     if ((rc = make_tmap_bf16(&c_lo, p.Clo, p.M, n_split_cols, p.lds, 32)) != EDA_OK) return rc;
   }
+  if constexpr (kCanEx) { if (ex) return launch_gemm2<EPI, true, false, true>(a_hi, a_lo, b_hi, b_lo, c, c_hi, c_lo, p, st); }
   return launch_gemm2<EPI, true>(a_hi, a_lo, b_hi, b_lo, c, c_hi, c_lo, p, st);
 }
 
@@ -870,24 +900,28 @@ int eda_gemm_split_ex(const void* a_hi, const void* a_lo, int lda, const void* w
 
 int eda_gemm_split_train(const void* a_hi, const void* a_lo, int lda, const void* w_hi, const void* w_lo, int ldw,
                          const float* bias, const float* resid, int ldr, const float* ln_gamma, const float* ln_beta,
-                         float* C, int ldc, void* c_hi, void* c_lo, int ldcs, float* rstd_out, int M, int N, int K,
-                         int epilogue, int prec, void* stream) {
-  EDA_REQUIRE(epilogue == EDA_EPI_BIAS_LN || epilogue == EDA_EPI_BIAS_RES_LN, "eda_gemm_split_train: LayerNorm epilogues only");
+                         float* C, int ldc, void* c_hi, void* c_lo, int ldcs, float* rstd_out, float p_drop,
+                         uint64_t seed, int site, int M, int N, int K, int epilogue, int prec, void* stream) {
+  EDA_REQUIRE(epilogue == EDA_EPI_BIAS_LN || epilogue == EDA_EPI_BIAS_RES_LN || epilogue == EDA_EPI_BIAS_RELU,
+              "eda_gemm_split_train: LayerNorm or ReLU epilogues only");
   EDA_REQUIRE(C || c_hi, "eda_gemm_split_train: no output requested");
+  EDA_REQUIRE(p_drop >= 0.f && p_drop < 1.f && (p_drop == 0.f || epilogue != EDA_EPI_BIAS_LN), "eda_gemm_split_train: bad dropout");
   eda::GemmParams p = {};
   p.bias = bias; p.resid = resid; p.ldr = ldr; p.gamma = ln_gamma; p.beta = ln_beta;
   p.C = C; p.ldc = ldc; p.Chi = (eda::bf16*)c_hi; p.Clo = (eda::bf16*)c_lo; p.lds = ldcs; p.M = M; p.N = N;
   p.rstd_out = rstd_out;
+  p.drop = eda::make_dropout(p_drop, seed, site);
   return eda::gemm_split(a_hi, a_lo, lda, w_hi, w_lo, ldw, p, K, epilogue, prec, (cudaStream_t)stream);
 }
 
 int eda_gemm_dgrad(const void* dy_hi, const void* dy_lo, int ld_dy, const void* wt_hi, const void* wt_lo, int ldw,
-                   const float* resid, int ldr, const void* relu_mask_hi, int ldm, float* dX, int ldx,
+                   const float* resid, int ldr, const void* relu_mask_hi, int ldm, float mask_scale, float* dX, int ldx,
                    void* dx_hi, void* dx_lo, int ldxs, int M, int K_in, int N_out, int prec, void* stream) {
   EDA_REQUIRE(dX || dx_hi, "eda_gemm_dgrad: no output requested");
   EDA_REQUIRE(!(resid && relu_mask_hi), "eda_gemm_dgrad: residual and ReLU mask are mutually exclusive");
   eda::GemmParams p = {};
   p.resid = resid; p.ldr = ldr; p.mask = (const eda::bf16*)relu_mask_hi; p.ldm = ldm;
+  p.mask_scale = mask_scale == 1.0f ? 0.f : mask_scale;
   p.C = dX; p.ldc = ldx; p.Chi = (eda::bf16*)dx_hi; p.Clo = (eda::bf16*)dx_lo; p.lds = ldxs; p.M = M; p.N = K_in;
   const int epi = resid ? EDA_EPI_BIAS_RES : relu_mask_hi ? EDA_EPI_RELU_MASK : EDA_EPI_BIAS;
   return eda::gemm_split(dy_hi, dy_lo, ld_dy, wt_hi, wt_lo, ldw, p, N_out, epi, prec, (cudaStream_t)stream);

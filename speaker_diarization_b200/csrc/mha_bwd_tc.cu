@@ -56,6 +56,7 @@ struct MhaBwdParams {
   float* dq_acc;           // (B*T, H*64) fp32, zeroed by the caller: dq' = dS k summed over key tiles
   bf16* dkv_hi; bf16* dkv_lo; int ld_dkv;     // split (B*T, ld): dk at column dk_col0 + 64h, dv at dv_col0 + 64h
   int dk_col0, dv_col0;
+  DropoutCfg drop;         // the forward's attention-weight dropout (thresh == 0 = off)
 };
 
 __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
@@ -216,13 +217,22 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
         tmem_wait_ld();
         const int key0 = k0 + half * 64 + c * 32;
         uint32_t pw[16], dw[16];
+        uint32_t keep4 = 0xfu;
+        const uint32_t drop_row = (uint32_t)((b * p.H + h) * p.T + q);
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
           float p0 = ex2_approx(fmaf(sv[e], kLog2e, -lse)), p1 = ex2_approx(fmaf(sv[e + 1], kLog2e, -lse));
           if (!q_ok || key0 + e >= p.T) p0 = 0.f;
           if (!q_ok || key0 + e + 1 >= p.T) p1 = 0.f;
-          pw[e >> 1] = pack_bf16x2(p0, p1);
-          dw[e >> 1] = pack_bf16x2(p0 * (dv[e] - dl), p1 * (dv[e + 1] - dl));
+          float pd0 = p0, pd1 = p1, g0 = dv[e], g1 = dv[e + 1];
+          if (p.drop.thresh) {     // O = (D * P / (1-p)) V: dV sees the dropped weights, dP = D * d(dropped) / (1-p)
+            if ((e & 3) == 0) keep4 = dropout_keep4(p.drop, drop_row, (uint32_t)(key0 + e) >> 2);
+            const bool k0b = (keep4 >> (e & 3)) & 1u, k1b = (keep4 >> ((e & 3) + 1)) & 1u;
+            pd0 = k0b ? p0 * p.drop.scale : 0.f; pd1 = k1b ? p1 * p.drop.scale : 0.f;
+            g0 = k0b ? g0 * p.drop.scale : 0.f; g1 = k1b ? g1 * p.drop.scale : 0.f;
+          }
+          pw[e >> 1] = pack_bf16x2(pd0, pd1);
+          dw[e >> 1] = pack_bf16x2(p0 * (g0 - dl), p1 * (g1 - dl));
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {                        // 16 B units c*4 + u of the 128 B row, XOR-swizzled by row
@@ -289,7 +299,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
 
 int mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
             const void* do_hi, const void* do_lo, int ld_do, const float* lse, const float* delta, int B, int T, int H,
-            float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, int prec, cudaStream_t st) {
+            float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, DropoutCfg drop, int prec, cudaStream_t st) {
   EDA_REQUIRE(qk_hi && qk_lo && vt_hi && vt_lo && do_hi && do_lo && lse && delta && dq_acc && dqkv_hi && dqkv_lo, "eda_mha_bwd: null argument");
   EDA_REQUIRE(B > 0 && T > 0 && H > 0 && ld_qk >= 2 * H * BDH && ld_qk % 8 == 0 && Tp >= T && Tp % 8 == 0 && ld_do % 8 == 0 &&
               ld_dqkv >= 3 * H * BDH && ld_dqkv % 8 == 0, "eda_mha_bwd: bad sizes / strides");
@@ -314,7 +324,7 @@ int mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, 
   p.T = T; p.H = H; p.B = B; p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
   p.lse = lse; p.delta = delta; p.dq_acc = dq_acc;
   p.dkv_hi = (bf16*)dqkv_hi; p.dkv_lo = (bf16*)dqkv_lo; p.ld_dkv = ld_dqkv;
-  p.dk_col0 = H * BDH; p.dv_col0 = 2 * H * BDH;
+  p.dk_col0 = H * BDH; p.dv_col0 = 2 * H * BDH; p.drop = drop;
   const int64_t n_cta = (int64_t)ceil_div(T, BT) * H * B;
   EDA_REQUIRE(n_cta < (int64_t(1) << 31), "eda_mha_bwd: too many (batch, head, key tile) items");
   mha_bwd_tc_kernel<<<(int)n_cta, B_THREADS, B_SMEM, st>>>(tq_hi, tq_lo, tv_hi, tv_lo, tg_hi, tg_lo, p);
@@ -326,8 +336,9 @@ int mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, 
 
 extern "C" int eda_mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
                            const void* do_hi, const void* do_lo, int ld_do, const float* lse, const float* delta, int B,
-                           int T, int n_heads, float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, int prec,
-                           void* stream) {
+                           int T, int n_heads, float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, float p_drop,
+                           uint64_t seed, int site, int prec, void* stream) {
+  EDA_REQUIRE(p_drop >= 0.f && p_drop < 1.f, "eda_mha_bwd: bad dropout probability");
   return eda::mha_bwd(qk_hi, qk_lo, ld_qk, vt_hi, vt_lo, Tp, do_hi, do_lo, ld_do, lse, delta, B, T, n_heads, dq_acc,
-                      dqkv_hi, dqkv_lo, ld_dqkv, prec, (cudaStream_t)stream);
+                      dqkv_hi, dqkv_lo, ld_dqkv, eda::make_dropout(p_drop, seed, site), prec, (cudaStream_t)stream);
 }

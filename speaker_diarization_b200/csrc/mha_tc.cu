@@ -56,6 +56,7 @@ struct MhaParams {
   bf16* out_hi; bf16* out_lo; int ld_os;  // optional split
   float* lse;                             // optional (training): (B*H, T) log2-domain log-sum-exp of each score row
   const int32_t* klens;                   // optional key_padding_mask (Conformer): keys t >= klens[b] are masked out
+  DropoutCfg drop;                        // training: dropout on the attention weights (thresh == 0 = off)
 };
 
 // D[tmem] (+)= A[tmem] * B[smem desc]
@@ -331,6 +332,8 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
       // packed hi pairs in the first 16 columns of the chunk, lo pairs in the last 16
       float l4[4] = {0.f, 0.f, 0.f, 0.f};
       float pk[32];
+      uint32_t keep4 = 0xfu;
+      const uint32_t drop_row = (uint32_t)((b * p.H + h) * p.T + q0 + row_in_tile);
 #pragma unroll
       for (int i = 0; i < 32; i += 2) {
         float p0 = ex2_approx(fmaf(v[i], kLog2e, -m_ref)), p1 = ex2_approx(fmaf(v[i + 1], kLog2e, -m_ref));
@@ -339,6 +342,11 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
           if (i + 1 >= n_valid) p1 = 0.f;
         }
         l4[i & 2] += p0; l4[(i & 2) + 1] += p1;
+        if (p.drop.thresh) {       // nn.MultiheadAttention drops normalised weights: the row sum keeps every term
+          if ((i & 3) == 0) keep4 = dropout_keep4(p.drop, drop_row, (uint32_t)(j * ABN + half * 32 + i) >> 2);
+          p0 = (keep4 >> (i & 3)) & 1u ? p0 * p.drop.scale : 0.f;
+          p1 = (keep4 >> ((i & 3) + 1)) & 1u ? p1 * p.drop.scale : 0.f;
+        }
         const uint32_t hi = pack_bf16x2(p0, p1);
         pk[i >> 1] = __uint_as_float(hi);
         pk[16 + (i >> 1)] = __uint_as_float(pack_bf16x2(p0 - __uint_as_float(hi << 16),
@@ -435,7 +443,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
 // ------------------------------------------------------------------------- host ---------
 int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
               int B, int T, int H, float* out, int ld_out, void* out_hi, void* out_lo, int ld_os, int prec,
-              cudaStream_t st, float* lse = nullptr, const int32_t* klens = nullptr) {
+              cudaStream_t st, float* lse = nullptr, const int32_t* klens = nullptr, DropoutCfg drop = DropoutCfg{}) {
   EDA_REQUIRE(qk_hi && qk_lo && vt_hi && vt_lo && B > 0 && T > 0 && H > 0, "eda_mha_split: bad arguments");
   EDA_REQUIRE(ld_qk >= 2 * H * ADH && ld_qk % 8 == 0 && Tp >= T && Tp % 8 == 0, "eda_mha_split: ld_qk / Tp must be multiples of 8 and large enough");
   EDA_REQUIRE(out || (out_hi && out_lo), "eda_mha_split: no output requested");
@@ -459,7 +467,7 @@ int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi
   MhaParams p = {};
   p.T = T; p.H = H; p.B = B; p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
   p.out = out; p.ld_out = ld_out; p.out_hi = (bf16*)out_hi; p.out_lo = (bf16*)out_lo; p.ld_os = ld_os;
-  p.lse = lse; p.klens = klens;
+  p.lse = lse; p.klens = klens; p.drop = drop;
   const int64_t n_items = (int64_t)ceil_div(T, ABM) * H * B;
   EDA_REQUIRE(n_items < (int64_t(1) << 31), "eda_mha_split: too many (batch, head, query tile) items");
   const int grid = (int)std::min<int64_t>(n_items, (int64_t)A_CTAS_PER_SM * num_sms());
@@ -523,10 +531,10 @@ extern "C" int eda_mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, co
 
 extern "C" int eda_mha_split_train(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
                                    int Tp, int B, int T, int n_heads, void* out_hi, void* out_lo, int ld_os, float* lse,
-                                   int prec, void* stream) {
-  EDA_REQUIRE(lse && out_hi && out_lo, "eda_mha_split_train: null argument");
+                                   float p_drop, uint64_t seed, int site, int prec, void* stream) {
+  EDA_REQUIRE(lse && out_hi && out_lo && p_drop >= 0.f && p_drop < 1.f, "eda_mha_split_train: bad argument");
   return eda::mha_split(qk_hi, qk_lo, ld_qk, vt_hi, vt_lo, Tp, B, T, n_heads, nullptr, 0, out_hi, out_lo, ld_os, prec,
-                        (cudaStream_t)stream, lse);
+                        (cudaStream_t)stream, lse, nullptr, eda::make_dropout(p_drop, seed, site));
 }
 
 extern "C" int eda_mha_split_masked(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,

@@ -154,10 +154,13 @@ class TransformerEdaModel(nn.Module):
         return dev
 
     def _check_mode(self):
+        """The inference-cost forward has no dropout: it serves eval() mode (the reference's dev loop,
+        train_eda.py:205) and train() mode only when dropout is 0; train-mode dropout lives in the
+        training path (training.py), which needs gradients enabled and a tensor-core precision."""
         if self.training and self.dropout_p > 0:
             raise NotImplementedError(
-                "train-mode dropout is not implemented in the CUDA path; call .eval() "
-                "(as the reference's dev loop does, train_eda.py:205) or build with dropout=0")
+                "train-mode dropout runs in the training path only (gradients enabled, precision 'bf16x3' or "
+                "'bf16'); call .eval() for inference or build with dropout=0")
 
     # ------------------------------------------------------------------- encoder --------
     def _to_device_flat(self, seqs: List[Tensor], dev) -> Tensor:

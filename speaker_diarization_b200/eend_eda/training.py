@@ -16,7 +16,13 @@ for ``--optimizer noam``.  Here:
 * ``NoamAdam`` keeps parameters, gradients and Adam moments in flat buffers: one fused Adam kernel
   per step and, under ``torch.distributed``, one NCCL all-reduce of the whole gradient.
 
-Dropout: the kernels have no train-mode dropout; build the model with ``dropout=0`` to train.
+Dropout (``nn.TransformerEncoderLayer`` in train() mode, p = the constructor's ``dropout``): applied at
+the layer's four sites (attention weights, after out_proj, after the ReLU, after linear2) by a counter-based
+Philox function of (seed, site, row, column) that the forward epilogues and the backward kernels both
+evaluate - no mask is stored.  The step's seed derives from ``torch.initial_seed()`` and a step counter
+(``torch.manual_seed`` makes a run repeatable, the global generator is not consumed); the masks are NOT torch's own Philox stream, so with
+dropout > 0 a step matches the reference in distribution, and exactly when the oracle is fed these masks
+(``dropout_sites`` / ``ops_train.dropout_mask``).
 """
 from __future__ import annotations
 
@@ -98,15 +104,41 @@ def train_workspace(model, B: int, Tmax: int, n_dec: int, dev) -> dict:
     return ws
 
 
+# ----------------------------------------------------------------------------- dropout --------
+SITE_ATTN, SITE_OUT, SITE_FFN, SITE_FFN2 = 0, 1, 2, 3
+
+
+def site_id(layer: int, which: int) -> int:
+    return layer * 4 + which
+
+
+def dropout_sites(model, seed: int, B: int, Tmax: int, layer: int, device):
+    """The four keep masks of one layer as torch.nn.TransformerEncoderLayer would apply them (bool tensors):
+    attention weights (B, H, T, T), dropout1 (B, T, D), FFN dropout (B, T, FF), dropout2 (B, T, D)."""
+    p, H, D, FF = model.dropout_p, model.n_heads, model.n_units, model.dim_feedforward
+    Tc = _round_up(Tmax, 4)
+    att = OT.dropout_mask(p, seed, site_id(layer, SITE_ATTN), B * H * Tmax, Tc, device)[:, :Tmax].view(B, H, Tmax, Tmax)
+    d1 = OT.dropout_mask(p, seed, site_id(layer, SITE_OUT), B * Tmax, D, device).view(B, Tmax, D)
+    ff = OT.dropout_mask(p, seed, site_id(layer, SITE_FFN), B * Tmax, FF, device).view(B, Tmax, FF)
+    d2 = OT.dropout_mask(p, seed, site_id(layer, SITE_FFN2), B * Tmax, D, device).view(B, Tmax, D)
+    return att.bool(), d1.bool(), ff.bool(), d2.bool()
+
+
 # ----------------------------------------------------------------------------- forward --------
 def forward_train(model, src: List[Tensor], ts: List[Tensor]):
     """models.py:236-295 with everything the backward pass needs kept in the workspace.
     Returns (loss (0-d), stats dict, saved dict)."""
     dev = model._device()
-    model._check_mode()
     P = model.precision
     if P == L.PREC_FP32:
         raise NotImplementedError("training runs on the tensor-core pipeline: use precision 'bf16x3' or 'bf16'")
+    pd = float(model.dropout_p)
+    # one seed per step from torch's seed and a step counter: repeatable under torch.manual_seed without consuming
+    # the global generator (the frame shuffle must draw the same numbers as the reference's, models.py:229-232)
+    model._drop_step = getattr(model, "_drop_step", 0) + 1
+    seed = ((torch.initial_seed() * 0x9E3779B97F4A7C15 + model._drop_step * 0xD1B54A32D192ED03) & (2 ** 63 - 1)) if pd > 0 else 0
+    model._last_drop_seed = seed
+    drop = lambda layer, which: (pd, seed, site_id(layer, which)) if pd > 0 else OT.NO_DROP
     w = prepared_train(model)
     ilens = [int(x.shape[0]) for x in src]
     B, Tmax = len(ilens), max(ilens)
@@ -127,12 +159,14 @@ def forward_train(model, src: List[Tensor], ts: List[Tensor]):
                         gamma=w["g_in"], beta=w["be_in"], out=x_f[0], out_split=x_s[0])
     for i, (lw, a) in enumerate(zip(w["layers"], ws["layers"])):
         ops.gemm_qkv(x_s[i], lw["sw_qkv"], lw["b_qkv"], a["qk"], a["vt"], B, Tmax, Tp, D, H, P)
-        OT.mha_split_train(a["qk"], a["vt"], B, Tmax, Tp, H, model.attn_precision, a["ctx"], a["lse"])
+        OT.mha_split_train(a["qk"], a["vt"], B, Tmax, Tp, H, model.attn_precision, a["ctx"], a["lse"],
+                           drop=drop(i, SITE_ATTN))
         OT.gemm_split_train(a["ctx"], lw["sw_o"], lw["b_o"], M, D, D, L.EPI_BIAS_RES_LN, P, a["rstd1"], resid=x_f[i],
-                            gamma=lw["g1"], beta=lw["be1"], out=a["y1_f"], out_split=a["y1_s"])
-        ops.gemm_split(a["y1_s"], lw["sw_1"], lw["b_1"], M, FF, D, L.EPI_BIAS_RELU, P, out_split=a["ff"])
+                            gamma=lw["g1"], beta=lw["be1"], out=a["y1_f"], out_split=a["y1_s"], drop=drop(i, SITE_OUT))
+        OT.gemm_split_train(a["y1_s"], lw["sw_1"], lw["b_1"], M, FF, D, L.EPI_BIAS_RELU, P, None, out_split=a["ff"],
+                            drop=drop(i, SITE_FFN))
         OT.gemm_split_train(a["ff"], lw["sw_2"], lw["b_2"], M, D, FF, L.EPI_BIAS_RES_LN, P, a["rstd2"], resid=a["y1_f"],
-                            gamma=lw["g2"], beta=lw["be2"], out=x_f[i + 1], out_split=x_s[i + 1])
+                            gamma=lw["g2"], beta=lw["be2"], out=x_f[i + 1], out_split=x_s[i + 1], drop=drop(i, SITE_FFN2))
     emb, emb_s = x_f[-1], x_s[-1]
     label = ops.pad_pack(model._to_device_flat(list(ts), dev), seq_off, lens_dev, B, Tmax, S, -1.0).view(B, Tmax, S)
     perm = model._draw_perm(ilens, Tmax, dev)
@@ -147,7 +181,7 @@ def forward_train(model, src: List[Tensor], ts: List[Tensor]):
     counts = ops.der_counters(pred, label_perm, lens_dev)
     loss = (model.diar_weight * loss_pit + model.attractor_weight * loss_att).reshape(())
     saved = dict(ws=ws, B=B, Tmax=Tmax, S=S, n_dec=n_dec, lens_dev=lens_dev, perm=perm, order=order, att=att,
-                 probs=probs, pred=pred, label_perm=label_perm, sum_len=float(sum(ilens)))
+                 probs=probs, pred=pred, label_perm=label_perm, sum_len=float(sum(ilens)), p_drop=pd, seed=seed)
     model.last = dict(emb=emb.view(B, Tmax, -1), attractors=att, probs=probs, pred=pred, min_idx=min_idx,
                       label_permute=label_perm, counts=counts)
     return loss, loss_att, loss_pit, counts, saved
@@ -191,25 +225,28 @@ def backward_train(model, saved: dict) -> Tensor:
     OT.gemm_dgrad(ws["dxproj"], w["wt_ih"], M, D, 4 * D, P, resid=ws["demb"], out=dy)
 
     g_f, g_s = ws["g_f"], ws["g_s"]
+    pd, seed = saved["p_drop"], saved["seed"]
+    drop = lambda layer, which: (pd, seed, site_id(layer, which)) if pd > 0 else OT.NO_DROP
+    keep_scale = 1.0 / (1.0 - pd) if pd > 0 else 1.0
     for i in range(model.n_layers - 1, -1, -1):
         lw, a = w["layers"][i], ws["layers"][i]
         pre = f"{model.NAMES['stack']}.layers.{i}."
         # norm2 / linear2 / ReLU / linear1
         OT.ln_bwd(dy, ws["x_f"][i + 1], lw["g2"], lw["be2"], a["rstd2"], work, G[pre + "norm2.weight"],
-                  G[pre + "norm2.bias"], G[pre + "linear2.bias"], dx=g_f, dx_split=g_s)
+                  G[pre + "norm2.bias"], G[pre + "linear2.bias"], dx=g_f, dx_split=g_s, drop=drop(i, SITE_FFN2))
         OT.gemm_wgrad(g_s, a["ff"], M, D, FF, G[pre + "linear2.weight"], work, P)
-        OT.gemm_dgrad(g_s, lw["wt_2"], M, FF, D, P, relu_mask=a["ff"], out_split=ws["dh"])
+        OT.gemm_dgrad(g_s, lw["wt_2"], M, FF, D, P, relu_mask=a["ff"], out_split=ws["dh"], mask_scale=keep_scale)
         OT.colsum_split(ws["dh"], M, FF, G[pre + "linear1.bias"], work)
         OT.gemm_wgrad(ws["dh"], a["y1_s"], M, FF, D, G[pre + "linear1.weight"], work, P)
         OT.gemm_dgrad(ws["dh"], lw["wt_1"], M, D, FF, P, resid=g_f, out=dy_other)
         # norm1 / out_proj / attention / in_proj
         OT.ln_bwd(dy_other, a["y1_f"], lw["g1"], lw["be1"], a["rstd1"], work, G[pre + "norm1.weight"],
-                  G[pre + "norm1.bias"], G[pre + "self_attn.out_proj.bias"], dx=g_f, dx_split=g_s)
+                  G[pre + "norm1.bias"], G[pre + "self_attn.out_proj.bias"], dx=g_f, dx_split=g_s, drop=drop(i, SITE_OUT))
         OT.gemm_wgrad(g_s, a["ctx"], M, D, D, G[pre + "self_attn.out_proj.weight"], work, P)
         OT.gemm_dgrad(g_s, lw["wt_o"], M, D, D, P, out_split=ws["dctx"])
         OT.mha_delta(ws["dctx"], a["ctx"], M, D, ws["delta"])
         OT.mha_bwd(a["qk"], a["vt"], ws["Tp"], ws["dctx"], a["lse"], ws["delta"], B, Tmax, H, ws["dq_acc"],
-                   ws["dqkv"], model.attn_precision)
+                   ws["dqkv"], model.attn_precision, drop=drop(i, SITE_ATTN))
         OT.scale_split(ws["dq_acc"], 0.125, ws["dqkv"], cols=D)
         OT.colsum_split(ws["dqkv"], M, 3 * D, G[pre + "self_attn.in_proj_bias"], work)
         OT.gemm_wgrad(ws["dqkv"], ws["x_s"][i], M, 3 * D, D, G[pre + "self_attn.in_proj_weight"], work, P)

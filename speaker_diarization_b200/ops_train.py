@@ -16,24 +16,30 @@ def _sp(s: Optional[Split]):
     return (L.ptr(s.hi), L.ptr(s.lo), s.ld) if s is not None else (None, None, 0)
 
 
+NO_DROP = (0.0, 0, 0)      # (p, seed, site): dropout off
+
+
 def gemm_split_train(a: Split, w: Split, bias: Tensor, M: int, N: int, K: int, epilogue: int, prec: int,
-                     rstd: Tensor, resid: Optional[Tensor] = None, gamma: Optional[Tensor] = None,
-                     beta: Optional[Tensor] = None, out: Optional[Tensor] = None, out_split: Optional[Split] = None):
+                     rstd: Optional[Tensor], resid: Optional[Tensor] = None, gamma: Optional[Tensor] = None,
+                     beta: Optional[Tensor] = None, out: Optional[Tensor] = None, out_split: Optional[Split] = None,
+                     drop=NO_DROP):
+    """``drop`` = (p, seed, site): dropout on relu(..) (EPI_BIAS_RELU) or on A.W^T + bias before the residual."""
     oh, ol, old = _sp(out_split)
     L.call("eda_gemm_split_train", L.ptr(a.hi), L.ptr(a.lo), a.ld, L.ptr(w.hi), L.ptr(w.lo), w.ld, L.ptr(bias),
            L.ptr(resid), resid.stride(0) if resid is not None else 0, L.ptr(gamma), L.ptr(beta),
-           L.ptr(out), out.stride(0) if out is not None else 0, oh, ol, old, L.ptr(rstd), M, N, K, epilogue, prec,
-           L.stream())
+           L.ptr(out), out.stride(0) if out is not None else 0, oh, ol, old, L.ptr(rstd), float(drop[0]), int(drop[1]),
+           int(drop[2]), M, N, K, epilogue, prec, L.stream())
 
 
 def gemm_dgrad(dy: Split, wt: Split, M: int, K_in: int, N_out: int, prec: int, resid: Optional[Tensor] = None,
-               relu_mask: Optional[Split] = None, out: Optional[Tensor] = None, out_split: Optional[Split] = None):
+               relu_mask: Optional[Split] = None, out: Optional[Tensor] = None, out_split: Optional[Split] = None,
+               mask_scale: float = 1.0):
     """dX (M, K_in) = dY (M, N_out) . W with wt = W^T (K_in, N_out) split; + resid or ReLU mask."""
     oh, ol, old = _sp(out_split)
     L.call("eda_gemm_dgrad", L.ptr(dy.hi), L.ptr(dy.lo), dy.ld, L.ptr(wt.hi), L.ptr(wt.lo), wt.ld,
            L.ptr(resid), resid.stride(0) if resid is not None else 0,
            L.ptr(relu_mask.hi) if relu_mask is not None else None, relu_mask.ld if relu_mask is not None else 0,
-           L.ptr(out), out.stride(0) if out is not None else 0, oh, ol, old, M, K_in, N_out, prec, L.stream())
+           float(mask_scale), L.ptr(out), out.stride(0) if out is not None else 0, oh, ol, old, M, K_in, N_out, prec, L.stream())
 
 
 def gemm_wgrad(dy: Split, x: Split, M: int, N_out: int, K_in: int, dW: Tensor, work: Tensor, prec: int,
@@ -47,12 +53,13 @@ def gemm_wgrad(dy: Split, x: Split, M: int, N_out: int, K_in: int, dW: Tensor, w
 
 def ln_bwd(dy: Tensor, y: Tensor, gamma: Tensor, beta: Tensor, rstd: Tensor, work: Tensor, dgamma: Tensor,
            dbeta: Tensor, dcolsum: Optional[Tensor] = None, dx: Optional[Tensor] = None,
-           dx_split: Optional[Split] = None, accumulate: bool = False):
+           dx_split: Optional[Split] = None, accumulate: bool = False, drop=NO_DROP):
     M, D = dy.shape
     oh, ol, old = _sp(dx_split)
     L.call("eda_ln_bwd", L.ptr(_f32(dy)), dy.stride(0), L.ptr(_f32(y)), y.stride(0), L.ptr(gamma), L.ptr(beta),
            L.ptr(rstd), M, D, L.ptr(dx), dx.stride(0) if dx is not None else 0, oh, ol, old, L.ptr(dgamma),
-           L.ptr(dbeta), L.ptr(dcolsum), L.ptr(work), work.numel() * work.element_size(), int(accumulate), L.stream())
+           L.ptr(dbeta), L.ptr(dcolsum), L.ptr(work), work.numel() * work.element_size(), int(accumulate),
+           float(drop[0]), int(drop[1]), int(drop[2]), L.stream())
 
 
 def colsum_split(x: Split, M: int, N: int, out: Tensor, work: Tensor, accumulate: bool = False):
@@ -61,9 +68,10 @@ def colsum_split(x: Split, M: int, N: int, out: Tensor, work: Tensor, accumulate
 
 
 def mha_split_train(qk: Split, vt: Split, B: int, T: int, Tp: int, n_heads: int, prec: int, out_split: Split,
-                    lse: Tensor):
+                    lse: Tensor, drop=NO_DROP):
     L.call("eda_mha_split_train", L.ptr(qk.hi), L.ptr(qk.lo), qk.ld, L.ptr(vt.hi), L.ptr(vt.lo), Tp, B, T, n_heads,
-           L.ptr(out_split.hi), L.ptr(out_split.lo), out_split.ld, L.ptr(lse), prec, L.stream())
+           L.ptr(out_split.hi), L.ptr(out_split.lo), out_split.ld, L.ptr(lse), float(drop[0]), int(drop[1]),
+           int(drop[2]), prec, L.stream())
 
 
 def mha_delta(do: Split, o: Split, M: int, D: int, delta: Tensor):
@@ -72,10 +80,10 @@ def mha_delta(do: Split, o: Split, M: int, D: int, delta: Tensor):
 
 
 def mha_bwd(qk: Split, vt: Split, Tp: int, do: Split, lse: Tensor, delta: Tensor, B: int, T: int, n_heads: int,
-            dq_acc: Tensor, dqkv: Split, prec: int):
+            dq_acc: Tensor, dqkv: Split, prec: int, drop=NO_DROP):
     L.call("eda_mha_bwd", L.ptr(qk.hi), L.ptr(qk.lo), qk.ld, L.ptr(vt.hi), L.ptr(vt.lo), Tp, L.ptr(do.hi),
            L.ptr(do.lo), do.ld, L.ptr(lse), L.ptr(delta), B, T, n_heads, L.ptr(dq_acc), L.ptr(dqkv.hi),
-           L.ptr(dqkv.lo), dqkv.ld, prec, L.stream())
+           L.ptr(dqkv.lo), dqkv.ld, float(drop[0]), int(drop[1]), int(drop[2]), prec, L.stream())
 
 
 def scale_split(src: Tensor, scale: float, dst: Split, cols: Optional[int] = None):
@@ -126,3 +134,10 @@ def scale_dev(scale: Tensor, x: Tensor):
 def adam_step(p: Tensor, g: Tensor, m: Tensor, v: Tensor, lr: float, beta1: float, beta2: float, eps: float, step: int):
     L.call("eda_adam_step", L.ptr(p), L.ptr(g), L.ptr(m), L.ptr(v), p.numel(), float(lr), float(beta1), float(beta2),
            float(eps), int(step), L.stream())
+
+
+def dropout_mask(p: float, seed: int, site: int, rows: int, cols: int, device) -> Tensor:
+    """The keep mask (uint8 rows x cols) the kernels apply at dropout site ``site`` (tests)."""
+    keep = torch.empty((rows, cols), dtype=torch.uint8, device=device)
+    L.call("eda_dropout_mask", float(p), int(seed), int(site), rows, cols, L.ptr(keep), L.stream())
+    return keep

@@ -136,3 +136,59 @@ def test_grad_accumulation_and_eval_mode(dev, manifest):
     with torch.no_grad():
         loss_n, _ = model(src, ts)
     assert not loss_n.requires_grad
+
+
+def test_dropout_masks_statistics(dev):
+    """The Philox keep masks: rate 1 - p, different per site / seed, identical on replay."""
+    from speaker_diarization_b200 import ops_train as OT
+    a = OT.dropout_mask(0.1, 1234, 5, 4096, 2048, dev)
+    assert abs(a.float().mean().item() - 0.9) < 2e-3
+    assert torch.equal(a, OT.dropout_mask(0.1, 1234, 5, 4096, 2048, dev))
+    b = OT.dropout_mask(0.1, 1234, 6, 4096, 2048, dev)
+    c = OT.dropout_mask(0.1, 1235, 5, 4096, 2048, dev)
+    for other in (b, c):
+        agree = (a == other).float().mean().item()
+        assert abs(agree - 0.82) < 5e-3                    # independent masks agree with probability 0.9^2 + 0.1^2
+    assert abs(a.float().mean(0).std().item() - (0.09 / 4096) ** 0.5) < 2e-3    # no column structure
+
+
+@pytest.mark.parametrize("name", ["train_l1_ragged", "train_l2_s3"])
+def test_dropout_training_step_matches_oracle_with_the_same_masks(dev, manifest, name):
+    """train() mode with dropout 0.1 (conf/eend_eda/*train.yaml: transformer_encoder_dropout): loss and every
+    gradient against the oracle's autograd fed the very masks the kernels applied (exported with
+    eda_dropout_mask); and the masks change the result (the run differs from the dropout-free one)."""
+    from oracle.eend_eda_oracle import forward_backward
+    from oracle.weights import EdaConfig, synth_features, synth_labels, synth_state_dict
+    from speaker_diarization_b200.eend_eda.models import TransformerEdaModel
+    from speaker_diarization_b200.eend_eda.training import dropout_sites
+    case = manifest["cases"][name]
+    cfg, sd = _case(case)
+    src = synth_features(case["lengths"], cfg.in_size, case["data_seed"])
+    ts = synth_labels(case["lengths"], case["n_speakers"], case["data_seed"])
+    m = TransformerEdaModel(cfg.n_speakers, cfg.in_size, cfg.n_heads, cfg.n_units, cfg.n_layers, dropout=0.1, precision="bf16x3")
+    m.load_state_dict(sd)
+    m = m.to(dev).train()
+    torch.manual_seed(3000 + case["data_seed"])
+    loss, _ = m(src, ts)
+    loss.backward()
+    B, Tmax = len(case["lengths"]), max(case["lengths"])
+    masks = [tuple(t.cpu() for t in dropout_sites(m, m._last_drop_seed, B, Tmax, l, dev)) for l in range(cfg.n_layers)]
+    torch.manual_seed(3000 + case["data_seed"])
+    loss_o, grads_o, _ = forward_backward(sd, src, ts, drop=(0.1, masks))
+    assert abs(loss.item() - loss_o.item()) < 1e-3
+    assert abs(loss.item() - float(load_golden(name)["loss"])) > 1e-3        # dropout did something
+    worst = 0.0
+    for k, p in m.named_parameters():
+        g, r = p.grad.cpu(), grads_o[k]
+        if r.norm() < 1e-7 or k.endswith("in_proj_bias"):
+            continue
+        worst = max(worst, _rel(g, r))
+        assert _rel(g, r) < 3e-3, (k, _rel(g, r))
+    print(f"{name} dropout 0.1: worst relative gradient error {worst:.2e}")
+    # replay: same torch seed and step counter -> same masks -> same loss
+    m2 = TransformerEdaModel(cfg.n_speakers, cfg.in_size, cfg.n_heads, cfg.n_units, cfg.n_layers, dropout=0.1, precision="bf16x3")
+    m2.load_state_dict(sd)
+    m2 = m2.to(dev).train()
+    torch.manual_seed(3000 + case["data_seed"])
+    loss2, _ = m2(src, ts)
+    assert loss2.item() == loss.item()

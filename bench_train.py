@@ -7,7 +7,7 @@ all-reduce of the flat gradient per step).
     (also reachable as  python bench.py --workload train ...)
 
 Workload C5: batch 32 x 2000-frame chunks of 345-d features (randn), 3 speakers (Bernoulli-run
-labels), 4-layer 256-d encoder, dropout 0.  ``value``: features and labels resident in HBM;
+labels), 4-layer 256-d encoder, dropout 0.1 (the reference's training yaml).  ``value``: features and labels resident in HBM;
 ``e2e``: host tensors through ``model(src, ts)`` / ``loss.backward()`` / ``opt.step()`` with the
 H2D of the step's features + labels and the D2H of its loss / DER counters inside the timed region.
 """
@@ -75,7 +75,7 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    model = TransformerEdaModel(S, IN, HEADS, UNITS, LAYERS, dim_feedforward=FF, dropout=0.0, precision=args.precision)
+    model = TransformerEdaModel(S, IN, HEADS, UNITS, LAYERS, dim_feedforward=FF, dropout=args.dropout, precision=args.precision)
     model.load_state_dict(synth_state_dict(EdaConfig(n_layers=LAYERS, n_speakers=S), 777))
     model = model.to(dev).train()
     opt = NoamAdam(model, lr=1.0, warmup_steps=25000)
@@ -138,10 +138,10 @@ def run_ours(args):
         shares = {k: round(sum(m for m, _ in v) / tot, 4) for k, v in prof.items()}
         times = {k: round(sum(m for m, _ in v), 4) for k, v in prof.items()}
         # GEMM launches (forward, input gradient, weight gradient): algorithmic 2*M*N*K each
-        gemm = [(m, 2.0 * a[17] * a[18] * min(a[19], IN if a[19] == 352 else a[19])) for m, a in prof.get("eda_gemm_split_train", [])]
+        gemm = [(m, 2.0 * a[20] * a[21] * min(a[22], IN if a[22] == 352 else a[22])) for m, a in prof.get("eda_gemm_split_train", [])]
         gemm += [(m, 2.0 * a[16] * a[17] * a[18]) for m, a in prof.get("eda_gemm_split", [])]
         gemm += [(m, 2.0 * a[12] * a[13] * 3 * a[15] * a[15]) for m, a in prof.get("eda_gemm_qkv", [])]
-        gemm += [(m, 2.0 * a[15] * a[16] * a[17]) for m, a in prof.get("eda_gemm_dgrad", [])]
+        gemm += [(m, 2.0 * a[16] * a[17] * a[18]) for m, a in prof.get("eda_gemm_dgrad", [])]
         gemm += [(m, 2.0 * a[6] * a[7] * a[8]) for m, a in prof.get("eda_gemm_wgrad", [])]
         g_ms, g_fl = sum(m for m, _ in gemm), sum(f for _, f in gemm)
         pk = peaks()
@@ -167,7 +167,7 @@ def run_ours(args):
             "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": {"bf16x3": "bf16x3(f32 accum)", "bf16": "bf16"}[args.precision], "data": "synthetic",
             "config": {"workload": f"configs[4]: EEND-EDA training step (forward + batched PIT loss + backward + Adam/Noam), "
-                                   f"{LAYERS}-layer {UNITS}-d encoder, batch {B} x {T}-frame chunks, {S} speakers, dropout 0, per GPU",
+                                   f"{LAYERS}-layer {UNITS}-d encoder, batch {B} x {T}-frame chunks, {S} speakers, dropout {args.dropout}, per GPU",
                        "global_batch": world * B, "frames_per_step": world * B * T, "precision": args.precision,
                        "parallelism": f"dp{world} (one NCCL all-reduce of the 20 MB flat gradient per step)",
                        "l2": "two alternating batches; > 5 GB of saved activations per step exceed the 126 MB L2"},
@@ -206,6 +206,7 @@ def main(argv=None):
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "bf16"])
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--dropout", type=float, default=0.1, help="transformer_encoder_dropout (conf/eend_eda/*train.yaml: 0.1)")
     args = ap.parse_args(argv)
     out = run_reference(args) if args.impl == "reference" else run_ours(args)
     if out is not None:

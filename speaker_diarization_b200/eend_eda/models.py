@@ -15,8 +15,8 @@ Training: in ``train()`` mode with gradients enabled and a tens
 ``forward`` returns a loss with a ``grad_fn`` whose backward runs the hand-written backward kernels
 (``training.py``); in ``eval()`` mode or under ``no_grad`` it is the inference-cost forward.
 
-Not covered: train-mode dropout > 0 (build with ``dropout=0`` to train), ``has_pos=True`` (never
-enabled by the reference drivers, train_eda.py:81), gradients under ``precision='fp32'``.
+Not covered: ``has_pos=True`` (never enabled by the reference drivers, train_eda.py:81), gradients
+under ``precision='fp32'``.
 """
 from __future__ import annotations
 

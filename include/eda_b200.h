@@ -243,7 +243,8 @@ int eda_rttm_segments(const float* post, const uint8_t* labels, int ld, const in
 
 /* Dropout (nn.TransformerEncoderLayer in train() mode: on the attention weights, after out_proj, after the
  * ReLU, after linear2) is a counter-based Philox4x32-7 function of (seed, site, row, column): element
- * (row, col) is kept iff word (col & 3) of philox(key = seed, counter = (col >> 2, row, site, 0)) >= p * 2^32,
+ * (row, col) is kept iff 16-bit half (col & 1) of word ((col & 7) >> 1) of philox(key = seed, counter =
+ * (col >> 3, row, site, 0)) >= round(p * 2^16) (one call decides 8 elements; cols % 8 == 0 in eda_dropout_mask),
  * kept values are multiplied by 1 / (1 - p).  The forward epilogues and the backward kernels evaluate the
  * same function, so no mask is stored; eda_dropout_mask writes one out (tests).  For the attention weights
  * row = (b * n_heads + h) * T + query, col = key.                                                          */

@@ -98,7 +98,9 @@ ln_bwd_kernel(const float* __restrict__ dy, int ld_dy, const float* __restrict__
       *reinterpret_cast<float4*>(dx + (size_t)row * ld_dx + c1) = make_float4(o[4], o[5], o[6], o[7]);
     }
     if (drop.thresh) {   // the Linear branch went through dropout in the forward: same mask, same scale
-      const uint32_t k0 = dropout_keep4(drop, (uint32_t)row, (uint32_t)lane), k1 = dropout_keep4(drop, (uint32_t)row, 32u + lane);
+      // this lane's columns 4 lane .. +3 and 128 + 4 lane .. +3 are one half of an 8-column group each
+      const uint32_t k0 = dropout_keep8(drop, (uint32_t)row, (uint32_t)(lane >> 1)) >> (4 * (lane & 1));
+      const uint32_t k1 = dropout_keep8(drop, (uint32_t)row, 16u + (lane >> 1)) >> (4 * (lane & 1));
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         o[j] = (k0 >> j) & 1u ? o[j] * drop.scale : 0.f;
@@ -372,19 +374,19 @@ int scale_split(const float* src, int ld, int rows, int cols, float scale, void*
 
 // keep[row][col] of one dropout site (test / debugging aid: the kernels never materialise a mask)
 __global__ void dropout_mask_kernel(const DropoutCfg d, int64_t rows, int cols, uint8_t* __restrict__ keep) {
-  const int64_t n = rows * (int64_t)(cols / 4);
+  const int64_t n = rows * (int64_t)(cols / 8);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / (cols / 4);
-    const int g = (int)(i % (cols / 4));
-    const uint32_t k = d.thresh ? dropout_keep4(d, (uint32_t)r, (uint32_t)g) : 0xfu;
+    const int64_t r = i / (cols / 8);
+    const int g = (int)(i % (cols / 8));
+    const uint32_t k = d.thresh ? dropout_keep8(d, (uint32_t)r, (uint32_t)g) : 0xffu;
 #pragma unroll
-    for (int e = 0; e < 4; ++e) keep[r * cols + 4 * g + e] = (k >> e) & 1u;
+    for (int e = 0; e < 8; ++e) keep[r * cols + 8 * g + e] = (k >> e) & 1u;
   }
 }
 
 int dropout_mask(float p, uint64_t seed, int site, int64_t rows, int cols, uint8_t* keep, cudaStream_t st) {
-  EDA_REQUIRE(keep && rows > 0 && cols > 0 && cols % 4 == 0 && p >= 0.f && p < 1.f, "eda_dropout_mask: bad arguments (cols %% 4 == 0)");
-  const int64_t n = rows * (int64_t)(cols / 4);
+  EDA_REQUIRE(keep && rows > 0 && cols > 0 && cols % 8 == 0 && p >= 0.f && p < 1.f, "eda_dropout_mask: bad arguments (cols %% 8 == 0)");
+  const int64_t n = rows * (int64_t)(cols / 8);
   dropout_mask_kernel<<<(int)std::min<int64_t>(ceil_div<int64_t>(n, 256), num_sms() * 16), 256, 0, st>>>(make_dropout(p, seed, site), rows, cols, keep);
   EDA_LAUNCH_CHECK();
   return EDA_OK;

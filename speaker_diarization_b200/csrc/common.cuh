@@ -70,16 +70,16 @@ __device__ __forceinline__ float warp_max(float v) {
 
 // ---- dropout (training step): counter-based Philox4x32-7, the same function in the forward
 // epilogues, the backward kernels and eda_dropout_mask (tests), so a mask is never stored.
-// Element (row, col) of site `site` keeps its value iff word (col & 3) of
-// philox(key = seed, counter = (col >> 2, row, site, 0)) >= thresh = p * 2^32.
+// Element (row, col) of site `site` keeps its value iff the 16-bit half (col & 1) of word ((col & 7) >> 1) of
+// philox(key = seed, counter = (col >> 3, row, site, 0)) >= thresh = round(p * 2^16): one call decides 8 elements.
 struct DropoutCfg {
-  uint32_t thresh;       // 0 = dropout off
+  uint32_t thresh;       // 16-bit threshold; 0 = dropout off
   uint32_t seed_lo, seed_hi, site;
   float scale;           // 1 / (1 - p)
 };
 __host__ __device__ inline DropoutCfg make_dropout(float p, uint64_t seed, int site) {
   DropoutCfg d;
-  d.thresh = p > 0.f ? (uint32_t)((double)p * 4294967296.0) : 0u;
+  d.thresh = p > 0.f ? (uint32_t)((double)p * 65536.0 + 0.5) : 0u;
   d.seed_lo = (uint32_t)seed; d.seed_hi = (uint32_t)(seed >> 32); d.site = (uint32_t)site;
   d.scale = p > 0.f ? 1.0f / (1.0f - p) : 1.0f;
   return d;
@@ -94,10 +94,15 @@ __device__ __forceinline__ uint4 philox4x32_7(uint32_t c0, uint32_t c1, uint32_t
   }
   return make_uint4(c0, c1, c2, c3);
 }
-// keep-bits of the 4 elements (row, 4 * colgroup .. + 3): bit j set = element kept
-__device__ __forceinline__ uint32_t dropout_keep4(const DropoutCfg& d, uint32_t row, uint32_t colgroup) {
+// keep-bits of the 8 elements (row, 8 * colgroup .. + 7): bit j set = element kept
+__device__ __forceinline__ uint32_t dropout_keep8(const DropoutCfg& d, uint32_t row, uint32_t colgroup) {
   const uint4 r = philox4x32_7(colgroup, row, d.site, 0u, d.seed_lo, d.seed_hi);
-  return (r.x >= d.thresh ? 1u : 0u) | (r.y >= d.thresh ? 2u : 0u) | (r.z >= d.thresh ? 4u : 0u) | (r.w >= d.thresh ? 8u : 0u);
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+  uint32_t k = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    k |= ((w[j] & 0xffffu) >= d.thresh ? 1u : 0u) << (2 * j) | ((w[j] >> 16) >= d.thresh ? 2u : 0u) << (2 * j);
+  return k;
 }
 
 // sigmoid the way ATen's CPU/GPU kernels define it: 1 / (1 + exp(-x)), fp32.

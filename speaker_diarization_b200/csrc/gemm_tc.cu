@@ -78,13 +78,13 @@ __device__ __forceinline__ void split2(float x0, float x1, __nv_bfloat162& hi, _
                           __float2bfloat16_rn(x1 - __bfloat162float(h1)));
 }
 
-// dropout on 32 consecutive columns col0.. of one row (8 Philox calls)
+// dropout on 32 consecutive columns col0.. (col0 % 8 == 0) of one row: 4 Philox calls
 __device__ __forceinline__ void apply_dropout32(float (&v)[32], const DropoutCfg& d, int row, int col0) {
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const uint32_t keep = dropout_keep4(d, (uint32_t)row, (uint32_t)(col0 >> 2) + j);
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t keep = dropout_keep8(d, (uint32_t)row, (uint32_t)(col0 >> 3) + j);
 #pragma unroll
-    for (int e = 0; e < 4; ++e) v[4 * j + e] = (keep >> e) & 1u ? v[4 * j + e] * d.scale : 0.f;
+    for (int e = 0; e < 8; ++e) v[8 * j + e] = (keep >> e) & 1u ? v[8 * j + e] * d.scale : 0.f;
   }
 }
 

@@ -407,15 +407,20 @@ struct LstmBwd {
   int B, Tmax, n_dec;
 };
 
-// wt[i][gate][0..1] = packed W[gate*256 + 32 i + 4 kc + {0,1 | 2,3}][32 cta + u]
-__device__ __forceinline__ void load_wt(uint64_t (&wt)[8][4][2], const float* __restrict__ W, int cta, int u, int kc) {
+// Mat-vec mapping of the backward kernel: warp w owns the 4 hidden units 4w..4w+3, lane l the 32 gate rows
+// {gate = l >> 3, source CTA j, unit 4 (l & 7) + e : j < 8, e < 4} - one 16-byte chunk of every source CTA's
+// slice, so a warp reads each (source CTA, sequence) slice of 512 B exactly once (no two lanes load the same
+// gate gradient; the forward-style mapping read every value 4 times and was bound by shared-memory wavefronts).
+// wt[j][e][0..1] = packed W[row(j, e)][32 cta + 4 w + {0,1 | 2,3}]
+__device__ __forceinline__ void load_wt(uint64_t (&wt)[8][4][2], const float* __restrict__ W, int cta, int warp, int lane) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i)
+  for (int j = 0; j < 8; ++j)
 #pragma unroll
-    for (int gate = 0; gate < 4; ++gate) {
-      const float* src = W + (size_t)(gate * kD + 32 * i + 4 * kc) * kD + cta * kUnits + u;
-      wt[i][gate][0] = pack2(__ldg(src), __ldg(src + kD));
-      wt[i][gate][1] = pack2(__ldg(src + 2 * kD), __ldg(src + 3 * kD));
+    for (int e = 0; e < 4; ++e) {
+      const int row = (lane >> 3) * kD + 32 * j + 4 * (lane & 7) + e;
+      const float4 v = __ldg(reinterpret_cast<const float4*>(W + (size_t)row * kD + cta * kUnits + 4 * warp));
+      wt[j][e][0] = pack2(v.x, v.y);
+      wt[j][e][1] = pack2(v.z, v.w);
     }
 }
 
@@ -461,7 +466,7 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
     if (n_total > 2) bar_arm(&bars[0], kStepBytes);
   }
   uint64_t wt[8][4][2];
-  load_wt(wt, n_dec > 0 ? P.w_dec : P.w_enc, cta, u, kc);
+  load_wt(wt, n_dec > 0 ? P.w_dec : P.w_enc, cta, warp, lane);
 
   const int my_b = owner ? s_seq[seq] : -1;
   const int my_len = owner ? s_len[seq] : 0;
@@ -511,30 +516,42 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
     StepIn nxt;
     load_step(gs - 1, nxt);                 // in flight under the mat-vec
     if (r > 0) {
-      if (n_dec > 0 && gs + 1 == max_len - 1) load_wt(wt, P.w_enc, cta, u, kc);   // the later step is an encoder step from here on
+      if (n_dec > 0 && gs + 1 == max_len - 1) load_wt(wt, P.w_enc, cta, warp, lane);   // the later step is an encoder step from here on
       bar_wait(&bars[cur], ((r - 1) >> 1) & 1);
       if (tid == 0 && r + 2 < n_total) bar_arm(&bars[cur], kStepBytes);
-      uint64_t acc[kG];
+      uint64_t acc[kG][2];                     // (units 0,1 | 2,3) of this warp, partial over this lane's 32 rows
 #pragma unroll
-      for (int g = 0; g < kG; ++g) acc[g] = 0ull;
+      for (int g = 0; g < kG; ++g) acc[g][0] = acc[g][1] = 0ull;
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+      for (int j = 0; j < 8; ++j)
 #pragma unroll
-        for (int g = 0; g < kG; ++g)
+        for (int g = 0; g < kG; ++g) {
+          const float4 dv = *reinterpret_cast<const float4*>(&dg[cur][j][g][lane >> 3][4 * (lane & 7)]);
+          const float d4[4] = {dv.x, dv.y, dv.z, dv.w};
 #pragma unroll
-          for (int gate = 0; gate < 4; ++gate) {
-            const float4 dv = *reinterpret_cast<const float4*>(&dg[cur][i][g][gate][4 * kc]);
-            acc[g] = ffma2(wt[i][gate][0], pack2(dv.x, dv.y), acc[g]);
-            acc[g] = ffma2(wt[i][gate][1], pack2(dv.z, dv.w), acc[g]);
+          for (int e = 0; e < 4; ++e) {
+            const uint64_t dd = pack2(d4[e], d4[e]);
+            acc[g][0] = ffma2(wt[j][e][0], dd, acc[g][0]);
+            acc[g][1] = ffma2(wt[j][e][1], dd, acc[g][1]);
           }
+        }
+      // reduce over the 32 row slices: two halving rounds hand each lane ONE unit (lane bits 4,3 = unit, like
+      // the owner mapping u = 4 warp + (lane >> 3)), three butterfly rounds finish the sums for all sequences
       float rsum = 0.f;
+      {
+        const bool up4 = (lane & 16) != 0, up3 = (lane & 8) != 0;
 #pragma unroll
-      for (int g = 0; g < kG; ++g) {
-        float v = sum2(acc[g]);
-        v += __shfl_xor_sync(0xffffffffu, v, 1);
-        v += __shfl_xor_sync(0xffffffffu, v, 2);
-        v += __shfl_xor_sync(0xffffffffu, v, 4);
-        if (kc == g) rsum = v;
+        for (int g = 0; g < kG; ++g) {
+          const float v0 = __uint_as_float((uint32_t)acc[g][0]), v1 = __uint_as_float((uint32_t)(acc[g][0] >> 32));
+          const float v2 = __uint_as_float((uint32_t)acc[g][1]), v3 = __uint_as_float((uint32_t)(acc[g][1] >> 32));
+          const float k0 = (up4 ? v2 : v0) + __shfl_xor_sync(0xffffffffu, up4 ? v0 : v2, 16);
+          const float k1 = (up4 ? v3 : v1) + __shfl_xor_sync(0xffffffffu, up4 ? v1 : v3, 16);
+          float t = (up3 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, up3 ? k0 : k1, 8);
+          t += __shfl_xor_sync(0xffffffffu, t, 4);
+          t += __shfl_xor_sync(0xffffffffu, t, 2);
+          t += __shfl_xor_sync(0xffffffffu, t, 1);
+          if (kc == g) rsum = t;
+        }
       }
       carry_dh += rsum;
     }

@@ -226,8 +226,8 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
           if (!q_ok || key0 + e + 1 >= p.T) p1 = 0.f;
           float pd0 = p0, pd1 = p1, g0 = dv[e], g1 = dv[e + 1];
           if (p.drop.thresh) {     // O = (D * P / (1-p)) V: dV sees the dropped weights, dP = D * d(dropped) / (1-p)
-            if ((e & 3) == 0) keep4 = dropout_keep4(p.drop, drop_row, (uint32_t)(key0 + e) >> 2);
-            const bool k0b = (keep4 >> (e & 3)) & 1u, k1b = (keep4 >> ((e & 3) + 1)) & 1u;
+            if ((e & 7) == 0) keep4 = dropout_keep8(p.drop, drop_row, (uint32_t)(key0 + e) >> 3);
+            const bool k0b = (keep4 >> (e & 7)) & 1u, k1b = (keep4 >> ((e & 7) + 1)) & 1u;
             pd0 = k0b ? p0 * p.drop.scale : 0.f; pd1 = k1b ? p1 * p.drop.scale : 0.f;
             g0 = k0b ? g0 * p.drop.scale : 0.f; g1 = k1b ? g1 * p.drop.scale : 0.f;
           }

@@ -343,9 +343,9 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
         }
         l4[i & 2] += p0; l4[(i & 2) + 1] += p1;
         if (p.drop.thresh) {       // nn.MultiheadAttention drops normalised weights: the row sum keeps every term
-          if ((i & 3) == 0) keep4 = dropout_keep4(p.drop, drop_row, (uint32_t)(j * ABN + half * 32 + i) >> 2);
-          p0 = (keep4 >> (i & 3)) & 1u ? p0 * p.drop.scale : 0.f;
-          p1 = (keep4 >> ((i & 3) + 1)) & 1u ? p1 * p.drop.scale : 0.f;
+          if ((i & 7) == 0) keep4 = dropout_keep8(p.drop, drop_row, (uint32_t)(j * ABN + half * 32 + i) >> 3);
+          p0 = (keep4 >> (i & 7)) & 1u ? p0 * p.drop.scale : 0.f;
+          p1 = (keep4 >> ((i & 7) + 1)) & 1u ? p1 * p.drop.scale : 0.f;
         }
         const uint32_t hi = pack_bf16x2(p0, p1);
         pk[i >> 1] = __uint_as_float(hi);

@@ -116,7 +116,7 @@ def dropout_sites(model, seed: int, B: int, Tmax: int, layer: int, device):
     """The four keep masks of one layer as torch.nn.TransformerEncoderLayer would apply them (bool tensors):
     attention weights (B, H, T, T), dropout1 (B, T, D), FFN dropout (B, T, FF), dropout2 (B, T, D)."""
     p, H, D, FF = model.dropout_p, model.n_heads, model.n_units, model.dim_feedforward
-    Tc = _round_up(Tmax, 4)
+    Tc = _round_up(Tmax, 8)
     att = OT.dropout_mask(p, seed, site_id(layer, SITE_ATTN), B * H * Tmax, Tc, device)[:, :Tmax].view(B, H, Tmax, Tmax)
     d1 = OT.dropout_mask(p, seed, site_id(layer, SITE_OUT), B * Tmax, D, device).view(B, Tmax, D)
     ff = OT.dropout_mask(p, seed, site_id(layer, SITE_FFN), B * Tmax, FF, device).view(B, Tmax, FF)

@@ -159,11 +159,14 @@ int eda_mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* v
  * attractors: (B, n_dec, D) fp32.  hc_out (optional, may be NULL): (B, 2, D) final
  * encoder (h, c).  `order` (optional, may be NULL = identity): a permutation of 0..B-1;
  * sequences are co-scheduled in groups in that order (pass them sorted by length so a
- * group finishes together).  D must be 256.                                             */
+ * group finishes together).  D must be 256.
+ * prec: EDA_PREC_FP32 = the recurrent mat-vec W_hh.h in fp32 on the CUDA cores; EDA_PREC_BF16X3 /
+ * EDA_PREC_BF16 = on the tensor cores as split-bf16 products (W_hi.h_hi + W_lo.h_hi + W_hi.h_lo,
+ * fp32 accumulate; both keep the three products: the recurrence is not where bf16 would pay). */
 int eda_lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens,
                         const int32_t* order, const float* w_hh_enc, const float* w_hh_dec, const float* dec_bias,
                         int B, int Tmax, int D, int n_dec,
-                        float* attractors, float* hc_out, void* stream);
+                        float* attractors, float* hc_out, int prec, void* stream);
 
 /* Number of 8-CTA clusters of the recurrence kernel the device keeps resident at once; each
  * advances 4 sequences, so batches above 4x this value take more than one wave.            */
@@ -317,7 +320,7 @@ int eda_lstm_attractors_train(const float* xproj, const int32_t* perm, const int
                               const float* w_hh_enc, const float* w_hh_dec, const float* dec_bias, int B, int Tmax,
                               int D, int n_dec, float* attractors, float* hc_out, float* gates, float* c,
                               void* hprev_hi, void* hprev_lo, float* dec_gates, float* dec_c, void* dec_hprev_hi,
-                              void* dec_hprev_lo, void* stream);
+                              void* dec_hprev_lo, int prec, void* stream);
 /* BPTT through decoder and encoder from dattractors (B, n_dec, D).  Writes the gradient w.r.t.
  * the gate pre-activations as split pairs: dxproj (B*Tmax, 4D) in FRAME order (rows of padded
  * frames are zero), ddec (B*n_dec, 4D).  The caller turns them into weight / input gradients

@@ -39,7 +39,7 @@ SIGNATURES = {
     "eda_gemm_split": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "eda_gemm_qkv": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "eda_mha_split": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _i, _p, _p, _i, _i, _p]),
-    "eda_lstm_attractors": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p]),
+    "eda_lstm_attractors": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _i, _p]),
     "eda_lstm_max_active_clusters": (_i, []),
     "eda_attractor_head": (_i, [_p, _p, _p, _i, _i, _i, _p, _i, _p, _p]),
     "eda_posterior": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p, _p]),
@@ -59,7 +59,7 @@ SIGNATURES = {
     "eda_mha_delta": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _p, _p]),
     "eda_mha_bwd": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _i, _i, _i, _p, _p, _p, _i, _f, _u64, _i, _i, _p]),
     "eda_scale_split": (_i, [_p, _i, _i, _i, _f, _p, _p, _i, _p]),
-    "eda_lstm_attractors_train": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "eda_lstm_attractors_train": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
     "eda_lstm_attractors_bwd": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p]),
     "eda_posterior_bwd": (_i, [_p, _p, _i, _p, _i, _i, _i, _i, _i, _p, _i, _p, _p]),
     "eda_attractor_head_bwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _f, _p, _p, _p, _i, _p]),

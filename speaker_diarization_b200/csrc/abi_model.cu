@@ -10,7 +10,7 @@ int mha_f32(const float*, int, float*, int, int, int, int, cudaStream_t);
 int mha_tc(const float*, int, float*, int, int, int, int, int, cudaStream_t);
 struct LstmSave { float* gates; float* c; void* hprev_hi; void* hprev_lo; float* dec_gates; float* dec_c; void* dec_hprev_hi; void* dec_hprev_lo; };
 int lstm_attractors(const float*, const int32_t*, const int32_t*, const int32_t*, const float*,
-                    const float*, const float*, int, int, int, int, float*, float*, const LstmSave&, cudaStream_t);
+                    const float*, const float*, int, int, int, int, float*, float*, const LstmSave&, int, cudaStream_t);
 int pad_pack(const float*, const int64_t*, const int32_t*, int, int, int, float, float*, int, cudaStream_t);
 int pad_pack_split(const float*, int, const int64_t*, const int32_t*, int, int, int, float, void*, void*, int, cudaStream_t);
 int attractor_head(const float*, const float*, const float*, int, int, int, float*, int, float*, cudaStream_t);
@@ -56,20 +56,20 @@ int eda_mha_fwd(const float* qkv, int ld_qkv, float* out, int ld_out, int B, int
 int eda_lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens,
                         const int32_t* order, const float* w_hh_enc, const float* w_hh_dec,
                         const float* dec_bias, int B, int Tmax, int D, int n_dec, float* attractors,
-                        float* hc_out, void* stream) {
+                        float* hc_out, int prec, void* stream) {
   EDA_REQUIRE(xproj && perm && lens && w_hh_enc && w_hh_dec && dec_bias && attractors, "eda_lstm_attractors: null argument");
   eda::LstmSave sv = {};
-  return eda::lstm_attractors(xproj, perm, lens, order, w_hh_enc, w_hh_dec, dec_bias, B, Tmax, D, n_dec, attractors, hc_out, sv, (cudaStream_t)stream);
+  return eda::lstm_attractors(xproj, perm, lens, order, w_hh_enc, w_hh_dec, dec_bias, B, Tmax, D, n_dec, attractors, hc_out, sv, prec, (cudaStream_t)stream);
 }
 
 int eda_lstm_attractors_train(const float* xproj, const int32_t* perm, const int32_t* lens, const int32_t* order,
                               const float* w_hh_enc, const float* w_hh_dec, const float* dec_bias, int B, int Tmax,
                               int D, int n_dec, float* attractors, float* hc_out, float* gates, float* c,
                               void* hprev_hi, void* hprev_lo, float* dec_gates, float* dec_c, void* dec_hprev_hi,
-                              void* dec_hprev_lo, void* stream) {
+                              void* dec_hprev_lo, int prec, void* stream) {
   EDA_REQUIRE(xproj && perm && lens && w_hh_enc && w_hh_dec && dec_bias && attractors && gates, "eda_lstm_attractors_train: null argument");
   eda::LstmSave sv = {gates, c, hprev_hi, hprev_lo, dec_gates, dec_c, dec_hprev_hi, dec_hprev_lo};
-  return eda::lstm_attractors(xproj, perm, lens, order, w_hh_enc, w_hh_dec, dec_bias, B, Tmax, D, n_dec, attractors, hc_out, sv, (cudaStream_t)stream);
+  return eda::lstm_attractors(xproj, perm, lens, order, w_hh_enc, w_hh_dec, dec_bias, B, Tmax, D, n_dec, attractors, hc_out, sv, prec, (cudaStream_t)stream);
 }
 
 int eda_attractor_head(const float* attractors, const float* w, const float* bias, int B, int n_dec,

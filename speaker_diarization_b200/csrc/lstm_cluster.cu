@@ -116,6 +116,15 @@ struct LstmSave {
   __nv_bfloat16* dec_hprev_lo;
 };
 
+#ifdef EDA_LSTM_TRACE
+// probe build only (scripts/lstm_trace.py): clock64 stamps of thread 0 of every CTA for steps 64..71,
+// 8 slots per step: wake, mat-vec done, reduced, cell done, staged + synced, pushed
+__device__ long long g_lstm_trace[1024 * 64];
+#define LSTM_STAMP(slot) do { if (tid == 0 && gs >= 64 && gs < 72) g_lstm_trace[(size_t)blockIdx.x * 64 + (gs - 64) * 8 + (slot)] = clock64(); } while (0)
+#else
+#define LSTM_STAMP(slot) do { } while (0)
+#endif
+
 template <int kG>
 __global__ void __launch_bounds__(256, 1)
 lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__ perm,
@@ -181,11 +190,12 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
     load_x(p_cur, xg);
     if (my_len > 1) p_next = __ldg(perm + (size_t)my_b * Tmax + 1);
   }
-  // thread r < 8 pushes this CTA's slice to rank r: remote slice / barrier addresses per buffer
+  // lane 0 of warp r pushes this CTA's slice to rank r (one bulk copy per warp: 8 copies issued by one
+  // warp instruction serialise, ~600 cycles): remote slice / barrier addresses per buffer
   uint32_t r_h0 = 0, r_h1 = 0, r_bar0 = 0, r_bar1 = 0;
-  if (tid < kCluster) {
-    r_h0 = map_rank(s_u32(&hs[0][cta][0][0]), tid); r_h1 = map_rank(s_u32(&hs[1][cta][0][0]), tid);
-    r_bar0 = map_rank(s_u32(&bars[0]), tid); r_bar1 = map_rank(s_u32(&bars[1]), tid);
+  if (lane == 0) {
+    r_h0 = map_rank(s_u32(&hs[0][cta][0][0]), warp); r_h1 = map_rank(s_u32(&hs[1][cta][0][0]), warp);
+    r_bar0 = map_rank(s_u32(&bars[0]), warp); r_bar1 = map_rank(s_u32(&bars[1]), warp);
   }
   cluster.sync();   // barriers initialised and h buffers zeroed everywhere before any remote write
 
@@ -213,6 +223,7 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
       bar_wait(&bars[cur], ((gs - 1) >> 1) & 1);       // all 8 slices of h_gs have landed
       if (tid == 0 && gs + 2 < n_total) bar_arm(&bars[cur], kStepBytes);   // re-arm for h_{gs+2}
     }
+    LSTM_STAMP(0);
     uint64_t acc[4][kG];
 #pragma unroll
     for (int gate = 0; gate < 4; ++gate)
@@ -234,6 +245,7 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
     // transpose-reduce over the 8 k-slices (lane bits 2,1,0): every round halves the set of
     // sequences a lane keeps and adds the partner's partial sums for them
     float v4[4];
+    LSTM_STAMP(1);
     if constexpr (kG <= 4) {
       float v8[4][2];
       {
@@ -286,6 +298,7 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
       }
     }
 
+    LSTM_STAMP(2);
     const bool active = dec ? (my_b >= 0) : (s < my_len);
     if (active) {
       const float ig = fast_sigmoid(v4[0] + xg[0]), fg = fast_sigmoid(v4[1] + xg[1]);
@@ -304,12 +317,15 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
       if (sv.gates != nullptr && owner) (dec ? sv.dec_c : sv.c)[(dec ? (size_t)my_b * n_dec + s : (size_t)my_b * Tmax + s) * kD + col] = c_state;
       if (dec && owner) attractors[((size_t)my_b * n_dec + s) * kD + col] = h_state;
     }
+    LSTM_STAMP(3);
     if (gs + 1 < n_total) {           // publish h (changed or not) into the next buffer of all 8 CTAs
       if (owner) hstage[cur][seq][u] = h_state;
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncthreads();
-      if (tid < kCluster)
+      LSTM_STAMP(4);
+      if (lane == 0)
         bulk_push(cur ? r_h0 : r_h1, s_u32(&hstage[cur][0][0]), kG * kUnits * 4, cur ? r_bar0 : r_bar1);
+      LSTM_STAMP(5);
     }
     if (!dec) {
 #pragma unroll
@@ -321,12 +337,246 @@ lstm_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__
   cluster.sync();    // nobody exits while a peer may still be reading its own buffers' traffic
 }
 
+// ------------------------------------------------------------------ tensor-core recurrence -----
+// Same cluster protocol, but the per-step mat-vec W_hh[own 128 rows] . h runs on the tensor cores as
+// split-bf16 products (W_hi.h_hi + W_lo.h_hi + W_hi.h_lo, fp32 accumulate) with mma.sync m16n8k16:
+// the FFMA version above is bound by register-file bandwidth (3 x 64-bit operands per FFMA2, ~1800-2200
+// cycles per step measured), the MMA version issues 48 instructions per warp and step (~770 cycles).
+// W stays register resident: warp w holds the A fragments of its 16 gate rows (4 units x {i,f,g,o}) for
+// all 16 k-steps, hi and lo (128 registers, what the fp32 weights took).  N = 8 = sequences of the cluster.
+//   rows of warp w's tile: thread group g = lane / 4 owns tile rows g and g + 8;
+//     g even -> unit 4w + g/2, gates i (row g) and f (row g + 8); g odd -> same unit, gates g~ and o
+//   one xor-4 shuffle pair swaps the halves so that lane (g, q) ends with the 4 gates of
+//     (unit 4w + g/2, sequence 2q + (g & 1)): 4 units x 8 sequences per warp.
+//   k ordering is free (it is summed over), so it is chosen for the loads: k-steps 2i, 2i+1 cover source
+//     CTA i's 32 units and thread q takes units 32i + 8q + {0..3} / {4..7} -> its B fragments of both
+//     steps are ONE 16-byte shared-memory load (hi) + one (lo), conflict-free.
+//   h travels as split bf16 by the same bulk copies: slice layout [source CTA][sequence][128 B] with
+//     hi | lo in the two 64-byte halves (swapped for odd sequences: keeps the fragment loads conflict-free).
+//   (Tried and rejected: per-lane st.async remote stores instead of staging + bulk copy: the exchange took
+//    ~1500 cycles instead of ~900.)
+__device__ __forceinline__ void mma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t& lo) {
+  const __nv_bfloat16 xh = __float2bfloat16_rn(x), yh = __float2bfloat16_rn(y);
+  const __nv_bfloat16 xl = __float2bfloat16_rn(x - __bfloat162float(xh)), yl = __float2bfloat16_rn(y - __bfloat162float(yh));
+  hi = (uint32_t)__bfloat16_as_ushort(xh) | ((uint32_t)__bfloat16_as_ushort(yh) << 16);
+  lo = (uint32_t)__bfloat16_as_ushort(xl) | ((uint32_t)__bfloat16_as_ushort(yl) << 16);
+}
+// A fragments of k-step t = 2i + s: a0a1 = (row g, units kb, kb+1), a2a3 = (row g+8, same), a4a5 = (row g, kb+2, kb+3),
+// a6a7 = (row g+8, same) with kb = 32i + 8q + 4s
+__device__ __forceinline__ void load_w_mma(uint32_t (&wh)[16][4], uint32_t (&wl)[16][4], const float* __restrict__ W,
+                                           int cta, int warp, int lane) {
+  const int g = lane >> 2, q = lane & 3;
+  const int unit = cta * kUnits + warp * 4 + (g >> 1);
+  const float* r0 = W + (size_t)(((g & 1) * 2 + 0) * kD + unit) * kD;   // gate i or g~
+  const float* r1 = W + (size_t)(((g & 1) * 2 + 1) * kD + unit) * kD;   // gate f or o
+#pragma unroll
+  for (int t = 0; t < 16; ++t) {
+    const int kb = 32 * (t >> 1) + 8 * q + 4 * (t & 1);
+    const float4 v0 = __ldg(reinterpret_cast<const float4*>(r0 + kb));
+    const float4 v1 = __ldg(reinterpret_cast<const float4*>(r1 + kb));
+    split2(v0.x, v0.y, wh[t][0], wl[t][0]);
+    split2(v1.x, v1.y, wh[t][1], wl[t][1]);
+    split2(v0.z, v0.w, wh[t][2], wl[t][2]);
+    split2(v1.z, v1.w, wh[t][3], wl[t][3]);
+  }
+}
+
+template <int kG>
+__global__ void __launch_bounds__(256, 1)
+lstm_mma_cluster_kernel(const float* __restrict__ xproj, const int32_t* __restrict__ perm,
+                        const int32_t* __restrict__ lens, const int32_t* __restrict__ order,
+                        const float* __restrict__ w_enc, const float* __restrict__ w_dec,
+                        const float* __restrict__ dec_bias, int B, int Tmax, int n_dec,
+                        float* __restrict__ attractors, float* __restrict__ hc_out, const LstmSave sv) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const int cta = (int)cluster.block_rank();
+  const int group = blockIdx.x / kCluster;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, q = lane & 3;
+  const int u = warp * 4 + (g >> 1);                   // local hidden unit of this lane
+  const int seq = 2 * q + (g & 1);                     // sequence whose gates end up in this lane
+  const bool owner = seq < kG;
+
+  // h_t double buffered: [source CTA][sequence 0..7][hi 64 B | lo 64 B] (halves swapped for odd sequences)
+  __shared__ __align__(128) uint8_t hs[2][kCluster][8][128];
+  __shared__ __align__(128) uint8_t hstage[2][8][128];
+  __shared__ __align__(8) uint64_t bars[2];
+  __shared__ int s_seq[kG], s_len[kG];
+
+  if (tid < kG) {
+    const int slot = group * kG + tid;
+    int b = -1, n = 0;
+    if (slot < B) { b = order ? order[slot] : slot; n = lens[b]; }
+    s_seq[tid] = b; s_len[tid] = n;
+  }
+  for (int i = tid; i < 2 * kCluster * 8 * 32; i += 256) reinterpret_cast<uint32_t*>(&hs[0][0][0][0])[i] = 0u;
+  for (int i = tid; i < 2 * 8 * 32; i += 256) reinterpret_cast<uint32_t*>(&hstage[0][0][0])[i] = 0u;
+  if (tid == 0) {
+    bar_init(&bars[0], 1); bar_init(&bars[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  int max_len = 0;
+#pragma unroll
+  for (int x = 0; x < kG; ++x) max_len = max(max_len, s_len[x]);
+  const int n_total = max_len + n_dec;
+  constexpr uint32_t kSliceBytes = kG * 128;
+  constexpr uint32_t kStepBytes = kCluster * kSliceBytes;
+  if (tid == 0) {
+    if (n_total > 1) bar_arm(&bars[1], kStepBytes);
+    if (n_total > 2) bar_arm(&bars[0], kStepBytes);
+  }
+
+  uint32_t wh[16][4], wl[16][4];
+  load_w_mma(wh, wl, w_enc, cta, warp, lane);
+
+  const int my_b = owner ? s_seq[seq] : -1;
+  const int my_len = owner ? s_len[seq] : 0;
+  float c_state = 0.f, h_state = 0.f;
+  float xg[4] = {0.f, 0.f, 0.f, 0.f};
+  int p_next = 0, p_cur = 0;
+  const size_t col = (size_t)cta * kUnits + u;
+  auto load_x = [&](int p, float (&dst)[4]) {
+    const float* row = xproj + ((size_t)my_b * Tmax + p) * (4 * kD) + col;
+#pragma unroll
+    for (int x = 0; x < 4; ++x) dst[x] = __ldg(row + x * kD);
+  };
+  if (my_len > 0) {
+    p_cur = __ldg(perm + (size_t)my_b * Tmax);
+    load_x(p_cur, xg);
+    if (my_len > 1) p_next = __ldg(perm + (size_t)my_b * Tmax + 1);
+  }
+  uint32_t r_h0 = 0, r_h1 = 0, r_bar0 = 0, r_bar1 = 0;
+  if (lane == 0) {    // lane 0 of warp r pushes this CTA's slice to rank r
+    r_h0 = map_rank(s_u32(&hs[0][cta][0][0]), warp); r_h1 = map_rank(s_u32(&hs[1][cta][0][0]), warp);
+    r_bar0 = map_rank(s_u32(&bars[0]), warp); r_bar1 = map_rank(s_u32(&bars[1]), warp);
+  }
+  // this lane's fragment source inside a slice: sequence g, 16-byte chunk q of the hi / lo half
+  const int frag_hi = g * 128 + (g & 1) * 64 + q * 16, frag_lo = g * 128 + (1 - (g & 1)) * 64 + q * 16;
+  // where this lane's new h goes inside the staged slice
+  const int st_hi = seq * 128 + (seq & 1) * 64 + 2 * u, st_lo = seq * 128 + (1 - (seq & 1)) * 64 + 2 * u;
+  cluster.sync();
+
+  for (int gs = 0; gs < n_total; ++gs) {
+    const bool dec = gs >= max_len;
+    const int s = dec ? gs - max_len : gs;
+    const int cur = gs & 1;
+    if (gs == max_len) {
+      load_w_mma(wh, wl, w_dec, cta, warp, lane);
+#pragma unroll
+      for (int x = 0; x < 4; ++x) xg[x] = __ldg(dec_bias + x * kD + col);
+      if (hc_out && my_b >= 0 && owner) {
+        hc_out[((size_t)my_b * 2 + 0) * kD + col] = h_state;
+        hc_out[((size_t)my_b * 2 + 1) * kD + col] = c_state;
+      }
+    }
+    float xn[4] = {0.f, 0.f, 0.f, 0.f};
+    int p_next2 = 0;
+    if (!dec && s + 1 < my_len) {
+      load_x(p_next, xn);
+      if (s + 2 < my_len) p_next2 = __ldg(perm + (size_t)my_b * Tmax + s + 2);
+    }
+    if (gs > 0) {
+      bar_wait(&bars[cur], ((gs - 1) >> 1) & 1);
+      if (tid == 0 && gs + 2 < n_total) bar_arm(&bars[cur], kStepBytes);
+    }
+    LSTM_STAMP(0);
+    // one accumulation chain per product (hi.hi, lo.hi, hi.lo): with 2 warps per scheduler that keeps
+    // 6 MMAs in flight, and the small terms are summed among themselves first
+    float acc[3][4];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+      for (int x = 0; x < 4; ++x) acc[a][x] = 0.f;
+#pragma unroll
+    for (int i = 0; i < kCluster; ++i) {
+      const uint4 bh = *reinterpret_cast<const uint4*>(&hs[cur][i][0][0] + frag_hi);
+      const uint4 bl = *reinterpret_cast<const uint4*>(&hs[cur][i][0][0] + frag_lo);
+      mma_bf16(acc[0], wh[2 * i], bh.x, bh.y);
+      mma_bf16(acc[1], wl[2 * i], bh.x, bh.y);
+      mma_bf16(acc[2], wh[2 * i], bl.x, bl.y);
+      mma_bf16(acc[0], wh[2 * i + 1], bh.z, bh.w);
+      mma_bf16(acc[1], wl[2 * i + 1], bh.z, bh.w);
+      mma_bf16(acc[2], wh[2 * i + 1], bl.z, bl.w);
+    }
+    LSTM_STAMP(1);
+    float c4[4];
+#pragma unroll
+    for (int x = 0; x < 4; ++x) c4[x] = (acc[1][x] + acc[2][x]) + acc[0][x];
+    // c4 = (row g, seq 2q), (row g, seq 2q+1), (row g+8, seq 2q), (row g+8, seq 2q+1): swap halves with lane ^ 4
+    const bool odd = (g & 1) != 0;
+    const float r0 = __shfl_xor_sync(0xffffffffu, odd ? c4[0] : c4[1], 4);
+    const float r1 = __shfl_xor_sync(0xffffffffu, odd ? c4[2] : c4[3], 4);
+    float v4[4];
+    v4[0] = odd ? r0 : c4[0]; v4[1] = odd ? r1 : c4[2];      // i, f
+    v4[2] = odd ? c4[1] : r0; v4[3] = odd ? c4[3] : r1;      // g~, o
+    LSTM_STAMP(2);
+
+    const bool active = dec ? (my_b >= 0) : (s < my_len);
+    if (active) {
+      const float ig = fast_sigmoid(v4[0] + xg[0]), fg = fast_sigmoid(v4[1] + xg[1]);
+      const float gg = fast_tanh(v4[2] + xg[2]), og = fast_sigmoid(v4[3] + xg[3]);
+      if (sv.gates != nullptr) {
+        const size_t row = dec ? (size_t)my_b * n_dec + s : (size_t)my_b * Tmax + s;
+        float* gsv = (dec ? sv.dec_gates : sv.gates) + row * (4 * kD) + col;
+        gsv[0] = ig; gsv[kD] = fg; gsv[2 * kD] = gg; gsv[3 * kD] = og;
+        const size_t hrow = dec ? row : (size_t)my_b * Tmax + p_cur;
+        const __nv_bfloat16 hh = __float2bfloat16_rn(h_state);
+        (dec ? sv.dec_hprev_hi : sv.hprev_hi)[hrow * kD + col] = hh;
+        (dec ? sv.dec_hprev_lo : sv.hprev_lo)[hrow * kD + col] = __float2bfloat16_rn(h_state - __bfloat162float(hh));
+      }
+      c_state = fg * c_state + ig * gg;
+      h_state = og * fast_tanh(c_state);
+      if (sv.gates != nullptr) (dec ? sv.dec_c : sv.c)[(dec ? (size_t)my_b * n_dec + s : (size_t)my_b * Tmax + s) * kD + col] = c_state;
+      if (dec) attractors[((size_t)my_b * n_dec + s) * kD + col] = h_state;
+    }
+    LSTM_STAMP(3);
+    if (gs + 1 < n_total) {
+      if (owner) {
+        const __nv_bfloat16 hh = __float2bfloat16_rn(h_state);
+        *reinterpret_cast<__nv_bfloat16*>(&hstage[cur][0][0] + st_hi) = hh;
+        *reinterpret_cast<__nv_bfloat16*>(&hstage[cur][0][0] + st_lo) = __float2bfloat16_rn(h_state - __bfloat162float(hh));
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncthreads();
+      LSTM_STAMP(4);
+      if (lane == 0)
+        bulk_push(cur ? r_h0 : r_h1, s_u32(&hstage[cur][0][0]), kSliceBytes, cur ? r_bar0 : r_bar1);
+      LSTM_STAMP(5);
+    }
+    if (!dec) {
+#pragma unroll
+      for (int x = 0; x < 4; ++x) xg[x] = xn[x];
+      p_cur = p_next;
+      p_next = p_next2;
+    }
+  }
+  cluster.sync();
+}
+
+#ifdef EDA_LSTM_TRACE
+}  // namespace eda
+extern "C" int eda_lstm_trace_read(long long* host, int n_cta) {
+  return cudaMemcpyFromSymbol(host, eda::g_lstm_trace, sizeof(long long) * 64 * (size_t)n_cta) == cudaSuccess ? 0 : 1;
+}
+namespace eda {
+#endif
+
 template <int kG>
 static int launch_lstm(cudaLaunchConfig_t& cfg, const float* xproj, const int32_t* perm, const int32_t* lens,
                        const int32_t* order, const float* w_enc, const float* w_dec, const float* dec_bias,
-                       int B, int Tmax, int n_dec, float* attractors, float* hc_out, const LstmSave& sv) {
-  EDA_CUDA(cudaLaunchKernelEx(&cfg, lstm_cluster_kernel<kG>, xproj, perm, lens, order, w_enc, w_dec,
-                              dec_bias, B, Tmax, n_dec, attractors, hc_out, sv));
+                       int B, int Tmax, int n_dec, float* attractors, float* hc_out, const LstmSave& sv, bool tensor) {
+  if (tensor)
+    EDA_CUDA(cudaLaunchKernelEx(&cfg, lstm_mma_cluster_kernel<kG>, xproj, perm, lens, order, w_enc, w_dec,
+                                dec_bias, B, Tmax, n_dec, attractors, hc_out, sv));
+  else
+    EDA_CUDA(cudaLaunchKernelEx(&cfg, lstm_cluster_kernel<kG>, xproj, perm, lens, order, w_enc, w_dec,
+                                dec_bias, B, Tmax, n_dec, attractors, hc_out, sv));
   count_launch();
   return EDA_OK;
 }
@@ -355,7 +605,9 @@ int lstm_max_active_clusters() {
     lstm_launch_config(cfg, attr, 64, nullptr);
     int n = 0;
     if (cudaOccupancyMaxActiveClusters(&n, lstm_cluster_kernel<4>, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
-    cached = n;
+    int m = 0;
+    if (cudaOccupancyMaxActiveClusters(&m, lstm_mma_cluster_kernel<4>, &cfg) != cudaSuccess) { cudaGetLastError(); m = 0; }
+    cached = std::min(n, m);
   }
   return cached;
 }
@@ -363,8 +615,10 @@ int lstm_max_active_clusters() {
 int lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens,
                     const int32_t* order, const float* w_enc, const float* w_dec,
                     const float* dec_bias, int B, int Tmax, int D, int n_dec, float* attractors,
-                    float* hc_out, const LstmSave& sv, cudaStream_t st) {
+                    float* hc_out, const LstmSave& sv, int prec, cudaStream_t st) {
   EDA_REQUIRE(D == kD, "eda_lstm_attractors: D must be 256 (got %d)", D);
+  EDA_REQUIRE(prec == EDA_PREC_FP32 || prec == EDA_PREC_BF16X3 || prec == EDA_PREC_BF16, "eda_lstm_attractors: bad precision %d", prec);
+  const bool tensor = prec != EDA_PREC_FP32;
   EDA_REQUIRE(B > 0 && Tmax > 0 && n_dec >= 0, "eda_lstm_attractors: bad sizes");
   EDA_REQUIRE(((uintptr_t)w_enc | (uintptr_t)w_dec) % 16 == 0, "eda_lstm_attractors: weights must be 16B aligned");
   // one wave if at all possible: the smallest G in 4..8 whose cluster count fits the device
@@ -378,11 +632,11 @@ int lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens
   cudaLaunchAttribute attr[1];
   lstm_launch_config(cfg, attr, ceil_div(B, G), st);
   switch (G) {
-    case 4: return launch_lstm<4>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv);
-    case 5: return launch_lstm<5>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv);
-    case 6: return launch_lstm<6>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv);
-    case 7: return launch_lstm<7>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv);
-    default: return launch_lstm<8>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv);
+    case 4: return launch_lstm<4>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv, tensor);
+    case 5: return launch_lstm<5>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv, tensor);
+    case 6: return launch_lstm<6>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv, tensor);
+    case 7: return launch_lstm<7>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv, tensor);
+    default: return launch_lstm<8>(cfg, xproj, perm, lens, order, w_enc, w_dec, dec_bias, B, Tmax, n_dec, attractors, hc_out, sv, tensor);
   }
 }
 
@@ -502,9 +756,9 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
   load_step(n_total - 1, cur_in);
 
   uint32_t r_d0 = 0, r_d1 = 0, r_bar0 = 0, r_bar1 = 0;
-  if (tid < kCluster) {
-    r_d0 = map_rank(s_u32(&dg[0][cta][0][0][0]), tid); r_d1 = map_rank(s_u32(&dg[1][cta][0][0][0]), tid);
-    r_bar0 = map_rank(s_u32(&bars[0]), tid); r_bar1 = map_rank(s_u32(&bars[1]), tid);
+  if (lane == 0) {    // lane 0 of warp r pushes to rank r
+    r_d0 = map_rank(s_u32(&dg[0][cta][0][0][0]), warp); r_d1 = map_rank(s_u32(&dg[1][cta][0][0][0]), warp);
+    r_bar0 = map_rank(s_u32(&bars[0]), warp); r_bar1 = map_rank(s_u32(&bars[1]), warp);
   }
   cluster.sync();
 
@@ -587,7 +841,7 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
     if (r + 1 < n_total) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncthreads();
-      if (tid < kCluster)
+      if (lane == 0)
         bulk_push(cur ? r_d0 : r_d1, s_u32(&stage[cur][0][0][0]), kG * 512, cur ? r_bar0 : r_bar1);
     }
     cur_in = nxt;

@@ -65,7 +65,7 @@ class LstmEncoderDedecoderAttractor(nn.Module):
         order = torch.tensor(sorted(range(B), key=lambda b: -lens_host[b]), dtype=torch.int32).to(
             emb2d.device, non_blocking=True)
         att, _ = ops.lstm_attractors(xproj, perm, lens_dev, order, w["u_enc"], w["u_dec"], w["b_dec"],
-                                     B, Tmax, n_dec)
+                                     B, Tmax, n_dec, prec=self.precision)
         probs, loss_att = ops.attractor_head(att, w["w_lin"], w["b_lin"], n_spk_label)
         return att, probs, loss_att
 

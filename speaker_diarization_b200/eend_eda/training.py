@@ -174,7 +174,7 @@ def forward_train(model, src: List[Tensor], ts: List[Tensor]):
     ops.gemm_split(emb_s, e["sw_ih"], e["b_enc"], M, 4 * D, D, L.EPI_BIAS, P, out=ws["xproj"])
     order = torch.tensor(sorted(range(B), key=lambda b: -ilens[b]), dtype=torch.int32).to(dev, non_blocking=True)
     att = OT.lstm_attractors_train(ws["xproj"], perm, lens_dev, order, e["u_enc"], e["u_dec"], e["b_dec"], B, Tmax,
-                                   n_dec, ws["sv"])
+                                   n_dec, ws["sv"], P)
     probs, loss_att = ops.attractor_head(att, e["w_lin"], e["b_lin"], S)
     pred, _, _ = ops.posterior(emb, att, B, Tmax, S, want_logits=True, want_post=False)
     loss_pit, min_idx, label_perm, _ = ops.pit_loss(pred, label, lens_dev)

@@ -54,14 +54,15 @@ def mha(qkv: Tensor, B: int, T: int, n_heads: int, prec: int = L.PREC_FP32) -> T
 
 
 def lstm_attractors(xproj: Tensor, perm: Tensor, lens: Tensor, order: Optional[Tensor], w_hh_enc: Tensor,
-                    w_hh_dec: Tensor, dec_bias: Tensor, B: int, Tmax: int, n_dec: int, want_hc: bool = False):
+                    w_hh_dec: Tensor, dec_bias: Tensor, B: int, Tmax: int, n_dec: int, want_hc: bool = False,
+                    prec: int = L.PREC_FP32):
     D = w_hh_enc.shape[1]
     att = torch.empty((B, n_dec, D), dtype=torch.float32, device=xproj.device)
     hc = torch.empty((B, 2, D), dtype=torch.float32, device=xproj.device) if want_hc else None
     assert perm.dtype == torch.int32 and lens.dtype == torch.int32
     L.call("eda_lstm_attractors", L.ptr(_f32(xproj)), L.ptr(perm), L.ptr(lens), L.ptr(order),
            L.ptr(_f32(w_hh_enc)), L.ptr(_f32(w_hh_dec)), L.ptr(_f32(dec_bias)), B, Tmax, D, n_dec,
-           L.ptr(att), L.ptr(hc), L.stream())
+           L.ptr(att), L.ptr(hc), prec, L.stream())
     return att, hc
 
 

@@ -93,7 +93,8 @@ def scale_split(src: Tensor, scale: float, dst: Split, cols: Optional[int] = Non
 
 
 def lstm_attractors_train(xproj: Tensor, perm: Tensor, lens: Tensor, order: Optional[Tensor], w_hh_enc: Tensor,
-                          w_hh_dec: Tensor, dec_bias: Tensor, B: int, Tmax: int, n_dec: int, sv: dict) -> Tensor:
+                          w_hh_dec: Tensor, dec_bias: Tensor, B: int, Tmax: int, n_dec: int, sv: dict,
+                          prec: int = L.PREC_FP32) -> Tensor:
     """``sv``: the save buffers (gates, c, hprev: Split, dec_gates, dec_c, dec_hprev: Split, hc)."""
     D = w_hh_enc.shape[1]
     att = torch.empty((B, n_dec, D), dtype=torch.float32, device=xproj.device)
@@ -101,7 +102,7 @@ def lstm_attractors_train(xproj: Tensor, perm: Tensor, lens: Tensor, order: Opti
            L.ptr(_f32(w_hh_enc)), L.ptr(_f32(w_hh_dec)), L.ptr(_f32(dec_bias)), B, Tmax, D, n_dec, L.ptr(att),
            L.ptr(sv["hc"]), L.ptr(sv["gates"]), L.ptr(sv["c"]), L.ptr(sv["hprev"].hi), L.ptr(sv["hprev"].lo),
            L.ptr(sv["dec_gates"]), L.ptr(sv["dec_c"]), L.ptr(sv["dec_hprev"].hi), L.ptr(sv["dec_hprev"].lo),
-           L.stream())
+           prec, L.stream())
     return att
 
 

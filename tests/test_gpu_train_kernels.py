@@ -229,7 +229,8 @@ def _lstm_ref(emb, lens, perms, n_dec, We, Ue, be, Ud, bd):
 
 
 @pytest.mark.parametrize("lens,n_dec", [([40, 17, 40, 1, 33], 3), ([64] * 9, 4), ([5], 1), ([30, 0, 12], 2)])
-def test_lstm_bwd(dev, lens, n_dec):
+@pytest.mark.parametrize("lstm_prec", ["fp32", "bf16x3"])     # forward recurrence on CUDA cores / tensor cores
+def test_lstm_bwd(dev, lens, n_dec, lstm_prec):
     """Forward with saves + BPTT kernel + the GEMMs that turn gate gradients into parameter / input
     gradients, against autograd through a python-loop LSTM."""
     from speaker_diarization_b200 import _lib as L, ops, ops_train as OT
@@ -257,8 +258,8 @@ def test_lstm_bwd(dev, lens, n_dec):
               dec_gates=torch.zeros((B * n_dec, 4 * D), device=dev), dec_c=torch.zeros((B * n_dec, D), device=dev),
               dec_hprev=ops.Split.empty(B * n_dec, D, dev), hc=torch.zeros((B, 2, D), device=dev))
     att = OT.lstm_attractors_train(xproj, perm_d, lens_d, None, Ue.detach().to(dev), Ud.detach().to(dev),
-                                   bd.detach().to(dev), B, Tmax, n_dec, sv)
-    assert (att.cpu() - att_ref.detach()).abs().max().item() < 2e-5
+                                   bd.detach().to(dev), B, Tmax, n_dec, sv, L.PRECISIONS[lstm_prec])
+    assert (att.cpu() - att_ref.detach()).abs().max().item() < (2e-5 if lstm_prec == "fp32" else 1e-4)
     dxp, ddec = ops.Split.empty(M, 4 * D, dev), ops.Split.empty(B * n_dec, 4 * D, dev)
     OT.lstm_attractors_bwd(perm_d, lens_d, None, Ue.detach().to(dev), Ud.detach().to(dev), sv, datt.to(dev), B, Tmax,
                            n_dec, dxp, ddec)

@@ -644,10 +644,10 @@ int lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens
 // BPTT through the decoder and encoder LSTMs, same cluster shape as the forward:
 // CTA c owns hidden units [32c, 32c+32).  Walking the steps backwards, per step
 //   wait until all 8 CTAs' gate gradients of the LATER step have landed (mbarrier + DSMEM bulk
-//   pushes, 4 x the forward's volume: 128 gate rows per CTA and sequence)
-//   -> dh[own 32 units] += W_hh[:, own units]^T . dgates  (the 1024 x 32 column slice of W_hh is
-//      register resident: thread (unit u, slice kc) holds rows {gate*256 + 32i + 4kc + j}; packed
-//      FFMA2, butterfly reduction over the 8 slice lanes)
+//   pushes of split-bf16 pairs, 4 x the forward's volume: 128 gate rows per CTA and sequence)
+//   -> dh[own 32 units] += W_hh[:, own units]^T . dgates on the tensor cores (the 1024 x 32 column slice of
+//      W_hh is register resident as split-bf16 MMA fragments, see load_wt_mma; the 8 warps' partial tiles are
+//      summed through shared memory)
 //   -> lane kc == sequence finishes the cell backward from the saved activated gates / cell states
 //   -> its 4 gate gradients go to HBM as the split-bf16 operand of the weight / input gradient
 //      GEMMs (frame order, row b*Tmax + perm[s]) and to the peers for the next (earlier) step.
@@ -661,20 +661,28 @@ struct LstmBwd {
   int B, Tmax, n_dec;
 };
 
-// Mat-vec mapping of the backward kernel: warp w owns the 4 hidden units 4w..4w+3, lane l the 32 gate rows
-// {gate = l >> 3, source CTA j, unit 4 (l & 7) + e : j < 8, e < 4} - one 16-byte chunk of every source CTA's
-// slice, so a warp reads each (source CTA, sequence) slice of 512 B exactly once (no two lanes load the same
-// gate gradient; the forward-style mapping read every value 4 times and was bound by shared-memory wavefronts).
-// wt[j][e][0..1] = packed W[row(j, e)][32 cta + 4 w + {0,1 | 2,3}]
-__device__ __forceinline__ void load_wt(uint64_t (&wt)[8][4][2], const float* __restrict__ W, int cta, int warp, int lane) {
+// Mat-vec of the backward kernel on the tensor cores (mma.sync m16n8k16, split-bf16 x 3 products like the
+// forward): dh[unit (M = 32: two 16-row tiles)][sequence (N = 8)] = sum over the 1024 gate rows (K) of
+// W_hh[row][own unit] . dgates[row][sequence].  Warp w takes the K range that arrives from source CTA w
+// (8 k-steps) for both M tiles: 2 x 8 x 4 A registers, hi and lo = 128 registers, resident.  The 8 warps'
+// partial tiles are summed through shared memory by the lane that owns (unit, sequence).
+// k order inside a source slice (free, chosen for the 8-byte stores of the producer and the 16-byte loads of
+// the consumer): 16-byte chunk c of a sequence's row holds units 2c, 2c+1 x gates i,f,g,o; thread q reads
+// chunks q + 4j: k-step 2j = unit 2(q+4j), k-step 2j+1 = unit 2(q+4j)+1, logical k {2q,2q+1 | 2q+8,2q+9} = gates {0,1 | 2,3}.
+__device__ __forceinline__ void load_wt_mma(uint32_t (&wh)[2][8][4], uint32_t (&wl)[2][8][4], const float* __restrict__ W,
+                                            int cta, int warp, int lane) {
+  const int g = lane >> 2, q = lane & 3;
+  constexpr size_t kGate = (size_t)kD * kD;
 #pragma unroll
-  for (int j = 0; j < 8; ++j)
+  for (int m = 0; m < 2; ++m)
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int row = (lane >> 3) * kD + 32 * j + 4 * (lane & 7) + e;
-      const float4 v = __ldg(reinterpret_cast<const float4*>(W + (size_t)row * kD + cta * kUnits + 4 * warp));
-      wt[j][e][0] = pack2(v.x, v.y);
-      wt[j][e][1] = pack2(v.z, v.w);
+    for (int t = 0; t < 8; ++t) {
+      const int v = 2 * (q + 4 * (t >> 1)) + (t & 1);                       // unit inside source CTA `warp`
+      const float* base = W + (size_t)(32 * warp + v) * kD + cta * kUnits + m * 16 + g;
+      split2(__ldg(base), __ldg(base + kGate), wh[m][t][0], wl[m][t][0]);                       // out unit g,   gates i, f
+      split2(__ldg(base + 8), __ldg(base + kGate + 8), wh[m][t][1], wl[m][t][1]);               // out unit g+8, gates i, f
+      split2(__ldg(base + 2 * kGate), __ldg(base + 3 * kGate), wh[m][t][2], wl[m][t][2]);       // out unit g,   gates g~, o
+      split2(__ldg(base + 2 * kGate + 8), __ldg(base + 3 * kGate + 8), wh[m][t][3], wl[m][t][3]);
     }
 }
 
@@ -686,15 +694,18 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
   const int group = blockIdx.x / kCluster;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rg = lane >> 3, kc = lane & 7;
-  const int u = warp * 4 + rg;
+  const int u = warp * 4 + rg;                 // (unit, sequence) this lane owns for the cell backward: tid = 8 u + seq
   const int seq = kc;
   const bool owner = kc < kG;
+  const int g = lane >> 2, q = lane & 3;       // MMA fragment coordinates
 
   extern __shared__ __align__(128) uint8_t lsm_raw[];
-  // gate gradients of one step, [buffer][source CTA][sequence][gate][unit]: a CTA's slice is kG*512 B
-  float (*dg)[kCluster][kG][4][kUnits] = reinterpret_cast<float (*)[kCluster][kG][4][kUnits]>(lsm_raw);
-  float (*stage)[kG][4][kUnits] = reinterpret_cast<float (*)[kG][4][kUnits]>(lsm_raw + 2 * kCluster * kG * 512);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(lsm_raw + 2 * kCluster * kG * 512 + 2 * kG * 512);
+  // gate gradients of one step as split bf16, [buffer][source CTA][sequence][hi 256 B | lo 256 B]; inside a half,
+  // 16-byte chunk c (units 2c, 2c+1 x 4 gates) sits at c ^ (4 * (sequence & 1)): conflict-free fragment loads
+  uint8_t* dg = lsm_raw;
+  uint8_t* stage = lsm_raw + 2 * kCluster * kG * 512;
+  float* red = reinterpret_cast<float*>(lsm_raw + 2 * kCluster * kG * 512 + 2 * kG * 512);   // [warp][unit 32][sequence 8]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(red + 8 * 32 * 8);
   int* s_seq = reinterpret_cast<int*>(bars + 2);
   int* s_len = s_seq + 8;
 
@@ -711,7 +722,7 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
   __syncthreads();
   int max_len = 0;
 #pragma unroll
-  for (int g = 0; g < kG; ++g) max_len = max(max_len, s_len[g]);
+  for (int x = 0; x < kG; ++x) max_len = max(max_len, s_len[x]);
   const int n_dec = P.n_dec, Tmax = P.Tmax;
   const int n_total = max_len + n_dec;
   constexpr uint32_t kStepBytes = kCluster * kG * 512;
@@ -719,8 +730,8 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
     if (n_total > 1) bar_arm(&bars[1], kStepBytes);
     if (n_total > 2) bar_arm(&bars[0], kStepBytes);
   }
-  uint64_t wt[8][4][2];
-  load_wt(wt, n_dec > 0 ? P.w_dec : P.w_enc, cta, warp, lane);
+  uint32_t wh[2][8][4], wl[2][8][4];
+  load_wt_mma(wh, wl, n_dec > 0 ? P.w_dec : P.w_enc, cta, warp, lane);
 
   const int my_b = owner ? s_seq[seq] : -1;
   const int my_len = owner ? s_len[seq] : 0;
@@ -757,9 +768,16 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
 
   uint32_t r_d0 = 0, r_d1 = 0, r_bar0 = 0, r_bar1 = 0;
   if (lane == 0) {    // lane 0 of warp r pushes to rank r
-    r_d0 = map_rank(s_u32(&dg[0][cta][0][0][0]), warp); r_d1 = map_rank(s_u32(&dg[1][cta][0][0][0]), warp);
+    r_d0 = map_rank(s_u32(dg + (size_t)cta * kG * 512), warp);
+    r_d1 = map_rank(s_u32(dg + (size_t)(kCluster + cta) * kG * 512), warp);
     r_bar0 = map_rank(s_u32(&bars[0]), warp); r_bar1 = map_rank(s_u32(&bars[1]), warp);
   }
+  // fragment source of this lane inside source CTA `warp`'s slice: row of sequence g (clamped: columns >= kG are
+  // never used), chunk q + 4j swizzled by the row's parity
+  const int g_row = g < kG ? g : kG - 1;
+  const int frag = warp * kG * 512 + g_row * 512, frag_sw = 4 * (g_row & 1);   // chunk (q + 4j) ^ frag_sw, + 256 for lo
+  // where the owner lane's 4 gate gradients go inside the staged slice
+  const int st_off = seq * 512 + (((u >> 1) ^ (4 * (seq & 1))) * 16) + (u & 1) * 8;
   cluster.sync();
 
   for (int r = 0; r < n_total; ++r) {
@@ -770,79 +788,81 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
     StepIn nxt;
     load_step(gs - 1, nxt);                 // in flight under the mat-vec
     if (r > 0) {
-      if (n_dec > 0 && gs + 1 == max_len - 1) load_wt(wt, P.w_enc, cta, warp, lane);   // the later step is an encoder step from here on
+      if (n_dec > 0 && gs + 1 == max_len - 1) load_wt_mma(wh, wl, P.w_enc, cta, warp, lane);   // the later step is an encoder step from here on
       bar_wait(&bars[cur], ((r - 1) >> 1) & 1);
       if (tid == 0 && r + 2 < n_total) bar_arm(&bars[cur], kStepBytes);
-      uint64_t acc[kG][2];                     // (units 0,1 | 2,3) of this warp, partial over this lane's 32 rows
+      float acc[2][3][4];
 #pragma unroll
-      for (int g = 0; g < kG; ++g) acc[g][0] = acc[g][1] = 0ull;
+      for (int m = 0; m < 2; ++m)
 #pragma unroll
-      for (int j = 0; j < 8; ++j)
+        for (int a = 0; a < 3; ++a)
 #pragma unroll
-        for (int g = 0; g < kG; ++g) {
-          const float4 dv = *reinterpret_cast<const float4*>(&dg[cur][j][g][lane >> 3][4 * (lane & 7)]);
-          const float d4[4] = {dv.x, dv.y, dv.z, dv.w};
+          for (int x = 0; x < 4; ++x) acc[m][a][x] = 0.f;
+      const uint8_t* src = dg + (size_t)cur * kCluster * kG * 512 + frag;
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const uint64_t dd = pack2(d4[e], d4[e]);
-            acc[g][0] = ffma2(wt[j][e][0], dd, acc[g][0]);
-            acc[g][1] = ffma2(wt[j][e][1], dd, acc[g][1]);
-          }
-        }
-      // reduce over the 32 row slices: two halving rounds hand each lane ONE unit (lane bits 4,3 = unit, like
-      // the owner mapping u = 4 warp + (lane >> 3)), three butterfly rounds finish the sums for all sequences
-      float rsum = 0.f;
-      {
-        const bool up4 = (lane & 16) != 0, up3 = (lane & 8) != 0;
+      for (int j = 0; j < 4; ++j) {
+        const uint4 bh = *reinterpret_cast<const uint4*>(src + ((q + 4 * j) ^ frag_sw) * 16);
+        const uint4 bl = *reinterpret_cast<const uint4*>(src + ((q + 4 * j) ^ frag_sw) * 16 + 256);
 #pragma unroll
-        for (int g = 0; g < kG; ++g) {
-          const float v0 = __uint_as_float((uint32_t)acc[g][0]), v1 = __uint_as_float((uint32_t)(acc[g][0] >> 32));
-          const float v2 = __uint_as_float((uint32_t)acc[g][1]), v3 = __uint_as_float((uint32_t)(acc[g][1] >> 32));
-          const float k0 = (up4 ? v2 : v0) + __shfl_xor_sync(0xffffffffu, up4 ? v0 : v2, 16);
-          const float k1 = (up4 ? v3 : v1) + __shfl_xor_sync(0xffffffffu, up4 ? v1 : v3, 16);
-          float t = (up3 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, up3 ? k0 : k1, 8);
-          t += __shfl_xor_sync(0xffffffffu, t, 4);
-          t += __shfl_xor_sync(0xffffffffu, t, 2);
-          t += __shfl_xor_sync(0xffffffffu, t, 1);
-          if (kc == g) rsum = t;
+        for (int m = 0; m < 2; ++m) {
+          mma_bf16(acc[m][0], wh[m][2 * j], bh.x, bh.y);
+          mma_bf16(acc[m][1], wl[m][2 * j], bh.x, bh.y);
+          mma_bf16(acc[m][2], wh[m][2 * j], bl.x, bl.y);
+          mma_bf16(acc[m][0], wh[m][2 * j + 1], bh.z, bh.w);
+          mma_bf16(acc[m][1], wl[m][2 * j + 1], bh.z, bh.w);
+          mma_bf16(acc[m][2], wh[m][2 * j + 1], bl.z, bl.w);
         }
       }
+      // this warp's partial tile -> shared memory; the owner of (unit, sequence) adds the 8 partials
+      float* mine = red + warp * 256;
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        float c4[4];
+#pragma unroll
+        for (int x = 0; x < 4; ++x) c4[x] = (acc[m][1][x] + acc[m][2][x]) + acc[m][0][x];
+        *reinterpret_cast<float2*>(mine + (m * 16 + g) * 8 + 2 * q) = make_float2(c4[0], c4[1]);
+        *reinterpret_cast<float2*>(mine + (m * 16 + g + 8) * 8 + 2 * q) = make_float2(c4[2], c4[3]);
+      }
+      __syncthreads();
+      float rsum = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) rsum += red[w * 256 + tid];
       carry_dh += rsum;
     }
     if (owner) {
       const bool active = my_b >= 0 && (dec || s < my_len);
-      float d4[4] = {0.f, 0.f, 0.f, 0.f};
+      uint2 hi2 = make_uint2(0u, 0u), lo2 = make_uint2(0u, 0u);
       if (active) {
         const float ig = cur_in.g[0], fg = cur_in.g[1], gg = cur_in.g[2], og = cur_in.g[3];
         const float dh = carry_dh + cur_in.da;
         const float tc = fast_tanh(cur_in.c);
         const float dc = carry_dc + dh * og * (1.f - tc * tc);
+        float d4[4];
         d4[0] = dc * gg * ig * (1.f - ig);
         d4[1] = dc * cur_in.cp * fg * (1.f - fg);
         d4[2] = dc * ig * (1.f - gg * gg);
         d4[3] = dh * tc * og * (1.f - og);
         carry_dc = dc * fg;
         carry_dh = 0.f;
+        split2(d4[0], d4[1], hi2.x, lo2.x);
+        split2(d4[2], d4[3], hi2.y, lo2.y);
         const size_t row = dec ? (size_t)my_b * n_dec + s : (size_t)my_b * Tmax + cur_in.p;
-        __nv_bfloat16* oh = (dec ? P.ddec_hi : P.dxp_hi) + row * (4 * kD) + col;
-        __nv_bfloat16* ol = (dec ? P.ddec_lo : P.dxp_lo) + row * (4 * kD) + col;
-#pragma unroll
-        for (int x = 0; x < 4; ++x) {
-          const __nv_bfloat16 hv = __float2bfloat16_rn(d4[x]);
-          oh[x * kD] = hv;
-          ol[x * kD] = __float2bfloat16_rn(d4[x] - __bfloat162float(hv));
-        }
+        uint16_t* oh = reinterpret_cast<uint16_t*>(dec ? P.ddec_hi : P.dxp_hi) + row * (4 * kD) + col;
+        uint16_t* ol = reinterpret_cast<uint16_t*>(dec ? P.ddec_lo : P.dxp_lo) + row * (4 * kD) + col;
+        oh[0] = (uint16_t)hi2.x; oh[kD] = (uint16_t)(hi2.x >> 16); oh[2 * kD] = (uint16_t)hi2.y; oh[3 * kD] = (uint16_t)(hi2.y >> 16);
+        ol[0] = (uint16_t)lo2.x; ol[kD] = (uint16_t)(lo2.x >> 16); ol[2 * kD] = (uint16_t)lo2.y; ol[3 * kD] = (uint16_t)(lo2.y >> 16);
       }
       if (r + 1 < n_total) {
-#pragma unroll
-        for (int x = 0; x < 4; ++x) stage[cur][seq][x][u] = d4[x];
+        uint8_t* st = stage + cur * kG * 512 + st_off;
+        *reinterpret_cast<uint2*>(st) = hi2;
+        *reinterpret_cast<uint2*>(st + 256) = lo2;
       }
     }
     if (r + 1 < n_total) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncthreads();
       if (lane == 0)
-        bulk_push(cur ? r_d0 : r_d1, s_u32(&stage[cur][0][0][0]), kG * 512, cur ? r_bar0 : r_bar1);
+        bulk_push(cur ? r_d0 : r_d1, s_u32(stage + cur * kG * 512), kG * 512, cur ? r_bar0 : r_bar1);
     }
     cur_in = nxt;
   }
@@ -851,7 +871,7 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
 
 template <int kG>
 static int launch_lstm_bwd(cudaLaunchConfig_t& cfg, const LstmBwd& P) {
-  const int smem = 2 * kCluster * kG * 512 + 2 * kG * 512 + 16 + 64 + 128;
+  const int smem = 2 * kCluster * kG * 512 + 2 * kG * 512 + 8 * 32 * 8 * 4 + 16 + 64 + 128;
   static bool attr = false;
   if (!attr) {
     EDA_CUDA(cudaFuncSetAttribute(lstm_bwd_cluster_kernel<kG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -64,6 +64,8 @@ def main():
     kG = 4
     while (B + kG - 1) // kG > mc and kG < 8:
         kG += 1
+    if prec != 0:
+        kG = min(8, max(4, B))      # the tensor-core inference launch packs 8 sequences per cluster
     n_cta = 8 * ((B + kG - 1) // kG)
     buf = np.zeros((n_cta, 8, 8), dtype=np.int64)
     lib.eda_lstm_trace_read.argtypes = [p, C.c_int]

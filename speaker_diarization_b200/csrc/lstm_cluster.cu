@@ -628,6 +628,11 @@ int lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens
   const int fit = std::max(1, lstm_max_active_clusters());
   int G = 4;
   while (G < 8 && ceil_div(B, G) > fit) ++G;
+  // the MMA tile is 8 sequences wide whatever G is: a step costs about the same for 8 sequences as for 4
+  // (+5 % measured), so the inference launch packs 8 per cluster and leaves the other SMs to the batches
+  // running beside it on the pipeline's other streams (+4 % end to end).  The training launch (nothing runs
+  // beside it, and every owner lane also stores 7 values per step) keeps the smallest G.
+  if (tensor && sv.gates == nullptr) G = std::min(8, std::max(4, B));
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attr[1];
   lstm_launch_config(cfg, attr, ceil_div(B, G), st);

@@ -252,6 +252,11 @@ int eda_rttm_segments(const float* post, const uint8_t* labels, int ld, const in
  * same function, so no mask is stored; eda_dropout_mask writes one out (tests).  For the attention weights
  * row = (b * n_heads + h) * T + query, col = key.                                                          */
 int eda_dropout_mask(float p_drop, uint64_t seed, int site, int64_t rows, int cols, uint8_t* keep, void* stream);
+/* The same mask as bits: bits[row * ld_words + w] holds columns 32w .. 32w+31 (bit e set = column 32w + e kept;
+ * ld_words >= ceil(cols / 32)).  The attention kernels take it as `drop_bits` (may be NULL = evaluate the
+ * function in the kernel): one precomputed word per thread and 32 keys replaces 4 Philox calls in the softmax
+ * warps of BOTH the forward and the backward kernel (the one place where a mask is stored: 1 bit per weight). */
+int eda_dropout_bits(float p_drop, uint64_t seed, int site, int64_t rows, int cols, uint32_t* bits, int ld_words, void* stream);
 
 /* eda_gemm_split for model.train(): LayerNorm epilogues also store rstd (M) = 1/sqrt(var + eps) per row
  * (rstd_out may be NULL); p_drop > 0 applies dropout to relu(A.W^T + bias) (EDA_EPI_BIAS_RELU) or to
@@ -298,7 +303,7 @@ int eda_colsum_split(const void* hi, const void* lo, int M, int N, int ld, float
 /* eda_mha_split that also stores lse (B*n_heads, T): log2-domain log-sum-exp of every score row. */
 int eda_mha_split_train(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
                         int Tp, int B, int T, int n_heads, void* out_hi, void* out_lo, int ld_os, float* lse,
-                        float p_drop, uint64_t seed, int site, int prec, void* stream);
+                        float p_drop, uint64_t seed, int site, const uint32_t* drop_bits, int ld_bits, int prec, void* stream);
 /* delta (B*T, 4) = rowsum over each head's 64 columns of dO * O (both split pairs, D == 256). */
 int eda_mha_delta(const void* do_hi, const void* do_lo, int ld_do, const void* o_hi, const void* o_lo, int ld_o,
                   int M, int D, float* delta, void* stream);
@@ -309,7 +314,7 @@ int eda_mha_delta(const void* do_hi, const void* do_lo, int ld_do, const void* o
 int eda_mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
                 const void* do_hi, const void* do_lo, int ld_do, const float* lse, const float* delta, int B,
                 int T, int n_heads, float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, float p_drop,
-                uint64_t seed, int site, int prec, void* stream);
+                uint64_t seed, int site, const uint32_t* drop_bits, int ld_bits, int prec, void* stream);
 /* (hi, lo) = split(src * scale): fp32 (rows, cols) -> split pair with row stride ld_s.           */
 int eda_scale_split(const float* src, int ld, int rows, int cols, float scale, void* hi, void* lo, int ld_s, void* stream);
 

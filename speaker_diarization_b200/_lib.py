@@ -50,14 +50,15 @@ SIGNATURES = {
     "eda_rttm_segments": (_i, [_p, _p, _i, _p, _i, _p, _i, _f, _i, _i, _p, _p, _p]),
     # ---- training step
     "eda_dropout_mask": (_i, [_f, _u64, _i, _i64, _i, _p, _p]),
+    "eda_dropout_bits": (_i, [_f, _u64, _i, _i64, _i, _p, _i, _p]),
     "eda_gemm_split_train": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _p, _f, _u64, _i, _i, _i, _i, _i, _i, _p]),
     "eda_gemm_dgrad": (_i, [_p, _p, _i, _p, _p, _i, _p, _i, _p, _i, _f, _p, _i, _p, _p, _i, _i, _i, _i, _i, _p]),
     "eda_gemm_wgrad": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _i, _p, _i64, _i, _i, _p]),
     "eda_ln_bwd": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _i, _p, _i, _p, _p, _i, _p, _p, _p, _p, _i64, _i, _f, _u64, _i, _p]),
     "eda_colsum_split": (_i, [_p, _p, _i, _i, _i, _p, _p, _i64, _i, _p]),
-    "eda_mha_split_train": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _p, _i, _p, _f, _u64, _i, _i, _p]),
+    "eda_mha_split_train": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _i, _p, _p, _i, _p, _f, _u64, _i, _p, _i, _i, _p]),
     "eda_mha_delta": (_i, [_p, _p, _i, _p, _p, _i, _i, _i, _p, _p]),
-    "eda_mha_bwd": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _i, _i, _i, _p, _p, _p, _i, _f, _u64, _i, _i, _p]),
+    "eda_mha_bwd": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _i, _i, _i, _p, _p, _p, _i, _f, _u64, _i, _p, _i, _i, _p]),
     "eda_scale_split": (_i, [_p, _i, _i, _i, _f, _p, _p, _i, _p]),
     "eda_lstm_attractors_train": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
     "eda_lstm_attractors_bwd": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p]),

@@ -384,6 +384,29 @@ __global__ void dropout_mask_kernel(const DropoutCfg d, int64_t rows, int cols, 
   }
 }
 
+// The same mask as bits: word w of a row holds columns 32w .. 32w+31 (bit e = column 32w + e kept).  The
+// attention kernels read one word per thread and 32 keys instead of evaluating Philox in their softmax warps.
+__global__ void dropout_bits_kernel(const DropoutCfg d, int64_t rows, int words, int ld, uint32_t* __restrict__ bits) {
+  const int64_t n = rows * (int64_t)words;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / words;
+    const int w = (int)(i % words);
+    uint32_t k = 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) k |= dropout_keep8(d, (uint32_t)r, (uint32_t)(4 * w + c)) << (8 * c);
+    bits[r * ld + w] = k;
+  }
+}
+int dropout_bits(float p, uint64_t seed, int site, int64_t rows, int cols, uint32_t* bits, int ld_words, cudaStream_t st) {
+  const int words = ceil_div(cols, 32);
+  EDA_REQUIRE(bits && rows > 0 && cols > 0 && ld_words >= words && p > 0.f && p < 1.f, "eda_dropout_bits: bad arguments");
+  const int64_t n = rows * (int64_t)words;
+  dropout_bits_kernel<<<(int)std::min<int64_t>(ceil_div<int64_t>(n, 256), num_sms() * 16), 256, 0, st>>>(make_dropout(p, seed, site), rows, words, ld_words, bits);
+  EDA_LAUNCH_CHECK();
+  count_launch();
+  return EDA_OK;
+}
+
 int dropout_mask(float p, uint64_t seed, int site, int64_t rows, int cols, uint8_t* keep, cudaStream_t st) {
   EDA_REQUIRE(keep && rows > 0 && cols > 0 && cols % 8 == 0 && p >= 0.f && p < 1.f, "eda_dropout_mask: bad arguments (cols %% 8 == 0)");
   const int64_t n = rows * (int64_t)(cols / 8);
@@ -444,6 +467,9 @@ int eda_ln_bwd(const float* dy, int ld_dy, const float* y, int ld_y, const float
                      (cudaStream_t)stream);
 }
 
+int eda_dropout_bits(float p_drop, uint64_t seed, int site, int64_t rows, int cols, uint32_t* bits, int ld_words, void* stream) {
+  return eda::dropout_bits(p_drop, seed, site, rows, cols, bits, ld_words, (cudaStream_t)stream);
+}
 int eda_dropout_mask(float p_drop, uint64_t seed, int site, int64_t rows, int cols, uint8_t* keep, void* stream) {
   return eda::dropout_mask(p_drop, seed, site, rows, cols, keep, (cudaStream_t)stream);
 }

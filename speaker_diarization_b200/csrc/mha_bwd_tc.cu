@@ -57,6 +57,7 @@ struct MhaBwdParams {
   bf16* dkv_hi; bf16* dkv_lo; int ld_dkv;     // split (B*T, ld): dk at column dk_col0 + 64h, dv at dv_col0 + 64h
   int dk_col0, dv_col0;
   DropoutCfg drop;         // the forward's attention-weight dropout (thresh == 0 = off)
+  const uint32_t* drop_bits; int ld_bits;     // optional: the same keep mask as bits (eda_dropout_bits)
 };
 
 __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
@@ -199,6 +200,16 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
     constexpr float kLog2e = 1.4426950408889634f;
     const uint32_t sP = smem_u32(smem + B_OFF_P) + half * 16384 + r * 128;
     const uint32_t sDS = smem_u32(smem + B_OFF_DS) + half * 16384 + r * 128;
+    uint32_t keep_n0 = 0xffffffffu, keep_n1 = 0xffffffffu;
+    auto load_keep = [&](int tile) {
+      const int qn = tile * BT + r;
+      if (p.drop_bits != nullptr && qn < p.T) {
+        const uint32_t* bw = p.drop_bits + (size_t)((b * p.H + h) * p.T + qn) * p.ld_bits + ((k0 + half * 64) >> 5);
+        if (k0 + half * 64 < p.T) keep_n0 = __ldg(bw);
+        if (k0 + half * 64 + 32 < p.T) keep_n1 = __ldg(bw + 1);
+      }
+    };
+    load_keep(0);
     for (int i = 0; i < n_t; ++i) {
       const int q = i * BT + r;
       const bool q_ok = q < p.T;
@@ -207,6 +218,9 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
         lse = __ldg(p.lse + ((size_t)b * p.H + h) * p.T + q);
         dl = __ldg(p.delta + ((size_t)b * p.T + q) * p.H + h);
       }
+      // keep bits of this thread's 2 x 32 keys (precomputed masks), fetched one query tile ahead
+      const uint32_t keep_w0 = keep_n0, keep_w1 = keep_n1;
+      load_keep(i + 1);
       mbar_wait(bar_s, i & 1);
       tc_fence_after();
 #pragma unroll 1
@@ -217,8 +231,13 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
         tmem_wait_ld();
         const int key0 = k0 + half * 64 + c * 32;
         uint32_t pw[16], dw[16];
-        uint32_t keep4 = 0xfu;
         const uint32_t drop_row = (uint32_t)((b * p.H + h) * p.T + q);
+        uint32_t kw = c ? keep_w1 : keep_w0;
+        if (p.drop.thresh && p.drop_bits == nullptr) {
+#pragma unroll
+          for (int cc = 0; cc < 4; ++cc)
+            kw = (cc == 0 ? 0u : kw) | dropout_keep8(p.drop, drop_row, (uint32_t)(key0 >> 3) + cc) << (8 * cc);
+        }
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
           float p0 = ex2_approx(fmaf(sv[e], kLog2e, -lse)), p1 = ex2_approx(fmaf(sv[e + 1], kLog2e, -lse));
@@ -226,8 +245,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
           if (!q_ok || key0 + e + 1 >= p.T) p1 = 0.f;
           float pd0 = p0, pd1 = p1, g0 = dv[e], g1 = dv[e + 1];
           if (p.drop.thresh) {     // O = (D * P / (1-p)) V: dV sees the dropped weights, dP = D * d(dropped) / (1-p)
-            if ((e & 7) == 0) keep4 = dropout_keep8(p.drop, drop_row, (uint32_t)(key0 + e) >> 3);
-            const bool k0b = (keep4 >> (e & 7)) & 1u, k1b = (keep4 >> ((e & 7) + 1)) & 1u;
+            const bool k0b = (kw >> e) & 1u, k1b = (kw >> (e + 1)) & 1u;
             pd0 = k0b ? p0 * p.drop.scale : 0.f; pd1 = k1b ? p1 * p.drop.scale : 0.f;
             g0 = k0b ? g0 * p.drop.scale : 0.f; g1 = k1b ? g1 * p.drop.scale : 0.f;
           }
@@ -299,7 +317,9 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
 
 int mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
             const void* do_hi, const void* do_lo, int ld_do, const float* lse, const float* delta, int B, int T, int H,
-            float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, DropoutCfg drop, int prec, cudaStream_t st) {
+            float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, DropoutCfg drop, const uint32_t* drop_bits, int ld_bits,
+            int prec, cudaStream_t st) {
+  EDA_REQUIRE(!drop_bits || (drop.thresh && ld_bits * 32 >= T), "eda_mha_bwd: drop_bits needs p_drop > 0 and ld_bits >= ceil(T / 32)");
   EDA_REQUIRE(qk_hi && qk_lo && vt_hi && vt_lo && do_hi && do_lo && lse && delta && dq_acc && dqkv_hi && dqkv_lo, "eda_mha_bwd: null argument");
   EDA_REQUIRE(B > 0 && T > 0 && H > 0 && ld_qk >= 2 * H * BDH && ld_qk % 8 == 0 && Tp >= T && Tp % 8 == 0 && ld_do % 8 == 0 &&
               ld_dqkv >= 3 * H * BDH && ld_dqkv % 8 == 0, "eda_mha_bwd: bad sizes / strides");
@@ -325,6 +345,7 @@ int mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, 
   p.lse = lse; p.delta = delta; p.dq_acc = dq_acc;
   p.dkv_hi = (bf16*)dqkv_hi; p.dkv_lo = (bf16*)dqkv_lo; p.ld_dkv = ld_dqkv;
   p.dk_col0 = H * BDH; p.dv_col0 = 2 * H * BDH; p.drop = drop;
+  p.drop_bits = drop.thresh ? drop_bits : nullptr; p.ld_bits = ld_bits;
   const int64_t n_cta = (int64_t)ceil_div(T, BT) * H * B;
   EDA_REQUIRE(n_cta < (int64_t(1) << 31), "eda_mha_bwd: too many (batch, head, key tile) items");
   mha_bwd_tc_kernel<<<(int)n_cta, B_THREADS, B_SMEM, st>>>(tq_hi, tq_lo, tv_hi, tv_lo, tg_hi, tg_lo, p);
@@ -337,8 +358,9 @@ int mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, 
 extern "C" int eda_mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
                            const void* do_hi, const void* do_lo, int ld_do, const float* lse, const float* delta, int B,
                            int T, int n_heads, float* dq_acc, void* dqkv_hi, void* dqkv_lo, int ld_dqkv, float p_drop,
-                           uint64_t seed, int site, int prec, void* stream) {
+                           uint64_t seed, int site, const uint32_t* drop_bits, int ld_bits, int prec, void* stream) {
   EDA_REQUIRE(p_drop >= 0.f && p_drop < 1.f, "eda_mha_bwd: bad dropout probability");
   return eda::mha_bwd(qk_hi, qk_lo, ld_qk, vt_hi, vt_lo, Tp, do_hi, do_lo, ld_do, lse, delta, B, T, n_heads, dq_acc,
-                      dqkv_hi, dqkv_lo, ld_dqkv, eda::make_dropout(p_drop, seed, site), prec, (cudaStream_t)stream);
+                      dqkv_hi, dqkv_lo, ld_dqkv, eda::make_dropout(p_drop, seed, site), drop_bits, ld_bits, prec,
+                      (cudaStream_t)stream);
 }

@@ -57,6 +57,7 @@ struct MhaParams {
   float* lse;                             // optional (training): (B*H, T) log2-domain log-sum-exp of each score row
   const int32_t* klens;                   // optional key_padding_mask (Conformer): keys t >= klens[b] are masked out
   DropoutCfg drop;                        // training: dropout on the attention weights (thresh == 0 = off)
+  const uint32_t* drop_bits; int ld_bits; // optional: the keep mask of this site as bits (eda_dropout_bits), row (b*H+h)*T + q
 };
 
 // D[tmem] (+)= A[tmem] * B[smem desc]
@@ -289,8 +290,16 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
     const int q0 = (item % n_qt) * ABM, h = (item / n_qt) % p.H, b = item / (n_qt * p.H);
     const int n_kt = kt_of(b), n_keys = keys_of(b);
     float m_ref = -INFINITY, l_sum = 0.f;       // m_ref in log2 units (S * log2 e)
+    uint32_t keep_next = 0xffffffffu;
+    if (p.drop_bits != nullptr && q0 + row_in_tile < p.T && half * 32 < p.T)
+      keep_next = __ldg(p.drop_bits + (size_t)((b * p.H + h) * p.T + q0 + row_in_tile) * p.ld_bits + half);
     for (int j = 0; j < n_kt; ++j, ++g) {
       const uint32_t tS = tS0 + (g & 1) * ABN;
+      // keep bits of this thread's 32 keys (precomputed masks: one load instead of 4 Philox evaluations in the
+      // softmax warps), fetched one key tile ahead so that the load never sits on the tile's critical path
+      uint32_t keep_w = keep_next;
+      if (p.drop_bits != nullptr && q0 + row_in_tile < p.T && (j + 1) * ABN + half * 32 < p.T)
+        keep_next = __ldg(p.drop_bits + (size_t)((b * p.H + h) * p.T + q0 + row_in_tile) * p.ld_bits + (((j + 1) * ABN + half * 32) >> 5));
       mbar_wait(&bar_s[g & 1], (g >> 1) & 1);
 #ifdef EDA_MHA_TRACE
       if (threadIdx.x == 64) MHA_STAMP(48 + 2 * j);
@@ -332,8 +341,12 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
       // packed hi pairs in the first 16 columns of the chunk, lo pairs in the last 16
       float l4[4] = {0.f, 0.f, 0.f, 0.f};
       float pk[32];
-      uint32_t keep4 = 0xfu;
       const uint32_t drop_row = (uint32_t)((b * p.H + h) * p.T + q0 + row_in_tile);
+      if (p.drop.thresh && p.drop_bits == nullptr) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          keep_w = (c == 0 ? 0u : keep_w) | dropout_keep8(p.drop, drop_row, (uint32_t)((j * ABN + half * 32) >> 3) + c) << (8 * c);
+      }
 #pragma unroll
       for (int i = 0; i < 32; i += 2) {
         float p0 = ex2_approx(fmaf(v[i], kLog2e, -m_ref)), p1 = ex2_approx(fmaf(v[i + 1], kLog2e, -m_ref));
@@ -343,9 +356,8 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
         }
         l4[i & 2] += p0; l4[(i & 2) + 1] += p1;
         if (p.drop.thresh) {       // nn.MultiheadAttention drops normalised weights: the row sum keeps every term
-          if ((i & 7) == 0) keep4 = dropout_keep8(p.drop, drop_row, (uint32_t)(j * ABN + half * 32 + i) >> 3);
-          p0 = (keep4 >> (i & 7)) & 1u ? p0 * p.drop.scale : 0.f;
-          p1 = (keep4 >> ((i & 7) + 1)) & 1u ? p1 * p.drop.scale : 0.f;
+          p0 = (keep_w >> i) & 1u ? p0 * p.drop.scale : 0.f;
+          p1 = (keep_w >> (i + 1)) & 1u ? p1 * p.drop.scale : 0.f;
         }
         const uint32_t hi = pack_bf16x2(p0, p1);
         pk[i >> 1] = __uint_as_float(hi);
@@ -443,7 +455,8 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
 // ------------------------------------------------------------------------- host ---------
 int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
               int B, int T, int H, float* out, int ld_out, void* out_hi, void* out_lo, int ld_os, int prec,
-              cudaStream_t st, float* lse = nullptr, const int32_t* klens = nullptr, DropoutCfg drop = DropoutCfg{}) {
+              cudaStream_t st, float* lse = nullptr, const int32_t* klens = nullptr, DropoutCfg drop = DropoutCfg{},
+              const uint32_t* drop_bits = nullptr, int ld_bits = 0) {
   EDA_REQUIRE(qk_hi && qk_lo && vt_hi && vt_lo && B > 0 && T > 0 && H > 0, "eda_mha_split: bad arguments");
   EDA_REQUIRE(ld_qk >= 2 * H * ADH && ld_qk % 8 == 0 && Tp >= T && Tp % 8 == 0, "eda_mha_split: ld_qk / Tp must be multiples of 8 and large enough");
   EDA_REQUIRE(out || (out_hi && out_lo), "eda_mha_split: no output requested");
@@ -468,6 +481,8 @@ int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi
   p.T = T; p.H = H; p.B = B; p.passes = prec == EDA_PREC_BF16 ? 1 : 3;
   p.out = out; p.ld_out = ld_out; p.out_hi = (bf16*)out_hi; p.out_lo = (bf16*)out_lo; p.ld_os = ld_os;
   p.lse = lse; p.klens = klens; p.drop = drop;
+  EDA_REQUIRE(!drop_bits || (drop.thresh && ld_bits * 32 >= T), "eda_mha_split_train: drop_bits needs p_drop > 0 and ld_bits >= ceil(T / 32)");
+  p.drop_bits = drop.thresh ? drop_bits : nullptr; p.ld_bits = ld_bits;
   const int64_t n_items = (int64_t)ceil_div(T, ABM) * H * B;
   EDA_REQUIRE(n_items < (int64_t(1) << 31), "eda_mha_split: too many (batch, head, query tile) items");
   const int grid = (int)std::min<int64_t>(n_items, (int64_t)A_CTAS_PER_SM * num_sms());
@@ -531,10 +546,11 @@ extern "C" int eda_mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, co
 
 extern "C" int eda_mha_split_train(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
                                    int Tp, int B, int T, int n_heads, void* out_hi, void* out_lo, int ld_os, float* lse,
-                                   float p_drop, uint64_t seed, int site, int prec, void* stream) {
+                                   float p_drop, uint64_t seed, int site, const uint32_t* drop_bits, int ld_bits,
+                                   int prec, void* stream) {
   EDA_REQUIRE(lse && out_hi && out_lo && p_drop >= 0.f && p_drop < 1.f, "eda_mha_split_train: bad argument");
   return eda::mha_split(qk_hi, qk_lo, ld_qk, vt_hi, vt_lo, Tp, B, T, n_heads, nullptr, 0, out_hi, out_lo, ld_os, prec,
-                        (cudaStream_t)stream, lse, nullptr, eda::make_dropout(p_drop, seed, site));
+                        (cudaStream_t)stream, lse, nullptr, eda::make_dropout(p_drop, seed, site), drop_bits, ld_bits);
 }
 
 extern "C" int eda_mha_split_masked(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,

@@ -112,6 +112,44 @@ def site_id(layer: int, which: int) -> int:
     return layer * 4 + which
 
 
+def _step_seed(model, step: int) -> int:
+    return (torch.initial_seed() * 0x9E3779B97F4A7C15 + step * 0xD1B54A32D192ED03) & (2 ** 63 - 1)
+
+
+def _fill_keep_bits(model, bufs, pd: float, seed: int, B: int, H: int, Tmax: int):
+    for i, buf in enumerate(bufs):
+        OT.dropout_bits(pd, seed, site_id(i, SITE_ATTN), B * H * Tmax, Tmax, buf)
+
+
+def _attention_keep_bits(model, ws: dict, pd: float, seed: int, B: int, H: int, Tmax: int, dev):
+    """The attention-weight keep masks of this step as bits (1 bit per weight, 16 MB per layer at 32 x 2000 frames), one
+    buffer per layer: evaluated once instead of in the softmax warps of both attention kernels (the other three sites
+    stay recomputed in their epilogues).  Two sets alternate: the previous step evaluated this step's set on a side
+    stream beside its LSTM recurrence (``_prefetch_keep_bits``); if it guessed the seed and shape right, only wait."""
+    sets = ws.setdefault("bits", [[torch.empty((B * H * Tmax, _round_up(Tmax, 128) // 32), dtype=torch.int32, device=dev)
+                                   for _ in range(model.n_layers)] for _ in range(2)])
+    which = model._drop_step & 1
+    ready = ws.get("bits_ready")
+    if ready is not None and ready[0] == (seed, which):
+        torch.cuda.current_stream(dev).wait_event(ready[1])
+    else:
+        _fill_keep_bits(model, sets[which], pd, seed, B, H, Tmax)
+    ws["bits_ready"] = None
+    return sets[which]
+
+
+def _prefetch_keep_bits(model, ws: dict, pd: float, B: int, H: int, Tmax: int, dev, fork):
+    nxt = model._drop_step + 1
+    seed, which = _step_seed(model, nxt), nxt & 1
+    side = ws.setdefault("side_stream", torch.cuda.Stream(device=dev))
+    side.wait_event(fork)              # the other set was last read by the previous step's backward: long finished
+    with torch.cuda.stream(side):
+        _fill_keep_bits(model, ws["bits"][which], pd, seed, B, H, Tmax)
+        done = torch.cuda.Event()
+        done.record(side)
+    ws["bits_ready"] = ((seed, which), done)
+
+
 def dropout_sites(model, seed: int, B: int, Tmax: int, layer: int, device):
     """The four keep masks of one layer as torch.nn.TransformerEncoderLayer would apply them (bool tensors):
     attention weights (B, H, T, T), dropout1 (B, T, D), FFN dropout (B, T, FF), dropout2 (B, T, D)."""
@@ -136,7 +174,7 @@ def forward_train(model, src: List[Tensor], ts: List[Tensor]):
     # one seed per step from torch's seed and a step counter: repeatable under torch.manual_seed without consuming
     # the global generator (the frame shuffle must draw the same numbers as the reference's, models.py:229-232)
     model._drop_step = getattr(model, "_drop_step", 0) + 1
-    seed = ((torch.initial_seed() * 0x9E3779B97F4A7C15 + model._drop_step * 0xD1B54A32D192ED03) & (2 ** 63 - 1)) if pd > 0 else 0
+    seed = _step_seed(model, model._drop_step) if pd > 0 else 0
     model._last_drop_seed = seed
     drop = lambda layer, which: (pd, seed, site_id(layer, which)) if pd > 0 else OT.NO_DROP
     w = prepared_train(model)
@@ -157,10 +195,11 @@ def forward_train(model, src: List[Tensor], ts: List[Tensor]):
     x_f, x_s = ws["x_f"], ws["x_s"]
     OT.gemm_split_train(ws["xin"], w["ws_in"], w["b_in"], M, D, ws["xin"].ld, L.EPI_BIAS_LN, P, ws["rstd0"],
                         gamma=w["g_in"], beta=w["be_in"], out=x_f[0], out_split=x_s[0])
+    bits = _attention_keep_bits(model, ws, pd, seed, B, H, Tmax, dev) if pd > 0 else None
     for i, (lw, a) in enumerate(zip(w["layers"], ws["layers"])):
         ops.gemm_qkv(x_s[i], lw["sw_qkv"], lw["b_qkv"], a["qk"], a["vt"], B, Tmax, Tp, D, H, P)
         OT.mha_split_train(a["qk"], a["vt"], B, Tmax, Tp, H, model.attn_precision, a["ctx"], a["lse"],
-                           drop=drop(i, SITE_ATTN))
+                           drop=drop(i, SITE_ATTN), drop_bits=bits[i] if pd > 0 else None)
         OT.gemm_split_train(a["ctx"], lw["sw_o"], lw["b_o"], M, D, D, L.EPI_BIAS_RES_LN, P, a["rstd1"], resid=x_f[i],
                             gamma=lw["g1"], beta=lw["be1"], out=a["y1_f"], out_split=a["y1_s"], drop=drop(i, SITE_OUT))
         OT.gemm_split_train(a["y1_s"], lw["sw_1"], lw["b_1"], M, FF, D, L.EPI_BIAS_RELU, P, None, out_split=a["ff"],
@@ -173,15 +212,21 @@ def forward_train(model, src: List[Tensor], ts: List[Tensor]):
     e = model.eda._prepared()
     ops.gemm_split(emb_s, e["sw_ih"], e["b_enc"], M, 4 * D, D, L.EPI_BIAS, P, out=ws["xproj"])
     order = torch.tensor(sorted(range(B), key=lambda b: -ilens[b]), dtype=torch.int32).to(dev, non_blocking=True)
+    fork = torch.cuda.Event() if pd > 0 else None
+    if pd > 0:
+        fork.record()
     att = OT.lstm_attractors_train(ws["xproj"], perm, lens_dev, order, e["u_enc"], e["u_dec"], e["b_dec"], B, Tmax,
                                    n_dec, ws["sv"], P)
+    if pd > 0:          # the recurrence leaves 84 SMs idle for ~2.5 ms: the NEXT step's masks are evaluated beside it
+        _prefetch_keep_bits(model, ws, pd, B, H, Tmax, dev, fork)
     probs, loss_att = ops.attractor_head(att, e["w_lin"], e["b_lin"], S)
     pred, _, _ = ops.posterior(emb, att, B, Tmax, S, want_logits=True, want_post=False)
     loss_pit, min_idx, label_perm, _ = ops.pit_loss(pred, label, lens_dev)
     counts = ops.der_counters(pred, label_perm, lens_dev)
     loss = (model.diar_weight * loss_pit + model.attractor_weight * loss_att).reshape(())
     saved = dict(ws=ws, B=B, Tmax=Tmax, S=S, n_dec=n_dec, lens_dev=lens_dev, perm=perm, order=order, att=att,
-                 probs=probs, pred=pred, label_perm=label_perm, sum_len=float(sum(ilens)), p_drop=pd, seed=seed)
+                 probs=probs, pred=pred, label_perm=label_perm, sum_len=float(sum(ilens)), p_drop=pd, seed=seed,
+                 bits=bits)
     model.last = dict(emb=emb.view(B, Tmax, -1), attractors=att, probs=probs, pred=pred, min_idx=min_idx,
                       label_permute=label_perm, counts=counts)
     return loss, loss_att, loss_pit, counts, saved
@@ -246,7 +291,7 @@ def backward_train(model, saved: dict) -> Tensor:
         OT.gemm_dgrad(g_s, lw["wt_o"], M, D, D, P, out_split=ws["dctx"])
         OT.mha_delta(ws["dctx"], a["ctx"], M, D, ws["delta"])
         OT.mha_bwd(a["qk"], a["vt"], ws["Tp"], ws["dctx"], a["lse"], ws["delta"], B, Tmax, H, ws["dq_acc"],
-                   ws["dqkv"], model.attn_precision, drop=drop(i, SITE_ATTN))
+                   ws["dqkv"], model.attn_precision, drop=drop(i, SITE_ATTN), drop_bits=saved["bits"][i] if pd > 0 else None)
         OT.scale_split(ws["dq_acc"], 0.125, ws["dqkv"], cols=D)
         OT.colsum_split(ws["dqkv"], M, 3 * D, G[pre + "self_attn.in_proj_bias"], work)
         OT.gemm_wgrad(ws["dqkv"], ws["x_s"][i], M, 3 * D, D, G[pre + "self_attn.in_proj_weight"], work, P)

@@ -68,10 +68,11 @@ def colsum_split(x: Split, M: int, N: int, out: Tensor, work: Tensor, accumulate
 
 
 def mha_split_train(qk: Split, vt: Split, B: int, T: int, Tp: int, n_heads: int, prec: int, out_split: Split,
-                    lse: Tensor, drop=NO_DROP):
+                    lse: Tensor, drop=NO_DROP, drop_bits: Optional[Tensor] = None):
+    """``drop_bits``: (B*n_heads*T, ld) int32 keep bits of this site from ``dropout_bits`` (None = evaluated in the kernel)."""
     L.call("eda_mha_split_train", L.ptr(qk.hi), L.ptr(qk.lo), qk.ld, L.ptr(vt.hi), L.ptr(vt.lo), Tp, B, T, n_heads,
            L.ptr(out_split.hi), L.ptr(out_split.lo), out_split.ld, L.ptr(lse), float(drop[0]), int(drop[1]),
-           int(drop[2]), prec, L.stream())
+           int(drop[2]), L.ptr(drop_bits), drop_bits.stride(0) if drop_bits is not None else 0, prec, L.stream())
 
 
 def mha_delta(do: Split, o: Split, M: int, D: int, delta: Tensor):
@@ -80,10 +81,11 @@ def mha_delta(do: Split, o: Split, M: int, D: int, delta: Tensor):
 
 
 def mha_bwd(qk: Split, vt: Split, Tp: int, do: Split, lse: Tensor, delta: Tensor, B: int, T: int, n_heads: int,
-            dq_acc: Tensor, dqkv: Split, prec: int, drop=NO_DROP):
+            dq_acc: Tensor, dqkv: Split, prec: int, drop=NO_DROP, drop_bits: Optional[Tensor] = None):
     L.call("eda_mha_bwd", L.ptr(qk.hi), L.ptr(qk.lo), qk.ld, L.ptr(vt.hi), L.ptr(vt.lo), Tp, L.ptr(do.hi),
            L.ptr(do.lo), do.ld, L.ptr(lse), L.ptr(delta), B, T, n_heads, L.ptr(dq_acc), L.ptr(dqkv.hi),
-           L.ptr(dqkv.lo), dqkv.ld, float(drop[0]), int(drop[1]), int(drop[2]), prec, L.stream())
+           L.ptr(dqkv.lo), dqkv.ld, float(drop[0]), int(drop[1]), int(drop[2]), L.ptr(drop_bits),
+           drop_bits.stride(0) if drop_bits is not None else 0, prec, L.stream())
 
 
 def scale_split(src: Tensor, scale: float, dst: Split, cols: Optional[int] = None):
@@ -135,6 +137,13 @@ def scale_dev(scale: Tensor, x: Tensor):
 def adam_step(p: Tensor, g: Tensor, m: Tensor, v: Tensor, lr: float, beta1: float, beta2: float, eps: float, step: int):
     L.call("eda_adam_step", L.ptr(p), L.ptr(g), L.ptr(m), L.ptr(v), p.numel(), float(lr), float(beta1), float(beta2),
            float(eps), int(step), L.stream())
+
+
+def dropout_bits(p: float, seed: int, site: int, rows: int, cols: int, out: Tensor):
+    """Keep bits of dropout site ``site`` into ``out`` (rows, >= ceil(cols / 32)) int32: the attention kernels' ``drop_bits``."""
+    assert out.dtype == torch.int32 and out.is_cuda and out.stride(1) == 1 and out.shape[0] >= rows
+    L.call("eda_dropout_bits", float(p), int(seed), int(site), rows, cols, L.ptr(out), out.stride(0), L.stream())
+    return out
 
 
 def dropout_mask(p: float, seed: int, site: int, rows: int, cols: int, device) -> Tensor:

@@ -205,6 +205,52 @@ def test_mha_bwd(dev, prec, B, T):
         assert e < tol, (name, e)
 
 
+@pytest.mark.parametrize("B,T", [(2, 200), (1, 333)])
+def test_mha_dropout_bits_equal_inline_masks_and_autograd(dev, B, T):
+    """Attention with dropout on the weights: the kernels fed precomputed keep bits (eda_dropout_bits) and the
+    kernels evaluating the Philox function themselves give the same forward output and the same dk, dv bit for
+    bit (dq is summed with atomics: compared to rounding); both match autograd with the exported mask."""
+    from speaker_diarization_b200 import _lib as L, ops, ops_train as OT
+    H, D, p, seed, site = 4, 256, 0.1, 4242, 9
+    M, Tp = B * T, (T + 7) // 8 * 8
+    g = torch.Generator().manual_seed(B * 77 + T)
+    x = torch.randn((M, D), generator=g)
+    w = (torch.rand((3 * D, D), generator=g) * 2 - 1) * (6.0 / (4 * D)) ** 0.5 * 2
+    b = torch.randn((3 * D,), generator=g) * 0.1
+    dO = torch.randn((M, D), generator=g)
+    P = L.PREC_BF16X3
+    qk, vt = ops.Split.empty(M, 2 * D, dev), ops.Split.empty(B * H * 64, Tp, dev)
+    vt.hi.zero_(); vt.lo.zero_()
+    ops.gemm_qkv(_split(x, dev), _split(w, dev), b.to(dev), qk, vt, B, T, Tp, D, H, P)
+    bits = torch.empty((B * H * T, (T + 31) // 32 + 1), dtype=torch.int32, device=dev)
+    OT.dropout_bits(p, seed, site, B * H * T, T, bits)
+    do = _split(dO, dev)
+    outs = []
+    for db in (None, bits):
+        ctx, lse = ops.Split.empty(M, D, dev), torch.empty((B * H, T), device=dev)
+        OT.mha_split_train(qk, vt, B, T, Tp, H, P, ctx, lse, drop=(p, seed, site), drop_bits=db)
+        delta = torch.empty((M, H), device=dev)
+        OT.mha_delta(do, ctx, M, D, delta)
+        dq_acc, dqkv = torch.empty((M, D), device=dev), ops.Split.empty(M, 3 * D, dev)
+        OT.mha_bwd(qk, vt, Tp, do, lse, delta, B, T, H, dq_acc, dqkv, P, drop=(p, seed, site), drop_bits=db)
+        OT.scale_split(dq_acc, 0.125, dqkv, cols=D)
+        outs.append((ctx.float().cpu(), dqkv.float().cpu()))
+    assert torch.equal(outs[0][0], outs[1][0])
+    assert torch.equal(outs[0][1][:, D:], outs[1][1][:, D:])
+    assert rel_err(outs[0][1][:, :D], outs[1][1][:, :D]) < 1e-5
+    # autograd with the exported mask
+    keep = OT.dropout_mask(p, seed, site, B * H * T, (T + 7) // 8 * 8, dev)[:, :T].view(B, H, T, T).cpu().float()
+    qkv_leaf = F.linear(x.view(B, T, D), w, b).detach().requires_grad_(True)
+    q, k, v = (qkv_leaf.view(B, T, 3, H, 64)[:, :, i].transpose(1, 2) for i in range(3))
+    a = ((torch.softmax(q @ k.transpose(-1, -2) / 8.0, dim=-1) * keep / (1 - p)) @ v).transpose(1, 2).reshape(M, D)
+    a.backward(dO)
+    e = rel_err(outs[1][0], a.detach())
+    assert e < 4e-5, e            # 2.2e-5 measured: fewer, 1/(1-p) larger terms per row than the dropout-free case
+    ref = qkv_leaf.grad.view(M, 3 * D)
+    for sl in (slice(0, D), slice(D, 2 * D), slice(2 * D, 3 * D)):
+        assert ((outs[1][1][:, sl] - ref[:, sl]).norm() / ref[:, sl].norm()).item() < 6e-3
+
+
 def _lstm_ref(emb, lens, perms, n_dec, We, Ue, be, Ud, bd):
     B = emb.shape[0]
     hs, cs = [], []

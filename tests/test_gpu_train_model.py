@@ -152,6 +152,20 @@ def test_dropout_masks_statistics(dev):
     assert abs(a.float().mean(0).std().item() - (0.09 / 4096) ** 0.5) < 2e-3    # no column structure
 
 
+@pytest.mark.parametrize("rows,cols", [(300, 2000), (17, 96), (5, 1)])
+def test_dropout_bits_are_the_same_mask(dev, rows, cols):
+    """eda_dropout_bits (what the attention kernels read in the training step) == eda_dropout_mask, bit for bit."""
+    from speaker_diarization_b200 import ops_train as OT
+    words = (cols + 31) // 32
+    bits = torch.full((rows, words + 3), -1, dtype=torch.int32, device=dev)       # row stride > words: untouched padding
+    OT.dropout_bits(0.1, 99, 7, rows, cols, bits)
+    keep = OT.dropout_mask(0.1, 99, 7, rows, words * 32, dev)[:, :cols].cpu()
+    b = bits.cpu()
+    assert torch.all(b[:, words:] == -1)
+    got = ((b[:, :words].unsqueeze(-1) >> torch.arange(32, dtype=torch.int32)) & 1).reshape(rows, words * 32)[:, :cols]
+    assert torch.equal(got.to(torch.uint8), keep)
+
+
 @pytest.mark.parametrize("name", ["train_l1_ragged", "train_l2_s3"])
 def test_dropout_training_step_matches_oracle_with_the_same_masks(dev, manifest, name):
     """train() mode with dropout 0.1 (conf/eend_eda/*train.yaml: transformer_encoder_dropout): loss and every

@@ -206,3 +206,41 @@ def test_dropout_training_step_matches_oracle_with_the_same_masks(dev, manifest,
     torch.manual_seed(3000 + case["data_seed"])
     loss2, _ = m2(src, ts)
     assert loss2.item() == loss.item()
+
+
+def test_prefetched_attention_masks_equal_masks_evaluated_in_line(dev, manifest):
+    """Steps 2.. of a training run take their attention keep bits from the side stream that evaluated them beside the
+    previous step's LSTM (training._prefetch_keep_bits).  Three steps with the prefetch must give the losses of three
+    steps with the prefetch discarded before every step (bits evaluated in line), and the prefetch must actually hit."""
+    from oracle.weights import synth_features, synth_labels
+    from speaker_diarization_b200.eend_eda import training as TR
+    from speaker_diarization_b200.eend_eda.models import TransformerEdaModel
+    case = manifest["cases"]["train_l2_s3"]
+    cfg, sd = _case(case)
+    src = synth_features(case["lengths"], cfg.in_size, case["data_seed"])
+    ts = synth_labels(case["lengths"], case["n_speakers"], case["data_seed"])
+
+    def run(discard: bool):
+        m = TransformerEdaModel(cfg.n_speakers, cfg.in_size, cfg.n_heads, cfg.n_units, cfg.n_layers, dropout=0.1, precision="bf16x3")
+        m.load_state_dict(sd)
+        m = m.to(dev).train()
+        torch.manual_seed(77)
+        losses, hits = [], 0
+        for _ in range(3):
+            for ws in m._ws.values():
+                if isinstance(ws, dict) and ws.get("bits_ready") is not None:
+                    if discard:
+                        ws["bits_ready"] = None
+                    else:
+                        hits += 1
+            loss, _ = m(src, ts)
+            loss.backward()
+            losses.append(loss.item())
+        return losses, hits
+
+    with_prefetch, hits = run(False)
+    in_line, _ = run(True)
+    assert hits == 2                                   # steps 2 and 3 found their masks ready
+    assert len(set(with_prefetch)) == 3                # three different masks
+    for a, b in zip(with_prefetch, in_line):
+        assert abs(a - b) < 1e-6, (with_prefetch, in_line)

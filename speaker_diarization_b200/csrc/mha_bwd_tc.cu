@@ -78,6 +78,16 @@ __device__ __forceinline__ float ex2_approx(float x) {
 }
 constexpr uint32_t kAmn = 1u << 15, kBmn = 1u << 16;      // instruction-descriptor bits: operand is MN-major
 
+#ifdef EDA_MHABWD_TRACE
+// probe build only (scripts/mha_bwd_trace.py): clock64 stamps of query tile 3 of every CTA, 16 slots:
+// 0 TMA: qfree(2) passed = loads of tile 3 issued | 1 MMA: Q/dO landed | 2 S, dP issued | 3 P/dS arrived | 4 gradient MMAs issued
+// 8 softmax warp 2: S/dP committed | 9 first 32 keys done | 10 P/dS stored + arrived | 11 dQ committed | 12 dQ read | 13 reds issued
+__device__ long long g_mhabwd_trace[4096 * 16];
+#define BWD_STAMP(slot) do { if (i == 3) g_mhabwd_trace[(size_t)blockIdx.x * 16 + (slot)] = clock64(); } while (0)
+#else
+#define BWD_STAMP(slot) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(B_THREADS, 1)
 mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant__ CUtensorMap tmQK_lo,
                   const __grid_constant__ CUtensorMap tmV_hi, const __grid_constant__ CUtensorMap tmV_lo,
@@ -86,13 +96,15 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bar_kv = reinterpret_cast<uint64_t*>(smem + B_OFF_BAR);
-  uint64_t* bar_q = bar_kv + 1;        // Q_i, dO_i landed
-  uint64_t* bar_qfree = bar_kv + 2;    // the gradient products of tile i have read Q, dO, P, dS
+  uint64_t* bar_q = bar_kv + 1;        // Q_i landed
+  uint64_t* bar_qfree = bar_kv + 2;    // the dK products of tile i have read Q (and dS): Q_{i+1} may land
   uint64_t* bar_s = bar_kv + 3;        // S and dP of tile i are in TMEM
   uint64_t* bar_p = bar_kv + 4;        // P, dS of tile i are in shared memory (8 warps)
   uint64_t* bar_dq = bar_kv + 5;       // dQ of tile i (and every earlier MMA) complete
   uint64_t* bar_dqfree = bar_kv + 6;   // dQ of tile i has been read out of TMEM (8 warps)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_kv + 8);
+  uint64_t* bar_dofree = bar_kv + 7;   // the dV products of tile i have read dO (and P): dO_{i+1} may land
+  uint64_t* bar_do = bar_kv + 8;       // dO_i landed (its own barrier: dP = dO V^T is issued while Q_i is still in flight)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_kv + 10);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_t = (p.T + BT - 1) / BT;
@@ -104,7 +116,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
     tma_prefetch_desc(&tmQK_hi); tma_prefetch_desc(&tmQK_lo); tma_prefetch_desc(&tmV_hi); tma_prefetch_desc(&tmV_lo);
     tma_prefetch_desc(&tmDO_hi); tma_prefetch_desc(&tmDO_lo);
     mbar_init(bar_kv, 1); mbar_init(bar_q, 1); mbar_init(bar_qfree, 1); mbar_init(bar_s, 1);
-    mbar_init(bar_p, 8); mbar_init(bar_dq, 1); mbar_init(bar_dqfree, 8);
+    mbar_init(bar_p, 8); mbar_init(bar_dq, 1); mbar_init(bar_dqfree, 8); mbar_init(bar_dofree, 1); mbar_init(bar_do, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, B_TMEM_COLS);
@@ -125,15 +137,19 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
         tma_load_3d(smem + B_OFF_V + B_TILE, &tmV_lo, bar_kv, k0, 0, b * p.H + h);
         tma_load_3d(smem + B_OFF_V + B_TILE + B_TILE / 2, &tmV_lo, bar_kv, k0 + 64, 0, b * p.H + h);
       }
+      // the gradient products run dV (reads dO), dK (reads Q), dQ (reads neither): the next tile's dO and Q are
+      // requested as soon as their readers have completed, 2/3 and 1/3 of the gradient phase before its end
+      // (the 64 KB of loads took ~1900 cycles per tile on the critical path when they waited for all of it)
       for (int i = 0; i < n_t; ++i) {
+        if (i > 0) mbar_wait(bar_dofree, (i - 1) & 1);
+        BWD_STAMP(0);
+        mbar_expect_tx(bar_do, x3 ? 2 * B_TILE : B_TILE);
+        tma_load_3d(smem + B_OFF_DO, &tmDO_hi, bar_do, h * BDH, i * BT, b);
+        if (x3) tma_load_3d(smem + B_OFF_DO + B_TILE, &tmDO_lo, bar_do, h * BDH, i * BT, b);
         if (i > 0) mbar_wait(bar_qfree, (i - 1) & 1);
-        mbar_expect_tx(bar_q, x3 ? 4 * B_TILE : 2 * B_TILE);
+        mbar_expect_tx(bar_q, x3 ? 2 * B_TILE : B_TILE);
         tma_load_3d(smem + B_OFF_Q, &tmQK_hi, bar_q, h * BDH, i * BT, b);
-        tma_load_3d(smem + B_OFF_DO, &tmDO_hi, bar_q, h * BDH, i * BT, b);
-        if (x3) {
-          tma_load_3d(smem + B_OFF_Q + B_TILE, &tmQK_lo, bar_q, h * BDH, i * BT, b);
-          tma_load_3d(smem + B_OFF_DO + B_TILE, &tmDO_lo, bar_q, h * BDH, i * BT, b);
-        }
+        if (x3) tma_load_3d(smem + B_OFF_Q + B_TILE, &tmQK_lo, bar_q, h * BDH, i * BT, b);
       }
     }
   } else if (warp == 1) {
@@ -148,7 +164,18 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
                      tDQ = tmem_base + TM_DQ;
       mbar_wait(bar_kv, 0);
       for (int i = 0; i < n_t; ++i) {
+        mbar_wait(bar_do, i & 1);                            // dO arrives first: dP while Q is still in flight
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < BDH / 16; ++k) {
+          const uint32_t kk = k * 32, km = k * 2048;         // V^T tile: 16 d-rows of 128 B per step, key blocks 8 KB apart
+          const uint64_t g_hi = smem_desc_sw128(sb + B_OFF_DO + kk), g_lo = smem_desc_sw128(sb + B_OFF_DO + B_TILE + kk);
+          const uint64_t v_hi = smem_desc_sw128_mn(sb + B_OFF_V + km, 8192), v_lo = smem_desc_sw128_mn(sb + B_OFF_V + B_TILE + km, 8192);
+          umma_bf16(tDP, g_hi, v_hi, id_dp, k != 0);
+          if (x3) { umma_bf16(tDP, g_hi, v_lo, id_dp, 1); umma_bf16(tDP, g_lo, v_hi, id_dp, 1); }
+        }
         mbar_wait(bar_q, i & 1);
+        BWD_STAMP(1);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < BDH / 16; ++k) {                 // contraction over d: +32 B per step in K-major tiles
@@ -158,29 +185,30 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
           umma_bf16(tS, q_hi, k_hi, id_s, k != 0);
           if (x3) { umma_bf16(tS, q_hi, k_lo, id_s, 1); umma_bf16(tS, q_lo, k_hi, id_s, 1); }
         }
-#pragma unroll
-        for (int k = 0; k < BDH / 16; ++k) {
-          const uint32_t kk = k * 32, km = k * 2048;         // V^T tile: 16 d-rows of 128 B per step, key blocks 8 KB apart
-          const uint64_t g_hi = smem_desc_sw128(sb + B_OFF_DO + kk), g_lo = smem_desc_sw128(sb + B_OFF_DO + B_TILE + kk);
-          const uint64_t v_hi = smem_desc_sw128_mn(sb + B_OFF_V + km, 8192), v_lo = smem_desc_sw128_mn(sb + B_OFF_V + B_TILE + km, 8192);
-          umma_bf16(tDP, g_hi, v_hi, id_dp, k != 0);
-          if (x3) { umma_bf16(tDP, g_hi, v_lo, id_dp, 1); umma_bf16(tDP, g_lo, v_hi, id_dp, 1); }
-        }
         umma_commit(bar_s);
+        BWD_STAMP(2);
         mbar_wait(bar_p, i & 1);
         if (i > 0) mbar_wait(bar_dqfree, (i - 1) & 1);
+        BWD_STAMP(3);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < BT / 16; ++k) {                  // contraction over the 128 queries: 16 rows = 2048 B per step
           const uint32_t km = k * 2048;
-          const uint64_t pa = smem_desc_sw128_mn(sb + B_OFF_P + km, 16384), da = smem_desc_sw128_mn(sb + B_OFF_DS + km, 16384);
+          const uint64_t pa = smem_desc_sw128_mn(sb + B_OFF_P + km, 16384);
           const uint64_t g_hi = smem_desc_sw128_mn(sb + B_OFF_DO + km), g_lo = smem_desc_sw128_mn(sb + B_OFF_DO + B_TILE + km);
-          const uint64_t q_hi = smem_desc_sw128_mn(sb + B_OFF_Q + km), q_lo = smem_desc_sw128_mn(sb + B_OFF_Q + B_TILE + km);
           umma_bf16(tDV, pa, g_hi, id_g, (i | k) != 0);
           if (x3) umma_bf16(tDV, pa, g_lo, id_g, 1);
+        }
+        umma_commit(bar_dofree);
+#pragma unroll
+        for (int k = 0; k < BT / 16; ++k) {
+          const uint32_t km = k * 2048;
+          const uint64_t da = smem_desc_sw128_mn(sb + B_OFF_DS + km, 16384);
+          const uint64_t q_hi = smem_desc_sw128_mn(sb + B_OFF_Q + km), q_lo = smem_desc_sw128_mn(sb + B_OFF_Q + B_TILE + km);
           umma_bf16(tDK, da, q_hi, id_g, (i | k) != 0);
           if (x3) umma_bf16(tDK, da, q_lo, id_g, 1);
         }
+        umma_commit(bar_qfree);
 #pragma unroll
         for (int k = 0; k < BT / 16; ++k) {                  // contraction over the 128 keys
           const uint64_t da = smem_desc_sw128(sb + B_OFF_DS + (k >> 2) * 16384 + (k & 3) * 32);
@@ -188,8 +216,8 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
           umma_bf16(tDQ, da, k_hi, id_dq, k != 0);
           if (x3) umma_bf16(tDQ, da, k_lo, id_dq, 1);
         }
-        umma_commit(bar_qfree);
         umma_commit(bar_dq);
+        BWD_STAMP(4);
       }
     }
   } else {
@@ -222,6 +250,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
       const uint32_t keep_w0 = keep_n0, keep_w1 = keep_n1;
       load_keep(i + 1);
       mbar_wait(bar_s, i & 1);
+      if (threadIdx.x == 64) BWD_STAMP(8);
       tc_fence_after();
 #pragma unroll 1
       for (int c = 0; c < 2; ++c) {                          // 32 keys at a time
@@ -258,25 +287,30 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
           asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(sP + off), "r"(pw[4 * u]), "r"(pw[4 * u + 1]), "r"(pw[4 * u + 2]), "r"(pw[4 * u + 3]) : "memory");
           asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(sDS + off), "r"(dw[4 * u]), "r"(dw[4 * u + 1]), "r"(dw[4 * u + 2]), "r"(dw[4 * u + 3]) : "memory");
         }
+        if (threadIdx.x == 64 && c == 0) BWD_STAMP(9);
       }
       fence_proxy_async();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_p);
+      if (threadIdx.x == 64) BWD_STAMP(10);
       // dQ tile -> HBM accumulator
       mbar_wait(bar_dq, i & 1);
+      if (threadIdx.x == 64) BWD_STAMP(11);
       tc_fence_after();
       float o[32];
       tmem_ld32(tmem_base + TM_DQ + lane_off + half * 32, o);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_dqfree);
+      if (threadIdx.x == 64) BWD_STAMP(12);
       if (q_ok) {
         float* dst = p.dq_acc + ((size_t)b * p.T + q) * (p.H * BDH) + h * BDH + half * 32;
 #pragma unroll
         for (int e = 0; e < 32; e += 4)
           asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + e), "f"(o[e]), "f"(o[e + 1]), "f"(o[e + 2]), "f"(o[e + 3]) : "memory");
       }
+      if (threadIdx.x == 64) BWD_STAMP(13);
     }
     // dK, dV of this key tile (complete: the last bar_dq covers every MMA issued before it)
     const int key = k0 + r;
@@ -354,6 +388,12 @@ int mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, 
 }
 
 }  // namespace eda
+
+#ifdef EDA_MHABWD_TRACE
+extern "C" int eda_mha_bwd_trace_read(long long* host, int n_cta) {
+  return cudaMemcpyFromSymbol(host, eda::g_mhabwd_trace, sizeof(long long) * 16 * (size_t)n_cta) == cudaSuccess ? 0 : 1;
+}
+#endif
 
 extern "C" int eda_mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo, int Tp,
                            const void* do_hi, const void* do_lo, int ld_do, const float* lse, const float* delta, int B,

@@ -22,6 +22,7 @@
 // P and dS are rounded to bf16 once (their products take the hi and lo halves of the other
 // operand), fp32 accumulation throughout.
 #include <algorithm>
+#include <type_traits>
 
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -267,20 +268,32 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
           for (int cc = 0; cc < 4; ++cc)
             kw = (cc == 0 ? 0u : kw) | dropout_keep8(p.drop, drop_row, (uint32_t)(key0 >> 3) + cc) << (8 * cc);
         }
+        // P = exp2(S log2e - lse), dS = P (dP - delta); with dropout O = (D P / (1-p)) V: dV sees the dropped weights and
+        // dP = D d(dropped) / (1-p).  Compiled four ways: the bounds checks only exist for the ragged last tiles and
+        // the keep factors only with dropout (a quarter of this loop's instructions each).
+        auto body = [&](auto full_c, auto drop_c) {
+          constexpr bool kFull = decltype(full_c)::value, kDrop = decltype(drop_c)::value;
 #pragma unroll
-        for (int e = 0; e < 32; e += 2) {
-          float p0 = ex2_approx(fmaf(sv[e], kLog2e, -lse)), p1 = ex2_approx(fmaf(sv[e + 1], kLog2e, -lse));
-          if (!q_ok || key0 + e >= p.T) p0 = 0.f;
-          if (!q_ok || key0 + e + 1 >= p.T) p1 = 0.f;
-          float pd0 = p0, pd1 = p1, g0 = dv[e], g1 = dv[e + 1];
-          if (p.drop.thresh) {     // O = (D * P / (1-p)) V: dV sees the dropped weights, dP = D * d(dropped) / (1-p)
-            const bool k0b = (kw >> e) & 1u, k1b = (kw >> (e + 1)) & 1u;
-            pd0 = k0b ? p0 * p.drop.scale : 0.f; pd1 = k1b ? p1 * p.drop.scale : 0.f;
-            g0 = k0b ? g0 * p.drop.scale : 0.f; g1 = k1b ? g1 * p.drop.scale : 0.f;
+          for (int e = 0; e < 32; e += 2) {
+            float p0 = ex2_approx(fmaf(sv[e], kLog2e, -lse)), p1 = ex2_approx(fmaf(sv[e + 1], kLog2e, -lse));
+            if (!kFull) {
+              if (!q_ok || key0 + e >= p.T) p0 = 0.f;
+              if (!q_ok || key0 + e + 1 >= p.T) p1 = 0.f;
+            }
+            float pd0 = p0, pd1 = p1, g0 = dv[e], g1 = dv[e + 1];
+            if (kDrop) {
+              const float ks0 = (kw >> e) & 1u ? p.drop.scale : 0.f, ks1 = (kw >> (e + 1)) & 1u ? p.drop.scale : 0.f;
+              pd0 = p0 * ks0; pd1 = p1 * ks1;
+              g0 *= ks0; g1 *= ks1;
+            }
+            pw[e >> 1] = pack_bf16x2(pd0, pd1);
+            dw[e >> 1] = pack_bf16x2(p0 * (g0 - dl), p1 * (g1 - dl));
           }
-          pw[e >> 1] = pack_bf16x2(pd0, pd1);
-          dw[e >> 1] = pack_bf16x2(p0 * (g0 - dl), p1 * (g1 - dl));
-        }
+        };
+        const bool full = __all_sync(0xffffffffu, q_ok && key0 + 32 <= p.T);
+        using T_ = std::true_type; using F_ = std::false_type;
+        if (p.drop.thresh) { if (full) body(T_{}, T_{}); else body(F_{}, T_{}); }
+        else               { if (full) body(T_{}, F_{}); else body(F_{}, F_{}); }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {                        // 16 B units c*4 + u of the 128 B row, XOR-swizzled by row
           const uint32_t off = uint32_t(((c * 4 + u) ^ (r & 7)) << 4);

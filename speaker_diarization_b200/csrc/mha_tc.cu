@@ -17,6 +17,7 @@
 //              chunk it was computed from (16 columns of packed hi pairs, 16 of lo pairs; the
 //              A operand of P.V comes from TMEM), O rescaled in TMEM when the running max
 //              moves; final O / l -> split bf16 (and/or fp32), thread-per-row 32-byte stores.
+#include <type_traits>
 #include <algorithm>
 
 #include "common.cuh"
@@ -347,23 +348,31 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_constant
         for (int c = 0; c < 4; ++c)
           keep_w = (c == 0 ? 0u : keep_w) | dropout_keep8(p.drop, drop_row, (uint32_t)((j * ABN + half * 32) >> 3) + c) << (8 * c);
       }
+      // compiled four ways (both conditions are warp-uniform): the bounds checks only exist for a ragged last key
+      // tile, the keep factors only in train() mode with dropout
+      auto body = [&](auto whole_c, auto drop_c) {
+        constexpr bool kWhole = decltype(whole_c)::value, kDrop = decltype(drop_c)::value;
 #pragma unroll
-      for (int i = 0; i < 32; i += 2) {
-        float p0 = ex2_approx(fmaf(v[i], kLog2e, -m_ref)), p1 = ex2_approx(fmaf(v[i + 1], kLog2e, -m_ref));
-        if (!whole) {
-          if (i >= n_valid) p0 = 0.f;
-          if (i + 1 >= n_valid) p1 = 0.f;
+        for (int i = 0; i < 32; i += 2) {
+          float p0 = ex2_approx(fmaf(v[i], kLog2e, -m_ref)), p1 = ex2_approx(fmaf(v[i + 1], kLog2e, -m_ref));
+          if (!kWhole) {
+            if (i >= n_valid) p0 = 0.f;
+            if (i + 1 >= n_valid) p1 = 0.f;
+          }
+          l4[i & 2] += p0; l4[(i & 2) + 1] += p1;
+          if (kDrop) {               // nn.MultiheadAttention drops normalised weights: the row sum keeps every term
+            p0 *= (keep_w >> i) & 1u ? p.drop.scale : 0.f;
+            p1 *= (keep_w >> (i + 1)) & 1u ? p.drop.scale : 0.f;
+          }
+          const uint32_t hi = pack_bf16x2(p0, p1);
+          pk[i >> 1] = __uint_as_float(hi);
+          pk[16 + (i >> 1)] = __uint_as_float(pack_bf16x2(p0 - __uint_as_float(hi << 16),
+                                                          p1 - __uint_as_float(hi & 0xffff0000u)));
         }
-        l4[i & 2] += p0; l4[(i & 2) + 1] += p1;
-        if (p.drop.thresh) {       // nn.MultiheadAttention drops normalised weights: the row sum keeps every term
-          p0 = (keep_w >> i) & 1u ? p0 * p.drop.scale : 0.f;
-          p1 = (keep_w >> (i + 1)) & 1u ? p1 * p.drop.scale : 0.f;
-        }
-        const uint32_t hi = pack_bf16x2(p0, p1);
-        pk[i >> 1] = __uint_as_float(hi);
-        pk[16 + (i >> 1)] = __uint_as_float(pack_bf16x2(p0 - __uint_as_float(hi << 16),
-                                                        p1 - __uint_as_float(hi & 0xffff0000u)));
-      }
+      };
+      using T_ = std::true_type; using F_ = std::false_type;
+      if (p.drop.thresh) { if (whole) body(T_{}, T_{}); else body(F_{}, T_{}); }
+      else               { if (whole) body(T_{}, F_{}); else body(F_{}, F_{}); }
       tmem_st32(tS, pk);
       l_sum += (l4[0] + l4[1]) + (l4[2] + l4[3]);
       tmem_wait_st();

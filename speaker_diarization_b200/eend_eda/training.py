@@ -383,3 +383,82 @@ class NoamAdam:
         self.sched_steps += 1           # the reference calls scheduler.step() right after optimizer.step()
         self.model._prep = None         # the kernels' split / transposed weight copies are stale now
         self.model.eda._prep = None
+
+
+class DeviceBatches:
+    """Iterate ``(src, ts)`` host batches (lists of (T_i, F) / (T_i, S) CPU tensors, what the reference's DataLoader
+    + collate yields, train_eda.py:150-171) as lists of CUDA tensors, staging batch i+1 while step i runs: each batch is
+    concatenated into a pinned buffer and sent with ONE H2D copy per side on a copy stream (what
+    ``DataLoader(pin_memory=True)`` + ``.to(device, non_blocking=True)`` do for the reference); the tensors handed out
+    are views into that device buffer.  ``depth`` staging sets alternate; a set is reused only after the copy that read
+    it has completed and the step that consumed its device buffer has been enqueued."""
+
+    def __init__(self, batches, device, depth: int = 2):
+        self.batches, self.device, self.depth = batches, torch.device(device), max(2, depth)
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self._sets = [dict() for _ in range(self.depth + 1)]
+
+    def _stage(self, k: int, seqs: List[Tensor], name: str):
+        st = self._sets[k]
+        total, cols = sum(int(s.shape[0]) for s in seqs), int(seqs[0].shape[1])
+        key = name + "_dev"
+        if key not in st or st[key].shape != (total, cols):
+            st[key] = torch.empty((total, cols), dtype=torch.float32, device=self.device)
+        views = list(st[key].split([int(s.shape[0]) for s in seqs], dim=0))
+        if all(s.is_pinned() and s.dtype == torch.float32 for s in seqs):
+            # what DataLoader(pin_memory=True) yields: one DMA per sequence straight into its slice, no host-side copy
+            # (concatenating 88 MB on one host thread costs more than the whole GPU step)
+            for v, s_ in zip(views, seqs):
+                v.copy_(s_, non_blocking=True)
+        else:
+            hk = name + "_host"
+            if hk not in st or st[hk].shape != (total, cols):
+                st[hk] = torch.empty((total, cols), dtype=torch.float32, pin_memory=True)
+            torch.cat([s_.float() for s_ in seqs], dim=0, out=st[hk])
+            st[key].copy_(st[hk], non_blocking=True)
+        return views
+
+    def _submit(self, k: int, batch):
+        st = self._sets[k]
+        if "copied" in st:
+            st["copied"].synchronize()                 # the pinned buffers of this set are free again
+        src, ts = batch
+        if "consumed" in st:
+            self.copy_stream.wait_event(st["consumed"])    # the step that read this set's device buffers is enqueued and done
+        with torch.cuda.stream(self.copy_stream):
+            out = (self._stage(k, list(src), "src"), self._stage(k, list(ts), "ts"))
+            st["copied"] = torch.cuda.Event()
+            st["copied"].record(self.copy_stream)
+        return out
+
+    def __iter__(self):
+        return self.iterate(self.batches)
+
+    def iterate(self, batches):
+        """Generator over ``batches`` (the staging buffers are kept between calls: a second pass allocates nothing)."""
+        pending = []                                   # (set index, device batch)
+        k = 0
+        self._last_k = None
+        for st in self._sets:
+            st.pop("consumed", None)
+        torch.cuda.current_stream(self.device).synchronize()
+        for batch in batches:
+            pending.append((k, self._submit(k, batch)))
+            k = (k + 1) % len(self._sets)
+            if len(pending) >= self.depth:
+                yield self._hand_out(pending.pop(0))
+        while pending:
+            yield self._hand_out(pending.pop(0))
+
+    def _hand_out(self, item):
+        k, dev_batch = item
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(self._sets[k]["copied"])
+        # whatever the caller enqueues on the current stream before asking for the next batch reads this set
+        prev = getattr(self, "_last_k", None)
+        if prev is not None:
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            self._sets[prev]["consumed"] = ev
+        self._last_k = k
+        return dev_batch

@@ -244,3 +244,25 @@ def test_prefetched_attention_masks_equal_masks_evaluated_in_line(dev, manifest)
     assert len(set(with_prefetch)) == 3                # three different masks
     for a, b in zip(with_prefetch, in_line):
         assert abs(a - b) < 1e-6, (with_prefetch, in_line)
+
+
+def test_device_batches_prefetcher_hands_out_the_host_batches(dev):
+    """training.DeviceBatches: 7 ragged batches through 3 alternating staging sets arrive intact and in order, also
+    when the consumer overwrites nothing and when shapes change between batches."""
+    from speaker_diarization_b200.eend_eda.training import DeviceBatches
+    g = torch.Generator().manual_seed(5)
+    host = []
+    for i in range(7):
+        lens = [50 + 7 * i, 20 + i, 64]
+        pin = (lambda t: t.pin_memory()) if i % 2 else (lambda t: t)       # pinned sequences are copied without staging
+        host.append(([pin(torch.randn((n, 345), generator=g)) for n in lens],
+                     [pin(torch.randint(0, 2, (n, 3), generator=g).float()) for n in lens]))
+    seen = 0
+    for (src, ts), (hs, ht) in zip(DeviceBatches(iter(host), dev), host):
+        assert all(a.is_cuda for a in src + ts)
+        y = sum(a.sum() for a in src)                      # some work on the current stream that reads the batch
+        for a, b in zip(src + ts, hs + ht):
+            assert torch.equal(a.cpu(), b)
+        assert torch.isfinite(y).item()
+        seen += 1
+    assert seen == 7

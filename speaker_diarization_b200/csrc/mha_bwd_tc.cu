@@ -78,6 +78,24 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 constexpr uint32_t kAmn = 1u << 15, kBmn = 1u << 16;      // instruction-descriptor bits: operand is MN-major
+// D[tmem] (+)= A[tmem] * B[smem desc]
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st16u(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%16], "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15};"
+      ::"r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+        "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+        "r"(taddr)
+      : "memory");
+}
 
 #ifdef EDA_MHABWD_TRACE
 // probe build only (scripts/mha_bwd_trace.py): clock64 stamps of query tile 3 of every CTA, 16 slots:
@@ -212,10 +230,10 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
         umma_commit(bar_qfree);
 #pragma unroll
         for (int k = 0; k < BT / 16; ++k) {                  // contraction over the 128 keys
-          const uint64_t da = smem_desc_sw128(sb + B_OFF_DS + (k >> 2) * 16384 + (k & 3) * 32);
+          const uint32_t da = tS + (k >> 2) * 64 + (k & 3) * 8;          // dS of keys 16k .. 16k+15: 8 packed columns
           const uint64_t k_hi = smem_desc_sw128_mn(sb + B_OFF_K + k * 2048), k_lo = smem_desc_sw128_mn(sb + B_OFF_K + B_TILE + k * 2048);
-          umma_bf16(tDQ, da, k_hi, id_dq, k != 0);
-          if (x3) umma_bf16(tDQ, da, k_lo, id_dq, 1);
+          umma_bf16_ts(tDQ, da, k_hi, id_dq, k != 0);
+          if (x3) umma_bf16_ts(tDQ, da, k_lo, id_dq, 1);
         }
         umma_commit(bar_dq);
         BWD_STAMP(4);
@@ -300,8 +318,12 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQK_hi, const __grid_cons
           asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(sP + off), "r"(pw[4 * u]), "r"(pw[4 * u + 1]), "r"(pw[4 * u + 2]), "r"(pw[4 * u + 3]) : "memory");
           asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(sDS + off), "r"(dw[4 * u]), "r"(dw[4 * u + 1]), "r"(dw[4 * u + 2]), "r"(dw[4 * u + 3]) : "memory");
         }
+        // dS also stays in TMEM, packed two keys per column over the S columns this thread has already consumed
+        // ([64 half, 64 half + 32)): it is the A operand of dQ = dS K, which then reads no shared memory for A
+        tmem_st16u(tmem_base + TM_S + lane_off + half * 64 + c * 16, dw);
         if (threadIdx.x == 64 && c == 0) BWD_STAMP(9);
       }
+      tmem_wait_st();
       fence_proxy_async();
       tc_fence_before();
       __syncwarp();

@@ -75,7 +75,8 @@ def test_mha(dev, prec, B, T):
 
 @pytest.mark.parametrize("lens,n_dec", [([40, 17, 1, 40, 33], 3), ([300] * 9, 15), ([5], 15), ([64, 0, 20], 4),
                                         ([37 + (i * 7) % 23 for i in range(66)], 3),      # 5 sequences per cluster
-                                        ([20 + (i * 5) % 11 for i in range(117)], 2)])    # 8 per cluster
+                                        ([20 + (i * 5) % 11 for i in range(117)], 2),     # 8 per cluster
+                                        ([10 + i % 7 for i in range(130)], 2)])           # more clusters than fit at once
 @pytest.mark.parametrize("lstm_prec", ["fp32", "bf16x3"])     # CUDA-core fp32 / tensor-core split-bf16 recurrence
 def test_lstm_attractors(dev, lens, n_dec, lstm_prec):
     from oracle.eend_eda_oracle import eda as oracle_eda

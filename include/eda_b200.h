@@ -199,6 +199,18 @@ int eda_posterior(const float* emb, int ld_emb, const float* attractors, int att
 int eda_pit_loss(const float* pred, const float* label, const int32_t* lens, int B, int T, int S,
                  float* loss, int64_t* min_idx, float* label_perm, int32_t* perm_out,
                  void* stream);
+/* eda_pit_loss for callers that must not allocate (code under CUDA graph capture, serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same kernel and bit-identical results; the per-sequence cost
+ * scratch and the completion counter live in a file-scope static device array of
+ * 8 * EDA_PIT_STATIC_MAX_B + 256 bytes that every GPU loading the library holds until exit.  The call
+ * makes no cudaMalloc / cudaFree (eda_pit_loss grows a scratch buffer on demand) and returns
+ * EDA_EINVAL for B > EDA_PIT_STATIC_MAX_B.  All calls on a device share the array: calls that overlap
+ * on the GPU (different streams without an ordering between them) race; same-stream calls are safe. */
+#define EDA_PIT_STATIC_MAX_B 4096
+int eda_pit_loss_static(const float* pred, const float* label, const int32_t* lens, int B, int T, int S,
+                        float* loss, int64_t* min_idx, float* label_perm, int32_t* perm_out,
+                        void* stream);
 /* d loss / d pred = mask * (sigmoid(pred) - label_perm) / (S * sum lens) * grad_scale. */
 int eda_pit_loss_bwd(const float* pred, const float* label_perm, const int32_t* lens,
                      int B, int T, int S, float grad_scale, float* dpred, void* stream);

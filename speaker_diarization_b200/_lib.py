@@ -44,6 +44,7 @@ SIGNATURES = {
     "eda_attractor_head": (_i, [_p, _p, _p, _i, _i, _i, _p, _i, _p, _p]),
     "eda_posterior": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p, _p]),
     "eda_pit_loss": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p]),
+    "eda_pit_loss_static": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p]),
     "eda_pit_loss_bwd": (_i, [_p, _p, _p, _i, _i, _i, _f, _p, _p]),
     "eda_der_counters": (_i, [_p, _p, _p, _i, _i, _i, _p, _p]),
     "eda_frame_labels": (_i, [_p, _p, _p, _p, _i64, _p, _p, _p, _p, _i, _i64, _i, C.c_double, _i, _i, _p, _i, _i, _p]),

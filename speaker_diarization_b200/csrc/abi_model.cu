@@ -16,6 +16,7 @@ int pad_pack_split(const float*, int, const int64_t*, const int32_t*, int, int, 
 int attractor_head(const float*, const float*, const float*, int, int, int, float*, int, float*, cudaStream_t);
 int posterior(const float*, int, const float*, int, int, int, int, int, float, float*, float*, uint8_t*, cudaStream_t);
 int pit_loss(const float*, const float*, const int32_t*, int, int, int, float*, int64_t*, float*, int32_t*, cudaStream_t);
+int pit_loss_static(const float*, const float*, const int32_t*, int, int, int, float*, int64_t*, float*, int32_t*, cudaStream_t);
 int pit_loss_bwd(const float*, const float*, const int32_t*, int, int, int, float, float*, cudaStream_t);
 int der_counters(const float*, const float*, const int32_t*, int, int, int, int64_t*, cudaStream_t);
 }  // namespace eda
@@ -89,6 +90,12 @@ int eda_pit_loss(const float* pred, const float* label, const int32_t* lens, int
                  float* loss, int64_t* min_idx, float* label_perm, int32_t* perm_out, void* stream) {
   EDA_REQUIRE(pred && label && lens, "eda_pit_loss: null argument");
   return eda::pit_loss(pred, label, lens, B, T, S, loss, min_idx, label_perm, perm_out, (cudaStream_t)stream);
+}
+
+int eda_pit_loss_static(const float* pred, const float* label, const int32_t* lens, int B, int T, int S,
+                        float* loss, int64_t* min_idx, float* label_perm, int32_t* perm_out, void* stream) {
+  EDA_REQUIRE(pred && label && lens, "eda_pit_loss_static: null argument");
+  return eda::pit_loss_static(pred, label, lens, B, T, S, loss, min_idx, label_perm, perm_out, (cudaStream_t)stream);
 }
 
 int eda_pit_loss_bwd(const float* pred, const float* label_perm, const int32_t* lens, int B, int T,

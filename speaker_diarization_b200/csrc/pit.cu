@@ -178,6 +178,52 @@ int pit_loss(const float* pred, const float* label, const int32_t* lens, int B, 
   return EDA_OK;
 }
 
+// ---- eda_pit_loss_static: the same kernel with its scratch in a file-scope device array -------
+// For callers that may not allocate (CUDA graph capture, serving loops): no cudaMalloc / cudaFree,
+// no growth.  Layout of the array: [0, 8 * kStaticMaxB) best cost per sequence (double),
+// then one unsigned completion counter on its own 256-byte line.  Every GPU that loads the
+// library holds these bytes until exit; every call on a device shares them, so calls that overlap
+// on the GPU (two streams) race - serialise them.
+constexpr int kStaticMaxB = EDA_PIT_STATIC_MAX_B;
+constexpr size_t kStaticBytes = sizeof(double) * kStaticMaxB + 256;
+static __device__ __align__(256) unsigned char g_pit_static[kStaticBytes];
+
+// In host code `g_pit_static` is only a stand-in for the symbol: the device address is looked up once
+// per device, with that device current.
+constexpr int kMaxDevices = 64;
+static void* g_pit_static_addr[kMaxDevices] = {};
+
+int pit_loss_static(const float* pred, const float* label, const int32_t* lens, int B, int T, int S,
+                    float* loss, int64_t* min_idx, float* label_perm, int32_t* perm_out, cudaStream_t st) {
+  EDA_REQUIRE(S >= 1 && S <= kMaxS, "eda_pit_loss_static: S must be in [1,%d] (got %d)", kMaxS, S);
+  EDA_REQUIRE(B > 0 && T > 0 && loss && min_idx, "eda_pit_loss_static: bad arguments");
+  EDA_REQUIRE(B <= kStaticMaxB,
+              "eda_pit_loss_static: B = %d exceeds the static scratch (EDA_PIT_STATIC_MAX_B = %d sequences); "
+              "use eda_pit_loss", B, kStaticMaxB);
+  int dev = -1;
+  EDA_CUDA(cudaGetDevice(&dev));
+  EDA_REQUIRE(dev >= 0 && dev < kMaxDevices, "eda_pit_loss_static: device ordinal %d not supported", dev);
+  void* base = __atomic_load_n(&g_pit_static_addr[dev], __ATOMIC_ACQUIRE);
+  if (!base) {
+    EDA_CUDA(cudaGetSymbolAddress(&base, g_pit_static));
+    EDA_REQUIRE(base != nullptr, "eda_pit_loss_static: cudaGetSymbolAddress returned a null address");
+    __atomic_store_n(&g_pit_static_addr[dev], base, __ATOMIC_RELEASE);
+  }
+  double* best = reinterpret_cast<double*>(base);
+  unsigned* counter = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(base) + sizeof(double) * kStaticMaxB);
+  // the array keeps the previous call's contents: the counter must start at zero (the best costs are
+  // all rewritten before they are read)
+  EDA_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned), st));
+#define EDA_PIT_CASE(s) case s: launch_pit<s>(pred, label, lens, B, T, loss, min_idx, label_perm, perm_out, best, counter, st); break;
+  switch (S) {
+    EDA_PIT_CASE(1) EDA_PIT_CASE(2) EDA_PIT_CASE(3) EDA_PIT_CASE(4)
+    EDA_PIT_CASE(5) EDA_PIT_CASE(6) EDA_PIT_CASE(7) EDA_PIT_CASE(8)
+  }
+#undef EDA_PIT_CASE
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
+}
+
 // d loss / d pred (models.py:373-413 differentiated): mask*(sigmoid(x) - y)/(S*sum len)
 __global__ void pit_bwd_kernel(const float* __restrict__ pred, const float* __restrict__ lab,
                                const int32_t* __restrict__ lens, int B, int T, int S, float scale,

@@ -159,7 +159,7 @@ def run_ours(args):
     dev_audio = [a.to(dev) for a in host_audio]
     ns = [SECONDS * RATE] * B
     if world > 1:       # the path's one collective: result collection on rank 0
-        gather_buf = [torch.empty((B, T, MAXSPK - 1), device=dev) for _ in range(world)] if rank == 0 else None
+        gather_buf = [torch.empty((B * T, MAXSPK - 1), device=dev) for _ in range(world)] if rank == 0 else None
         pipe.gather = lambda post: dist.gather(post, gather_buf, dst=0)
 
     def run_steps(audio_list, n):
@@ -198,7 +198,7 @@ def run_ours(args):
         dist.barrier()
     t0 = time.perf_counter()
     res = run_steps(host_audio, args.steps)           # every step: H2D of its audio, D2H of its posteriors
-    assert res["posteriors"].shape == (B, T, MAXSPK - 1) and len(res["n_speakers"]) == B
+    assert res["posteriors"].shape == (B * T, MAXSPK - 1) and len(res["n_speakers"]) == B
     torch.cuda.synchronize()
     e2e_s = torch.tensor([(time.perf_counter() - t0) / args.steps], device=dev)
     if world > 1:

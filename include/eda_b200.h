@@ -111,6 +111,14 @@ int eda_linear(const float* A, int lda, const float* W, int ldw, const float* bi
 int eda_mha_fwd(const float* qkv, int ld_qkv, float* out, int ld_out, int B, int T,
                 int n_heads, int head_dim, int prec, void* stream);
 
+/* eda_mha_fwd for a batch of INDEPENDENT sequences: keys t >= key_lens[b] take no part (rows of padded
+ * queries are computed but meaningless).  With it a padded batch of chunks gives every chunk the result of
+ * the reference's own loop, which runs one chunk per model call so that no padding ever exists
+ * (infer_eda.py:102-113; models.py:223 passes no mask because B = 1 there).  prec must be EDA_PREC_FP32;
+ * the tensor-core pipeline's form is eda_mha_split_masked.                                      */
+int eda_mha_fwd_masked(const float* qkv, int ld_qkv, float* out, int ld_out, int B, int T,
+                       int n_heads, int head_dim, const int32_t* key_lens, int prec, void* stream);
+
 /* ---------------------------------------------------- split-bf16 tensor-core pipeline --
  * The tensor-core precisions keep activations in HBM as "split" bf16 pairs (x = hi + lo,
  * hi = bf16(x), lo = bf16(x - hi); two bf16 matrices with the same row stride) so that a
@@ -189,6 +197,13 @@ int eda_attractor_head(const float* attractors, const float* w, const float* bia
 int eda_posterior(const float* emb, int ld_emb, const float* attractors, int att_stride_rows,
                   int B, int Tmax, int D, int n_att, float threshold,
                   float* logits, float* post, uint8_t* labels, void* stream);
+
+/* eda_posterior writing the time-axis concatenation the reference's driver builds with np.vstack(out_chunks)
+ * (infer_eda.py:113,121): frame t < lens[b] of sequence b lands in row out_off[b] + t of logits / post / labels
+ * ((total rows, n_att) matrices); rows of padded frames are not written.  out_off: (B) int64, lens: (B) int32. */
+int eda_posterior_packed(const float* emb, int ld_emb, const float* attractors, int att_stride_rows,
+                         int B, int Tmax, int D, int n_att, float threshold, const int64_t* out_off,
+                         const int32_t* lens, float* logits, float* post, uint8_t* labels, void* stream);
 
 /* ------------------------------------------------------------------- PIT loss ------
  * TransformerEdaModel.pit_loss (models.py:373-421).  pred, label (B, T, S) fp32; lens (B).
@@ -383,7 +398,9 @@ int eda_layernorm_split(const float* x, int ld, const float* gamma, const float*
  * scale[c] = bn_w / sqrt(running_var + eps), shift[c] = (conv_bias - running_mean) * scale + bn_b. */
 int eda_dwconv_bn_silu(const float* x, int ld, const float* w, const float* scale, const float* shift, int B, int T, int C,
                        int K, void* out_hi, void* out_lo, int ld_s, void* stream);
-/* eda_mha_split with nn.MultiheadAttention's key_padding_mask: keys t >= key_lens[b] do not take part. */
+/* eda_mha_split with nn.MultiheadAttention's key_padding_mask: keys t >= key_lens[b] do not take part
+ * (Conformer variant, models.py:525-528; and the transformer path's independent-chunk batches, see
+ * eda_mha_fwd_masked). */
 int eda_mha_split_masked(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, const void* vt_lo,
                          int Tp, int B, int T, int n_heads, const int32_t* key_lens, void* out_hi, void* out_lo,
                          int ld_os, int prec, void* stream);

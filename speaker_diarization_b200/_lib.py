@@ -34,6 +34,7 @@ SIGNATURES = {
     "eda_pad_pack": (_i, [_p, _p, _p, _i, _i, _i, _f, _p, _i, _p]),
     "eda_linear": (_i, [_p, _i, _p, _i, _p, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "eda_mha_fwd": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "eda_mha_fwd_masked": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _p, _i, _p]),
     "eda_split_bf16": (_i, [_p, _i, _i, _i, _p, _p, _i, _p]),
     "eda_pad_pack_split": (_i, [_p, _i, _p, _p, _i, _i, _i, _f, _p, _p, _i, _p]),
     "eda_gemm_split": (_i, [_p, _p, _i, _p, _p, _i, _p, _p, _i, _p, _p, _p, _i, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
@@ -43,6 +44,7 @@ SIGNATURES = {
     "eda_lstm_max_active_clusters": (_i, []),
     "eda_attractor_head": (_i, [_p, _p, _p, _i, _i, _i, _p, _i, _p, _p]),
     "eda_posterior": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p, _p]),
+    "eda_posterior_packed": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p, _p, _p, _p]),
     "eda_pit_loss": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p]),
     "eda_pit_loss_static": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p]),
     "eda_pit_loss_bwd": (_i, [_p, _p, _p, _i, _i, _i, _f, _p, _p]),

@@ -6,7 +6,7 @@ int linear_f32(const float*, int, const float*, int, const float*, const float*,
                const float*, float*, int, int, int, int, int, cudaStream_t);
 int linear_tc(const float*, int, const float*, int, const float*, const float*, int, const float*,
               const float*, float*, int, int, int, int, int, int, cudaStream_t);
-int mha_f32(const float*, int, float*, int, int, int, int, cudaStream_t);
+int mha_f32(const float*, int, float*, int, int, int, int, cudaStream_t, const int32_t* key_lens = nullptr);
 int mha_tc(const float*, int, float*, int, int, int, int, int, cudaStream_t);
 struct LstmSave { float* gates; float* c; void* hprev_hi; void* hprev_lo; float* dec_gates; float* dec_c; void* dec_hprev_hi; void* dec_hprev_lo; };
 int lstm_attractors(const float*, const int32_t*, const int32_t*, const int32_t*, const float*,
@@ -14,7 +14,8 @@ int lstm_attractors(const float*, const int32_t*, const int32_t*, const int32_t*
 int pad_pack(const float*, const int64_t*, const int32_t*, int, int, int, float, float*, int, cudaStream_t);
 int pad_pack_split(const float*, int, const int64_t*, const int32_t*, int, int, int, float, void*, void*, int, cudaStream_t);
 int attractor_head(const float*, const float*, const float*, int, int, int, float*, int, float*, cudaStream_t);
-int posterior(const float*, int, const float*, int, int, int, int, int, float, float*, float*, uint8_t*, cudaStream_t);
+int posterior(const float*, int, const float*, int, int, int, int, int, float, float*, float*, uint8_t*, cudaStream_t,
+              const int64_t* out_off = nullptr, const int32_t* lens = nullptr);
 int pit_loss(const float*, const float*, const int32_t*, int, int, int, float*, int64_t*, float*, int32_t*, cudaStream_t);
 int pit_loss_static(const float*, const float*, const int32_t*, int, int, int, float*, int64_t*, float*, int32_t*, cudaStream_t);
 int pit_loss_bwd(const float*, const float*, const int32_t*, int, int, int, float, float*, cudaStream_t);
@@ -54,6 +55,14 @@ int eda_mha_fwd(const float* qkv, int ld_qkv, float* out, int ld_out, int B, int
   return eda::mha_tc(qkv, ld_qkv, out, ld_out, B, T, n_heads, prec, (cudaStream_t)stream);
 }
 
+int eda_mha_fwd_masked(const float* qkv, int ld_qkv, float* out, int ld_out, int B, int T, int n_heads,
+                       int head_dim, const int32_t* key_lens, int prec, void* stream) {
+  EDA_REQUIRE(qkv && out && key_lens && B > 0 && T > 0 && n_heads > 0, "eda_mha_fwd_masked: bad arguments");
+  EDA_REQUIRE(head_dim == 64, "eda_mha_fwd_masked: head_dim must be 64 (got %d)", head_dim);
+  EDA_REQUIRE(prec == EDA_PREC_FP32, "eda_mha_fwd_masked: fp32 only (the tensor-core form is eda_mha_split_masked)");
+  return eda::mha_f32(qkv, ld_qkv, out, ld_out, B, T, n_heads, (cudaStream_t)stream, key_lens);
+}
+
 int eda_lstm_attractors(const float* xproj, const int32_t* perm, const int32_t* lens,
                         const int32_t* order, const float* w_hh_enc, const float* w_hh_dec,
                         const float* dec_bias, int B, int Tmax, int D, int n_dec, float* attractors,
@@ -84,6 +93,14 @@ int eda_posterior(const float* emb, int ld_emb, const float* attractors, int att
                   uint8_t* labels, void* stream) {
   EDA_REQUIRE(emb && attractors && B > 0 && Tmax > 0, "eda_posterior: bad arguments");
   return eda::posterior(emb, ld_emb, attractors, att_stride_rows, B, Tmax, D, n_att, threshold, logits, post, labels, (cudaStream_t)stream);
+}
+
+int eda_posterior_packed(const float* emb, int ld_emb, const float* attractors, int att_stride_rows, int B,
+                         int Tmax, int D, int n_att, float threshold, const int64_t* out_off, const int32_t* lens,
+                         float* logits, float* post, uint8_t* labels, void* stream) {
+  EDA_REQUIRE(emb && attractors && out_off && lens && B > 0 && Tmax > 0, "eda_posterior_packed: bad arguments");
+  return eda::posterior(emb, ld_emb, attractors, att_stride_rows, B, Tmax, D, n_att, threshold, logits, post, labels,
+                        (cudaStream_t)stream, out_off, lens);
 }
 
 int eda_pit_loss(const float* pred, const float* label, const int32_t* lens, int B, int T, int S,

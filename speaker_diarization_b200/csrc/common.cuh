@@ -49,6 +49,20 @@ inline int num_sms() {
   return n;
 }
 
+// One-time per-DEVICE set-up (cudaFuncSetAttribute is per device, a process may drive several GPUs):
+//   static DeviceOnce once;  if (!once.done()) { ...set attributes...; once.mark(); }
+struct DeviceOnce {
+  unsigned long long mask = 0;
+  static unsigned long long bit() { int dev = 0; cudaGetDevice(&dev); return 1ull << (dev & 63); }
+  bool done() const { return (__atomic_load_n(&mask, __ATOMIC_ACQUIRE) & bit()) != 0; }
+  void mark() { __atomic_fetch_or(&mask, bit(), __ATOMIC_RELEASE); }
+};
+
+// Library-owned scratch of the convenience entry points, keyed by (device, stream, tag): calls in flight on
+// different streams or GPUs never share a buffer; calls on one stream reuse it in stream order.  Grow-only;
+// growing waits for that stream.  Returns nullptr (error set) on failure.
+void* stream_scratch(int tag, cudaStream_t st, size_t bytes);
+
 template <typename T>
 __host__ __device__ constexpr T ceil_div(T a, T b) { return (a + b - 1) / b; }
 

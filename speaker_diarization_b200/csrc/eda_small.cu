@@ -142,7 +142,8 @@ template <int NATT>
 __global__ void __launch_bounds__(256)
 posterior_kernel(const float* __restrict__ emb, int ld_emb, const float* __restrict__ att,
                  int att_stride_rows, int Tmax, int n_att, float thr, float* __restrict__ logits,
-                 float* __restrict__ post, uint8_t* __restrict__ labels) {
+                 float* __restrict__ post, uint8_t* __restrict__ labels,
+                 const int64_t* __restrict__ out_off, const int32_t* __restrict__ lens) {
   constexpr int D = 256;
   __shared__ __align__(16) float As[NATT][D];
   const int b = blockIdx.y;
@@ -150,7 +151,9 @@ posterior_kernel(const float* __restrict__ emb, int ld_emb, const float* __restr
     As[i / D][i % D] = __ldg(att + (size_t)b * att_stride_rows * D + i);
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int t = blockIdx.x * 8 + warp; t < Tmax; t += gridDim.x * 8) {
+  // packed output (eda_posterior_packed): frame t of sequence b goes to row out_off[b] + t, padding is skipped
+  const int t_end = out_off ? min(Tmax, __ldg(lens + b)) : Tmax;
+  for (int t = blockIdx.x * 8 + warp; t < t_end; t += gridDim.x * 8) {
     const size_t row = (size_t)b * Tmax + t;
     const float4* e = reinterpret_cast<const float4*>(emb + row * ld_emb);
     const float4 e0 = __ldg(e + lane), e1 = __ldg(e + 32 + lane);
@@ -168,7 +171,7 @@ posterior_kernel(const float* __restrict__ emb, int ld_emb, const float* __restr
       }
     }
     if (lane < n_att) {
-      const size_t o = row * n_att + lane;
+      const size_t o = (out_off ? (size_t)(__ldg(out_off + b) + t) : row) * n_att + lane;
       const float p = sigmoidf_ref(mine);
       if (logits) logits[o] = mine;
       if (post) post[o] = p;
@@ -179,13 +182,15 @@ posterior_kernel(const float* __restrict__ emb, int ld_emb, const float* __restr
 
 int posterior(const float* emb, int ld_emb, const float* att, int att_stride_rows, int B, int Tmax,
               int D, int n_att, float thr, float* logits, float* post, uint8_t* labels,
-              cudaStream_t st) {
+              cudaStream_t st, const int64_t* out_off, const int32_t* lens) {
   EDA_REQUIRE(D == 256, "eda_posterior: D must be 256 (got %d)", D);
   EDA_REQUIRE(n_att >= 1 && n_att <= 16, "eda_posterior: n_att must be in [1,16] (got %d)", n_att);
   EDA_REQUIRE(ld_emb % 4 == 0 && (uintptr_t)emb % 16 == 0, "eda_posterior: emb must be 16B aligned");
   EDA_REQUIRE(B <= 65535, "eda_posterior: B too large");
   dim3 grid(max(1, min(ceil_div(Tmax, 8), ceil_div(num_sms() * 8, B))), B);
-  posterior_kernel<16><<<grid, 256, 0, st>>>(emb, ld_emb, att, att_stride_rows, Tmax, n_att, thr, logits, post, labels);
+  EDA_REQUIRE((out_off == nullptr) == (lens == nullptr), "eda_posterior_packed: out_off and lens go together");
+  posterior_kernel<16><<<grid, 256, 0, st>>>(emb, ld_emb, att, att_stride_rows, Tmax, n_att, thr, logits, post, labels,
+                                             out_off, lens);
   EDA_LAUNCH_CHECK();
   return EDA_OK;
 }

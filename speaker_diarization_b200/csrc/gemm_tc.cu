@@ -699,10 +699,10 @@ template <int EPI, bool ST, bool WG = false, bool EX = false>
 static int launch_gemm2(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi, const CUtensorMap& b_lo,
                         const CUtensorMap& c, const CUtensorMap& c_hi, const CUtensorMap& c_lo, const GemmParams& p,
                         cudaStream_t st) {
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (!attr.done()) {
     EDA_CUDA(cudaFuncSetAttribute(gemm_split_kernel<EPI, ST, WG, EX>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
-    attr = true;
+    attr.mark();
   }
   const int n_tiles = ceil_div(p.N, GBN) * ceil_div(p.M, 2 * GBM) * (WG ? p.ksplit : 1);   // one 256 x 256 tile per CTA pair
   cudaLaunchConfig_t cfg = {};
@@ -834,18 +834,6 @@ int gemm_wgrad(const void* dy_hi, const void* dy_lo, int ld_dy, const void* x_hi
   return EDA_OK;
 }
 
-// grow-only scratch for eda_linear's on-the-fly operand split (stream-ordered reuse)
-static bf16* g_split[2] = {nullptr, nullptr};
-static size_t g_split_cap[2] = {0, 0};
-static int ensure_split(int which, size_t elems) {
-  if (elems > g_split_cap[which]) {
-    if (g_split[which]) { EDA_CUDA(cudaDeviceSynchronize()); EDA_CUDA(cudaFree(g_split[which])); }
-    g_split_cap[which] = elems + elems / 4;
-    EDA_CUDA(cudaMalloc(&g_split[which], g_split_cap[which] * sizeof(bf16)));
-  }
-  return EDA_OK;
-}
-
 // eda_linear on the tensor cores: fp32 operands are split on the fly, fp32 result.
 int linear_tc(const float* A, int lda, const float* W, int ldw, const float* bias, const float* resid, int ldr,
               const float* gamma, const float* beta, float* C, int ldc, int M, int N, int K, int epi, int prec,
@@ -853,9 +841,11 @@ int linear_tc(const float* A, int lda, const float* W, int ldw, const float* bia
   const int Kp = (K + 7) / 8 * 8;
   const size_t a_el = (size_t)M * Kp, w_el = (size_t)N * Kp;
   int rc;
-  if ((rc = ensure_split(0, 2 * a_el)) != EDA_OK) return rc;
-  if ((rc = ensure_split(1, 2 * w_el)) != EDA_OK) return rc;
-  bf16 *a_hi = g_split[0], *a_lo = g_split[0] + a_el, *w_hi = g_split[1], *w_lo = g_split[1] + w_el;
+  // on-the-fly operand split into per-(device, stream) scratch (tags 1, 2)
+  bf16* sa = (bf16*)stream_scratch(1, st, 2 * a_el * sizeof(bf16));
+  bf16* sw = (bf16*)stream_scratch(2, st, 2 * w_el * sizeof(bf16));
+  if (!sa || !sw) return EDA_ECUDA;
+  bf16 *a_hi = sa, *a_lo = sa + a_el, *w_hi = sw, *w_lo = sw + w_el;
   if ((rc = split_bf16(A, lda, M, K, a_hi, a_lo, Kp, st)) != EDA_OK) return rc;
   if ((rc = split_bf16(W, ldw, N, K, w_hi, w_lo, Kp, st)) != EDA_OK) return rc;
   GemmParams p = {};

@@ -877,10 +877,10 @@ lstm_bwd_cluster_kernel(const LstmBwd P) {
 template <int kG>
 static int launch_lstm_bwd(cudaLaunchConfig_t& cfg, const LstmBwd& P) {
   const int smem = 2 * kCluster * kG * 512 + 2 * kG * 512 + 8 * 32 * 8 * 4 + 16 + 64 + 128;
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (!attr.done()) {
     EDA_CUDA(cudaFuncSetAttribute(lstm_bwd_cluster_kernel<kG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr = true;
+    attr.mark();
   }
   cfg.dynamicSmemBytes = smem;
   EDA_CUDA(cudaLaunchKernelEx(&cfg, lstm_bwd_cluster_kernel<kG>, P));

@@ -394,10 +394,10 @@ int mha_bwd(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi, 
               ld_dqkv >= 3 * H * BDH && ld_dqkv % 8 == 0, "eda_mha_bwd: bad sizes / strides");
   EDA_REQUIRE(((uintptr_t)dq_acc | (uintptr_t)dqkv_hi | (uintptr_t)dqkv_lo) % 16 == 0, "eda_mha_bwd: outputs must be 16B aligned");
   EDA_REQUIRE(prec == EDA_PREC_BF16X3 || prec == EDA_PREC_BF16, "eda_mha_bwd: precision must be BF16X3 or BF16");
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (!attr.done()) {
     EDA_CUDA(cudaFuncSetAttribute(mha_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM));
-    attr = true;
+    attr.mark();
   }
   EDA_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)B * T * H * BDH * sizeof(float), st));
   CUtensorMap tq_hi, tq_lo, tv_hi, tv_lo, tg_hi, tg_lo;

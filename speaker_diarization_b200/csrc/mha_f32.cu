@@ -1,7 +1,9 @@
 // Multi-head self-attention forward, fp32 CUDA-core path (EDA_PREC_FP32).
 //
 // softmax(q k^T / sqrt(64)) v per (batch, head) with NO mask (the reference attends to the
-// -1-padded frames too, models.py:223).  Flash-style: one CTA owns 64 queries of one
+// -1-padded frames too, models.py:223), or with per-sequence key counts (eda_mha_fwd_masked: a batch
+// of chunks in which every sequence sees only its own frames, as in the reference's one-chunk-per-call
+// loop, infer_eda.py:102-113).  Flash-style: one CTA owns 64 queries of one
 // (b, h), streams 64-key tiles, keeps the running max / sum / output in registers.
 // 256 threads as 16 x 16: thread (ty, tx) owns score rows ty*4+i, score columns tx+16*j
 // (interleaved, so LDS.128 along k is conflict-free with a 68-float row stride) and output
@@ -15,7 +17,7 @@ constexpr int kLd = 68;  // smem row stride in floats
 
 __global__ void __launch_bounds__(256, 2)
 mha_f32_kernel(const float* __restrict__ qkv, int ld_qkv, float* __restrict__ out, int ld_out,
-               int T, int D) {
+               int T, int D, const int32_t* __restrict__ key_lens) {
   extern __shared__ __align__(16) float smem[];
   float(*Qs)[kLd] = reinterpret_cast<float(*)[kLd]>(smem);
   float(*Ks)[kLd] = reinterpret_cast<float(*)[kLd]>(smem + 64 * kLd);
@@ -25,6 +27,7 @@ mha_f32_kernel(const float* __restrict__ qkv, int ld_qkv, float* __restrict__ ou
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int q0 = blockIdx.x * 64, h = blockIdx.y, b = blockIdx.z;
   const float* base = qkv + (size_t)b * T * ld_qkv + h * kDh;
+  const int klen = key_lens ? min(T, max(1, __ldg(key_lens + b))) : T;     // keys >= klen take no part
 
   // Q tile, pre-scaled by 1/sqrt(64) = 0.125 (exact in fp32)
 #pragma unroll
@@ -44,13 +47,13 @@ mha_f32_kernel(const float* __restrict__ qkv, int ld_qkv, float* __restrict__ ou
     for (int j = 0; j < 4; ++j) o[i][j] = 0.f;
   }
 
-  for (int k0 = 0; k0 < T; k0 += 64) {
+  for (int k0 = 0; k0 < klen; k0 += 64) {
     __syncthreads();  // previous tile fully consumed (also orders the Q stores on the first pass)
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       int f = tid + i * 256, r = f >> 4, c = (f & 15) * 4;
       float4 kv = make_float4(0.f, 0.f, 0.f, 0.f), vv = kv;
-      if (k0 + r < T) {
+      if (k0 + r < klen) {
         const float* p = base + (size_t)(k0 + r) * ld_qkv + c;
         kv = __ldg(reinterpret_cast<const float4*>(p + D));
         vv = __ldg(reinterpret_cast<const float4*>(p + 2 * D));
@@ -82,18 +85,18 @@ mha_f32_kernel(const float* __restrict__ qkv, int ld_qkv, float* __restrict__ ou
           s[i][j] = fmaf(a[i].w, bb[j].w, s[i][j]);
         }
     }
-    // mask keys beyond T, online softmax update
+    // mask keys beyond the sequence, online softmax update
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       float mx = -INFINITY;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        if (k0 + tx + 16 * j >= T) s[i][j] = -INFINITY;
+        if (k0 + tx + 16 * j >= klen) s[i][j] = -INFINITY;
         mx = fmaxf(mx, s[i][j]);
       }
 #pragma unroll
       for (int off = 8; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-      const float mn = fmaxf(m[i], mx);          // finite: key k0 (< T) is always valid
+      const float mn = fmaxf(m[i], mx);          // finite: key k0 (< klen) is always valid
       const float sc = expf(m[i] - mn);          // exp(-inf) = 0 on the first tile
       float ps = 0.f;
 #pragma unroll
@@ -144,19 +147,19 @@ mha_f32_kernel(const float* __restrict__ qkv, int ld_qkv, float* __restrict__ ou
 }
 
 int mha_f32(const float* qkv, int ld_qkv, float* out, int ld_out, int B, int T, int n_heads,
-            cudaStream_t st) {
+            cudaStream_t st, const int32_t* key_lens) {
   const int D = n_heads * kDh;
   EDA_REQUIRE(ld_qkv % 4 == 0 && ld_out % 4 == 0, "eda_mha_fwd: strides must be multiples of 4");
   EDA_REQUIRE(((uintptr_t)qkv | (uintptr_t)out) % 16 == 0, "eda_mha_fwd: pointers must be 16B aligned");
   EDA_REQUIRE(B <= 65535 && n_heads <= 65535, "eda_mha_fwd: B/n_heads too large for the grid");
-  static bool attr_set = false;
+  static DeviceOnce attr_set;
   const int smem = 4 * 64 * kLd * (int)sizeof(float);
-  if (!attr_set) {
+  if (!attr_set.done()) {
     EDA_CUDA(cudaFuncSetAttribute(mha_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
+    attr_set.mark();
   }
   dim3 grid(ceil_div(T, 64), n_heads, B);
-  mha_f32_kernel<<<grid, 256, smem, st>>>(qkv, ld_qkv, out, ld_out, T, D);
+  mha_f32_kernel<<<grid, 256, smem, st>>>(qkv, ld_qkv, out, ld_out, T, D, key_lens);
   EDA_LAUNCH_CHECK();
   return EDA_OK;
 }

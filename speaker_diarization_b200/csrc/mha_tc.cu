@@ -472,10 +472,10 @@ int mha_split(const void* qk_hi, const void* qk_lo, int ld_qk, const void* vt_hi
   EDA_REQUIRE(!out || (ld_out % 2 == 0 && (uintptr_t)out % 8 == 0), "eda_mha_split: fp32 output misaligned");
   EDA_REQUIRE(!out_hi || (ld_os % 2 == 0), "eda_mha_split: split output stride must be even");
   EDA_REQUIRE(prec == EDA_PREC_BF16X3 || prec == EDA_PREC_BF16, "eda_mha_split: precision must be BF16X3 or BF16");
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (!attr.done()) {
     EDA_CUDA(cudaFuncSetAttribute(mha_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, A_SMEM));
-    attr = true;
+    attr.mark();
   }
   CUtensorMap tq_hi, tq_lo, tk_hi, tk_lo, tv_hi, tv_lo;
   int rc;
@@ -524,19 +524,13 @@ __global__ void qkv_split_kernel(const float* __restrict__ qkv, int ld_qkv, int 
   }
 }
 
-static bf16* g_mha_scratch = nullptr;
-static size_t g_mha_cap = 0;
-
 int mha_tc(const float* qkv, int ld_qkv, float* out, int ld_out, int B, int T, int H, int prec, cudaStream_t st) {
   const int D = H * ADH, Tp = (T + 7) / 8 * 8;
   const size_t qk_el = (size_t)B * T * 2 * D, vt_el = (size_t)B * D * Tp;
   const size_t need = 2 * qk_el + 2 * vt_el;
-  if (need > g_mha_cap) {
-    if (g_mha_scratch) { EDA_CUDA(cudaDeviceSynchronize()); EDA_CUDA(cudaFree(g_mha_scratch)); }
-    g_mha_cap = need + need / 4;
-    EDA_CUDA(cudaMalloc(&g_mha_scratch, g_mha_cap * sizeof(bf16)));
-  }
-  bf16 *qk_hi = g_mha_scratch, *qk_lo = qk_hi + qk_el, *vt_hi = qk_lo + qk_el, *vt_lo = vt_hi + vt_el;
+  bf16* scratch = (bf16*)stream_scratch(3, st, need * sizeof(bf16));      // per (device, stream)
+  if (!scratch) return EDA_ECUDA;
+  bf16 *qk_hi = scratch, *qk_lo = qk_hi + qk_el, *vt_hi = qk_lo + qk_el, *vt_lo = vt_hi + vt_el;
   const int64_t n = (int64_t)B * T * 3 * D;
   qkv_split_kernel<<<(int)std::min<int64_t>(ceil_div<int64_t>(n, 256), num_sms() * 16), 256, 0, st>>>(
       qkv, ld_qkv, B, T, H, Tp, qk_hi, qk_lo, vt_hi, vt_lo);

@@ -152,22 +152,18 @@ static void launch_pit(const float* pred, const float* label, const int32_t* len
   pit_kernel<S><<<B, 256, 0, st>>>(pred, label, lens, B, T, loss, min_idx, label_perm, perm_out, best, counter);
 }
 
-// scratch (best cost per sequence + completion counter) grows on demand; it is the only
-// allocation the library makes outside plan_create and is reused across calls.
-static double* g_best = nullptr;
-static unsigned* g_counter = nullptr;
-static int g_best_cap = 0;
-
+// scratch (best cost per sequence + completion counter): library-owned, one buffer per (device, stream),
+// so calls in flight on different streams or GPUs never share the counter; the counter is zeroed on the
+// launch stream before every launch.
 int pit_loss(const float* pred, const float* label, const int32_t* lens, int B, int T, int S,
              float* loss, int64_t* min_idx, float* label_perm, int32_t* perm_out, cudaStream_t st) {
   EDA_REQUIRE(S >= 1 && S <= kMaxS, "eda_pit_loss: S must be in [1,%d] (got %d)", kMaxS, S);
   EDA_REQUIRE(B > 0 && T > 0 && loss && min_idx, "eda_pit_loss: bad arguments");
-  if (B > g_best_cap) {
-    if (g_best) cudaFree(g_best);
-    if (!g_counter) { EDA_CUDA(cudaMalloc(&g_counter, sizeof(unsigned))); EDA_CUDA(cudaMemset(g_counter, 0, sizeof(unsigned))); }
-    g_best_cap = std::max(B, 1024);
-    EDA_CUDA(cudaMalloc(&g_best, sizeof(double) * g_best_cap));
-  }
+  unsigned char* scratch = (unsigned char*)stream_scratch(4, st, 256 + sizeof(double) * (size_t)std::max(B, 1024));
+  if (!scratch) return EDA_ECUDA;
+  unsigned* g_counter = reinterpret_cast<unsigned*>(scratch);
+  double* g_best = reinterpret_cast<double*>(scratch + 256);
+  EDA_CUDA(cudaMemsetAsync(g_counter, 0, sizeof(unsigned), st));
 #define EDA_PIT_CASE(s) case s: launch_pit<s>(pred, label, lens, B, T, loss, min_idx, label_perm, perm_out, g_best, g_counter, st); break;
   switch (S) {
     EDA_PIT_CASE(1) EDA_PIT_CASE(2) EDA_PIT_CASE(3) EDA_PIT_CASE(4)

@@ -30,12 +30,14 @@ class LstmEncoderDedecoderAttractor(nn.Module):
         self.input_size = input_size
         self.precision = L.PREC_FP32
         self._prep = None
+        self._prep_event = None
 
     # -- cached kernel-side views of the parameters ------------------------------------
-    def _prepared(self):
+    def _prepared(self, want_split: bool = False):
         key = tuple((p.data_ptr(), p._version) for p in self.parameters())
         if self._prep is None or self._prep[0] != key:
             e, d = self.encoder, self.decoder
+            self._prep_event = None
             self._prep = (key, dict(
                 w_ih=e.weight_ih_l0.detach().contiguous(),
                 b_enc=(e.bias_ih_l0 + e.bias_hh_l0).detach().contiguous(),
@@ -45,19 +47,28 @@ class LstmEncoderDedecoderAttractor(nn.Module):
                 w_lin=self.linear.weight.detach().reshape(-1).contiguous(),
                 b_lin=self.linear.bias.detach().contiguous(),
             ))
-        return self._prep[1]
+        w = self._prep[1]
+        if want_split and "sw_ih" not in w:
+            w["sw_ih"] = ops.split_bf16(w["w_ih"])
+            self._prep_event = None
+        if w["w_ih"].is_cuda:
+            # the copies are made on whichever stream asks first: every other stream is ordered after it
+            if self._prep_event is None:
+                self._prep_event = torch.cuda.Event()
+                self._prep_event.record(torch.cuda.current_stream(w["w_ih"].device))
+            torch.cuda.current_stream(w["w_ih"].device).wait_event(self._prep_event)
+        return w
 
     def attractors(self, emb2d: torch.Tensor, perm: torch.Tensor, lens_dev: torch.Tensor,
                    lens_host: List[int], B: int, Tmax: int, n_dec: int,
                    n_spk_label: int = -1, emb_split=None):
         """emb2d (B*Tmax, D) UNshuffled; perm (B, Tmax) int32 frame order per sequence.
         Returns attractors (B, n_dec, D), probs (B, n_dec), attractor loss (1,) or None."""
-        w = self._prepared()
-        if emb_split is not None and self.precision != L.PREC_FP32:
+        use_split = emb_split is not None and self.precision != L.PREC_FP32
+        w = self._prepared(use_split)
+        if use_split:
             # the encoder left emb as a split-bf16 pair: the input projection reads it directly
             es, xproj = emb_split
-            if "sw_ih" not in w:
-                w["sw_ih"] = ops.split_bf16(w["w_ih"])
             ops.gemm_split(es, w["sw_ih"], w["b_enc"], B * Tmax, 4 * self.input_size, self.input_size,
                            L.EPI_BIAS, self.precision, out=xproj)
         else:

@@ -63,6 +63,7 @@ class TransformerEdaModel(nn.Module):
         self.workspace_slot = 0     # callers with several batches in flight on different streams use one slot each
         self._perm_ring = {}
         self._emb_split = None
+        self._prep_event = None
 
     # state_dict names of the input projection, its LayerNorm and the encoder stack (models.py:185-193)
     NAMES = dict(in_linear="encoder", in_norm="encoder_norm", stack="transformer_encoder")
@@ -126,25 +127,57 @@ class TransformerEdaModel(nn.Module):
                     for k in ("w_qkv", "w_o", "w_1", "w_2"):
                         lw["s" + k] = ops.split_bf16(lw[k])
             self._prep = (key, prep)
+            self._prep_event = self._record_event(w.device)
+        self._wait_event(self._prep_event)
         return self._prep[1]
 
+    @staticmethod
+    def _record_event(dev):
+        if dev.type != "cuda":
+            return None
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(dev))
+        return ev
+
+    @staticmethod
+    def _wait_event(ev):
+        """Order the current stream after the stream that built the cached weight copies (several compute
+        streams share them: InferencePipeline, the dropout side stream of the training step)."""
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+
     def _workspace(self, B: int, Tmax: int, dev):
-        """Persistent per-shape buffers of the tensor-core pipeline (stable pointers keep the
-        TMA descriptor cache of libeda_b200 warm)."""
-        key = (B, Tmax, str(dev), self.workspace_slot)
-        ws = self._ws.get(key)
+        """Buffers of the tensor-core pipeline for a (B, Tmax) batch: views carved out of ONE arena per
+        (device, stream slot) that only grows to the largest batch seen, so ragged chunk batches
+        (infer_eda.py's per-recording loop: a different tail length per recording) neither pile up
+        multi-GB workspaces per shape nor thrash the allocator.  A shape always gets the same pointers
+        while the arena stands, which keeps libeda_b200's tensor-map cache (keyed on pointer + dims) warm."""
+        akey = ("arena", str(dev), self.workspace_slot)
+        M, D, H, FF = B * Tmax, self.n_units, self.n_heads, self.dim_feedforward
+        Tp, kpad = _round_up(Tmax, 8), _round_up(self.in_size, 16)
+        plan = [("xin", torch.bfloat16, (2, M, kpad)), ("xs0", torch.bfloat16, (2, M, D)), ("xs1", torch.bfloat16, (2, M, D)),
+                ("xf0", torch.float32, (M, D)), ("xf1", torch.float32, (M, D)), ("qk", torch.bfloat16, (2, M, 2 * D)),
+                ("vt", torch.bfloat16, (2, B * H * (D // H), Tp)), ("att", torch.bfloat16, (2, M, D)),
+                ("ff", torch.bfloat16, (2, M, FF)), ("xproj", torch.float32, (M, 4 * D))]
+        sizes = [_round_up(int(np.prod(shape)) * torch.empty((), dtype=dt).element_size(), 1024) for _, dt, shape in plan]
+        need = sum(sizes)
+        arena = self._ws.get(akey)
+        if arena is None or arena["buf"].numel() < need:
+            arena = dict(buf=torch.empty(need, dtype=torch.uint8, device=dev), views={})
+            self._ws[akey] = arena
+        ws = arena["views"].get((B, Tmax))
         if ws is None:
-            if len(self._ws) >= 8:
-                self._ws.clear()
-            M, D, H = B * Tmax, self.n_units, self.n_heads
-            Tp = _round_up(Tmax, 8)
-            ws = dict(Tp=Tp, xin=ops.Split.empty(M, _round_up(self.in_size, 16), dev),
-                      xs=[ops.Split.empty(M, D, dev) for _ in range(2)],
-                      xf=[torch.empty((M, D), dtype=torch.float32, device=dev) for _ in range(2)],
-                      qk=ops.Split.empty(M, 2 * D, dev), vt=ops.Split.empty(B * H * (D // H), Tp, dev),
-                      att=ops.Split.empty(M, D, dev), ff=ops.Split.empty(M, self.dim_feedforward, dev),
-                      xproj=torch.empty((M, 4 * D), dtype=torch.float32, device=dev))
-            self._ws[key] = ws
+            if len(arena["views"]) >= 32:
+                arena["views"].clear()
+            t, pos = {}, 0
+            for (name, dt, shape), nbytes in zip(plan, sizes):
+                t[name] = arena["buf"][pos:pos + nbytes].view(dt)[: int(np.prod(shape))].view(shape)
+                pos += nbytes
+            sp = lambda x: ops.Split(x[0], x[1])
+            # key columns [Tmax, Tp) of v^T are never written by the QKV epilogue and must not hold NaN bit patterns
+            ws = dict(Tp=Tp, vt_pad=t["vt"][:, :, Tmax:] if Tp != Tmax else None, xin=sp(t["xin"]), xs=[sp(t["xs0"]), sp(t["xs1"])], xf=[t["xf0"], t["xf1"]], qk=sp(t["qk"]),
+                      vt=sp(t["vt"]), att=sp(t["att"]), ff=sp(t["ff"]), xproj=t["xproj"])
+            arena["views"][(B, Tmax)] = ws
         return ws
 
     def _device(self) -> torch.device:
@@ -172,10 +205,13 @@ class TransformerEdaModel(nn.Module):
         torch.cat([s.float() for s in seqs], dim=0, out=stage)
         return stage.to(dev, non_blocking=True)
 
-    def _embed(self, src, ilens: Optional[List[int]] = None):
+    def _embed(self, src, ilens: Optional[List[int]] = None, independent: bool = False, offsets=None):
         """models.py:213-226 up to ``emb``; returns emb2d (B*Tmax, D) plus batch geometry.
         ``src`` is the reference's list of (T_i, F) tensors, or (with ``ilens``) ONE device
-        matrix holding the sequences back to back (row stride may exceed F)."""
+        matrix holding the sequences back to back (row stride may exceed F); ``offsets`` then gives each
+        sequence's first row in it (default: back to back in the order of ``ilens``).
+        ``independent``: attention masks keys >= ilen, so every sequence gets the result of a batch-of-one
+        call - the reference's inference loop (infer_eda.py:102-113), where padding never exists."""
         dev = self._device()
         self._check_mode()
         w = self._prepared()
@@ -184,7 +220,12 @@ class TransformerEdaModel(nn.Module):
             ilens = [int(x.shape[0]) for x in src]
         B, Tmax = len(ilens), max(ilens)
         off = np.zeros(B + 1, dtype=np.int64)
-        np.cumsum(ilens, out=off[1:])
+        if offsets is not None:
+            off[:B] = np.asarray(offsets, dtype=np.int64)
+            off[B] = off[B - 1] + ilens[-1]
+        else:
+            np.cumsum(ilens, out=off[1:])
+        masked = independent and min(ilens) != Tmax
         meta = torch.from_numpy(np.concatenate([off, np.asarray(ilens, dtype=np.int64)])).to(dev, non_blocking=True)
         seq_off = meta[: B + 1]
         lens_dev = meta[B + 1:].to(torch.int32)
@@ -193,19 +234,19 @@ class TransformerEdaModel(nn.Module):
         if flat_in and P == L.PREC_FP32 and not flat.is_contiguous():
             flat = flat.contiguous()
         if P != L.PREC_FP32:
-            return self._embed_tc(flat, w, seq_off, lens_dev, ilens, B, Tmax, dev)
+            return self._embed_tc(flat, w, seq_off, lens_dev, ilens, B, Tmax, dev, masked)
         self._emb_split = None
         x = ops.pad_pack(flat, seq_off, lens_dev, B, Tmax, w["kpad"], -1.0)
         x = ops.linear(x, w["w_in"], w["b_in"], L.EPI_BIAS_LN, P, gamma=w["g_in"], beta=w["be_in"])
         for lw in w["layers"]:
             qkv = ops.linear(x, lw["w_qkv"], lw["b_qkv"], L.EPI_BIAS, P)
-            att = ops.mha(qkv, B, Tmax, self.n_heads, self.attn_precision)
+            att = ops.mha(qkv, B, Tmax, self.n_heads, self.attn_precision, key_lens=lens_dev if masked else None)
             x = ops.linear(att, lw["w_o"], lw["b_o"], L.EPI_BIAS_RES_LN, P, resid=x, gamma=lw["g1"], beta=lw["be1"])
             ff = ops.linear(x, lw["w_1"], lw["b_1"], L.EPI_BIAS_RELU, P)
             x = ops.linear(ff, lw["w_2"], lw["b_2"], L.EPI_BIAS_RES_LN, P, resid=x, gamma=lw["g2"], beta=lw["be2"])
         return x, ilens, lens_dev, seq_off, B, Tmax
 
-    def _embed_tc(self, flat, w, seq_off, lens_dev, ilens, B, Tmax, dev):
+    def _embed_tc(self, flat, w, seq_off, lens_dev, ilens, B, Tmax, dev, masked=False):
         """The encoder on the split-bf16 tensor-core pipeline: every GEMM epilogue writes the
         next kernel's operands (split bf16) and, where needed, the fp32 residual stream."""
         P, D, H = self.precision, self.n_units, self.n_heads
@@ -214,6 +255,8 @@ class TransformerEdaModel(nn.Module):
         Tp = ws["Tp"]
         xin, (sa, sb), (xa, xb) = ws["xin"], ws["xs"], ws["xf"]
         ops.pad_pack_split(flat, seq_off, lens_dev, B, Tmax, xin, -1.0)
+        if ws["vt_pad"] is not None:
+            ws["vt_pad"].zero_()
         n_layers = len(w["layers"])
         emb = torch.empty((M, D), dtype=torch.float32, device=dev)      # returned to the caller: fresh
         ops.gemm_split(xin, w["ws_in"], w["b_in"], M, D, xin.ld, L.EPI_BIAS_LN, P, gamma=w["g_in"], beta=w["be_in"],
@@ -221,7 +264,10 @@ class TransformerEdaModel(nn.Module):
         for i, lw in enumerate(w["layers"]):
             last = i == n_layers - 1
             ops.gemm_qkv(sa, lw["sw_qkv"], lw["b_qkv"], ws["qk"], ws["vt"], B, Tmax, Tp, D, H, P)
-            ops.mha_split(ws["qk"], ws["vt"], B, Tmax, Tp, H, self.attn_precision, out_split=ws["att"])
+            if masked:
+                ops.mha_split_masked(ws["qk"], ws["vt"], B, Tmax, Tp, H, lens_dev, self.attn_precision, ws["att"])
+            else:
+                ops.mha_split(ws["qk"], ws["vt"], B, Tmax, Tp, H, self.attn_precision, out_split=ws["att"])
             ops.gemm_split(ws["att"], lw["sw_o"], lw["b_o"], M, D, D, L.EPI_BIAS_RES_LN, P, resid=xa,
                            gamma=lw["g1"], beta=lw["be1"], out=xb, out_split=sb)
             ops.gemm_split(sb, lw["sw_1"], lw["b_1"], M, self.dim_feedforward, D, L.EPI_BIAS_RELU, P,
@@ -231,32 +277,60 @@ class TransformerEdaModel(nn.Module):
         self._emb_split = (sa, ws["xproj"])
         return emb, ilens, lens_dev, seq_off, B, Tmax
 
-    def _draw_perm(self, ilens: List[int], Tmax: int, dev, perms=None) -> Tensor:
-        """models.py:229-232: one ``torch.randperm(ilen)`` per sequence from the global CPU
-        generator, in batch order; shipped as an int32 (B, Tmax) index (identity beyond ilen).
-        ``perms`` (extension): use these frame orders instead of drawing (callers that batch
-        chunks out of order draw them first, in the reference's order)."""
-        # pinned staging buffers are recycled through a small ring (an event per buffer guards
-        # the asynchronous H2D copy that last read it)
-        B = len(ilens)
+    def _perm_slot(self, B: int, Tmax: int):
+        """A pinned (B, Tmax) int32 staging buffer prefilled with the identity order, from a small ring
+        (an event per buffer guards the asynchronous H2D copy that last read it)."""
         ring = self._perm_ring.setdefault((B, Tmax), [])
         slot = next((r for r in ring if r[1].query()), None)
         if slot is None:
             slot = [torch.empty((B, Tmax), dtype=torch.int32, pin_memory=True), torch.cuda.Event()]
             if len(ring) < 8:
                 ring.append(slot)
-        perm = slot[0]
+            if len(self._perm_ring) > 16:                 # ragged workloads: do not keep a ring per shape forever
+                for k in list(self._perm_ring)[:8]:
+                    if k != (B, Tmax):
+                        del self._perm_ring[k]
         if self._arange is None or self._arange.numel() < Tmax:
             self._arange = torch.arange(max(Tmax, 4096), dtype=torch.int32)
-        perm[:] = self._arange[:Tmax]
+        slot[0][:] = self._arange[:Tmax]
+        return slot
+
+    @staticmethod
+    def _ship_perm(slot, dev) -> Tensor:
+        out = slot[0].to(dev, non_blocking=True)
+        slot[1].record(torch.cuda.current_stream(dev))
+        return out
+
+    def _draw_perm(self, ilens: List[int], Tmax: int, dev, perms=None) -> Tensor:
+        """models.py:229-232: one ``torch.randperm(ilen)`` per sequence from the global CPU
+        generator, in batch order; shipped as an int32 (B, Tmax) index (identity beyond ilen).
+        ``perms`` (extension): use these frame orders instead of drawing (callers that batch
+        chunks out of order draw them first, in the reference's order)."""
+        slot = self._perm_slot(len(ilens), Tmax)
+        perm = slot[0]
         for i, n in enumerate(ilens):
             if perms is None:        # int32 output draws the same numbers from the generator as the int64 default
                 torch.randperm(n, out=perm[i, :n])
             else:
                 perm[i, :n] = perms[i].to(torch.int32)
-        out = perm.to(dev, non_blocking=True)
-        slot[1].record(torch.cuda.current_stream(dev))
-        return out
+        return self._ship_perm(slot, dev)
+
+    def draw_perms(self, groups: List[List[int]], order, dev) -> List[Tensor]:
+        """Frame shuffles for several batches at once, DRAWN in the order the reference's driver would draw
+        them: ``groups[g]`` = sequence lengths of batch g, ``order`` = [(g, i)] in the driver's processing order
+        (recording by recording, chunk by chunk, infer_eda.py:92-113).  Returns one (B_g, Tmax_g) int32 device
+        index per batch."""
+        slots = [self._perm_slot(len(g), max(g)) for g in groups]
+        for g, i in order:
+            n = groups[g][i]
+            torch.randperm(n, out=slots[g][0][i, :n])
+        return [self._ship_perm(s, dev) for s in slots]
+
+    def prepare_weights(self) -> None:
+        """Build the kernel-side copies of the parameters now, on the current stream (they are otherwise made
+        lazily by the first call; other streams wait on the event recorded here)."""
+        self._prepared()
+        self.eda._prepared(self.precision != L.PREC_FP32)
 
     def forward_embedding(self, src: List[Tensor]):
         """Reference signature (models.py:213): (encoder_out_shuffled, emb, ilens)."""
@@ -306,27 +380,41 @@ class TransformerEdaModel(nn.Module):
 
     # ----------------------------------------------------------------------- infer -------
     @torch.no_grad()
-    def infer_device(self, feats: Tensor, ilens: List[int], max_n_speakers=15, activity_threshold=0.5, perms=None):
+    def infer_device(self, feats: Tensor, ilens: List[int], max_n_speakers=15, activity_threshold=0.5, perms=None,
+                     independent: bool = False, offsets=None, packed_out=None, perm_dev: Optional[Tensor] = None):
         """The device half of ``infer`` with NO host synchronisation: ``feats`` is one CUDA matrix
-        holding the sequences back to back (as ``FrontEnd.features_flat`` returns it).  Returns
-        (posteriors (B, Tmax, max_n_speakers-1), attractor existence probs (B, max_n_speakers),
-        uint8 activity labels) on the device; speaker counting / slicing is the caller's."""
-        x, ilens, lens_dev, _, B, Tmax = self._embed(feats, ilens)
-        perm = self._draw_perm(ilens, Tmax, x.device, perms)
+        holding the sequences back to back (as ``FrontEnd.features_flat`` returns it), or anywhere in it
+        with ``offsets``.  Returns (posteriors (B, Tmax, max_n_speakers-1), attractor existence probs
+        (B, max_n_speakers), uint8 activity labels) on the device; speaker counting / slicing is the
+        caller's.  ``independent``: see ``infer``.  ``packed_out`` = (post, labels) matrices with one row
+        per row of ``feats``: results of frame t of sequence b land in row offsets[b] + t (the time-axis
+        concatenation of infer_eda.py:121), nothing is written for padding, and (None, probs, None) is returned.
+        ``perm_dev``: the (B, Tmax) int32 frame orders already on the device (else drawn / taken from ``perms``)."""
+        x, ilens, lens_dev, seq_off, B, Tmax = self._embed(feats, ilens, independent, offsets)
+        perm = perm_dev if perm_dev is not None else self._draw_perm(ilens, Tmax, x.device, perms)
         att, probs, _ = self.eda.attractors(x, perm, lens_dev, ilens, B, Tmax, max_n_speakers,
                                             emb_split=self._emb_split)
+        if packed_out is not None:
+            ops.posterior_packed(x, att, B, Tmax, max_n_speakers - 1, seq_off, lens_dev, activity_threshold,
+                                 packed_out[0], packed_out[1])
+            return None, probs, None
         _, post, labels = ops.posterior(x, att, B, Tmax, max_n_speakers - 1, threshold=activity_threshold,
                                         want_labels=True)
         return post, probs, labels
 
     @torch.no_grad()
     def infer(self, src: List[Tensor], infer_num_speakers=None, max_n_speakers=15, attractor_threshold=0.5,
-              activity_threshold: Optional[float] = None, perms=None):
+              activity_threshold: Optional[float] = None, perms=None, independent: bool = False):
         """models.py:297-347: list of (Tmax, n_spk_b) posterior tensors.
 
         ``activity_threshold`` (extension): also keep the fused ``posterior > threshold``
-        uint8 decisions of bin/make_rttm.py:29 in ``self.last['labels']``."""
-        x, ilens, lens_dev, _, B, Tmax = self._embed(src)
+        uint8 decisions of bin/make_rttm.py:29 in ``self.last['labels']``.
+        ``independent`` (extension): every sequence is processed as if it were alone in the batch -
+        attention sees only its own frames and the returned tensor has ITS length, (T_b, n_spk_b).  That is
+        what the reference's driver computes (infer_eda.py:102-113 calls ``infer([chunk])`` once per chunk, so
+        no padding exists there); the default reproduces ``infer`` on a padded batch, where padded frames are
+        attended to (models.py:223 passes no mask) and every tensor has Tmax rows (models.py:333)."""
+        x, ilens, lens_dev, _, B, Tmax = self._embed(src, independent=independent)
         perm = self._draw_perm(ilens, Tmax, x.device, perms)
         att, probs, _ = self.eda.attractors(x, perm, lens_dev, ilens, B, Tmax, max_n_speakers,
                                             emb_split=self._emb_split)
@@ -335,19 +423,20 @@ class TransformerEdaModel(nn.Module):
                                         threshold=0.5 if activity_threshold is None else activity_threshold,
                                         want_labels=activity_threshold is not None)
         self.last = dict(emb=x.view(B, Tmax, -1), attractors=att, probs=probs, posteriors=post, labels=labels)
+        rows = (lambda b: ilens[b]) if independent else (lambda b: Tmax)
         ys_active = []
         if infer_num_speakers is not None:
             order = torch.sort(probs, dim=1, descending=True, stable=False)[1][:, :infer_num_speakers]
             if bool((order >= n_att).any()):      # the reference indexes 14 columns with it (models.py:339)
                 raise IndexError(f"index {n_att} is out of bounds for dimension 1 with size {n_att}")
             for b in range(B):
-                ys_active.append(post[b][:, order[b]])
+                ys_active.append(post[b][: rows(b), order[b]])
         elif attractor_threshold is not None:
             p_host = probs.cpu().numpy()          # the call's single device->host sync
             for b in range(B):
                 silence = np.where(p_host[b] < attractor_threshold)[0]
                 n_spk = int(silence[0]) if silence.size else None
-                ys_active.append(post[b][:, :n_spk])
+                ys_active.append(post[b][: rows(b), :n_spk])
         return ys_active
 
     # ---------------------------------------------------------------- loss pieces --------
@@ -468,11 +557,17 @@ class EendEdaModel(TransformerEdaModel):
             prep = dict(kpad=kpad, ws_in=ops.split_bf16(w_in), b_in=g(self.linear.bias), g_in=g(self.linear_norm.weight),
                         be_in=g(self.linear_norm.bias), layers=layers)
             self._prep = (key, prep)
+            self._prep_event = self._record_event(w.device)
+        self._wait_event(self._prep_event)
         return self._prep[1]
 
-    def _embed(self, src, ilens: Optional[List[int]] = None):
+    def _embed(self, src, ilens: Optional[List[int]] = None, independent: bool = False, offsets=None):
         if self.encoder_type == "transformer":
-            return super()._embed(src, ilens)
+            return super()._embed(src, ilens, independent, offsets)
+        if offsets is not None or (independent and ilens is not None and min(ilens) != max(ilens)):
+            raise NotImplementedError("the Conformer variant batches like the reference (key_padding_mask, convolution over "
+                                      "the padded time axis, models.py:525-528): independent / scattered sequences are a "
+                                      "transformer-path feature")
         dev = self._device()
         if self.training:
             raise NotImplementedError("the Conformer variant runs in eval() mode only (no backward kernels, BatchNorm "
@@ -494,6 +589,9 @@ class EendEdaModel(TransformerEdaModel):
         key = ("conformer", B, Tmax, str(dev), self.workspace_slot)
         ws = self._ws.get(key)
         if ws is None:
+            old = [k for k in self._ws if k[0] == "conformer"]
+            for k in old[: max(0, len(old) - 3)]:       # at most 4 shapes stay resident (oldest go first)
+                del self._ws[k]
             Tp = _round_up(Tmax, 8)
             f32 = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
             ws = dict(Tp=Tp, xin=ops.Split.empty(M, w["kpad"], dev), xa=f32(M, D), xb=f32(M, D), glu=f32(M, D),
@@ -545,9 +643,9 @@ class EendEdaModel(TransformerEdaModel):
 
     @torch.no_grad()
     def infer(self, src: List[Tensor], infer_num_speakers=None, max_n_speakers=15, attractor_threshold=0.5,
-              activity_threshold: Optional[float] = None, perms=None):
+              activity_threshold: Optional[float] = None, perms=None, independent: bool = False):
         """models.py:601-652."""
         if infer_num_speakers is None:
-            return super().infer(src, None, max_n_speakers, attractor_threshold, activity_threshold, perms)
-        ys = super().infer(src, None, max_n_speakers, -1.0, activity_threshold, perms)     # all columns, one pass
+            return super().infer(src, None, max_n_speakers, attractor_threshold, activity_threshold, perms, independent)
+        ys = super().infer(src, None, max_n_speakers, -1.0, activity_threshold, perms, independent)  # all columns, one pass
         return [y[:, :infer_num_speakers] for y in ys]

@@ -75,6 +75,11 @@ def train_workspace(model, B: int, Tmax: int, n_dec: int, dev) -> dict:
     ws = model._ws.get(key)
     if ws is not None:
         return ws
+    # a training workspace is ~5 GB at 32 x 2000 frames: keep at most two shapes (a steady batch shape + the
+    # ragged last batch of an epoch), oldest first out, independent of the inference arena
+    old = [k for k in model._ws if k[0] == "train"]
+    for k in old[: max(0, len(old) - 1)]:
+        del model._ws[k]
     M, D, H, FF = B * Tmax, model.n_units, model.n_heads, model.dim_feedforward
     Tp = _round_up(Tmax, 8)
     f32 = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
@@ -143,7 +148,7 @@ def _prefetch_keep_bits(model, ws: dict, pd: float, B: int, H: int, Tmax: int, d
     seed, which = _step_seed(model, nxt), nxt & 1
     side = ws.setdefault("side_stream", torch.cuda.Stream(device=dev))
     side.wait_event(fork)              # the other set was last read by the previous step's backward: long finished
-    with torch.cuda.stream(side):
+    with torch.cuda.stream(side), L.use_stream(side):    # explicit: a caller's use_stream() pin must not redirect these
         _fill_keep_bits(model, ws["bits"][which], pd, seed, B, H, Tmax)
         done = torch.cuda.Event()
         done.record(side)

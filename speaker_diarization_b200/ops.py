@@ -44,10 +44,15 @@ def linear(a: Tensor, w: Tensor, bias: Optional[Tensor], epilogue: int = L.EPI_B
     return out
 
 
-def mha(qkv: Tensor, B: int, T: int, n_heads: int, prec: int = L.PREC_FP32) -> Tensor:
+def mha(qkv: Tensor, B: int, T: int, n_heads: int, prec: int = L.PREC_FP32, key_lens: Optional[Tensor] = None) -> Tensor:
     _f32(qkv)
     D = qkv.shape[1] // 3
     out = torch.empty((B * T, D), dtype=torch.float32, device=qkv.device)
+    if key_lens is not None:
+        assert key_lens.dtype == torch.int32
+        L.call("eda_mha_fwd_masked", L.ptr(qkv), qkv.stride(0), L.ptr(out), out.stride(0), B, T, n_heads,
+               D // n_heads, L.ptr(key_lens), prec, L.stream())
+        return out
     L.call("eda_mha_fwd", L.ptr(qkv), qkv.stride(0), L.ptr(out), out.stride(0), B, T, n_heads,
            D // n_heads, prec, L.stream())
     return out
@@ -86,6 +91,17 @@ def posterior(emb: Tensor, att: Tensor, B: int, Tmax: int, n_att: int, threshold
     L.call("eda_posterior", L.ptr(_f32(emb)), emb.stride(0), L.ptr(_f32(att)), att.shape[1], B, Tmax, D,
            n_att, float(threshold), L.ptr(logits), L.ptr(post), L.ptr(labels), L.stream())
     return logits, post, labels
+
+
+def posterior_packed(emb: Tensor, att: Tensor, B: int, Tmax: int, n_att: int, out_off: Tensor, lens: Tensor,
+                     threshold: float, post: Optional[Tensor], labels: Optional[Tensor]) -> None:
+    """eda_posterior into (total rows, n_att) matrices: frame t of sequence b -> row out_off[b] + t."""
+    D = emb.shape[1]
+    assert out_off.dtype == torch.int64 and lens.dtype == torch.int32
+    assert post is None or (post.dtype == torch.float32 and post.is_contiguous() and post.shape[1] == n_att)
+    assert labels is None or (labels.dtype == torch.uint8 and labels.is_contiguous() and labels.shape[1] == n_att)
+    L.call("eda_posterior_packed", L.ptr(_f32(emb)), emb.stride(0), L.ptr(_f32(att)), att.shape[1], B, Tmax, D,
+           n_att, float(threshold), L.ptr(out_off), L.ptr(lens), None, L.ptr(post), L.ptr(labels), L.stream())
 
 
 def pit_loss(pred: Tensor, label: Tensor, lens: Tensor):

@@ -1,25 +1,35 @@
 """Overlapped EEND-EDA inference over a stream of recording batches.
 
 What the reference's ``infer_eda.py:92-124`` loop does one chunk at a time on the default
-stream (load -> feature.stft/transform/splice/subsample on the CPU -> H2D -> model.infer ->
-D2H), restructured for a B200: CUDA streams for audio H2D, compute and result D2H chained
-with events, ``depth`` batches in flight, results landing in pinned host buffers.  The host
+stream (load -> feature.stft/transform/splice/subsample on the CPU -> H2D -> model.infer([chunk])
+-> D2H -> np.vstack), restructured for a B200: CUDA streams for audio H2D, compute and result D2H
+chained with events, ``depth`` batches in flight, results landing in pinned host buffers.  The host
 never blocks on the batch it has just submitted, so its own work (drawing the reference's
 ``torch.randperm`` frame shuffles, staging, kernel launches) overlaps the GPU's.
 
-Consecutive batches alternate between ``compute_streams`` compute streams (each with its own
-model workspace): the attractor LSTM is a latency-bound recurrence that occupies 104 of the
-148 SMs at low utilisation for about a third of a batch, and with two streams the next
-batch's front end and attention CTAs run on the SMs it leaves idle.
+Semantics are the reference DRIVER's: every recording goes through the front end as a whole
+(recording-wide mean normalisation, feature.py:72-73), its frames are cut into ``chunk_size``-frame
+chunks (infer_eda.py:21-27), and every chunk is diarized as if it were alone in the model call
+(``independent=True``: attention sees only the chunk's own frames, which is what a batch of one
+computes).  The frame shuffles are drawn from torch's global CPU generator at ``submit`` time in the
+driver's order (recording by recording, chunk by chunk), so the same ``torch.manual_seed`` gives the
+reference driver's ``T_hat``.  On the device the chunks of ALL recordings of a batch run together in at
+most two model passes: the full ``chunk_size`` chunks, and the ragged tails padded to the longest tail.
 
-    pipe = InferencePipeline(model, frontend)
+    pipe = InferencePipeline(model, frontend, chunk_size=2000)
     for result in pipe.run(batches):          # batches: iterable of (audio, counts)
-        result["posteriors"]                  # (B, Tmax, 14) pinned host tensor
-        result["n_speakers"]                  # list[int], attractor-threshold speaker counts
+        result["posteriors"]                  # (sum of frames, 14) pinned host tensor, recordings back to back
+        result["rec_offsets"]                 # recording r = rows [rec_offsets[r], rec_offsets[r+1])
+        result["n_speakers"]                  # per chunk, attractor-threshold speaker counts (models.py:340-343)
+        InferencePipeline.t_hats(result)      # per recording: the (T, n_spk) matrix infer_eda.py:121 writes
 
-Semantics per batch are those of ``feature.extract`` + ``TransformerEdaModel.infer`` on the
-batch's recordings taken as one padded batch (models.py:297-347); the permutation draws happen
-at ``submit`` time, in submission order, from torch's global CPU generator.
+Result tensors are freshly allocated (torch's pinned caching allocator) for every batch and belong
+to the caller: they stay valid however many batches are submitted afterwards.
+
+Consecutive batches alternate between ``compute_streams`` compute streams (each with its own
+model workspace): the attractor LSTM is a latency-bound recurrence that occupies part of the SMs
+at low utilisation for about a quarter of a batch, and with several streams the next batch's front
+end and attention CTAs run on the SMs it leaves idle.
 """
 from __future__ import annotations
 
@@ -32,35 +42,73 @@ import torch
 from . import _lib as L
 
 
+def chunk_plan(rows: Sequence[int], chunk_size: Optional[int]):
+    """The driver's chunking (infer_eda.py:21-27, 102) over a batch of recordings whose features lie back
+    to back: [(recording, first row in the flat matrix, length)] in the driver's processing order."""
+    out, base = [], 0
+    for r, n in enumerate(rows):
+        step = chunk_size if chunk_size and chunk_size > 0 else max(n, 1)
+        for s in range(0, n, step):
+            out.append((r, base + s, min(step, n - s)))
+        base += n
+    return out
+
+
 class InferencePipeline:
     def __init__(self, model, frontend, max_n_speakers: int = 15, attractor_threshold: float = 0.5,
-                 activity_threshold: float = 0.5, depth: int = 3, ld: int = 352, compute_streams: int = 3):
+                 activity_threshold: float = 0.5, depth: int = 3, ld: int = 352, compute_streams: int = 3,
+                 chunk_size: Optional[int] = 2000, independent: bool = True):
         self.model, self.fe = model, frontend
         self.max_n_speakers, self.attractor_threshold = max_n_speakers, attractor_threshold
         self.activity_threshold, self.depth, self.ld = activity_threshold, max(1, depth), ld
+        self.chunk_size, self.independent = chunk_size, independent
         self.device = frontend.device
         if self.device.type != "cuda":
             raise L.EdaError("speaker_diarization_b200 has no CPU path")
         with torch.cuda.device(self.device):
             self.s_in, self.s_out = torch.cuda.Stream(), torch.cuda.Stream()
             self.s_computes = [torch.cuda.Stream() for _ in range(max(1, min(compute_streams, self.depth)))]
+            # kernel-side copies of the weights are made here, once, and every stream is ordered after them
+            model.prepare_weights()
+            torch.cuda.synchronize(self.device)
         self.s_compute = self.s_computes[0]
         self._n_submitted = 0
-        self._slots = [dict(busy=None) for _ in range(self.depth + 1)]
-        self._next = 0
         self._pending = deque()
+        self._plans = {}
         self.gather = None          # optional callable(post_dev) run on the compute stream (multi-GPU collection)
 
     # ------------------------------------------------------------------------------------
+    def _plan(self, rows: Sequence[int]):
+        """Chunk list, length buckets and device-side offsets of a batch geometry (cached per geometry)."""
+        key = tuple(rows)
+        p = self._plans.get(key)
+        if p is None:
+            if len(self._plans) > 64:
+                self._plans.clear()
+            chunks = chunk_plan(rows, self.chunk_size)
+            full = [i for i, c in enumerate(chunks) if self.chunk_size and c[2] == self.chunk_size]
+            tails = [i for i, c in enumerate(chunks) if not (self.chunk_size and c[2] == self.chunk_size)]
+            if not self.independent:
+                full, tails = list(range(len(chunks))), []        # one padded batch, like model.infer on a list
+            buckets = [b for b in (full, tails) if b]
+            where = {}
+            for g, b in enumerate(buckets):
+                for j, i in enumerate(b):
+                    where[i] = (g, j)
+            rec_off = np.zeros(len(rows) + 1, dtype=np.int64)
+            np.cumsum(rows, out=rec_off[1:])
+            p = dict(chunks=chunks, buckets=buckets, order=[where[i] for i in range(len(chunks))],
+                     lens=[[chunks[i][2] for i in b] for b in buckets], offs=[[chunks[i][1] for i in b] for b in buckets],
+                     inv=np.concatenate([np.asarray(b, dtype=np.int64) for b in buckets]).argsort(),
+                     rec_off=rec_off, chunk_rec=[c[0] for c in chunks], lengths=[c[2] for c in chunks])
+            self._plans[key] = p
+        return p
+
     def submit(self, audio, counts: Optional[Sequence[int]] = None) -> None:
         """Enqueue one batch.  ``audio``: one (n_rec, n) / flat tensor with ``counts`` samples per
         recording, or a list of 1-D arrays/tensors.  Host tensors should be pinned."""
         if len(self._pending) >= self.depth:
             raise RuntimeError("pipeline full: call collect() first")
-        slot = self._slots[self._next]
-        self._next = (self._next + 1) % len(self._slots)
-        if slot["busy"] is not None:
-            slot["busy"].synchronize()            # its previous results have been handed out long ago
         dev = self.device
         cur = torch.cuda.current_stream(dev)
         k = self._n_submitted % len(self.s_computes)
@@ -77,41 +125,67 @@ class InferencePipeline:
                 s_compute.wait_stream(self.s_in)
         else:
             dev_audio = audio                     # list of recordings: FrontEnd stages them itself
+        n_att = self.max_n_speakers - 1
         with torch.cuda.stream(s_compute), L.use_stream(s_compute):
             feats, rows = self.fe.features_flat(dev_audio, ld=self.ld, counts=counts)
-            post, probs, labels = self.model.infer_device(feats, rows, self.max_n_speakers, self.activity_threshold)
+            p = self._plan(rows)
+            total = int(p["rec_off"][-1])
+            post = torch.empty((total, n_att), dtype=torch.float32, device=dev)
+            labels = torch.empty((total, n_att), dtype=torch.uint8, device=dev)
+            perms = self.model.draw_perms(p["lens"], p["order"], dev)       # the driver's draw order
+            probs = []
+            for lens, offs, perm in zip(p["lens"], p["offs"], perms):
+                _, pr, _ = self.model.infer_device(feats, lens, self.max_n_speakers, self.activity_threshold,
+                                                   independent=self.independent, offsets=offs, packed_out=(post, labels),
+                                                   perm_dev=perm)
+                probs.append(pr)
+            probs = probs[0] if len(probs) == 1 else torch.cat(probs)
             if self.gather is not None:
                 self.gather(post)
             if isinstance(dev_audio, torch.Tensor):
                 dev_audio.record_stream(s_compute)
-        B, Tmax, n_att = post.shape
-        key = (B, Tmax, n_att)
-        if slot.get("key") != key:
-            slot.update(key=key,
-                        h_post=torch.empty((B, Tmax, n_att), dtype=torch.float32, pin_memory=True),
-                        h_probs=torch.empty((B, self.max_n_speakers), dtype=torch.float32, pin_memory=True),
-                        h_labels=torch.empty((B, Tmax, n_att), dtype=torch.uint8, pin_memory=True))
+        # results belong to the caller: fresh pinned buffers per batch (the pinned caching allocator recycles a
+        # block only after the copy that last touched it has completed AND the caller dropped the tensor)
+        h_post = torch.empty((total, n_att), dtype=torch.float32, pin_memory=True)
+        h_labels = torch.empty((total, n_att), dtype=torch.uint8, pin_memory=True)
+        h_probs = torch.empty((len(p["chunks"]), self.max_n_speakers), dtype=torch.float32, pin_memory=True)
         self.s_out.wait_stream(s_compute)
         with torch.cuda.stream(self.s_out):
-            slot["h_post"].copy_(post, non_blocking=True)
-            slot["h_probs"].copy_(probs, non_blocking=True)
-            slot["h_labels"].copy_(labels, non_blocking=True)
+            h_post.copy_(post, non_blocking=True)
+            h_probs.copy_(probs, non_blocking=True)
+            h_labels.copy_(labels, non_blocking=True)
             for t in (post, probs, labels):
                 t.record_stream(self.s_out)
             done = torch.cuda.Event()
             done.record(self.s_out)
-        slot["busy"] = done
-        self._pending.append((slot, done, list(rows)))
+        self._pending.append((done, p, h_post, h_probs, h_labels, list(rows)))
 
     def collect(self) -> dict:
-        """Block until the OLDEST submitted batch is on the host and return it."""
-        slot, done, rows = self._pending.popleft()
+        """Block until the OLDEST submitted batch is on the host and return it (see the module docstring)."""
+        done, p, h_post, h_probs, h_labels, rows = self._pending.popleft()
         done.synchronize()
-        below = slot["h_probs"].numpy() < self.attractor_threshold          # models.py:340-343, all rows at once
+        if len(p["buckets"]) > 1:                                  # back to the driver's chunk order
+            h_probs = h_probs[torch.from_numpy(p["inv"])]
+        below = h_probs.numpy() < self.attractor_threshold          # models.py:340-343, all chunks at once
         first = below.argmax(axis=1)
         n_spk = [int(f) if hit else self.max_n_speakers - 1 for f, hit in zip(first, below.any(axis=1))]
-        return dict(posteriors=slot["h_post"], probs=slot["h_probs"], labels=slot["h_labels"],
-                    n_speakers=n_spk, lengths=rows)
+        return dict(posteriors=h_post, probs=h_probs, labels=h_labels, n_speakers=n_spk, lengths=p["lengths"],
+                    chunk_rec=p["chunk_rec"], rec_offsets=p["rec_off"], rec_lengths=rows)
+
+    @staticmethod
+    def t_hats(result: dict) -> List[torch.Tensor]:
+        """Per recording the matrix the driver stores as ``T_hat`` (infer_eda.py:113-124): the chunks' (T, n_spk)
+        posteriors stacked on the time axis.  Like ``np.vstack`` there, it refuses chunks that disagree on n_spk."""
+        out = []
+        off = result["rec_offsets"]
+        for r in range(len(off) - 1):
+            ns = {n for n, cr in zip(result["n_speakers"], result["chunk_rec"]) if cr == r}
+            if len(ns) > 1:
+                raise ValueError(f"recording {r}: chunks decided different speaker counts {sorted(ns)}; the reference's "
+                                 "np.vstack(out_chunks) fails on this too (infer_eda.py:121)")
+            n = ns.pop() if ns else 0
+            out.append(result["posteriors"][int(off[r]):int(off[r + 1]), :n])
+        return out
 
     def run(self, batches: Iterable):
         """Generator over results, keeping ``depth`` batches in flight."""

@@ -218,13 +218,14 @@ def test_pipeline_matches_infer():
         want.append((m.last["posteriors"].cpu(), [int(y.shape[1]) for y in ys], m.last["labels"].cpu()))
     torch.manual_seed(5)
     pipe = InferencePipeline(m, fe, depth=2)
-    got = [dict(posteriors=r["posteriors"].clone(), n=r["n_speakers"], labels=r["labels"].clone(), lengths=r["lengths"])
-           for r in pipe.run(batches)]
+    got = list(pipe.run(batches))
     assert len(got) == 4
     for (wp, wn, wl), g in zip(want, got):
-        assert torch.equal(g["posteriors"], wp) and torch.equal(g["labels"], wl)
-        assert [min(x, 14) for x in g["n"]] == wn
-        assert g["lengths"] == [wp.shape[1]] * 3
+        B, T, n_att = wp.shape
+        # recordings lie back to back on the time axis (np.vstack of infer_eda.py:121); equal lengths here
+        assert torch.equal(g["posteriors"].view(B, T, n_att), wp) and torch.equal(g["labels"].view(B, T, n_att), wl)
+        assert [min(x, 14) for x in g["n_speakers"]] == wn
+        assert g["lengths"] == [T] * 3 and g["rec_offsets"].tolist() == [0, T, 2 * T, 3 * T]
 
 
 def _full_size_model(n_layers, precision):
@@ -237,9 +238,9 @@ def _full_size_model(n_layers, precision):
 
 
 def test_full_size_c2_batch_invariance():
-    """configs[1] at full size (64 x 500 frames, 4 layers) is too slow for the CPU oracle, so parity
-    rests on a size-independent property: a sequence's posteriors do not depend on what else is in
-    the batch.  The full batch must agree with single-sequence runs (same frame shuffle) to well
+    """configs[1] at full size (64 x 500 frames, 4 layers); the comparison with the reference itself is
+    tests/test_gpu_full.py.  Here a size-independent property: a sequence's posteriors do not depend on what
+    else is in the batch.  The full batch must agree with single-sequence runs (same frame shuffle) to well
     inside the parity bar, and the two precisions must agree with each other within it."""
     from oracle.weights import synth_features
     m, cfg = _full_size_model(4, "bf16x3")

@@ -30,7 +30,7 @@ METRIC, UNIT = "eend_eda_train_frames_per_sec", "frames/s"
 
 
 def make_batch(seed: int):
-    from oracle.weights import synth_features, synth_labels      # seeded inputs only (not the oracle path)
+    from speaker_diarization_b200.synth import synth_features, synth_labels      # seeded inputs only (not the oracle path)
     return synth_features([T] * B, IN, seed), synth_labels([T] * B, S, seed)
 
 
@@ -63,7 +63,7 @@ def cpu_reference(n_seq: int, steps: int, warmup: int, threads: int):
 
 def run_ours(args):
     import torch.distributed as dist
-    from oracle.weights import EdaConfig, synth_state_dict
+    from speaker_diarization_b200.synth import EdaConfig, synth_state_dict
     from speaker_diarization_b200 import _lib as L
     from speaker_diarization_b200.eend_eda.models import TransformerEdaModel
     from speaker_diarization_b200.eend_eda.training import NoamAdam

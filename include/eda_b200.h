@@ -63,6 +63,20 @@ int eda_frontend_logmel(const eda_frontend_plan* plan, const void* audio, int au
                         int n_rec, int64_t total_frames,
                         float* logmel, double* colsum, void* stream);
 
+/* The other feature.transform variants that run under the pinned librosa 0.10.2 (feature.py:43-47, 105-116; the
+ * variants that call librosa.filters.mel positionally raise TypeError there and are not reproduced):
+ *   EDA_TRANSFORM_LOGMEL_MN      'logmel23_mn'      = eda_frontend_logmel (out (frames, n_mels), colsum required)
+ *   EDA_TRANSFORM_NONE           None               |Y|                               out (frames, n_fft/2+1)
+ *   EDA_TRANSFORM_LOG            'log'              ln(max(|Y|, 1e-10))               out (frames, n_fft/2+1)
+ *   EDA_TRANSFORM_LOGMEL_ESPNET  'logmel23_espnet'  log10(max(1e-10, |Y| . mel^T))    out (frames, n_mels)
+ * colsum may be NULL except for LOGMEL_MN (the only variant with a mean).  eda_frontend_width = columns of `out`. */
+enum { EDA_TRANSFORM_LOGMEL_MN = 0, EDA_TRANSFORM_NONE = 1, EDA_TRANSFORM_LOG = 2, EDA_TRANSFORM_LOGMEL_ESPNET = 3 };
+int eda_frontend_transform(const eda_frontend_plan* plan, const void* audio, int audio_dtype,
+                           const int64_t* rec_sample_off, const int64_t* rec_frame_off,
+                           int n_rec, int64_t total_frames, int transform,
+                           float* out, double* colsum, void* stream);
+int eda_frontend_width(const eda_frontend_plan* plan, int transform);
+
 /* Pass 2: subtract the recording mean, splice +-context frames (zeros beyond the edges,
  * of the MEAN-NORMALISED signal, exactly like np.pad after transform) and keep every
  * `subsampling`-th row.  feats: (total_rows, ld_feats) fp32 with (2c+1)*n_mels valid
@@ -73,6 +87,13 @@ int eda_frontend_splice_subsample(const eda_frontend_plan* plan, const float* lo
                                   const int64_t* rec_row_off, int n_rec, int64_t total_rows,
                                   int context, int subsampling,
                                   float* feats, int ld_feats, void* stream);
+
+/* Pass 2 for any pass-1 width (feature.splice + [::subsampling] after any transform): src (total_frames, width);
+ * colsum (n_rec, width) fp64 or NULL = no mean removal.                                          */
+int eda_frontend_splice_subsample_w(const float* src, int width, const double* colsum,
+                                    const int64_t* rec_frame_off, const int64_t* rec_row_off, int n_rec,
+                                    int64_t total_rows, int context, int subsampling,
+                                    float* feats, int ld_feats, void* stream);
 
 /* ------------------------------------------------------------------- encoder -----
  * Building blocks of TransformerEdaModel.forward_embedding (models.py:213-234).     */

@@ -46,6 +46,28 @@ def transform_logmel23_mn(Y: np.ndarray, sample_rate: int) -> np.ndarray:
     return (lm - np.mean(lm, axis=0)).astype(np.float32)
 
 
+def transform(Y: np.ndarray, transform_type, sample_rate: int) -> np.ndarray:
+    """R:24-119 for the variants that run under the pinned librosa 0.10.2: None (R:44-45), 'log' (R:46-47),
+    'logmel23_mn' (R:64-73), 'logmel23_espnet' (R:105-116); the others call librosa.filters.mel positionally and
+    raise TypeError there (R:53,61,79,97)."""
+    if transform_type in ("logmel", "logmel23", "logmel23_swn", "logmel23_mvn"):
+        raise TypeError("mel() takes 0 positional arguments but 3 were given")
+    A = np.abs(Y)
+    if not transform_type:
+        out = A
+    elif transform_type == "log":
+        out = np.log(np.maximum(A, 1e-10))
+    elif transform_type == "logmel23_mn":
+        return transform_logmel23_mn(Y, sample_rate)
+    elif transform_type == "logmel23_espnet":
+        n_fft = 2 * (Y.shape[1] - 1)
+        basis = librosa_stub.mel(sr=sample_rate, n_fft=n_fft, n_mels=23, fmin=0, fmax=sample_rate / 2)
+        out = np.log10(np.maximum(1e-10, np.dot(A, basis.T)))
+    else:
+        raise ValueError("Unknown transform_type: %s" % transform_type)
+    return out.astype(np.float32)
+
+
 def splice(Y: np.ndarray, context_size: int = 0) -> np.ndarray:
     """R:130-152 — row t = concat(rows t-c … t+c) with zero rows beyond the edges."""
     T, F = Y.shape

@@ -34,3 +34,22 @@ def rttm_text(sessions, t_hats, threshold=0.5, frame_shift=256, subsampling=1, m
                              (e - s) * frame_shift * subsampling / sampling_rate,
                              session + "_" + str(spkid)), file=wf)                  # :38-42
     return wf.getvalue()
+
+
+def smooth_posteriors(lens, n_spk: int, seed: int):
+    """Seeded random posteriors with realistic segment lengths (moving sums of white noise through a sigmoid),
+    one float32 (T, n_spk) array per recording; shared by the golden generator and the tests."""
+    import torch
+    g = torch.Generator().manual_seed(0x577A + seed)
+    out = []
+    for n in lens:
+        x = torch.randn((n + 16, n_spk), generator=g).cumsum(0)
+        out.append(torch.sigmoid((x[16:] - x[:-16]) / 4.0).contiguous().numpy())
+    out[0][0, 0] = 0.5                  # exactly at the threshold: make_rttm.py:29 uses a strict '>'
+    return out
+
+
+def truth_rttm(session: str, segs) -> str:
+    """Ground-truth RTTM of a synthetic mixture from feature_oracle.synth_audio's (speaker, start s, end s)."""
+    fmt = "SPEAKER {:s} 1 {:7.2f} {:7.2f} <NA> <NA> {:s} <NA> <NA>\n"
+    return "".join(fmt.format(session, st, et - st, f"{session}_true{spk}") for spk, st, et in segs if et > st)

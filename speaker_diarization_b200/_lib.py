@@ -30,6 +30,9 @@ SIGNATURES = {
     "eda_frontend_plan_destroy": (_i, [_p]),
     "eda_frontend_num_frames": (_i64, [_i64, _i]),
     "eda_frontend_logmel": (_i, [_p, _p, _i, _p, _p, _i, _i64, _p, _p, _p]),
+    "eda_frontend_transform": (_i, [_p, _p, _i, _p, _p, _i, _i64, _i, _p, _p, _p]),
+    "eda_frontend_width": (_i, [_p, _i]),
+    "eda_frontend_splice_subsample_w": (_i, [_p, _i, _p, _p, _p, _i, _i64, _i, _i, _p, _i, _p]),
     "eda_frontend_splice_subsample": (_i, [_p, _p, _p, _p, _p, _i, _i64, _i, _i, _p, _i, _p]),
     "eda_pad_pack": (_i, [_p, _p, _p, _i, _i, _i, _f, _p, _i, _p]),
     "eda_linear": (_i, [_p, _i, _p, _i, _p, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),

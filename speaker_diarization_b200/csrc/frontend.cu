@@ -11,7 +11,9 @@
 // into the N/2+1 one-sided bins, squared, and reduced by the 23 Slaney triangles (lane m
 // owns filter m and walks its own bin range in ascending order -> deterministic sums).
 #include <math.h>
+#include <stdlib.h>
 
+#include <type_traits>
 #include <vector>
 
 #include <algorithm>
@@ -28,6 +30,8 @@ struct eda_frontend_plan {
   double* d_melw64;    // packed non-zero weights (as double), filter m at [mel_off[m], mel_off[m+1])
   int* d_mel_off;      // (n_mels + 1)
   int mel_nnz;
+  float* d_melw32;     // the same packed weights as float (what librosa stores), for logmel_t8_kernel
+  double2* d_tw_step;  // (16, 8) W_128^{t * k1} at [k1 * 8 + t]: twiddles between the two FFT steps of logmel_t8_kernel
 };
 
 namespace eda {
@@ -78,7 +82,9 @@ logmel_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_
               int n_fft, int hop, int n_mels, const double* __restrict__ window,
               const double2* __restrict__ tw, const float* __restrict__ melw,
               const int* __restrict__ mel_lo, const int* __restrict__ mel_hi,
-              float* __restrict__ logmel, double* __restrict__ colsum, int frames_per_warp) {
+              float* __restrict__ logmel, double* __restrict__ colsum, int frames_per_warp, int mode) {
+  // mode (EDA_TRANSFORM_*): 0 = log10 mel power (+ column sums), 1 = |Y|, 2 = ln max(|Y|, 1e-10),
+  // 3 = log10 max(1e-10, |Y| . mel^T); modes 1 / 2 write n_bins values per frame
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int M = n_fft >> 1, n_bins = M + 1;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -116,7 +122,7 @@ logmel_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_
 
   for (int64_t f = f_begin; f < f_end; ++f) {
     while (f >= r_f1) {   // crossed into the next recording (empty recordings are skipped)
-      if (lane < n_mels) atomicAdd(colsum + (size_t)rec * n_mels + lane, csum);
+      if (lane < n_mels && mode == 0) atomicAdd(colsum + (size_t)rec * n_mels + lane, csum);
       csum = 0.0;
       ++rec;
       r_f0 = rec_frame_off[rec]; r_f1 = rec_frame_off[rec + 1];
@@ -161,20 +167,24 @@ logmel_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_
         const double2 wo = cmul(s_tw[k], O);
         re = E.x + wo.x; im = E.y + wo.y;
       }
-      pw[k] = re * re + im * im;
+      const double p2 = re * re + im * im;
+      pw[k] = mode == 0 ? p2 : sqrt(p2);             // np.abs(Y) (feature.py:43) for the magnitude transforms
     }
     __syncwarp();
-    if (lane < n_mels) {
+    if (mode == 1 || mode == 2) {                    // feature.py:44-47: |Y| / log(max(|Y|, 1e-10)), n_bins columns
+      for (int k = lane; k <= M; k += 32)
+        logmel[(size_t)f * n_bins + k] = (float)(mode == 1 ? pw[k] : log(fmax(pw[k], 1e-10)));
+    } else if (lane < n_mels) {
       double acc = 0.0;
       const float* wrow = s_melw + (size_t)lane * n_bins;
       for (int k = my_lo; k <= my_hi; ++k) acc += pw[k] * (double)wrow[k];
-      const double v = log10(fmax(acc, 1e-10));
+      const double v = log10(fmax(acc, 1e-10));       // mode 3 = feature.py:105-116 on magnitudes, no mean removal
       logmel[(size_t)f * n_mels + lane] = (float)v;
       csum += v;
     }
     __syncwarp();
   }
-  if (lane < n_mels) atomicAdd(colsum + (size_t)rec * n_mels + lane, csum);
+  if (lane < n_mels && mode == 0) atomicAdd(colsum + (size_t)rec * n_mels + lane, csum);
 }
 
 // ---- pass 1, fast path (n_fft = 256 or 512) ---------------------------------------------
@@ -380,35 +390,351 @@ logmel_fast_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__
   if (lane < n_mels) atomicAdd(colsum + (size_t)rec * n_mels + lane, csum);
 }
 
-// ---- pass 2 ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-splice_kernel(const float* __restrict__ logmel, const double* __restrict__ colsum,
-              const int64_t* __restrict__ rec_frame_off, const int64_t* __restrict__ rec_row_off,
-              int n_rec, int64_t total_rows, int n_mels, int context, int subsampling,
-              float* __restrict__ feats, int ld_feats) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int width = (2 * context + 1) * n_mels;
-  for (int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp; row < total_rows;
-       row += (int64_t)gridDim.x * (blockDim.x >> 5)) {
+
+// ---- pass 1, n_fft = 256 (8 kHz configs): eight threads per frame -----------------------------------------
+// The previous kernel above (one warp per frame, 4 points per lane, five xor-shuffle stages) is bound by the
+// L1 data pipe: every fp64 complex exchange costs four SHFL wavefronts.  Here a frame's M = 128 packed complex
+// points live 16 per thread in 8 threads (a warp advances 4 frames at once):
+//   step 1  thread t holds z[t + 8 j], j = 0..15  ->  16-point FFT in registers  ->  x W_128^{t k1}
+//   transpose through shared memory, ONE pass of 2 KB per frame (STS.128 / LDS.128, xor-swizzled: conflict-free)
+//   step 2  thread u holds column k1 = u and column 16 - u (thread 0: columns 0 and 8)  ->  two 8-point FFTs
+//           = Z[k1 + 16 k2]
+//   real-FFT untangle: the partner of bin u + 16 k2 is bin (16 - u) + 16 (7 - k2) - in the SAME thread, so the
+//           bins k and M - k are finished without another exchange; powers leave as fp32
+//   mel + log10 in fp32 (sum of <= 29 non-negative terms; the result is stored as fp32 anyway): thread t of the
+//           frame's group owns filters t, t + 8, t + 16.
+// All FFT / untangle arithmetic is fp64 like the reference's numpy.
+struct cdx { double x, y; };
+__device__ __forceinline__ cdx operator+(cdx a, cdx b) { return {a.x + b.x, a.y + b.y}; }
+__device__ __forceinline__ cdx operator-(cdx a, cdx b) { return {a.x - b.x, a.y - b.y}; }
+__device__ __forceinline__ cdx mul_mi(cdx a) { return {a.y, -a.x}; }                    // a * (-i)
+__device__ __forceinline__ cdx mul_pi(cdx a) { return {-a.y, a.x}; }                    // a * (+i)
+__device__ __forceinline__ cdx cmulx(cdx a, double wx, double wy) { return {a.x * wx - a.y * wy, a.x * wy + a.y * wx}; }
+
+// 4-point DFT (W_4 = -i), in place, natural order
+__device__ __forceinline__ void dft4(cdx& a0, cdx& a1, cdx& a2, cdx& a3) {
+  const cdx s02 = a0 + a2, d02 = a0 - a2, s13 = a1 + a3, d13 = mul_mi(a1 - a3);
+  a0 = s02 + s13; a2 = s02 - s13; a1 = d02 + d13; a3 = d02 - d13;
+}
+
+// 16-point DIF FFT in registers: slot 4 r + s ends up holding X[r + 4 s]
+__device__ __forceinline__ void fft16(cdx (&a)[16]) {
+  constexpr double c1 = 0.92387953251128675613, s1 = 0.38268343236508977173, h = 0.70710678118654752440;
+#pragma unroll
+  for (int n0 = 0; n0 < 4; ++n0) dft4(a[n0], a[n0 + 4], a[n0 + 8], a[n0 + 12]);        // slot n0 + 4 r = y_r[n0]
+  // twiddles W_16^{n0 r}
+  a[5] = cmulx(a[5], c1, -s1);                                      // W^1
+  a[6] = cdx{(a[6].x + a[6].y) * h, (a[6].y - a[6].x) * h};         // W^2
+  a[7] = cmulx(a[7], s1, -c1);                                      // W^3
+  a[9] = cdx{(a[9].x + a[9].y) * h, (a[9].y - a[9].x) * h};         // W^2
+  a[10] = mul_mi(a[10]);                                            // W^4
+  a[11] = cdx{(a[11].y - a[11].x) * h, -(a[11].x + a[11].y) * h};   // W^6
+  a[13] = cmulx(a[13], s1, -c1);                                    // W^3
+  a[14] = cdx{(a[14].y - a[14].x) * h, -(a[14].x + a[14].y) * h};   // W^6
+  a[15] = cmulx(a[15], -c1, s1);                                    // W^9
+#pragma unroll
+  for (int r = 0; r < 4; ++r) dft4(a[4 * r], a[4 * r + 1], a[4 * r + 2], a[4 * r + 3]);
+}
+
+// 8-point DFT, natural order in and out
+__device__ __forceinline__ void fft8(cdx (&v)[8]) {
+  constexpr double h = 0.70710678118654752440;
+  cdx u0 = v[0] + v[4], u1 = v[1] + v[5], u2 = v[2] + v[6], u3 = v[3] + v[7];
+  cdx d0 = v[0] - v[4], d1 = v[1] - v[5], d2 = mul_mi(v[2] - v[6]), d3 = v[3] - v[7];
+  d1 = cdx{(d1.x + d1.y) * h, (d1.y - d1.x) * h};                   // W_8^1
+  d3 = cdx{(d3.y - d3.x) * h, -(d3.x + d3.y) * h};                  // W_8^3
+  dft4(u0, u1, u2, u3);
+  dft4(d0, d1, d2, d3);
+  v[0] = u0; v[2] = u1; v[4] = u2; v[6] = u3; v[1] = d0; v[3] = d1; v[5] = d2; v[7] = d3;
+}
+
+// Two neighbouring samples x[i0], x[i0 + 1] exactly as they lie in memory: the loads of the NEXT frame are issued
+// while the current one is transformed, so nothing may touch the loaded registers before they are consumed
+// (unpacking a 16-bit pair right after its load made every load a full memory round trip: 47 % of all stall samples).
+template <typename AudioT, bool WORDS> struct RawPair;
+template <> struct RawPair<int16_t, true> {             // every pair is one aligned 32-bit word (all recordings start on even samples, hop even)
+  uint32_t v;
+  __device__ __forceinline__ void load(const int16_t* rec, int64_t i0, int64_t n) {
+    const int16_t* p = rec + i0;
+    v = 0;
+    if (i0 >= 0 && i0 + 1 < n) v = __ldg(reinterpret_cast<const uint32_t*>(p));
+    else if (i0 >= 0 && i0 < n) v = __ldg(reinterpret_cast<const uint16_t*>(p));        // the last sample of an odd-length recording
+  }
+  // 16-bit PCM scaled the way soundfile hands it to the reference (x / 32768, exact in fp64)
+  __device__ __forceinline__ double a() const { return (double)(int)(int16_t)(v & 0xffffu) * (1.0 / 32768.0); }
+  __device__ __forceinline__ double b() const { return (double)((int)v >> 16) * (1.0 / 32768.0); }
+};
+template <> struct RawPair<int16_t, false> {            // general case: two 16-bit loads
+  uint16_t x, y;
+  __device__ __forceinline__ void load(const int16_t* rec, int64_t i0, int64_t n) {
+    x = (i0 >= 0 && i0 < n) ? __ldg(reinterpret_cast<const uint16_t*>(rec + i0)) : (uint16_t)0;
+    y = (i0 + 1 >= 0 && i0 + 1 < n) ? __ldg(reinterpret_cast<const uint16_t*>(rec + i0 + 1)) : (uint16_t)0;
+  }
+  __device__ __forceinline__ double a() const { return (double)(int)(int16_t)x * (1.0 / 32768.0); }
+  __device__ __forceinline__ double b() const { return (double)(int)(int16_t)y * (1.0 / 32768.0); }
+};
+template <bool W> struct RawPair<float, W> {
+  float x, y;
+  __device__ __forceinline__ void load(const float* rec, int64_t i0, int64_t n) {
+    x = (i0 >= 0 && i0 < n) ? __ldg(rec + i0) : 0.f;
+    y = (i0 + 1 >= 0 && i0 + 1 < n) ? __ldg(rec + i0 + 1) : 0.f;
+  }
+  __device__ __forceinline__ double a() const { return (double)x; }
+  __device__ __forceinline__ double b() const { return (double)y; }
+};
+template <bool W> struct RawPair<double, W> {
+  double x, y;
+  __device__ __forceinline__ void load(const double* rec, int64_t i0, int64_t n) {
+    x = (i0 >= 0 && i0 < n) ? __ldg(rec + i0) : 0.0;
+    y = (i0 + 1 >= 0 && i0 + 1 < n) ? __ldg(rec + i0 + 1) : 0.0;
+  }
+  __device__ __forceinline__ double a() const { return x; }
+  __device__ __forceinline__ double b() const { return y; }
+};
+
+constexpr int kT8Warps = 4;                            // warps per CTA
+constexpr int kT8SRow = 128 * 16 + 0;                  // bytes of one frame's transpose buffer
+static size_t logmel_t8_smem(int mel_nnz) {
+  // [window 128 double2][step twiddles 128 double2][W_256^k 128 double2][mel weights float][per warp: 4 frames x (2 KB + 136 floats)]
+  // (a frame's 2592 bytes = 20 x 128 + 32: the four frames of a warp sit 8 banks apart, so their STS.32 of the powers do not collide)
+  return 3 * 2048 + (size_t)((mel_nnz + 31) & ~31) * 4 + (size_t)kT8Warps * 4 * (2048 + 136 * 4);
+}
+
+template <typename AudioT>
+__global__ void __launch_bounds__(kT8Warps * 32, 3)
+logmel_t8_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_sample_off,
+                 const int64_t* __restrict__ rec_frame_off, int n_rec, int64_t total_frames, int hop, int n_mels,
+                 const double* __restrict__ window, const double2* __restrict__ tw_step, const double2* __restrict__ tw256,
+                 const float* __restrict__ melw32, const int* __restrict__ mel_off, const int* __restrict__ mel_lo,
+                 int mel_nnz, float* __restrict__ logmel, double* __restrict__ colsum, int frames_per_warp) {
+  constexpr int M = 128;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double2* s_win = reinterpret_cast<double2*>(smem_raw);                 // (w[2n], w[2n+1])
+  double2* s_step = s_win + 128;                                         // W_128^{t k1} at [k1 * 8 + t]
+  double2* s_tw = s_step + 128;                                          // W_256^k
+  float* s_melw = reinterpret_cast<float*>(s_tw + 128);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, q = lane >> 3, t = lane & 7;
+  unsigned char* wbase = smem_raw + 3 * 2048 + (size_t)((mel_nnz + 31) & ~31) * 4 + (size_t)(warp * 4 + q) * (2048 + 136 * 4);
+  double2* S = reinterpret_cast<double2*>(wbase);                        // this frame's transpose buffer [k1][t ^ (k1 & 7)]
+  float* Pw = reinterpret_cast<float*>(wbase + 2048);                    // this frame's power spectrum (129 floats)
+  for (int i = threadIdx.x; i < 128; i += blockDim.x) {
+    s_win[i] = make_double2(window[2 * i], window[2 * i + 1]);
+    s_step[i] = tw_step[i];
+    s_tw[i] = tw256[i];
+  }
+  for (int i = threadIdx.x; i < mel_nnz; i += blockDim.x) s_melw[i] = melw32[i];
+  __syncthreads();
+  // are all pairs aligned 32-bit words?  (16-bit audio: every recording starts on an even sample and the hop is even)
+  bool words = true;
+  if constexpr (sizeof(AudioT) == 2) {
+    bool ok = (hop & 1) == 0 && (reinterpret_cast<uintptr_t>(audio) & 3) == 0;
+    for (int r = threadIdx.x; r < n_rec; r += blockDim.x) ok = ok && (rec_sample_off[r] & 1) == 0;
+    words = __syncthreads_and(ok);
+  }
+
+  // this thread's mel filters (t, t + 8, t + 16) and untangle roles
+  int m_off[3], m_cnt[3], m_lo[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const int m = t + 8 * r;
+    const bool ok = m < n_mels;
+    m_off[r] = ok ? mel_off[m] : 0; m_cnt[r] = ok ? mel_off[m + 1] - m_off[r] : 0; m_lo[r] = ok ? mel_lo[m] : 0;
+  }
+  const int ka = t, kb = t == 0 ? 8 : 16 - t;                            // the two columns of step 2
+
+  const int64_t gwarp = (int64_t)blockIdx.x * kT8Warps + warp;
+  const int64_t f_begin = gwarp * frames_per_warp;
+  const int64_t f_end = min(total_frames, f_begin + frames_per_warp);
+  if (f_begin >= f_end) return;                                           // warp-uniform
+  // recording of this group's first frame
+  int64_t f = f_begin + q;
+  int rec = 0;
+  {
     int lo = 0, hi = n_rec - 1;
+    const int64_t f0 = min(f, total_frames - 1);
     while (lo < hi) {
-      int mid = (lo + hi + 1) >> 1;
-      if (rec_row_off[mid] <= row) lo = mid; else hi = mid - 1;
+      const int mid = (lo + hi + 1) >> 1;
+      if (rec_frame_off[mid] <= f0) lo = mid; else hi = mid - 1;
     }
-    const int rec = lo;
+    rec = lo;
+  }
+  int64_t r_f0 = rec_frame_off[rec], r_f1 = rec_frame_off[rec + 1];
+  int64_t r_s0 = rec_sample_off[rec], r_n = rec_sample_off[rec + 1] - r_s0;
+  double csum[3] = {0.0, 0.0, 0.0};
+  int rec_acc = rec;                       // the recording csum belongs to
+
+  auto flush = [&]() {
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      if (t + 8 * r < n_mels && csum[r] != 0.0) atomicAdd(colsum + (size_t)rec_acc * n_mels + t + 8 * r, csum[r]);
+      csum[r] = 0.0;
+    }
+  };
+
+  auto run = [&](auto words_tag) {
+  constexpr bool WORDS = decltype(words_tag)::value;
+  RawPair<AudioT, WORDS> raw[16] = {};
+  auto load_raw = [&](int64_t ff) {        // z[n] = x[2n] + i x[2n+1], n = t + 8 j; center=True: padded position 0 = sample -M
+    const int64_t s_start = (ff - r_f0) * hop - M + 2 * t;
+    const AudioT* rec_audio = audio + r_s0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) raw[j].load(rec_audio, s_start + 16 * j, r_n);
+  };
+  // fetch(ff): advance this group's recording to the one holding frame ff and load its samples
+  auto fetch = [&](int64_t ff) -> bool {
+    if (ff >= f_end) return false;
+    while (ff >= r_f1) {                                   // crossed into the next recording (empty ones are skipped)
+      ++rec;
+      r_f0 = rec_frame_off[rec]; r_f1 = rec_frame_off[rec + 1];
+      r_s0 = rec_sample_off[rec]; r_n = rec_sample_off[rec + 1] - r_s0;
+    }
+    load_raw(ff);
+    return true;
+  };
+
+  bool active_next = fetch(f_begin + q);
+  for (int64_t fb = f_begin; fb < f_end; fb += 4) {       // warp-uniform loop; f = fb + q is this group's frame
+    f = fb + q;
+    const bool active = active_next;
+    const int rec_cur = rec;                               // recording of the frame whose samples are in `raw`
+    cdx a[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const double2 w = s_win[t + 8 * j];
+      a[j] = active ? cdx{raw[j].a() * w.x, raw[j].b() * w.y} : cdx{0.0, 0.0};
+    }
+    active_next = fetch(f + 4);                            // the next frame's samples travel while this one is transformed
+    fft16(a);
+    // slot 4 r + s = Y_t[k1], k1 = r + 4 s;  x W_128^{t k1};  S[k1][t ^ (k1 & 7)]
+    __syncwarp();                                          // the previous iteration's readers of S / Pw are done
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int s2 = 0; s2 < 4; ++s2) {
+        const int k1 = r + 4 * s2;
+        cdx y = a[4 * r + s2];
+        if (k1 > 0) { const double2 w = s_step[k1 * 8 + t]; y = cmulx(y, w.x, w.y); }
+        S[k1 * 8 + (t ^ (k1 & 7))] = make_double2(y.x, y.y);
+      }
+    __syncwarp();
+    cdx za[8], zb[8];
+#pragma unroll
+    for (int n2 = 0; n2 < 8; ++n2) {
+      const double2 va = S[ka * 8 + (n2 ^ (ka & 7))], vb = S[kb * 8 + (n2 ^ (kb & 7))];
+      za[n2] = cdx{va.x, va.y}; zb[n2] = cdx{vb.x, vb.y};
+    }
+    fft8(za);                                              // za[k2] = Z[ka + 16 k2]
+    fft8(zb);                                              // zb[k2] = Z[kb + 16 k2]
+    // untangle pairs (lower bin k, partner bin M - k).  Threads 1..7: (za[i], zb[7 - i]), k = t + 16 i.
+    // Thread 0 (columns 0 and 8): (za[1], za[7]), (za[2], za[6]), (za[3], za[5]), (za[4], za[4]), (zb[i], zb[7 - i]) i = 0..3,
+    // plus the purely real bins 0 and M from za[0].
+    const bool t0 = t == 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      cdx zk, zm;
+      int k;
+      if (i < 4) {
+        zk = t0 ? za[i + 1] : za[i];
+        zm = t0 ? za[7 - i] : zb[7 - i];
+        k = t0 ? 16 * (i + 1) : t + 16 * i;
+      } else {
+        zk = t0 ? zb[i - 4] : za[i];
+        zm = t0 ? zb[11 - i] : zb[7 - i];
+        k = t0 ? 8 + 16 * (i - 4) : t + 16 * i;
+      }
+      const cdx E = {zk.x + zm.x, zk.y - zm.y};            // Z[k] + conj(Z[M-k])
+      const cdx D = {zk.x - zm.x, zk.y + zm.y};            // Z[k] - conj(Z[M-k])
+      const double2 w = s_tw[k];
+      const cdx T = cmulx(mul_mi(D), w.x, w.y);
+      const cdx pp = E + T, qq = E - T;
+      Pw[k] = (float)(0.25 * (pp.x * pp.x + pp.y * pp.y));
+      Pw[M - k] = (float)(0.25 * (qq.x * qq.x + qq.y * qq.y));
+    }
+    if (t0) {
+      const double sre = za[0].x + za[0].y, dre = za[0].x - za[0].y;
+      Pw[0] = (float)(sre * sre);
+      Pw[M] = (float)(dre * dre);
+    }
+    __syncwarp();
+    // mel projection + log10 (fp32): filters t, t + 8, t + 16 of this group's frame
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      float acc = 0.f;
+      const float* wrow = s_melw + m_off[r];
+      const float* prow = Pw + m_lo[r];
+      for (int i = 0; i < m_cnt[r]; ++i) acc = fmaf(prow[i], wrow[i], acc);
+      if (active && t + 8 * r < n_mels) {
+        if (r == 0 && rec_cur != rec_acc) { flush(); rec_acc = rec_cur; }
+        const float v = log10f(fmaxf(acc, 1e-10f));
+        logmel[(size_t)f * n_mels + t + 8 * r] = v;
+        csum[r] += (double)v;
+      }
+    }
+  }
+  flush();
+  };                                                       // run
+  if (words) run(std::true_type{}); else run(std::false_type{});
+}
+
+// ---- pass 2 ---------------------------------------------------------------------------
+// Row t of the output = frames t*sub - c .. t*sub + c of the (mean-normalised) pass-1 matrix side by side: since that
+// matrix is (frames, width) row-major, the (2c+1)*width values are ONE contiguous run of it (zeros where the run leaves
+// the recording).  A warp copies a run with coalesced loads and stores; the per-column means of the recording (colsum /
+// frames, fp64 like np.mean) sit in shared memory per CTA, which handles consecutive rows (almost always one recording).
+// colsum == nullptr: no mean removal (transforms other than logmel23_mn).
+__global__ void __launch_bounds__(256)
+splice_kernel(const float* __restrict__ src, const double* __restrict__ colsum,
+              const int64_t* __restrict__ rec_frame_off, const int64_t* __restrict__ rec_row_off,
+              int n_rec, int64_t total_rows, int width, int context, int subsampling,
+              float* __restrict__ feats, int ld_feats, int rows_per_cta) {
+  extern __shared__ double s_mean[];                   // (width) of the recording of the CTA's first row
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t row_begin = (int64_t)blockIdx.x * rows_per_cta;
+  const int64_t row_end = min(total_rows, row_begin + rows_per_cta);
+  if (row_begin >= row_end) return;
+  int lo = 0, hi = n_rec - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (rec_row_off[mid] <= row_begin) lo = mid; else hi = mid - 1;
+  }
+  const int rec0 = lo;
+  if (colsum) {
+    const double inv_n0 = 1.0 / (double)max((int64_t)1, rec_frame_off[rec0 + 1] - rec_frame_off[rec0]);
+    for (int m = threadIdx.x; m < width; m += blockDim.x) s_mean[m] = colsum[(size_t)rec0 * width + m] * inv_n0;
+  }
+  __syncthreads();
+  const int span = (2 * context + 1) * width;
+  for (int64_t row = row_begin + warp; row < row_end; row += blockDim.x >> 5) {
+    int rec = rec0;
+    while (row >= rec_row_off[rec + 1]) ++rec;           // rows ascend: at most a few steps
     const int64_t f0 = rec_frame_off[rec], nfr = rec_frame_off[rec + 1] - f0;
     const int64_t t = (row - rec_row_off[rec]) * subsampling;
-    const double inv_n = 1.0 / (double)nfr;
+    const int64_t e0 = (t - context) * width, e1 = nfr * width;       // run = elements [e0, e0 + span) of this recording
+    const float* base = src + f0 * width;
     float* dst = feats + row * (int64_t)ld_feats;
-    for (int c = lane; c < ld_feats; c += 32) {
-      float v = 0.f;
-      if (c < width) {
-        const int j = c / n_mels, m = c - j * n_mels;
-        const int64_t src = t - context + j;
-        if (src >= 0 && src < nfr)
-          v = (float)((double)__ldg(logmel + (f0 + src) * n_mels + m) - colsum[(size_t)rec * n_mels + m] * inv_n);
+    const bool same = rec == rec0;
+    const double inv_n = 1.0 / (double)max((int64_t)1, nfr);
+    const int step = 32 % width;
+    int m = lane % width;                                 // column of element e0 + c within its frame: (c mod width), e0 = 0 mod width
+    // four independent loads in flight per lane before the first store (the kernel is latency-, not bandwidth-bound)
+    for (int c0 = lane; c0 < ld_feats; c0 += 128) {
+      float x[4];
+      bool ok[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int c = c0 + 32 * u;
+        const int64_t e = e0 + c;
+        ok[u] = c < span && e >= 0 && e < e1;
+        x[u] = ok[u] ? __ldg(base + e) : 0.f;
       }
-      dst[c] = v;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int c = c0 + 32 * u;
+        float v = x[u];
+        if (ok[u] && colsum) v = (float)((double)x[u] - (same ? s_mean[m] : colsum[(size_t)rec * width + m] * inv_n));
+        if (c < ld_feats) dst[c] = v;
+        m += step; if (m >= width) m -= width;
+      }
     }
   }
 }
@@ -465,6 +791,19 @@ int eda_frontend_plan_create(int sample_rate, int frame_size, int frame_shift, i
   EDA_CUDA(cudaMalloc(&p->d_mel_off, sizeof(int) * (n_mels + 1)));
   EDA_CUDA(cudaMemcpy(p->d_melw64, w64.data(), sizeof(double) * w64.size(), cudaMemcpyHostToDevice));
   EDA_CUDA(cudaMemcpy(p->d_mel_off, woff.data(), sizeof(int) * (n_mels + 1), cudaMemcpyHostToDevice));
+  {
+    std::vector<float> w32(w64.begin(), w64.end());                    // the float32 values librosa stores
+    EDA_CUDA(cudaMalloc(&p->d_melw32, sizeof(float) * std::max<size_t>(1, w32.size())));
+    EDA_CUDA(cudaMemcpy(p->d_melw32, w32.data(), sizeof(float) * w32.size(), cudaMemcpyHostToDevice));
+    std::vector<double2> st(128);                                      // W_128^{t k1} at [k1 * 8 + t] (logmel_t8_kernel)
+    for (int k1 = 0; k1 < 16; ++k1)
+      for (int t = 0; t < 8; ++t) {
+        const double a = -2.0 * kPi * (double)((t * k1) % 128) / 128.0;
+        st[k1 * 8 + t] = make_double2(cos(a), sin(a));
+      }
+    EDA_CUDA(cudaMalloc(&p->d_tw_step, sizeof(double2) * 128));
+    EDA_CUDA(cudaMemcpy(p->d_tw_step, st.data(), sizeof(double2) * 128, cudaMemcpyHostToDevice));
+  }
   EDA_CUDA(cudaMalloc(&p->d_window, sizeof(double) * n_fft));
   EDA_CUDA(cudaMalloc(&p->d_tw, sizeof(double2) * (n_fft / 2)));
   EDA_CUDA(cudaMalloc(&p->d_melw, sizeof(float) * melw.size()));
@@ -479,6 +818,12 @@ int eda_frontend_plan_create(int sample_rate, int frame_size, int frame_shift, i
   EDA_CUDA(cudaFuncSetAttribute(logmel_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   EDA_CUDA(cudaFuncSetAttribute(logmel_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   EDA_CUDA(cudaFuncSetAttribute(logmel_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  if (n_fft == 256) {
+    const int tsm = (int)logmel_t8_smem(p->mel_nnz);
+    EDA_CUDA(cudaFuncSetAttribute(logmel_t8_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, tsm));
+    EDA_CUDA(cudaFuncSetAttribute(logmel_t8_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, tsm));
+    EDA_CUDA(cudaFuncSetAttribute(logmel_t8_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, tsm));
+  }
   if (n_fft == 256 || n_fft == 512) {
     const int M = n_fft / 2;
     const int fsm = (int)logmel_fast_smem(M, p->mel_nnz);
@@ -496,34 +841,54 @@ int eda_frontend_plan_create(int sample_rate, int frame_size, int frame_shift, i
 int eda_frontend_plan_destroy(eda_frontend_plan* p) {
   if (!p) return EDA_OK;
   cudaFree(p->d_window); cudaFree(p->d_tw); cudaFree(p->d_melw); cudaFree(p->d_mel_lo); cudaFree(p->d_mel_hi);
-  cudaFree(p->d_melw64); cudaFree(p->d_mel_off);
+  cudaFree(p->d_melw64); cudaFree(p->d_mel_off); cudaFree(p->d_melw32); cudaFree(p->d_tw_step);
   delete p;
   return EDA_OK;
 }
 
-int eda_frontend_logmel(const eda_frontend_plan* p, const void* audio, int audio_dtype,
-                        const int64_t* rec_sample_off, const int64_t* rec_frame_off, int n_rec,
-                        int64_t total_frames, float* logmel, double* colsum, void* stream) {
+int eda_frontend_transform(const eda_frontend_plan* p, const void* audio, int audio_dtype,
+                           const int64_t* rec_sample_off, const int64_t* rec_frame_off, int n_rec,
+                           int64_t total_frames, int transform, float* out, double* colsum, void* stream) {
   using namespace eda;
-  EDA_REQUIRE(p && audio && logmel && colsum && n_rec > 0, "eda_frontend_logmel: bad arguments");
+  EDA_REQUIRE(p && audio && out && n_rec > 0, "eda_frontend_transform: bad arguments");
+  EDA_REQUIRE(transform >= EDA_TRANSFORM_LOGMEL_MN && transform <= EDA_TRANSFORM_LOGMEL_ESPNET, "eda_frontend_transform: unknown transform %d", transform);
+  EDA_REQUIRE(transform != EDA_TRANSFORM_LOGMEL_MN || colsum, "eda_frontend_transform: logmel23_mn needs colsum");
   cudaStream_t st = (cudaStream_t)stream;
-  EDA_CUDA(cudaMemsetAsync(colsum, 0, sizeof(double) * (size_t)n_rec * p->n_mels, st));
+  if (transform == EDA_TRANSFORM_LOGMEL_MN) EDA_CUDA(cudaMemsetAsync(colsum, 0, sizeof(double) * (size_t)n_rec * p->n_mels, st));
   if (total_frames == 0) return EDA_OK;
+  EDA_REQUIRE(audio_dtype >= EDA_AUDIO_F32 && audio_dtype <= EDA_AUDIO_I16, "eda_frontend_transform: unknown audio dtype %d", audio_dtype);
+  const char* force = getenv("EDA_B200_FRONTEND");         // "warp" = the one-warp-per-frame kernel (A/B measurements)
+  if (transform == EDA_TRANSFORM_LOGMEL_MN && p->n_fft == 256 && p->n_mels <= 24 && !(force && force[0] == 'w')) {
+    // eight threads per frame, four frames per warp step; contiguous runs of frames per warp, ~2 waves of 12 warps per SM
+    const int64_t target_warps = (int64_t)num_sms() * 12 * 2;
+    int64_t fpw = std::max<int64_t>(4, ceil_div<int64_t>(total_frames, target_warps));
+    fpw = (fpw + 3) / 4 * 4;
+    const int64_t n_warps = ceil_div<int64_t>(total_frames, fpw);
+    const int blocks = (int)ceil_div<int64_t>(n_warps, kT8Warps);
+    const size_t smem = logmel_t8_smem(p->mel_nnz);
+#define EDA_T8(T)                                                                                                        \
+  logmel_t8_kernel<T><<<blocks, kT8Warps * 32, smem, st>>>((const T*)audio, rec_sample_off, rec_frame_off, n_rec,         \
+      total_frames, p->frame_shift, p->n_mels, p->d_window, p->d_tw_step, p->d_tw, p->d_melw32, p->d_mel_off, p->d_mel_lo, \
+      p->mel_nnz, out, colsum, (int)fpw)
+    if (audio_dtype == EDA_AUDIO_F64) EDA_T8(double); else if (audio_dtype == EDA_AUDIO_I16) EDA_T8(int16_t); else EDA_T8(float);
+#undef EDA_T8
+    EDA_LAUNCH_CHECK();
+    return EDA_OK;
+  }
   // contiguous runs of frames per warp (amortises the recording lookup and the atomics);
   // aim for >= 4 waves of 8-warp CTAs on the device
   const int64_t target_warps = (int64_t)num_sms() * 8 * 8;
   int fpw = (int)std::max<int64_t>(1, std::min<int64_t>(64, total_frames / target_warps));
   const int64_t n_warps = ceil_div<int64_t>(total_frames, fpw);
   const int blocks = (int)ceil_div<int64_t>(n_warps, 8);
-  EDA_REQUIRE(audio_dtype >= EDA_AUDIO_F32 && audio_dtype <= EDA_AUDIO_I16, "eda_frontend_logmel: unknown audio dtype %d", audio_dtype);
-  if (p->n_fft == 256 || p->n_fft == 512) {
-    // fast path: register-resident FFT, shuffles across lanes
+  if (transform == EDA_TRANSFORM_LOGMEL_MN && (p->n_fft == 256 || p->n_fft == 512)) {
+    // register-resident FFT, shuffles across lanes
     const int M = p->n_fft / 2;
     const size_t smem = logmel_fast_smem(M, p->mel_nnz);
 #define EDA_FAST(R, T)                                                                                      \
   logmel_fast_kernel<R, T><<<blocks, 256, smem, st>>>((const T*)audio, rec_sample_off, rec_frame_off, n_rec, \
       total_frames, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw64, p->d_mel_off, p->d_mel_lo, \
-      p->mel_nnz, logmel, colsum, fpw)
+      p->mel_nnz, out, colsum, fpw)
     if (p->n_fft == 256) {
       if (audio_dtype == EDA_AUDIO_F64) EDA_FAST(4, double); else if (audio_dtype == EDA_AUDIO_I16) EDA_FAST(4, int16_t); else EDA_FAST(4, float);
     } else {
@@ -536,9 +901,41 @@ int eda_frontend_logmel(const eda_frontend_plan* p, const void* audio, int audio
   const size_t smem = logmel_smem(p->n_fft, p->n_mels);
 #define EDA_GEN(T)                                                                                                \
   logmel_kernel<T><<<blocks, 256, smem, st>>>((const T*)audio, rec_sample_off, rec_frame_off, n_rec, total_frames, \
-      p->n_fft, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw, p->d_mel_lo, p->d_mel_hi, logmel, colsum, fpw)
+      p->n_fft, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw, p->d_mel_lo, p->d_mel_hi, out, colsum, fpw, transform)
   if (audio_dtype == EDA_AUDIO_F64) EDA_GEN(double); else if (audio_dtype == EDA_AUDIO_I16) EDA_GEN(int16_t); else EDA_GEN(float);
 #undef EDA_GEN
+  EDA_LAUNCH_CHECK();
+  return EDA_OK;
+}
+
+int eda_frontend_logmel(const eda_frontend_plan* p, const void* audio, int audio_dtype,
+                        const int64_t* rec_sample_off, const int64_t* rec_frame_off, int n_rec,
+                        int64_t total_frames, float* logmel, double* colsum, void* stream) {
+  EDA_REQUIRE(colsum, "eda_frontend_logmel: bad arguments");
+  return eda_frontend_transform(p, audio, audio_dtype, rec_sample_off, rec_frame_off, n_rec, total_frames,
+                                EDA_TRANSFORM_LOGMEL_MN, logmel, colsum, stream);
+}
+
+int eda_frontend_width(const eda_frontend_plan* p, int transform) {
+  if (!p) return 0;
+  return (transform == EDA_TRANSFORM_NONE || transform == EDA_TRANSFORM_LOG) ? p->n_bins : p->n_mels;
+}
+
+int eda_frontend_splice_subsample_w(const float* src, int width, const double* colsum, const int64_t* rec_frame_off,
+                                    const int64_t* rec_row_off, int n_rec, int64_t total_rows, int context,
+                                    int subsampling, float* feats, int ld_feats, void* stream) {
+  using namespace eda;
+  EDA_REQUIRE(src && feats && n_rec > 0 && subsampling > 0 && context >= 0 && width > 0, "eda_frontend_splice_subsample: bad arguments");
+  EDA_REQUIRE(ld_feats >= (2 * context + 1) * width, "eda_frontend_splice_subsample: ld_feats too small");
+  EDA_REQUIRE(width <= 4096, "eda_frontend_splice_subsample: width too large");
+  if (total_rows == 0) return EDA_OK;
+  // consecutive rows per CTA (one recording's means in shared memory), ~4 CTAs per SM
+  const int64_t want = ceil_div<int64_t>(total_rows, (int64_t)num_sms() * 4);
+  const int rows_per_cta = (int)std::max<int64_t>(8, std::min<int64_t>(64, (want + 7) / 8 * 8));
+  const int blocks = (int)ceil_div<int64_t>(total_rows, rows_per_cta);
+  splice_kernel<<<blocks, 256, sizeof(double) * width, (cudaStream_t)stream>>>(src, colsum, rec_frame_off, rec_row_off, n_rec,
+                                                                              total_rows, width, context, subsampling, feats,
+                                                                              ld_feats, rows_per_cta);
   EDA_LAUNCH_CHECK();
   return EDA_OK;
 }
@@ -547,15 +944,9 @@ int eda_frontend_splice_subsample(const eda_frontend_plan* p, const float* logme
                                   const int64_t* rec_frame_off, const int64_t* rec_row_off, int n_rec,
                                   int64_t total_rows, int context, int subsampling, float* feats,
                                   int ld_feats, void* stream) {
-  using namespace eda;
-  EDA_REQUIRE(p && logmel && colsum && feats && n_rec > 0 && subsampling > 0 && context >= 0, "eda_frontend_splice_subsample: bad arguments");
-  EDA_REQUIRE(ld_feats >= (2 * context + 1) * p->n_mels, "eda_frontend_splice_subsample: ld_feats too small");
-  if (total_rows == 0) return EDA_OK;
-  const int blocks = (int)std::min<int64_t>(ceil_div<int64_t>(total_rows, 8), (int64_t)num_sms() * 16);
-  splice_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(logmel, colsum, rec_frame_off, rec_row_off, n_rec, total_rows,
-                                                           p->n_mels, context, subsampling, feats, ld_feats);
-  EDA_LAUNCH_CHECK();
-  return EDA_OK;
+  EDA_REQUIRE(p && colsum, "eda_frontend_splice_subsample: bad arguments");
+  return eda_frontend_splice_subsample_w(logmel, p->n_mels, colsum, rec_frame_off, rec_row_off, n_rec, total_rows, context,
+                                         subsampling, feats, ld_feats, stream);
 }
 
 }  // extern "C"

@@ -30,10 +30,25 @@ Array = Union[np.ndarray, torch.Tensor]
 # reference (kaldi_data.py:82), so shipping int16 halves / quarters the host->device bytes.
 _AUDIO_DTYPES = {torch.float32: 0, torch.float64: 1, torch.int16: 2}
 
+# feature.transform variants (feature.py:43-47, 64-73, 105-116) -> EDA_TRANSFORM_* of include/eda_b200.h.  The
+# other names ('logmel', 'logmel23', 'logmel23_swn', 'logmel23_mvn') call librosa.filters.mel positionally, which
+# raises TypeError under the librosa==0.10.2 the reference pins (requirements.txt:15): they raise here as well.
+_TRANSFORMS = {"logmel23_mn": 0, None: 1, "": 1, "log": 2, "logmel23_espnet": 3}
+_POSITIONAL_MEL = ("logmel", "logmel23", "logmel23_swn", "logmel23_mvn")
+
+
+def _transform_id(transform_type):
+    if transform_type in _POSITIONAL_MEL:
+        raise TypeError(f"transform_type={transform_type!r}: mel() takes 0 positional arguments but 3 were given "
+                        "(feature.py calls librosa.filters.mel positionally for this variant; librosa>=0.10 rejects it)")
+    if transform_type not in _TRANSFORMS:
+        raise ValueError("Unknown transform_type: %s" % transform_type)           # feature.py:118
+    return _TRANSFORMS[transform_type]
+
 
 def get_input_dim(frame_size: int, context_size: int, transform_type: str) -> int:
     """feature.py:10-21."""
-    if transform_type.startswith("logmel23"):
+    if transform_type and transform_type.startswith("logmel23"):
         width = 23
     else:
         width = (1 << (frame_size - 1).bit_length()) // 2 + 1
@@ -49,9 +64,11 @@ class FrontEnd:
     """Batched ``stft -> logmel23_mn -> splice -> subsample`` on one CUDA device."""
 
     def __init__(self, sample_rate: int = 8000, frame_size: int = 200, frame_shift: int = 80,
-                 context_size: int = 7, subsampling: int = 10, n_mels: int = 23, device="cuda"):
+                 context_size: int = 7, subsampling: int = 10, n_mels: int = 23, device="cuda",
+                 transform_type="logmel23_mn"):
         self.sample_rate, self.frame_size, self.frame_shift = sample_rate, frame_size, frame_shift
         self.context_size, self.subsampling, self.n_mels = context_size, subsampling, n_mels
+        self.transform_type, self.transform = transform_type, _transform_id(transform_type)
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise L.EdaError("speaker_diarization_b200 has no CPU path")
@@ -59,6 +76,7 @@ class FrontEnd:
         self._off_cache = {}
         with torch.cuda.device(self.device):
             L.call("eda_frontend_plan_create", sample_rate, frame_size, frame_shift, n_mels, C.byref(self._plan))
+        self.width = int(L.load().eda_frontend_width(self._plan, self.transform))     # columns of the pass-1 matrix
 
     def __del__(self):
         try:
@@ -70,7 +88,7 @@ class FrontEnd:
 
     @property
     def feat_dim(self) -> int:
-        return (2 * self.context_size + 1) * self.n_mels
+        return (2 * self.context_size + 1) * self.width
 
     # ------------------------------------------------------------------ batching ------
     def _stage(self, recs, counts=None):
@@ -116,16 +134,16 @@ class FrontEnd:
         return offs, frames, rows
 
     def logmel(self, recs, counts=None):
-        """Pass 1.  Returns (logmel (total_frames, n_mels) fp32, colsum (n_rec, n_mels) fp64,
-        staging tuple)."""
+        """Pass 1 = stft + transform before the mean removal.  Returns (matrix (total_frames, width) fp32,
+        colsum (n_rec, width) fp64 - per-recording column sums, 'logmel23_mn' only, else None -, staging tuple)."""
         with torch.cuda.device(self.device):
             audio, is_f64, offs, frames, rows = self._stage(recs, counts)
             n_rec = len(frames)
             total = int(sum(frames))
-            lm = torch.empty((total, self.n_mels), dtype=torch.float32, device=self.device)
-            colsum = torch.empty((n_rec, self.n_mels), dtype=torch.float64, device=self.device)
-            L.call("eda_frontend_logmel", self._plan, L.ptr(audio), int(is_f64), L.ptr(offs[0]), L.ptr(offs[1]),
-                   n_rec, total, L.ptr(lm), L.ptr(colsum), L.stream())
+            lm = torch.empty((total, self.width), dtype=torch.float32, device=self.device)
+            colsum = torch.empty((n_rec, self.width), dtype=torch.float64, device=self.device) if self.transform == 0 else None
+            L.call("eda_frontend_transform", self._plan, L.ptr(audio), int(is_f64), L.ptr(offs[0]), L.ptr(offs[1]),
+                   n_rec, total, self.transform, L.ptr(lm), L.ptr(colsum), L.stream())
         return lm, colsum, (offs, frames, rows)
 
     def features(self, recs, ld: int = 0, counts=None) -> List[torch.Tensor]:
@@ -146,7 +164,7 @@ class FrontEnd:
         total_rows = int(sum(rows))
         with torch.cuda.device(self.device):
             feats = torch.empty((total_rows, ld), dtype=torch.float32, device=self.device)
-            L.call("eda_frontend_splice_subsample", self._plan, L.ptr(lm), L.ptr(colsum), L.ptr(offs[1]),
+            L.call("eda_frontend_splice_subsample_w", L.ptr(lm), self.width, L.ptr(colsum), L.ptr(offs[1]),
                    L.ptr(offs[2]), len(rows), total_rows, self.context_size, self.subsampling,
                    L.ptr(feats), ld, L.stream())
         return feats[:, : self.feat_dim], rows
@@ -159,9 +177,8 @@ def extract(data: Array, frame_size: int = 200, frame_shift: int = 80, transform
             sample_rate: int = 8000, context_size: int = 7, subsampling: int = 10, device="cuda") -> torch.Tensor:
     """One recording through ``stft -> transform -> splice -> [::subsampling]``
     (infer_eda.py:94-98) -> (T, 345) fp32 CUDA tensor."""
-    if transform_type != "logmel23_mn":
-        raise NotImplementedError("only 'logmel23_mn' (the transform every conf/eend_eda yaml uses)")
-    key = (sample_rate, frame_size, frame_shift, context_size, subsampling, str(device))
+    key = (sample_rate, frame_size, frame_shift, context_size, subsampling, str(device), transform_type)
     if key not in _frontends:
-        _frontends[key] = FrontEnd(sample_rate, frame_size, frame_shift, context_size, subsampling, device=device)
+        _frontends[key] = FrontEnd(sample_rate, frame_size, frame_shift, context_size, subsampling, device=device,
+                                   transform_type=transform_type)
     return _frontends[key].features([data])[0]

@@ -157,3 +157,85 @@ def test_pipeline_results_stay_valid_and_order_is_kept():
         assert torch.equal(r["posteriors"], s[0]) and torch.equal(r["labels"], s[1]) and torch.equal(r["probs"], s[2])
         assert torch.equal(r["posteriors"], a["posteriors"])     # same seed, same batches -> same results
         assert sum(r["lengths"]) == r["posteriors"].shape[0] and r["chunk_rec"][0] == 0
+
+
+# ---- RTTM post-processing pinned to the unmodified bin/make_rttm.py (tests/golden/rttm.json) --------------------
+def _rttm_golden():
+    import json, os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "rttm.json")) as f:
+        return json.load(f)
+
+
+def _kw(args):
+    kw = dict(threshold=0.5, frame_shift=256, subsampling=1, median=1, sampling_rate=16000)
+    for k, v in zip(args[::2], args[1::2]):
+        kw[k.lstrip("-")] = float(v) if k == "--threshold" else int(v)
+    return kw
+
+
+@pytest.mark.parametrize("name", ["smooth_default", "smooth_med11_8k", "smooth_thr_med5"])
+def test_device_rttm_equals_unmodified_make_rttm(name):
+    import io
+    from oracle.rttm_oracle import smooth_posteriors
+    from speaker_diarization_b200 import rttm
+    c = _rttm_golden()[name]
+    arrs = [torch.from_numpy(a).cuda() for a in smooth_posteriors(c["lens"], c["n_spk"], c["seed"])]
+    kw = _kw(c["args"])
+    wf = io.StringIO()
+    rttm.make_rttm(wf, c["sessions"], arrs, kw["threshold"], kw["frame_shift"], kw["subsampling"], kw["median"], kw["sampling_rate"])
+    assert wf.getvalue() == c["text"]
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_audio_to_rttm_equals_reference_driver_plus_make_rttm(precision, manifest):
+    """The whole chain on the device - int16 PCM -> front end -> chunked EEND-EDA -> threshold / median / segments -> RTTM
+    text - against infer_eda.py + bin/make_rttm.py, both run unmodified (golden).  Identical RTTM text means an
+    identical md-eval DER (frozen next to the text: tests/test_rttm_cpu.py::test_md_eval_der_loop).  fp32: identical
+    text.  bf16x3: one label of 150 100 differs (see the module docstring), which may move segment boundaries of one
+    speaker by one frame: at most 2 RTTM lines differ, i.e. 0.1 s of 4 440 s - far inside the 0.1 % DER bar."""
+    import io
+    from speaker_diarization_b200 import rttm
+    case, g, sd, recs = driver_case("full_c4_counts", manifest)
+    names, res, t_hats = _pipeline_run(case, g, sd, recs, precision)
+    c = _rttm_golden()["c4_driver"]
+    kw = _kw(c["args"])
+    wf = io.StringIO()
+    rttm.make_rttm(wf, names, [t.cuda() for t in t_hats], kw["threshold"], kw["frame_shift"], kw["subsampling"], kw["median"],
+                   kw["sampling_rate"])
+    mine, want = wf.getvalue().splitlines(), c["text"].splitlines()
+    if precision == "fp32":
+        assert mine == want
+    else:
+        diff = set(mine) ^ set(want)
+        assert len(diff) <= 4, sorted(diff)[:8]
+
+
+# ---- the other feature.transform variants (SURVEY 8f n3; goldens: oracle/make_golden_transforms.py) -------------
+@pytest.mark.parametrize("name", ["tf_none_8k", "tf_log_8k", "tf_log_8k_f32", "tf_espnet_8k", "tf_espnet_16k"])
+def test_transform_variants_match_reference(name):
+    import json
+    from conftest import load_golden
+    from oracle import feature_oracle as fo
+    from speaker_diarization_b200 import feature
+    g = load_golden("fe_transforms")
+    c = json.loads(str(g["meta"]))[name]
+    x, _ = fo.synth_audio(c["n_samples"], c["sample_rate"], 2, c["seed"], dtype=np.dtype(c["dtype"]).type)
+    fe = feature.FrontEnd(c["sample_rate"], c["frame_size"], c["frame_shift"], 7, 10, transform_type=c["transform_type"])
+    Y, colsum, _ = fe.logmel([x])
+    want = g[name + "/Y"]
+    assert tuple(Y.shape) == want.shape and colsum is None
+    # float64 audio: the reference runs in float64 and rounds once; float32 audio: the reference itself is complex64
+    tol = 2e-5 if c["dtype"] == "float64" else 2e-3
+    if c["transform_type"] in (None, ""):
+        assert np.abs(Y.cpu().numpy() - want).max() <= tol * max(1.0, float(np.abs(want).max()))
+    else:
+        # a log of a tiny magnitude amplifies the last-bit differences of |Y|: compare where the reference is above its floor
+        ok = want > np.log(1e-6) if c["transform_type"] == "log" else want > -5.5
+        assert np.abs(Y.cpu().numpy() - want)[ok].max() <= tol and ok.mean() > 0.95
+    feats = feature.extract(x, c["frame_size"], c["frame_shift"], c["transform_type"], c["sample_rate"], 7, 10)
+    assert tuple(feats.shape) == g[name + "/feats"].shape
+    assert torch.equal(feats, fe.features([x])[0])
+    with pytest.raises(TypeError):
+        feature.extract(x, c["frame_size"], c["frame_shift"], "logmel23_mvn", c["sample_rate"], 7, 10)
+    with pytest.raises(ValueError):
+        feature.extract(x, c["frame_size"], c["frame_shift"], "mfcc", c["sample_rate"], 7, 10)

@@ -92,3 +92,26 @@ def test_feature_oracle_matches_reference(name, manifest):
     feats = fo.frontend(x, case["sample_rate"], case["frame_size"], case["frame_shift"])
     np.testing.assert_allclose(feats, g["feats"], atol=1e-6, rtol=0)
     assert feats.shape[1] == fo.get_input_dim(case["frame_size"], 7, "logmel23_mn") == 345
+
+
+def _transform_cases():
+    import json
+    g = load_golden("fe_transforms")
+    return g, json.loads(str(g["meta"]))
+
+
+@pytest.mark.parametrize("name", ["tf_none_8k", "tf_log_8k", "tf_log_8k_f32", "tf_espnet_8k", "tf_espnet_16k"])
+def test_transform_variants_oracle_matches_reference(name):
+    g, meta = _transform_cases()
+    c = meta[name]
+    x, _ = fo.synth_audio(c["n_samples"], c["sample_rate"], 2, c["seed"], dtype=np.dtype(c["dtype"]).type)
+    Y = fo.transform(fo.stft(x, c["frame_size"], c["frame_shift"]), c["transform_type"], c["sample_rate"])
+    assert Y.dtype == np.float32 and Y.shape == g[name + "/Y"].shape
+    np.testing.assert_allclose(Y, g[name + "/Y"], atol=1e-6, rtol=1e-6)
+    feats = np.ascontiguousarray(fo.splice(Y, 7)[::10])
+    np.testing.assert_allclose(feats, g[name + "/feats"], atol=1e-6, rtol=1e-6)
+    if c["transform_type"]:
+        assert feats.shape[1] == fo.get_input_dim(c["frame_size"], 7, c["transform_type"]) == c["input_dim"]
+    assert set(meta["_positional_mel_variants_raise"].values()) == {"TypeError"}
+    with pytest.raises(TypeError):
+        fo.transform(fo.stft(x, c["frame_size"], c["frame_shift"]), "logmel23_mvn", c["sample_rate"])

@@ -29,3 +29,56 @@ def test_rttm_text_format_and_order():
     assert lines[0] == "SPEAKER a 1    0.20    0.30 <NA> <NA> a_0 <NA> <NA>"
     assert lines[1] == "SPEAKER a 1    0.70    0.30 <NA> <NA> a_1 <NA> <NA>"
     assert lines[2].startswith("SPEAKER b 1") and len(lines) == 4
+
+
+# ---- pinned to the UNMODIFIED bin/make_rttm.py (tests/golden/rttm.json, oracle/make_golden_rttm.py) ----------
+import json
+import os
+
+import pytest
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _rttm_golden():
+    with open(os.path.join(GOLD, "rttm.json")) as f:
+        return json.load(f)
+
+
+def _kw(args):
+    kw = dict(threshold=0.5, frame_shift=256, subsampling=1, median=1, sampling_rate=16000)
+    for k, v in zip(args[::2], args[1::2]):
+        kw[k.lstrip("-")] = float(v) if k == "--threshold" else int(v)
+    return kw
+
+
+@pytest.mark.parametrize("name", ["smooth_default", "smooth_med11_8k", "smooth_thr_med5"])
+def test_oracle_text_equals_unmodified_make_rttm(name):
+    c = _rttm_golden()[name]
+    arrs = R.smooth_posteriors(c["lens"], c["n_spk"], c["seed"])
+    assert R.rttm_text(c["sessions"], arrs, **_kw(c["args"])) == c["text"]
+
+
+def test_oracle_text_on_the_reference_drivers_t_hat():
+    c = _rttm_golden()["c4_driver"]
+    g = np.load(os.path.join(GOLD, "full_c4_counts.npz"))
+    assert R.rttm_text(c["sessions"], [g["T_hat_" + s] for s in c["sessions"]], **_kw(c["args"])) == c["text"]
+
+
+def test_md_eval_der_loop():
+    """make_rttm -> md-eval.pl -c 0.25.  The scorer is the reference's vendored NIST perl
+    script (third party, not copied into this repo): runs only where /root/reference exists."""
+    from oracle import make_golden_rttm as M
+    if not os.path.exists(M.MD_EVAL):
+        pytest.skip("md-eval.pl lives in /root/reference (build container only)")
+    c = _rttm_golden()["c4_driver"]
+    with open(os.path.join(GOLD, "manifest.json")) as f:
+        truth = M.c4_truth(json.load(f))
+    der = M.md_eval(truth, c["text"])
+    assert der == c["md_eval_der_percent"]
+    # an identical RTTM scores identically; one segment moved by one 0.1 s frame stays far inside 0.1 % abs
+    lines = c["text"].splitlines()
+    f = lines[5].split()
+    f[3] = f"{float(f[3]) + 0.1:.2f}"
+    moved = "\n".join(lines[:5] + [" ".join(f)] + lines[6:]) + "\n"
+    assert abs(M.md_eval(truth, moved) - der) < 0.1

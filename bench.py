@@ -343,7 +343,7 @@ def run_ours(args):
             roof["lstm"] = dict(bound="latency (T sequential steps)", achieved=round(lstm_bytes / (lstm_ms * 1e-3) / 1e9, 1),
                                 peak=pk["hbm"], unit="GB/s", frac=round(lstm_bytes / (lstm_ms * 1e-3) / 1e9 / pk["hbm"], 4),
                                 us_per_step=round(lstm_ms * 1e3 / (T + MAXSPK), 3))
-        fe_ms = sum(m for k in ("eda_frontend_logmel", "eda_frontend_splice_subsample") for m, _ in prof[k])
+        fe_ms = sum(m for k in ("eda_frontend_transform", "eda_frontend_splice_subsample_w") for m, _ in prof[k])
         fe_bytes = B * T * (4 * SHIFT * SUB + 4 * IN)            # 4580 B / model frame @8 kHz
         roof["frontend"] = dict(bound="hbm", achieved=round(fe_bytes / (fe_ms * 1e-3) / 1e9, 1), peak=pk["hbm"],
                                 unit="GB/s", frac=round(fe_bytes / (fe_ms * 1e-3) / 1e9 / pk["hbm"], 4))

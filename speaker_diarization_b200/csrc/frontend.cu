@@ -687,7 +687,7 @@ splice_kernel(const float* __restrict__ src, const double* __restrict__ colsum,
               const int64_t* __restrict__ rec_frame_off, const int64_t* __restrict__ rec_row_off,
               int n_rec, int64_t total_rows, int width, int context, int subsampling,
               float* __restrict__ feats, int ld_feats, int rows_per_cta) {
-  extern __shared__ double s_mean[];                   // (width) of the recording of the CTA's first row
+  extern __shared__ float2 s_mean[];                   // (width) column means of the recording of the CTA's first row, as hi + lo floats
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t row_begin = (int64_t)blockIdx.x * rows_per_cta;
   const int64_t row_end = min(total_rows, row_begin + rows_per_cta);
@@ -700,7 +700,11 @@ splice_kernel(const float* __restrict__ src, const double* __restrict__ colsum,
   const int rec0 = lo;
   if (colsum) {
     const double inv_n0 = 1.0 / (double)max((int64_t)1, rec_frame_off[rec0 + 1] - rec_frame_off[rec0]);
-    for (int m = threadIdx.x; m < width; m += blockDim.x) s_mean[m] = colsum[(size_t)rec0 * width + m] * inv_n0;
+    for (int m = threadIdx.x; m < width; m += blockDim.x) {
+      const double mu = colsum[(size_t)rec0 * width + m] * inv_n0;       // np.mean in fp64
+      const float hi_ = (float)mu;
+      s_mean[m] = make_float2(hi_, (float)(mu - (double)hi_));
+    }
   }
   __syncthreads();
   const int span = (2 * context + 1) * width;
@@ -731,7 +735,13 @@ splice_kernel(const float* __restrict__ src, const double* __restrict__ colsum,
       for (int u = 0; u < 4; ++u) {
         const int c = c0 + 32 * u;
         float v = x[u];
-        if (ok[u] && colsum) v = (float)((double)x[u] - (same ? s_mean[m] : colsum[(size_t)rec * width + m] * inv_n));
+        if (ok[u] && colsum) {
+          // x - mean with the mean as two floats: the difference is rounded to fp32 anyway and x already is an fp32
+          // rounding of the fp64 log-mel value, so (x - hi) - lo loses nothing against converting to fp64 first
+          // (the F2F.F64.F32 conversions were 26 % of this kernel's stall samples)
+          if (same) { const float2 mu = s_mean[m]; v = (x[u] - mu.x) - mu.y; }
+          else v = (float)((double)x[u] - colsum[(size_t)rec * width + m] * inv_n);
+        }
         if (c < ld_feats) dst[c] = v;
         m += step; if (m >= width) m -= width;
       }
@@ -930,10 +940,10 @@ int eda_frontend_splice_subsample_w(const float* src, int width, const double* c
   EDA_REQUIRE(width <= 4096, "eda_frontend_splice_subsample: width too large");
   if (total_rows == 0) return EDA_OK;
   // consecutive rows per CTA (one recording's means in shared memory), ~4 CTAs per SM
-  const int64_t want = ceil_div<int64_t>(total_rows, (int64_t)num_sms() * 4);
+  const int64_t want = ceil_div<int64_t>(total_rows, (int64_t)num_sms() * 16);
   const int rows_per_cta = (int)std::max<int64_t>(8, std::min<int64_t>(64, (want + 7) / 8 * 8));
   const int blocks = (int)ceil_div<int64_t>(total_rows, rows_per_cta);
-  splice_kernel<<<blocks, 256, sizeof(double) * width, (cudaStream_t)stream>>>(src, colsum, rec_frame_off, rec_row_off, n_rec,
+  splice_kernel<<<blocks, 256, sizeof(float2) * width, (cudaStream_t)stream>>>(src, colsum, rec_frame_off, rec_row_off, n_rec,
                                                                               total_rows, width, context, subsampling, feats,
                                                                               ld_feats, rows_per_cta);
   EDA_LAUNCH_CHECK();

@@ -77,6 +77,16 @@ int eda_frontend_transform(const eda_frontend_plan* plan, const void* audio, int
                            float* out, double* colsum, void* stream);
 int eda_frontend_width(const eda_frontend_plan* plan, int transform);
 
+/* eda_frontend_logmel for a SLICE of a recording (chunk-level sharding of one long recording over several GPUs,
+ * SURVEY 8e): the log-mel rows of all frames of every "recording" handed in are written, but only frames
+ * [sum_range[2r], sum_range[2r+1]) (indices within recording r) enter colsum - the slice's halo frames, which another
+ * rank owns, do not.  The ranks then add their colsum and frame counts (one 24-double all-reduce) to obtain the
+ * recording-wide mean feature.py:72-73 takes.                                                          */
+int eda_frontend_logmel_ranges(const eda_frontend_plan* plan, const void* audio, int audio_dtype,
+                               const int64_t* rec_sample_off, const int64_t* rec_frame_off,
+                               const int64_t* sum_range, int n_rec, int64_t total_frames,
+                               float* logmel, double* colsum, void* stream);
+
 /* Pass 2: subtract the recording mean, splice +-context frames (zeros beyond the edges,
  * of the MEAN-NORMALISED signal, exactly like np.pad after transform) and keep every
  * `subsampling`-th row.  feats: (total_rows, ld_feats) fp32 with (2c+1)*n_mels valid

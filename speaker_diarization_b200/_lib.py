@@ -31,6 +31,7 @@ SIGNATURES = {
     "eda_frontend_num_frames": (_i64, [_i64, _i]),
     "eda_frontend_logmel": (_i, [_p, _p, _i, _p, _p, _i, _i64, _p, _p, _p]),
     "eda_frontend_transform": (_i, [_p, _p, _i, _p, _p, _i, _i64, _i, _p, _p, _p]),
+    "eda_frontend_logmel_ranges": (_i, [_p, _p, _i, _p, _p, _p, _i, _i64, _p, _p, _p]),
     "eda_frontend_width": (_i, [_p, _i]),
     "eda_frontend_splice_subsample_w": (_i, [_p, _i, _p, _p, _p, _i, _i64, _i, _i, _p, _i, _p]),
     "eda_frontend_splice_subsample": (_i, [_p, _p, _p, _p, _p, _i, _i64, _i, _i, _p, _i, _p]),

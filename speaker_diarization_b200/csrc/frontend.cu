@@ -82,7 +82,8 @@ logmel_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_
               int n_fft, int hop, int n_mels, const double* __restrict__ window,
               const double2* __restrict__ tw, const float* __restrict__ melw,
               const int* __restrict__ mel_lo, const int* __restrict__ mel_hi,
-              float* __restrict__ logmel, double* __restrict__ colsum, int frames_per_warp, int mode) {
+              float* __restrict__ logmel, double* __restrict__ colsum, int frames_per_warp, int mode,
+              const int64_t* __restrict__ sum_range) {
   // mode (EDA_TRANSFORM_*): 0 = log10 mel power (+ column sums), 1 = |Y|, 2 = ln max(|Y|, 1e-10),
   // 3 = log10 max(1e-10, |Y| . mel^T); modes 1 / 2 write n_bins values per frame
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -180,7 +181,7 @@ logmel_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_
       for (int k = my_lo; k <= my_hi; ++k) acc += pw[k] * (double)wrow[k];
       const double v = log10(fmax(acc, 1e-10));       // mode 3 = feature.py:105-116 on magnitudes, no mean removal
       logmel[(size_t)f * n_mels + lane] = (float)v;
-      csum += v;
+      if (!sum_range || (f - r_f0 >= sum_range[2 * rec] && f - r_f0 < sum_range[2 * rec + 1])) csum += v;
     }
     __syncwarp();
   }
@@ -234,7 +235,7 @@ logmel_fast_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__
                    int n_mels, const double* __restrict__ window, const double2* __restrict__ tw,
                    const double* __restrict__ melw64, const int* __restrict__ mel_off,
                    const int* __restrict__ mel_lo, int mel_nnz, float* __restrict__ logmel,
-                   double* __restrict__ colsum, int frames_per_warp) {
+                   double* __restrict__ colsum, int frames_per_warp, const int64_t* __restrict__ sum_range) {
   constexpr int M = 32 * R, NFFT = 2 * M, RB = R == 8 ? 3 : 2, FB = kLogmelGroup;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   // layout: [tw: M double2][melw: mel_nnz double (padded to even)][per-warp: M double2 + FB x (M+2) double]
@@ -380,7 +381,7 @@ logmel_fast_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__
         if (fb < nfb) {
           const double v = log10(fmax(acc[fb], 1e-10));
           logmel[(size_t)(f + fb) * n_mels + lane] = (float)v;
-          csum += v;
+          if (!sum_range || (f + fb - r_f0 >= sum_range[2 * rec] && f + fb - r_f0 < sum_range[2 * rec + 1])) csum += v;
         }
       }
     }
@@ -506,7 +507,8 @@ logmel_t8_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ r
                  const int64_t* __restrict__ rec_frame_off, int n_rec, int64_t total_frames, int hop, int n_mels,
                  const double* __restrict__ window, const double2* __restrict__ tw_step, const double2* __restrict__ tw256,
                  const float* __restrict__ melw32, const int* __restrict__ mel_off, const int* __restrict__ mel_lo,
-                 int mel_nnz, float* __restrict__ logmel, double* __restrict__ colsum, int frames_per_warp) {
+                 int mel_nnz, float* __restrict__ logmel, double* __restrict__ colsum, int frames_per_warp,
+                 const int64_t* __restrict__ sum_range) {
   constexpr int M = 128;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double2* s_win = reinterpret_cast<double2*>(smem_raw);                 // (w[2n], w[2n+1])
@@ -597,6 +599,7 @@ logmel_t8_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ r
     f = fb + q;
     const bool active = active_next;
     const int rec_cur = rec;                               // recording of the frame whose samples are in `raw`
+    const int64_t fl_cur = f - r_f0;                       // its index within that recording
     cdx a[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
@@ -667,7 +670,7 @@ logmel_t8_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ r
         if (r == 0 && rec_cur != rec_acc) { flush(); rec_acc = rec_cur; }
         const float v = log10f(fmaxf(acc, 1e-10f));
         logmel[(size_t)f * n_mels + t + 8 * r] = v;
-        csum[r] += (double)v;
+        if (!sum_range || (fl_cur >= sum_range[2 * rec_cur] && fl_cur < sum_range[2 * rec_cur + 1])) csum[r] += (double)v;
       }
     }
   }
@@ -856,9 +859,10 @@ int eda_frontend_plan_destroy(eda_frontend_plan* p) {
   return EDA_OK;
 }
 
-int eda_frontend_transform(const eda_frontend_plan* p, const void* audio, int audio_dtype,
-                           const int64_t* rec_sample_off, const int64_t* rec_frame_off, int n_rec,
-                           int64_t total_frames, int transform, float* out, double* colsum, void* stream) {
+static int frontend_transform(const eda_frontend_plan* p, const void* audio, int audio_dtype,
+                              const int64_t* rec_sample_off, const int64_t* rec_frame_off, int n_rec,
+                              int64_t total_frames, int transform, float* out, double* colsum,
+                              const int64_t* sum_range, void* stream) {
   using namespace eda;
   EDA_REQUIRE(p && audio && out && n_rec > 0, "eda_frontend_transform: bad arguments");
   EDA_REQUIRE(transform >= EDA_TRANSFORM_LOGMEL_MN && transform <= EDA_TRANSFORM_LOGMEL_ESPNET, "eda_frontend_transform: unknown transform %d", transform);
@@ -879,7 +883,7 @@ int eda_frontend_transform(const eda_frontend_plan* p, const void* audio, int au
 #define EDA_T8(T)                                                                                                        \
   logmel_t8_kernel<T><<<blocks, kT8Warps * 32, smem, st>>>((const T*)audio, rec_sample_off, rec_frame_off, n_rec,         \
       total_frames, p->frame_shift, p->n_mels, p->d_window, p->d_tw_step, p->d_tw, p->d_melw32, p->d_mel_off, p->d_mel_lo, \
-      p->mel_nnz, out, colsum, (int)fpw)
+      p->mel_nnz, out, colsum, (int)fpw, sum_range)
     if (audio_dtype == EDA_AUDIO_F64) EDA_T8(double); else if (audio_dtype == EDA_AUDIO_I16) EDA_T8(int16_t); else EDA_T8(float);
 #undef EDA_T8
     EDA_LAUNCH_CHECK();
@@ -898,7 +902,7 @@ int eda_frontend_transform(const eda_frontend_plan* p, const void* audio, int au
 #define EDA_FAST(R, T)                                                                                      \
   logmel_fast_kernel<R, T><<<blocks, 256, smem, st>>>((const T*)audio, rec_sample_off, rec_frame_off, n_rec, \
       total_frames, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw64, p->d_mel_off, p->d_mel_lo, \
-      p->mel_nnz, out, colsum, fpw)
+      p->mel_nnz, out, colsum, fpw, sum_range)
     if (p->n_fft == 256) {
       if (audio_dtype == EDA_AUDIO_F64) EDA_FAST(4, double); else if (audio_dtype == EDA_AUDIO_I16) EDA_FAST(4, int16_t); else EDA_FAST(4, float);
     } else {
@@ -911,11 +915,26 @@ int eda_frontend_transform(const eda_frontend_plan* p, const void* audio, int au
   const size_t smem = logmel_smem(p->n_fft, p->n_mels);
 #define EDA_GEN(T)                                                                                                \
   logmel_kernel<T><<<blocks, 256, smem, st>>>((const T*)audio, rec_sample_off, rec_frame_off, n_rec, total_frames, \
-      p->n_fft, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw, p->d_mel_lo, p->d_mel_hi, out, colsum, fpw, transform)
+      p->n_fft, p->frame_shift, p->n_mels, p->d_window, p->d_tw, p->d_melw, p->d_mel_lo, p->d_mel_hi, out, colsum, fpw, transform, sum_range)
   if (audio_dtype == EDA_AUDIO_F64) EDA_GEN(double); else if (audio_dtype == EDA_AUDIO_I16) EDA_GEN(int16_t); else EDA_GEN(float);
 #undef EDA_GEN
   EDA_LAUNCH_CHECK();
   return EDA_OK;
+}
+
+int eda_frontend_transform(const eda_frontend_plan* p, const void* audio, int audio_dtype,
+                           const int64_t* rec_sample_off, const int64_t* rec_frame_off, int n_rec,
+                           int64_t total_frames, int transform, float* out, double* colsum, void* stream) {
+  return frontend_transform(p, audio, audio_dtype, rec_sample_off, rec_frame_off, n_rec, total_frames, transform, out,
+                            colsum, nullptr, stream);
+}
+
+int eda_frontend_logmel_ranges(const eda_frontend_plan* p, const void* audio, int audio_dtype,
+                               const int64_t* rec_sample_off, const int64_t* rec_frame_off, const int64_t* sum_range,
+                               int n_rec, int64_t total_frames, float* logmel, double* colsum, void* stream) {
+  EDA_REQUIRE(colsum && sum_range, "eda_frontend_logmel_ranges: bad arguments");
+  return frontend_transform(p, audio, audio_dtype, rec_sample_off, rec_frame_off, n_rec, total_frames,
+                            EDA_TRANSFORM_LOGMEL_MN, logmel, colsum, sum_range, stream);
 }
 
 int eda_frontend_logmel(const eda_frontend_plan* p, const void* audio, int audio_dtype,

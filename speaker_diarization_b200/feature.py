@@ -133,7 +133,7 @@ class FrontEnd:
         offs = torch.from_numpy(off).to(self.device, non_blocking=True)
         return offs, frames, rows
 
-    def logmel(self, recs, counts=None):
+    def logmel(self, recs, counts=None, sum_ranges=None):
         """Pass 1 = stft + transform before the mean removal.  Returns (matrix (total_frames, width) fp32,
         colsum (n_rec, width) fp64 - per-recording column sums, 'logmel23_mn' only, else None -, staging tuple)."""
         with torch.cuda.device(self.device):
@@ -142,9 +142,28 @@ class FrontEnd:
             total = int(sum(frames))
             lm = torch.empty((total, self.width), dtype=torch.float32, device=self.device)
             colsum = torch.empty((n_rec, self.width), dtype=torch.float64, device=self.device) if self.transform == 0 else None
-            L.call("eda_frontend_transform", self._plan, L.ptr(audio), int(is_f64), L.ptr(offs[0]), L.ptr(offs[1]),
-                   n_rec, total, self.transform, L.ptr(lm), L.ptr(colsum), L.stream())
+            if sum_ranges is not None:
+                # slices of recordings (chunk-level sharding): only frames [lo, hi) of each slice enter colsum
+                assert self.transform == 0 and len(sum_ranges) == n_rec
+                rng = torch.tensor([[int(a), int(b)] for a, b in sum_ranges], dtype=torch.int64).to(self.device)
+                L.call("eda_frontend_logmel_ranges", self._plan, L.ptr(audio), int(is_f64), L.ptr(offs[0]), L.ptr(offs[1]),
+                       L.ptr(rng), n_rec, total, L.ptr(lm), L.ptr(colsum), L.stream())
+            else:
+                L.call("eda_frontend_transform", self._plan, L.ptr(audio), int(is_f64), L.ptr(offs[0]), L.ptr(offs[1]),
+                       n_rec, total, self.transform, L.ptr(lm), L.ptr(colsum), L.stream())
         return lm, colsum, (offs, frames, rows)
+
+    def splice(self, lm: torch.Tensor, colsum, offs, rows, ld: int = 0) -> torch.Tensor:
+        """Pass 2 on a pass-1 matrix: mean removal (colsum / frames per recording; None = none), +-context splice,
+        every ``subsampling``-th row.  Returns (sum rows, feat_dim) fp32 (row stride ``ld`` if given)."""
+        ld = ld or self.feat_dim
+        total_rows = int(sum(rows))
+        with torch.cuda.device(self.device):
+            feats = torch.empty((total_rows, ld), dtype=torch.float32, device=self.device)
+            L.call("eda_frontend_splice_subsample_w", L.ptr(lm), self.width, L.ptr(colsum), L.ptr(offs[1]),
+                   L.ptr(offs[2]), len(rows), total_rows, self.context_size, self.subsampling,
+                   L.ptr(feats), ld, L.stream())
+        return feats[:, : self.feat_dim]
 
     def features(self, recs, ld: int = 0, counts=None) -> List[torch.Tensor]:
         """The whole chain for a batch of recordings: list of (ceil(frames/sub), feat_dim)
@@ -160,14 +179,7 @@ class FrontEnd:
         """Same, as ONE (sum rows, feat_dim) view (row stride ``ld``) plus the row count of each
         recording -- the form ``TransformerEdaModel.infer_device`` consumes without a copy."""
         lm, colsum, (offs, frames, rows) = self.logmel(recs, counts)
-        ld = ld or self.feat_dim
-        total_rows = int(sum(rows))
-        with torch.cuda.device(self.device):
-            feats = torch.empty((total_rows, ld), dtype=torch.float32, device=self.device)
-            L.call("eda_frontend_splice_subsample_w", L.ptr(lm), self.width, L.ptr(colsum), L.ptr(offs[1]),
-                   L.ptr(offs[2]), len(rows), total_rows, self.context_size, self.subsampling,
-                   L.ptr(feats), ld, L.stream())
-        return feats[:, : self.feat_dim], rows
+        return self.splice(lm, colsum, offs, rows, ld), rows
 
 
 _frontends = {}

@@ -250,3 +250,43 @@ def test_transform_variants_match_reference(name):
         feature.extract(x, c["frame_size"], c["frame_shift"], "logmel23_mvn", c["sample_rate"], 7, 10)
     with pytest.raises(ValueError):
         feature.extract(x, c["frame_size"], c["frame_shift"], "mfcc", c["sample_rate"], 7, 10)
+
+
+# ---- chunk-level sharding of one long recording: ranks emulated one after the other on one GPU --------
+@pytest.mark.parametrize("world", [2, 4])
+def test_chunk_level_sharding_reproduces_the_reference_driver(world, manifest):
+    """The 30-minute recording of full_c4_counts split over `world` ranks by CHUNKS: every rank runs the front end on its
+    slice of the audio (+ halo), the recording-wide mel mean comes from the sum of the ranks' partial sums (the 24-value
+    all-reduce, here the sum of the emulated ranks' vectors), and each rank diarizes its own chunks with the frame
+    shuffles the single-process driver would have drawn.  Stitched together = the reference driver's T_hat."""
+    from speaker_diarization_b200 import feature
+    from speaker_diarization_b200.sharding import diarize_sharded_recording, plan_chunk_shards
+    case, g, sd, recs = driver_case("full_c4_counts", manifest)
+    rec = case["rec_order"][0]
+    pcm = torch.from_numpy(recs[rec])
+    want = g["T_hat_" + rec]
+    m = _model(sd, case["n_layers"], "bf16x3")
+    fe = feature.FrontEnd(case["rate"], case["frame_size"], case["frame_shift"], 7, 10)
+    plan = plan_chunk_shards(len(pcm), case["frame_shift"], 256, 10, 2000, world)
+    parts = []
+    for sh in plan:                                   # what each rank contributes to the all-reduce
+        a0, a1 = sh["samples"]
+        _, colsum, _ = fe.logmel([pcm[a0:a1]], sum_ranges=[sh["sum_range"]])
+        parts.append(torch.cat([colsum[0], torch.tensor([float(sh["frames"][1] - sh["frames"][0])], dtype=torch.float64, device="cuda")]))
+    total = torch.stack(parts).sum(0)
+    assert int(total[-1].item()) == plan[0]["n_frames"]
+    outs, n_spk = [], []
+    for rank in range(world):
+        torch.set_rng_state(torch.from_numpy(g["rng_state"]))          # every rank replays the driver's draws
+        post, probs, labels, sh = diarize_sharded_recording(m, fe, pcm, rank, world, allreduce=lambda part: total.clone())
+        outs.append(post.cpu())
+        below = probs.cpu().numpy() < 0.5
+        n_spk += [int(b.argmax()) if b.any() else 14 for b in below]
+    t_hat = torch.cat(outs).numpy()
+    assert t_hat.shape[0] == want.shape[0] and set(n_spk) == {want.shape[1]} and len(n_spk) == 9
+    assert float(np.abs(t_hat[:, : want.shape[1]] - want).max()) <= POST_TOL["bf16x3"]
+    # and the sharded front end alone equals the whole-recording front end
+    whole = fe.features([pcm])[0]
+    from speaker_diarization_b200.sharding import shard_features
+    mine = torch.cat([shard_features(fe, pcm, sh, allreduce=lambda part: total.clone()) for sh in plan])
+    assert tuple(mine.shape) == tuple(whole.shape) and float((mine - whole).abs().max()) < 2e-6

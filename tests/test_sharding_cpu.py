@@ -95,3 +95,68 @@ def test_training_gradient_allreduce_world2_gloo():
         assert p.exitcode == 0
     assert res == [True, True]
     assert torch.equal(allreduce_mean_(torch.ones(3)), torch.ones(3))     # no process group: untouched
+
+
+# ------------------------------------------------------ chunk-level sharding of one recording ----------
+def test_chunk_shard_plan_partitions_the_recording():
+    from speaker_diarization_b200.sharding import HALO_FRAMES, plan_chunk_shards, stft_frames
+    for n, hop, n_fft, world in [(8000 * 1800, 80, 256, 4), (8000 * 430 + 2400, 80, 256, 2), (16000 * 480 + 911, 160, 512, 8),
+                                 (8000 * 20, 80, 256, 3), (79, 80, 256, 2)]:
+        plan = plan_chunk_shards(n, hop, n_fft, 10, 2000, world)
+        nf = stft_frames(n, hop)
+        assert [p["frames"][0] for p in plan][0] == 0 and plan[-1]["frames"][1] == nf
+        assert all(a["frames"][1] == b["frames"][0] and a["rows"][1] == b["rows"][0] and a["chunks"][1] == b["chunks"][0]
+                   for a, b in zip(plan, plan[1:]))                       # frames / rows / chunks: each exactly once
+        assert sum(sum(p["chunk_lens"]) for p in plan) == plan[0]["rows_total"] == (nf + 9) // 10
+        for p in plan:
+            a0, a1 = p["samples"]
+            assert 0 <= a0 <= a1 <= n and p["lead"] in (0, HALO_FRAMES)
+            assert (p["lead"] == 0) == (p["frames"][0] == 0 or p["rows"][1] == p["rows"][0])
+            if p["rows"][1] > p["rows"][0]:
+                # every frame the rank reads (own frames +- 7) has all its samples inside the slice or beyond the TRUE ends
+                lo, hi = max(0, p["frames"][0] - 7), min(nf, p["frames"][1] + 7)
+                assert max(0, lo * hop - n_fft // 2) >= a0 and min(n, (hi - 1) * hop + n_fft // 2) <= a1
+
+
+def _slice_worker(rank, world, port, n, q):
+    """Each rank runs the chunk-level front end on ITS slice with the oracle's numpy arithmetic standing in for the
+    kernels and the real gloo all-reduce for the mean; the rows must equal those of the whole-recording front end."""
+    import numpy as np
+    from oracle import feature_oracle as fo
+    from speaker_diarization_b200.sharding import allreduce_sum_, plan_chunk_shards
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        x, _ = fo.synth_audio(n, 8000, 2, 77, dtype=np.float64)
+        whole = fo.frontend(x, 8000, 200, 80, 7, 10)
+        sh = plan_chunk_shards(n, 80, 256, 10, 500, world)[rank]
+        a0, a1 = sh["samples"]
+        lm = fo.logmel23(fo.stft(x[a0:a1], 200, 80), 8000)                       # slice as if it were a recording
+        lo, hi = sh["sum_range"]
+        part = torch.from_numpy(np.concatenate([lm[lo:hi].sum(0), [float(hi - lo)]]))
+        tot = allreduce_sum_(part)                                                # the path's one data collective
+        mean = (tot[:-1] / tot[-1]).numpy()
+        feats = np.ascontiguousarray(fo.splice((lm - mean).astype(np.float32), 7)[::10])
+        k = sh["lead_rows"]
+        R0, R1 = sh["rows"]
+        mine = feats[k:k + R1 - R0]
+        q.put((rank, float(tot[-1]), bool(mine.shape == whole[R0:R1].shape), float(np.abs(mine - whole[R0:R1]).max()) if R1 > R0 else 0.0))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_chunk_level_front_end_world2_gloo():
+    from speaker_diarization_b200.sharding import stft_frames
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    n = 8000 * 130 + 333                                   # 13005 frames -> 1301 rows -> 3 chunks of 500 (2 + 1)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_slice_worker, args=(r, 2, port, n, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=180) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, count, shape_ok, err in res:
+        assert count == stft_frames(n, 80) and shape_ok and err < 2e-6, (rank, count, shape_ok, err)

@@ -424,9 +424,17 @@ def main():
     ap.add_argument("--depth", type=int, default=3, help="batches in flight in the pipeline")
     ap.add_argument("--compute-streams", type=int, default=3, help="compute streams the pipeline alternates batches over")
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg (profiling runs)")
-    ap.add_argument("--workload", default="infer", choices=["infer", "train"],
-                    help="infer = configs[1] (the headline metric); train = configs[4] training step (bench_train.py)")
+    ap.add_argument("--workload", default="infer", choices=["infer", "train", "c3", "c4"],
+                    help="infer = configs[1] (the headline metric); train = configs[4] training step (bench_train.py); "
+                         "c3 / c4 = configs[2] / configs[3], whole-job strong-scaling runs (bench_long.py)")
+    ap.add_argument("--recordings", type=int, default=0, help="c3 / c4: override the number of recordings")
     args = ap.parse_args()
+    if args.workload in ("c3", "c4"):
+        import bench_long
+        argv = ["--workload", args.workload, "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup),
+                "--precision", args.precision] + (["--skip-cpu"] if args.skip_cpu else []) + \
+               (["--recordings", str(args.recordings)] if args.recordings else [])
+        return bench_long.main(argv)
     if args.workload == "train":
         import bench_train
         argv = ["--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--impl", args.impl,

@@ -31,7 +31,8 @@ struct eda_frontend_plan {
   int* d_mel_off;      // (n_mels + 1)
   int mel_nnz;
   float* d_melw32;     // the same packed weights as float (what librosa stores), for logmel_t8_kernel
-  double2* d_tw_step;  // (16, 8) W_128^{t * k1} at [k1 * 8 + t]: twiddles between the two FFT steps of logmel_t8_kernel
+  double2* d_tw_step;  // n_fft 256: (16, 8) W_128^{t k1} at [k1 * 8 + t]; n_fft 512: (16, 16) W_256^{t k1} at [k1 * 16 + t]
+                       // (twiddles between the two FFT steps of logmel_t8_kernel / logmel_t16_kernel)
 };
 
 namespace eda {
@@ -679,6 +680,177 @@ logmel_t8_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ r
   if (words) run(std::true_type{}); else run(std::false_type{});
 }
 
+
+// ---- pass 1, n_fft = 512 (16 kHz configs): sixteen threads per frame ------------------------------------------
+// Same scheme as logmel_t8_kernel with M = 256 = 16 x 16: thread t holds z[t + 16 j] -> 16-point FFT -> x W_256^{t k1} ->
+// transpose through shared memory -> thread u holds column k1 = u -> 16-point FFT = Z[u + 16 k2].  The partner of bin
+// u + 16 k2 is (16 - u) + 16 (15 - k2), which lives in ANOTHER thread here, so the spectrum goes through the (now free)
+// transpose buffer once more in natural order and thread t untangles the pairs k = 1 + t + 16 i, M - k.  A warp advances
+// two frames.  Replaces the one-warp-per-frame kernel for this size (1 CTA per SM at 8 points per lane: latency-bound).
+constexpr int kT16Warps = 4;
+constexpr int kT16Frame = 4096 + 264 * 4 + 32;         // bytes per frame: spectrum buffer + powers (+ 8 banks of skew)
+static size_t logmel_t16_smem(int mel_nnz) {
+  return 3 * 4096 + (size_t)((mel_nnz + 31) & ~31) * 4 + (size_t)kT16Warps * 2 * kT16Frame;
+}
+
+template <typename AudioT>
+__global__ void __launch_bounds__(kT16Warps * 32, 3)
+logmel_t16_kernel(const AudioT* __restrict__ audio, const int64_t* __restrict__ rec_sample_off,
+                  const int64_t* __restrict__ rec_frame_off, int n_rec, int64_t total_frames, int hop, int n_mels,
+                  const double* __restrict__ window, const double2* __restrict__ tw_step, const double2* __restrict__ tw512,
+                  const float* __restrict__ melw32, const int* __restrict__ mel_off, const int* __restrict__ mel_lo,
+                  int mel_nnz, float* __restrict__ logmel, double* __restrict__ colsum, int frames_per_warp,
+                  const int64_t* __restrict__ sum_range) {
+  constexpr int M = 256;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double2* s_win = reinterpret_cast<double2*>(smem_raw);                 // (w[2n], w[2n+1]), n < 256
+  double2* s_step = s_win + 256;                                         // W_256^{t k1} at [k1 * 16 + t]
+  double2* s_tw = s_step + 256;                                          // W_512^k, k < 256
+  float* s_melw = reinterpret_cast<float*>(s_tw + 256);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, q = lane >> 4, t = lane & 15;
+  unsigned char* wbase = smem_raw + 3 * 4096 + (size_t)((mel_nnz + 31) & ~31) * 4 + (size_t)(warp * 2 + q) * kT16Frame;
+  double2* S = reinterpret_cast<double2*>(wbase);                        // transpose buffer [k1][t ^ k1], then Z[k] in natural order
+  float* Pw = reinterpret_cast<float*>(wbase + 4096);                    // power spectrum (257 floats)
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+    s_win[i] = make_double2(window[2 * i], window[2 * i + 1]);
+    s_step[i] = tw_step[i];
+    s_tw[i] = tw512[i];
+  }
+  for (int i = threadIdx.x; i < mel_nnz; i += blockDim.x) s_melw[i] = melw32[i];
+  __syncthreads();
+  bool words = true;
+  if constexpr (sizeof(AudioT) == 2) {
+    bool ok = (hop & 1) == 0 && (reinterpret_cast<uintptr_t>(audio) & 3) == 0;
+    for (int r = threadIdx.x; r < n_rec; r += blockDim.x) ok = ok && (rec_sample_off[r] & 1) == 0;
+    words = __syncthreads_and(ok);
+  }
+  int m_off[2], m_cnt[2], m_lo[2];                     // this thread's mel filters: t and t + 16
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int m = t + 16 * r;
+    const bool ok = m < n_mels;
+    m_off[r] = ok ? mel_off[m] : 0; m_cnt[r] = ok ? mel_off[m + 1] - m_off[r] : 0; m_lo[r] = ok ? mel_lo[m] : 0;
+  }
+  const int64_t gwarp = (int64_t)blockIdx.x * kT16Warps + warp;
+  const int64_t f_begin = gwarp * frames_per_warp;
+  const int64_t f_end = min(total_frames, f_begin + frames_per_warp);
+  if (f_begin >= f_end) return;                                           // warp-uniform
+  int64_t f = f_begin + q;
+  int rec = 0;
+  {
+    int lo = 0, hi = n_rec - 1;
+    const int64_t f0 = min(f, total_frames - 1);
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (rec_frame_off[mid] <= f0) lo = mid; else hi = mid - 1;
+    }
+    rec = lo;
+  }
+  int64_t r_f0 = rec_frame_off[rec], r_f1 = rec_frame_off[rec + 1];
+  int64_t r_s0 = rec_sample_off[rec], r_n = rec_sample_off[rec + 1] - r_s0;
+  double csum[2] = {0.0, 0.0};
+  int rec_acc = rec;
+  auto flush = [&]() {
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      if (t + 16 * r < n_mels && csum[r] != 0.0) atomicAdd(colsum + (size_t)rec_acc * n_mels + t + 16 * r, csum[r]);
+      csum[r] = 0.0;
+    }
+  };
+  auto run = [&](auto words_tag) {
+  constexpr bool WORDS = decltype(words_tag)::value;
+  RawPair<AudioT, WORDS> raw[16] = {};
+  auto load_raw = [&](int64_t ff) {        // z[n] = x[2n] + i x[2n+1], n = t + 16 j
+    const int64_t s_start = (ff - r_f0) * hop - M + 2 * t;
+    const AudioT* rec_audio = audio + r_s0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) raw[j].load(rec_audio, s_start + 32 * j, r_n);
+  };
+  auto fetch = [&](int64_t ff) -> bool {
+    if (ff >= f_end) return false;
+    while (ff >= r_f1) {
+      ++rec;
+      r_f0 = rec_frame_off[rec]; r_f1 = rec_frame_off[rec + 1];
+      r_s0 = rec_sample_off[rec]; r_n = rec_sample_off[rec + 1] - r_s0;
+    }
+    load_raw(ff);
+    return true;
+  };
+  bool active_next = fetch(f_begin + q);
+  for (int64_t fb = f_begin; fb < f_end; fb += 2) {       // warp-uniform loop; f = fb + q is this half-warp's frame
+    f = fb + q;
+    const bool active = active_next;
+    const int rec_cur = rec;
+    const int64_t fl_cur = f - r_f0;
+    cdx a[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const double2 w = s_win[t + 16 * j];
+      a[j] = active ? cdx{raw[j].a() * w.x, raw[j].b() * w.y} : cdx{0.0, 0.0};
+    }
+    active_next = fetch(f + 2);
+    fft16(a);                                              // slot 4 r + s = Y_t[k1], k1 = r + 4 s
+    __syncwarp();                                          // the previous iteration's readers of S / Pw are done
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int s2 = 0; s2 < 4; ++s2) {
+        const int k1 = r + 4 * s2;
+        cdx y = a[4 * r + s2];
+        if (k1 > 0) { const double2 w = s_step[k1 * 16 + t]; y = cmulx(y, w.x, w.y); }
+        S[k1 * 16 + (t ^ k1)] = make_double2(y.x, y.y);
+      }
+    __syncwarp();
+#pragma unroll
+    for (int n2 = 0; n2 < 16; ++n2) {
+      const double2 v = S[t * 16 + (n2 ^ t)];
+      a[n2] = cdx{v.x, v.y};
+    }
+    fft16(a);                                              // slot 4 r + s = Z[t + 16 k2], k2 = r + 4 s
+    __syncwarp();                                          // every lane has read its column: S is free
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int s2 = 0; s2 < 4; ++s2) S[t + 16 * (r + 4 * s2)] = make_double2(a[4 * r + s2].x, a[4 * r + s2].y);
+    __syncwarp();
+    // real-FFT untangle of the pairs (k, M - k), k = 1 + t + 16 i (k = M/2 pairs with itself)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int k = 1 + t + 16 * i;
+      const double2 zk = S[k], zm = S[M - k];
+      const cdx E = {zk.x + zm.x, zk.y - zm.y};
+      const cdx D = {zk.x - zm.x, zk.y + zm.y};
+      const double2 w = s_tw[k];
+      const cdx T = cmulx(mul_mi(D), w.x, w.y);
+      const cdx pp = E + T, qq = E - T;
+      Pw[k] = (float)(0.25 * (pp.x * pp.x + pp.y * pp.y));
+      Pw[M - k] = (float)(0.25 * (qq.x * qq.x + qq.y * qq.y));
+    }
+    if (t == 0) {
+      const double2 z0 = S[0];
+      Pw[0] = (float)((z0.x + z0.y) * (z0.x + z0.y));
+      Pw[M] = (float)((z0.x - z0.y) * (z0.x - z0.y));
+    }
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      float acc = 0.f;
+      const float* wrow = s_melw + m_off[r];
+      const float* prow = Pw + m_lo[r];
+      for (int i = 0; i < m_cnt[r]; ++i) acc = fmaf(prow[i], wrow[i], acc);
+      if (active && t + 16 * r < n_mels) {
+        if (r == 0 && rec_cur != rec_acc) { flush(); rec_acc = rec_cur; }
+        const float v = log10f(fmaxf(acc, 1e-10f));
+        logmel[(size_t)f * n_mels + t + 16 * r] = v;
+        if (!sum_range || (fl_cur >= sum_range[2 * rec_cur] && fl_cur < sum_range[2 * rec_cur + 1])) csum[r] += (double)v;
+      }
+    }
+  }
+  flush();
+  };                                                       // run
+  if (words) run(std::true_type{}); else run(std::false_type{});
+}
+
 // ---- pass 2 ---------------------------------------------------------------------------
 // Row t of the output = frames t*sub - c .. t*sub + c of the (mean-normalised) pass-1 matrix side by side: since that
 // matrix is (frames, width) row-major, the (2c+1)*width values are ONE contiguous run of it (zeros where the run leaves
@@ -808,14 +980,15 @@ int eda_frontend_plan_create(int sample_rate, int frame_size, int frame_shift, i
     std::vector<float> w32(w64.begin(), w64.end());                    // the float32 values librosa stores
     EDA_CUDA(cudaMalloc(&p->d_melw32, sizeof(float) * std::max<size_t>(1, w32.size())));
     EDA_CUDA(cudaMemcpy(p->d_melw32, w32.data(), sizeof(float) * w32.size(), cudaMemcpyHostToDevice));
-    std::vector<double2> st(128);                                      // W_128^{t k1} at [k1 * 8 + t] (logmel_t8_kernel)
+    const int nt = n_fft == 512 ? 16 : 8, mm = 16 * nt;                 // threads per frame, packed complex points
+    std::vector<double2> st(256);
     for (int k1 = 0; k1 < 16; ++k1)
-      for (int t = 0; t < 8; ++t) {
-        const double a = -2.0 * kPi * (double)((t * k1) % 128) / 128.0;
-        st[k1 * 8 + t] = make_double2(cos(a), sin(a));
+      for (int t = 0; t < nt; ++t) {
+        const double a = -2.0 * kPi * (double)((t * k1) % mm) / (double)mm;
+        st[k1 * nt + t] = make_double2(cos(a), sin(a));
       }
-    EDA_CUDA(cudaMalloc(&p->d_tw_step, sizeof(double2) * 128));
-    EDA_CUDA(cudaMemcpy(p->d_tw_step, st.data(), sizeof(double2) * 128, cudaMemcpyHostToDevice));
+    EDA_CUDA(cudaMalloc(&p->d_tw_step, sizeof(double2) * 256));
+    EDA_CUDA(cudaMemcpy(p->d_tw_step, st.data(), sizeof(double2) * 256, cudaMemcpyHostToDevice));
   }
   EDA_CUDA(cudaMalloc(&p->d_window, sizeof(double) * n_fft));
   EDA_CUDA(cudaMalloc(&p->d_tw, sizeof(double2) * (n_fft / 2)));
@@ -836,6 +1009,12 @@ int eda_frontend_plan_create(int sample_rate, int frame_size, int frame_shift, i
     EDA_CUDA(cudaFuncSetAttribute(logmel_t8_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, tsm));
     EDA_CUDA(cudaFuncSetAttribute(logmel_t8_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, tsm));
     EDA_CUDA(cudaFuncSetAttribute(logmel_t8_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, tsm));
+  }
+  if (n_fft == 512) {
+    const int tsm = (int)logmel_t16_smem(p->mel_nnz);
+    EDA_CUDA(cudaFuncSetAttribute(logmel_t16_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, tsm));
+    EDA_CUDA(cudaFuncSetAttribute(logmel_t16_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, tsm));
+    EDA_CUDA(cudaFuncSetAttribute(logmel_t16_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, tsm));
   }
   if (n_fft == 256 || n_fft == 512) {
     const int M = n_fft / 2;
@@ -886,6 +1065,23 @@ static int frontend_transform(const eda_frontend_plan* p, const void* audio, int
       p->mel_nnz, out, colsum, (int)fpw, sum_range)
     if (audio_dtype == EDA_AUDIO_F64) EDA_T8(double); else if (audio_dtype == EDA_AUDIO_I16) EDA_T8(int16_t); else EDA_T8(float);
 #undef EDA_T8
+    EDA_LAUNCH_CHECK();
+    return EDA_OK;
+  }
+  if (transform == EDA_TRANSFORM_LOGMEL_MN && p->n_fft == 512 && p->n_mels <= 32 && !(force && force[0] == 'w')) {
+    // sixteen threads per frame, two frames per warp step
+    const int64_t target_warps = (int64_t)num_sms() * 12 * 2;
+    int64_t fpw = std::max<int64_t>(2, ceil_div<int64_t>(total_frames, target_warps));
+    fpw = (fpw + 1) / 2 * 2;
+    const int64_t n_warps = ceil_div<int64_t>(total_frames, fpw);
+    const int blocks = (int)ceil_div<int64_t>(n_warps, kT16Warps);
+    const size_t smem = logmel_t16_smem(p->mel_nnz);
+#define EDA_T16(T)                                                                                                         \
+  logmel_t16_kernel<T><<<blocks, kT16Warps * 32, smem, st>>>((const T*)audio, rec_sample_off, rec_frame_off, n_rec,          \
+      total_frames, p->frame_shift, p->n_mels, p->d_window, p->d_tw_step, p->d_tw, p->d_melw32, p->d_mel_off, p->d_mel_lo, \
+      p->mel_nnz, out, colsum, (int)fpw, sum_range)
+    if (audio_dtype == EDA_AUDIO_F64) EDA_T16(double); else if (audio_dtype == EDA_AUDIO_I16) EDA_T16(int16_t); else EDA_T16(float);
+#undef EDA_T16
     EDA_LAUNCH_CHECK();
     return EDA_OK;
   }

@@ -118,14 +118,11 @@ def pin_to_gpu_numa(index: int):
             return None
         n_local = max(1, sum(1 for i in range(nv.nvmlDeviceGetCount())
                              if list(nv.nvmlDeviceGetCpuAffinity(nv.nvmlDeviceGetHandleByIndex(i), len(words))) == list(words)))
-        world = int(os.environ.get("WORLD_SIZE", 1))
-        if world > 1 and n_local > 1 and len(cores) >= 2 * n_local:
-            k = len(cores) // n_local
-            mine = cores[(index % n_local) * k:(index % n_local + 1) * k]
-        else:
-            mine = cores
-        os.sched_setaffinity(0, mine)
-        return f"{len(mine)} cores local to GPU {index}"
+        # the whole NUMA-local set, shared with the other ranks of that node: slicing it per rank (4 cores each on a
+        # 32-core box with 8 ranks) starved the rank's helper threads and cost 25 % of the 8-GPU device-timed throughput
+        del n_local
+        os.sched_setaffinity(0, cores)
+        return f"{len(cores)} cores local to GPU {index} (shared by the ranks of that NUMA node)"
     except Exception as e:  # pragma: no cover
         return f"unpinned ({type(e).__name__})"
 
@@ -382,6 +379,7 @@ def run_ours(args):
                     "d2h_bytes_per_step": d2h, "passes": E2E_PASSES, "steps_per_pass": args.steps,
                     "min": round(world * B * T / e2e_worst, 1), "max": round(world * B * T / e2e_best, 1),
                     "stat": "median over passes of (max over ranks of host wall time per step)"},
+            "host_submit_ms": round(1e3 * pipe.stats["submit_s"] / max(1, pipe.stats["submits"]), 3),
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
             "cpu_baseline": cpu,
         }

@@ -182,6 +182,17 @@ def main(argv=None):
     clocks = sampler.stop()
 
     out = None
+    prof_all = None
+    if chunk_level:
+        # the roofline leg of the chunk-level path contains the all-reduce: EVERY rank runs it (rank 0 alone would wait
+        # for its peers forever), only rank 0 keeps the timings
+        if rank == 0:
+            L.PROFILE = {}
+        run_steps(dev_batches, 1)
+        torch.cuda.synchronize()
+        if rank == 0:
+            prof_all = L.profile_ms()
+            L.PROFILE = None
     if rank == 0:
         pk = B0.peaks()
         # roofline leg: ONE batch (or one recording's shard) on one stream, every C-ABI call bracketed by CUDA events
@@ -193,12 +204,10 @@ def main(argv=None):
                 pass
             serial.submit(*dev_batches[0]); serial.collect()
             my_prof_frames = sum(rows[i] for i in batches[0])
+            prof = L.profile_ms()
+            L.PROFILE = None
         else:
-            L.PROFILE = {}
-            run_steps(dev_batches, 1)
-            my_prof_frames = my_frames
-        prof = L.profile_ms()
-        L.PROFILE = None
+            prof, my_prof_frames = prof_all, my_frames
         tot = sum(m for v in prof.values() for m, _ in v)
         shares = {k: round(sum(m for m, _ in v) / tot, 4) for k, v in prof.items()}
         gemm = [(m, 2.0 * a[16] * a[17] * min(a[18], IN if a[18] == 352 else a[18])) for m, a in prof.get("eda_gemm_split", [])]

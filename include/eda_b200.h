@@ -108,6 +108,13 @@ int eda_frontend_splice_subsample_w(const float* src, int width, const double* c
 /* ------------------------------------------------------------------- encoder -----
  * Building blocks of TransformerEdaModel.forward_embedding (models.py:213-234).     */
 
+/* HOST function (no device work): the per-sequence torch.randperm(ilen) draws of models.py:229-232 for a whole batch.
+ * left / next / state624 are the fields of torch's serialised CPU generator (32-bit Mersenne Twister); they are advanced
+ * exactly as n_seq torch.randperm calls would advance them.  rows[b]: host memory for the permutation of
+ * 0..lens[b]-1 of sequence b (sequences are drawn in the order b = 0, 1, ...).                  */
+int eda_host_randperm_batch(int32_t* left, uint64_t* next, uint64_t* state624, const int32_t* lens, int n_seq,
+                            int32_t* const* rows);
+
 /* pad_sequence(padding_value) of models.py:217 into a K-padded staging matrix:
  * dst (B*Tmax, ld_dst); row (b,t) = src row (seq_off[b]+t) for t < len[b] else `pad`;
  * columns >= n_cols are 0.  src is the concatenation of the sequences, (sum len, n_cols). */

@@ -35,6 +35,7 @@ SIGNATURES = {
     "eda_frontend_width": (_i, [_p, _i]),
     "eda_frontend_splice_subsample_w": (_i, [_p, _i, _p, _p, _p, _i, _i64, _i, _i, _p, _i, _p]),
     "eda_frontend_splice_subsample": (_i, [_p, _p, _p, _p, _p, _i, _i64, _i, _i, _p, _i, _p]),
+    "eda_host_randperm_batch": (_i, [_p, _p, _p, _p, _i, _p]),
     "eda_pad_pack": (_i, [_p, _p, _p, _i, _i, _i, _f, _p, _i, _p]),
     "eda_linear": (_i, [_p, _i, _p, _i, _p, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "eda_mha_fwd": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _i, _p]),
@@ -143,7 +144,15 @@ class use_stream:
 PROFILE = None
 
 
+# When RECORD is a list, every call is also appended to it as (name, [args]): the model replays such a recording of
+# its encoder with a handful of pointers patched instead of re-deriving ~30 argument lists per batch (host time per
+# batch is what limits 8 ranks sharing one host).
+RECORD = None
+
+
 def call(name: str, *args) -> None:
+    if RECORD is not None:
+        RECORD.append((name, list(args)))
     if PROFILE is None:
         rc = getattr(load(), name)(*args)
     else:

@@ -31,6 +31,7 @@ class LstmEncoderDedecoderAttractor(nn.Module):
         self.precision = L.PREC_FP32
         self._prep = None
         self._prep_event = None
+        self._order = {}
 
     # -- cached kernel-side views of the parameters ------------------------------------
     def _prepared(self, want_split: bool = False):
@@ -73,8 +74,12 @@ class LstmEncoderDedecoderAttractor(nn.Module):
                            L.EPI_BIAS, self.precision, out=xproj)
         else:
             xproj = ops.linear(emb2d, w["w_ih"], w["b_enc"], L.EPI_BIAS, self.precision)
-        order = torch.tensor(sorted(range(B), key=lambda b: -lens_host[b]), dtype=torch.int32).to(
-            emb2d.device, non_blocking=True)
+        okey = (tuple(lens_host), str(emb2d.device))
+        order = self._order.get(okey)
+        if order is None:                       # sequences co-scheduled by length; cached per geometry, blocking copy once
+            if len(self._order) > 256:
+                self._order.clear()
+            order = self._order[okey] = torch.tensor(sorted(range(B), key=lambda b: -lens_host[b]), dtype=torch.int32).to(emb2d.device)
         att, _ = ops.lstm_attractors(xproj, perm, lens_dev, order, w["u_enc"], w["u_dec"], w["b_dec"],
                                      B, Tmax, n_dec, prec=self.precision)
         probs, loss_att = ops.attractor_head(att, w["w_lin"], w["b_lin"], n_spk_label)

@@ -64,6 +64,8 @@ class TransformerEdaModel(nn.Module):
         self._perm_ring = {}
         self._emb_split = None
         self._prep_event = None
+        self._geo = {}
+        self._prep_gen = 0
 
     # state_dict names of the input projection, its LayerNorm and the encoder stack (models.py:185-193)
     NAMES = dict(in_linear="encoder", in_norm="encoder_norm", stack="transformer_encoder")
@@ -127,6 +129,7 @@ class TransformerEdaModel(nn.Module):
                     for k in ("w_qkv", "w_o", "w_1", "w_2"):
                         lw["s" + k] = ops.split_bf16(lw[k])
             self._prep = (key, prep)
+            self._prep_gen += 1
             self._prep_event = self._record_event(w.device)
         self._wait_event(self._prep_event)
         return self._prep[1]
@@ -153,6 +156,11 @@ class TransformerEdaModel(nn.Module):
         multi-GB workspaces per shape nor thrash the allocator.  A shape always gets the same pointers
         while the arena stands, which keeps libeda_b200's tensor-map cache (keyed on pointer + dims) warm."""
         akey = ("arena", str(dev), self.workspace_slot)
+        arena = self._ws.get(akey)
+        if arena is not None:
+            ws = arena["views"].get((B, Tmax))
+            if ws is not None:
+                return ws
         M, D, H, FF = B * Tmax, self.n_units, self.n_heads, self.dim_feedforward
         Tp, kpad = _round_up(Tmax, 8), _round_up(self.in_size, 16)
         plan = [("xin", torch.bfloat16, (2, M, kpad)), ("xs0", torch.bfloat16, (2, M, D)), ("xs1", torch.bfloat16, (2, M, D)),
@@ -175,7 +183,7 @@ class TransformerEdaModel(nn.Module):
                 pos += nbytes
             sp = lambda x: ops.Split(x[0], x[1])
             # key columns [Tmax, Tp) of v^T are never written by the QKV epilogue and must not hold NaN bit patterns
-            ws = dict(Tp=Tp, vt_pad=t["vt"][:, :, Tmax:] if Tp != Tmax else None, xin=sp(t["xin"]), xs=[sp(t["xs0"]), sp(t["xs1"])], xf=[t["xf0"], t["xf1"]], qk=sp(t["qk"]),
+            ws = dict(Tp=Tp, plans={}, vt_pad=t["vt"][:, :, Tmax:] if Tp != Tmax else None, xin=sp(t["xin"]), xs=[sp(t["xs0"]), sp(t["xs1"])], xf=[t["xf0"], t["xf1"]], qk=sp(t["qk"]),
                       vt=sp(t["vt"]), att=sp(t["att"]), ff=sp(t["ff"]), xproj=t["xproj"])
             arena["views"][(B, Tmax)] = ws
         return ws
@@ -219,16 +227,8 @@ class TransformerEdaModel(nn.Module):
         if not flat_in:
             ilens = [int(x.shape[0]) for x in src]
         B, Tmax = len(ilens), max(ilens)
-        off = np.zeros(B + 1, dtype=np.int64)
-        if offsets is not None:
-            off[:B] = np.asarray(offsets, dtype=np.int64)
-            off[B] = off[B - 1] + ilens[-1]
-        else:
-            np.cumsum(ilens, out=off[1:])
         masked = independent and min(ilens) != Tmax
-        meta = torch.from_numpy(np.concatenate([off, np.asarray(ilens, dtype=np.int64)])).to(dev, non_blocking=True)
-        seq_off = meta[: B + 1]
-        lens_dev = meta[B + 1:].to(torch.int32)
+        seq_off, lens_dev = self._geometry(ilens, offsets, dev)
         flat = src if flat_in else self._to_device_flat(src, dev)
         P = self.precision
         if flat_in and P == L.PREC_FP32 and not flat.is_contiguous():
@@ -246,19 +246,73 @@ class TransformerEdaModel(nn.Module):
             x = ops.linear(ff, lw["w_2"], lw["b_2"], L.EPI_BIAS_RES_LN, P, resid=x, gamma=lw["g2"], beta=lw["be2"])
         return x, ilens, lens_dev, seq_off, B, Tmax
 
+    def _geometry(self, ilens, offsets, dev):
+        """(row offsets int64 (B+1), lengths int32 (B)) of a batch on the device; cached per geometry (the pipeline sees
+        the same few geometries over and over), made with a blocking copy so that any stream may read them."""
+        key = (tuple(ilens), None if offsets is None else tuple(int(o) for o in offsets), str(dev))
+        hit = self._geo.get(key)
+        if hit is None:
+            if len(self._geo) > 256:
+                self._geo.clear()
+            B = len(ilens)
+            off = np.zeros(B + 1, dtype=np.int64)
+            if offsets is not None:
+                off[:B] = np.asarray(offsets, dtype=np.int64)
+                off[B] = off[B - 1] + ilens[-1]
+            else:
+                np.cumsum(ilens, out=off[1:])
+            hit = self._geo[key] = (torch.from_numpy(off).to(dev), torch.tensor([int(n) for n in ilens], dtype=torch.int32).to(dev))
+        return hit
+
     def _embed_tc(self, flat, w, seq_off, lens_dev, ilens, B, Tmax, dev, masked=False):
         """The encoder on the split-bf16 tensor-core pipeline: every GEMM epilogue writes the
         next kernel's operands (split bf16) and, where needed, the fp32 residual stream."""
         P, D, H = self.precision, self.n_units, self.n_heads
         M = B * Tmax
         ws = self._workspace(B, Tmax, dev)
+        if ws["vt_pad"] is not None:
+            ws["vt_pad"].zero_()
+        emb = torch.empty((M, D), dtype=torch.float32, device=dev)      # returned to the caller: fresh
+        self._emb_split = (ws["xs"][0], ws["xproj"])
+        # The ~20 launches of the encoder are the same for every batch of a geometry except for five pointers: replay a
+        # recording of them (made by the first call through the regular bindings) with those pointers patched.
+        key = (masked, self._prep_gen, P, self.attn_precision, int(flat.stride(0)), int(flat.shape[1]))
+        plan = ws["plans"].get(key) if L.PROFILE is None and L.RECORD is None else None
+        var = dict(flat=flat.data_ptr(), seq_off=seq_off.data_ptr(), lens=lens_dev.data_ptr(), emb=emb.data_ptr())
+        if plan is not None:
+            st = L.stream()
+            for fn, args, patches in plan:
+                for pos, which in patches:
+                    args[pos] = var[which]
+                args[-1] = st
+                rc = fn(*args)
+                if rc != 0:
+                    raise L.EdaError(f"{fn.__name__} failed ({rc}): {L.load().eda_last_error_string().decode()}")
+            return emb, ilens, lens_dev, seq_off, B, Tmax
+        record = L.PROFILE is None and L.RECORD is None
+        if record:
+            L.RECORD = []
+        try:
+            self._embed_tc_calls(flat, w, seq_off, lens_dev, B, Tmax, ws, emb, masked)
+        finally:
+            rec, L.RECORD = L.RECORD, None
+        if record and len(set(var.values())) == len(var):
+            lib, inv, plan = L.load(), {v: k for k, v in var.items()}, []
+            for name, args in rec:
+                patches = [(i, inv[a]) for i, a in enumerate(args[:-1]) if isinstance(a, int) and not isinstance(a, bool) and a in inv]
+                plan.append((getattr(lib, name), args, patches))
+            if len(ws["plans"]) > 8:
+                ws["plans"].clear()
+            ws["plans"][key] = plan
+        return emb, ilens, lens_dev, seq_off, B, Tmax
+
+    def _embed_tc_calls(self, flat, w, seq_off, lens_dev, B, Tmax, ws, emb, masked):
+        P, D, H = self.precision, self.n_units, self.n_heads
+        M = B * Tmax
         Tp = ws["Tp"]
         xin, (sa, sb), (xa, xb) = ws["xin"], ws["xs"], ws["xf"]
         ops.pad_pack_split(flat, seq_off, lens_dev, B, Tmax, xin, -1.0)
-        if ws["vt_pad"] is not None:
-            ws["vt_pad"].zero_()
         n_layers = len(w["layers"])
-        emb = torch.empty((M, D), dtype=torch.float32, device=dev)      # returned to the caller: fresh
         ops.gemm_split(xin, w["ws_in"], w["b_in"], M, D, xin.ld, L.EPI_BIAS_LN, P, gamma=w["g_in"], beta=w["be_in"],
                        out=xa if n_layers else emb, out_split=sa)
         for i, lw in enumerate(w["layers"]):
@@ -274,8 +328,6 @@ class TransformerEdaModel(nn.Module):
                            out_split=ws["ff"])
             ops.gemm_split(ws["ff"], lw["sw_2"], lw["b_2"], M, D, self.dim_feedforward, L.EPI_BIAS_RES_LN, P,
                            resid=xb, gamma=lw["g2"], beta=lw["be2"], out=emb if last else xa, out_split=sa)
-        self._emb_split = (sa, ws["xproj"])
-        return emb, ilens, lens_dev, seq_off, B, Tmax
 
     def _perm_slot(self, B: int, Tmax: int):
         """A pinned (B, Tmax) int32 staging buffer prefilled with the identity order, from a small ring
@@ -308,10 +360,13 @@ class TransformerEdaModel(nn.Module):
         chunks out of order draw them first, in the reference's order)."""
         slot = self._perm_slot(len(ilens), Tmax)
         perm = slot[0]
-        for i, n in enumerate(ilens):
-            if perms is None:        # int32 output draws the same numbers from the generator as the int64 default
-                torch.randperm(n, out=perm[i, :n])
-            else:
+        if perms is None:
+            rows = perm.data_ptr() + 4 * Tmax * np.arange(len(ilens), dtype=np.uint64)
+            if not ops.host_randperm_rows(ilens, rows):
+                for i, n in enumerate(ilens):   # int32 output draws the same numbers from the generator as the int64 default
+                    torch.randperm(n, out=perm[i, :n])
+        else:
+            for i, n in enumerate(ilens):
                 perm[i, :n] = perms[i].to(torch.int32)
         return self._ship_perm(slot, dev)
 
@@ -321,9 +376,14 @@ class TransformerEdaModel(nn.Module):
         (recording by recording, chunk by chunk, infer_eda.py:92-113).  Returns one (B_g, Tmax_g) int32 device
         index per batch."""
         slots = [self._perm_slot(len(g), max(g)) for g in groups]
-        for g, i in order:
-            n = groups[g][i]
-            torch.randperm(n, out=slots[g][0][i, :n])
+        gi = np.asarray(order, dtype=np.int64).reshape(-1, 2)
+        base = np.asarray([s[0].data_ptr() for s in slots], dtype=np.uint64)
+        stride = np.asarray([4 * max(g) for g in groups], dtype=np.uint64)
+        lens = [groups[g][i] for g, i in order]
+        rows = base[gi[:, 0]] + stride[gi[:, 0]] * gi[:, 1].astype(np.uint64)
+        if not ops.host_randperm_rows(lens, rows):
+            for g, i in order:
+                torch.randperm(groups[g][i], out=slots[g][0][i, : groups[g][i]])
         return [self._ship_perm(s, dev) for s in slots]
 
     def prepare_weights(self) -> None:

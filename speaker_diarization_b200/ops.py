@@ -19,6 +19,32 @@ def _f32(t: Tensor) -> Tensor:
     return t
 
 
+_MT_STATE_BYTES = 5056      # torch's serialised CPU generator (32-bit Mersenne Twister): seed u64 | left i32 | seeded i32 | next u64 | state u64[624] | ...
+
+
+def host_randperm_rows(lens, row_ptrs) -> bool:
+    """``torch.randperm(n)`` for every n in ``lens`` (in order) from torch's GLOBAL CPU generator, written as int32 to
+    the host addresses ``row_ptrs`` (numpy uint64 array) by ONE native call that advances the generator exactly like the
+    individual calls would (models.py:229-232 draws one per sequence; 64 dispatcher round trips per batch were the
+    largest item of the host path).  Returns False (nothing drawn) if the generator state has an unknown layout."""
+    import numpy as np
+    st = torch.get_rng_state()
+    if st.numel() != _MT_STATE_BYTES:
+        return False
+    a = st.numpy()
+    left, nxt, state = a[8:12].view(np.int32), a[16:24].view(np.uint64), a[24:24 + 624 * 8].view(np.uint64)
+    if not (1 <= int(left[0]) <= 624 and int(nxt[0]) <= 624 and int(a[12:16].view(np.int32)[0]) == 1):
+        return False
+    lens_a = np.ascontiguousarray(lens, dtype=np.int32)
+    rows = np.ascontiguousarray(row_ptrs, dtype=np.uint64)
+    rc = L.load().eda_host_randperm_batch(left.ctypes.data, nxt.ctypes.data, state.ctypes.data, lens_a.ctypes.data,
+                                          int(lens_a.size), rows.ctypes.data)
+    if rc != 0:
+        raise L.EdaError(f"eda_host_randperm_batch failed ({rc}): {L.load().eda_last_error_string().decode()}")
+    torch.set_rng_state(st)
+    return True
+
+
 def pad_pack(flat: Tensor, seq_off: Tensor, lens: Tensor, B: int, Tmax: int, ld_dst: int, pad: float) -> Tensor:
     """flat (sum T_i, C) -> (B*Tmax, ld_dst) padded with `pad` (models.py:217)."""
     _f32(flat)

@@ -33,6 +33,7 @@ end and attention CTAs run on the SMs it leaves idle.
 """
 from __future__ import annotations
 
+import time
 from collections import deque
 from typing import Iterable, List, Optional, Sequence
 
@@ -73,6 +74,7 @@ class InferencePipeline:
             torch.cuda.synchronize(self.device)
         self.s_compute = self.s_computes[0]
         self._n_submitted = 0
+        self.stats = dict(submit_s=0.0, submits=0)        # host seconds spent inside submit() (launch work, shuffle draws)
         self._pending = deque()
         self._plans = {}
         self.gather = None          # optional callable(post_dev) run on the compute stream (multi-GPU collection)
@@ -109,6 +111,7 @@ class InferencePipeline:
         recording, or a list of 1-D arrays/tensors.  Host tensors should be pinned."""
         if len(self._pending) >= self.depth:
             raise RuntimeError("pipeline full: call collect() first")
+        t_host = time.perf_counter()
         dev = self.device
         cur = torch.cuda.current_stream(dev)
         k = self._n_submitted % len(self.s_computes)
@@ -159,6 +162,8 @@ class InferencePipeline:
             done = torch.cuda.Event()
             done.record(self.s_out)
         self._pending.append((done, p, h_post, h_probs, h_labels, list(rows)))
+        self.stats["submit_s"] += time.perf_counter() - t_host
+        self.stats["submits"] += 1
 
     def collect(self) -> dict:
         """Block until the OLDEST submitted batch is on the host and return it (see the module docstring)."""

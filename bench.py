@@ -34,7 +34,7 @@ ORIG_AFFINITY = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else
 
 
 # DRAM traffic of the dominant kernel from the committed ncu capture (bytes per launch, bf16x3, configs[1])
-NCU_GEMM_DRAM_BYTES_PER_LAUNCH = 170.2e6
+NCU_GEMM_DRAM_BYTES_PER_LAUNCH = 170.0e6
 
 
 def peaks():
@@ -320,7 +320,7 @@ def run_ours(args):
                     unit="TFLOP/s", frac=round(achieved / pk["tf_sust"], 4),
                     traffic=NCU_GEMM_DRAM_BYTES_PER_LAUNCH if precision == "bf16x3" else None,
                     traffic_source="dram__bytes_read.sum + dram__bytes_write.sum averaged over the step's 18 gemm_split_kernel "
-                                   "launches, ncu --set full (profiles/r01_ncu_step_v2.md)",
+                                   "launches, ncu --set full (profiles/r02_ncu_step_v1.md)",
                     peak_source=pk["src"] + " (bf16 sustained)", issued_mma_factor=issued,
                     issued_tflops=round(issued * achieved, 2), tensor_pipe_frac_issued=round(issued * achieved / pk["tf_sust"], 4),
                     launches_per_step=len(gemm), avg_launch_ms=round(lin_ms / len(gemm), 4),

@@ -10,7 +10,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench as Bn  # noqa: E402
-from oracle.weights import EdaConfig, synth_state_dict  # noqa: E402  (seeded weights only)
+from speaker_diarization_b200.synth import EdaConfig, synth_state_dict  # noqa: E402  (seeded weights only)
 from speaker_diarization_b200 import feature  # noqa: E402
 from speaker_diarization_b200.eend_eda.models import TransformerEdaModel  # noqa: E402
 

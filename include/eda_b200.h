@@ -238,10 +238,14 @@ int eda_posterior(const float* emb, int ld_emb, const float* attractors, int att
 
 /* eda_posterior writing the time-axis concatenation the reference's driver builds with np.vstack(out_chunks)
  * (infer_eda.py:113,121): frame t < lens[b] of sequence b lands in row out_off[b] + t of logits / post / labels
- * ((total rows, n_att) matrices); rows of padded frames are not written.  out_off: (B) int64, lens: (B) int32. */
+ * ((total rows, n_att) matrices); rows of padded frames are not written.  out_off: (B) int64, lens: (B) int32.
+ * mask16 (optional, (total rows) uint16): the frame's thresholded decisions as a bit mask, bit s = attractor s active
+ * (bin/make_rttm.py:29 on all columns at once) - 2 bytes per frame, the form in which results are cheapest to collect
+ * from the other ranks.                                                                              */
 int eda_posterior_packed(const float* emb, int ld_emb, const float* attractors, int att_stride_rows,
                          int B, int Tmax, int D, int n_att, float threshold, const int64_t* out_off,
-                         const int32_t* lens, float* logits, float* post, uint8_t* labels, void* stream);
+                         const int32_t* lens, float* logits, float* post, uint8_t* labels, uint16_t* mask16,
+                         void* stream);
 
 /* ------------------------------------------------------------------- PIT loss ------
  * TransformerEdaModel.pit_loss (models.py:373-421).  pred, label (B, T, S) fp32; lens (B).

@@ -49,7 +49,7 @@ SIGNATURES = {
     "eda_lstm_max_active_clusters": (_i, []),
     "eda_attractor_head": (_i, [_p, _p, _p, _i, _i, _i, _p, _i, _p, _p]),
     "eda_posterior": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p, _p]),
-    "eda_posterior_packed": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p, _p, _p, _p]),
+    "eda_posterior_packed": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p, _p, _p, _p, _p]),
     "eda_pit_loss": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p]),
     "eda_pit_loss_static": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p]),
     "eda_pit_loss_bwd": (_i, [_p, _p, _p, _i, _i, _i, _f, _p, _p]),

@@ -15,7 +15,7 @@ int pad_pack(const float*, const int64_t*, const int32_t*, int, int, int, float,
 int pad_pack_split(const float*, int, const int64_t*, const int32_t*, int, int, int, float, void*, void*, int, cudaStream_t);
 int attractor_head(const float*, const float*, const float*, int, int, int, float*, int, float*, cudaStream_t);
 int posterior(const float*, int, const float*, int, int, int, int, int, float, float*, float*, uint8_t*, cudaStream_t,
-              const int64_t* out_off = nullptr, const int32_t* lens = nullptr);
+              const int64_t* out_off = nullptr, const int32_t* lens = nullptr, uint16_t* mask16 = nullptr);
 int pit_loss(const float*, const float*, const int32_t*, int, int, int, float*, int64_t*, float*, int32_t*, cudaStream_t);
 int pit_loss_static(const float*, const float*, const int32_t*, int, int, int, float*, int64_t*, float*, int32_t*, cudaStream_t);
 int pit_loss_bwd(const float*, const float*, const int32_t*, int, int, int, float, float*, cudaStream_t);
@@ -97,10 +97,10 @@ int eda_posterior(const float* emb, int ld_emb, const float* attractors, int att
 
 int eda_posterior_packed(const float* emb, int ld_emb, const float* attractors, int att_stride_rows, int B,
                          int Tmax, int D, int n_att, float threshold, const int64_t* out_off, const int32_t* lens,
-                         float* logits, float* post, uint8_t* labels, void* stream) {
+                         float* logits, float* post, uint8_t* labels, uint16_t* mask16, void* stream) {
   EDA_REQUIRE(emb && attractors && out_off && lens && B > 0 && Tmax > 0, "eda_posterior_packed: bad arguments");
   return eda::posterior(emb, ld_emb, attractors, att_stride_rows, B, Tmax, D, n_att, threshold, logits, post, labels,
-                        (cudaStream_t)stream, out_off, lens);
+                        (cudaStream_t)stream, out_off, lens, mask16);
 }
 
 int eda_pit_loss(const float* pred, const float* label, const int32_t* lens, int B, int T, int S,

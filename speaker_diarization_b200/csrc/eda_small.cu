@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(256)
 posterior_kernel(const float* __restrict__ emb, int ld_emb, const float* __restrict__ att,
                  int att_stride_rows, int Tmax, int n_att, float thr, float* __restrict__ logits,
                  float* __restrict__ post, uint8_t* __restrict__ labels,
-                 const int64_t* __restrict__ out_off, const int32_t* __restrict__ lens) {
+                 const int64_t* __restrict__ out_off, const int32_t* __restrict__ lens, uint16_t* __restrict__ mask16) {
   constexpr int D = 256;
   __shared__ __align__(16) float As[NATT][D];
   const int b = blockIdx.y;
@@ -177,12 +177,16 @@ posterior_kernel(const float* __restrict__ emb, int ld_emb, const float* __restr
       if (post) post[o] = p;
       if (labels) labels[o] = p > thr ? 1 : 0;
     }
+    if (mask16) {      // the frame's decisions as one bit per attractor (bit s = speaker s active): 2 bytes instead of 4 n_att
+      const unsigned m = __ballot_sync(0xffffffffu, lane < n_att && sigmoidf_ref(mine) > thr);
+      if (lane == 0) mask16[out_off ? (size_t)(__ldg(out_off + b) + t) : row] = (uint16_t)m;
+    }
   }
 }
 
 int posterior(const float* emb, int ld_emb, const float* att, int att_stride_rows, int B, int Tmax,
               int D, int n_att, float thr, float* logits, float* post, uint8_t* labels,
-              cudaStream_t st, const int64_t* out_off, const int32_t* lens) {
+              cudaStream_t st, const int64_t* out_off, const int32_t* lens, uint16_t* mask16) {
   EDA_REQUIRE(D == 256, "eda_posterior: D must be 256 (got %d)", D);
   EDA_REQUIRE(n_att >= 1 && n_att <= 16, "eda_posterior: n_att must be in [1,16] (got %d)", n_att);
   EDA_REQUIRE(ld_emb % 4 == 0 && (uintptr_t)emb % 16 == 0, "eda_posterior: emb must be 16B aligned");
@@ -190,7 +194,7 @@ int posterior(const float* emb, int ld_emb, const float* att, int att_stride_row
   dim3 grid(max(1, min(ceil_div(Tmax, 8), ceil_div(num_sms() * 8, B))), B);
   EDA_REQUIRE((out_off == nullptr) == (lens == nullptr), "eda_posterior_packed: out_off and lens go together");
   posterior_kernel<16><<<grid, 256, 0, st>>>(emb, ld_emb, att, att_stride_rows, Tmax, n_att, thr, logits, post, labels,
-                                             out_off, lens);
+                                             out_off, lens, mask16);
   EDA_LAUNCH_CHECK();
   return EDA_OK;
 }

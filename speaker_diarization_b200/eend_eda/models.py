@@ -446,7 +446,7 @@ class TransformerEdaModel(nn.Module):
         holding the sequences back to back (as ``FrontEnd.features_flat`` returns it), or anywhere in it
         with ``offsets``.  Returns (posteriors (B, Tmax, max_n_speakers-1), attractor existence probs
         (B, max_n_speakers), uint8 activity labels) on the device; speaker counting / slicing is the
-        caller's.  ``independent``: see ``infer``.  ``packed_out`` = (post, labels) matrices with one row
+        caller's.  ``independent``: see ``infer``.  ``packed_out`` = (post, labels[, bit masks]) matrices with one row
         per row of ``feats``: results of frame t of sequence b land in row offsets[b] + t (the time-axis
         concatenation of infer_eda.py:121), nothing is written for padding, and (None, probs, None) is returned.
         ``perm_dev``: the (B, Tmax) int32 frame orders already on the device (else drawn / taken from ``perms``)."""
@@ -456,7 +456,7 @@ class TransformerEdaModel(nn.Module):
                                             emb_split=self._emb_split)
         if packed_out is not None:
             ops.posterior_packed(x, att, B, Tmax, max_n_speakers - 1, seq_off, lens_dev, activity_threshold,
-                                 packed_out[0], packed_out[1])
+                                 packed_out[0], packed_out[1], packed_out[2] if len(packed_out) > 2 else None)
             return None, probs, None
         _, post, labels = ops.posterior(x, att, B, Tmax, max_n_speakers - 1, threshold=activity_threshold,
                                         want_labels=True)

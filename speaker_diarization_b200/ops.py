@@ -120,14 +120,15 @@ def posterior(emb: Tensor, att: Tensor, B: int, Tmax: int, n_att: int, threshold
 
 
 def posterior_packed(emb: Tensor, att: Tensor, B: int, Tmax: int, n_att: int, out_off: Tensor, lens: Tensor,
-                     threshold: float, post: Optional[Tensor], labels: Optional[Tensor]) -> None:
-    """eda_posterior into (total rows, n_att) matrices: frame t of sequence b -> row out_off[b] + t."""
+                     threshold: float, post: Optional[Tensor], labels: Optional[Tensor], mask16: Optional[Tensor] = None) -> None:
+    """eda_posterior into (total rows, n_att) matrices: frame t of sequence b -> row out_off[b] + t; ``mask16`` (total rows,)
+    int16 = the thresholded decisions of a frame as bits."""
     D = emb.shape[1]
     assert out_off.dtype == torch.int64 and lens.dtype == torch.int32
     assert post is None or (post.dtype == torch.float32 and post.is_contiguous() and post.shape[1] == n_att)
     assert labels is None or (labels.dtype == torch.uint8 and labels.is_contiguous() and labels.shape[1] == n_att)
     L.call("eda_posterior_packed", L.ptr(_f32(emb)), emb.stride(0), L.ptr(_f32(att)), att.shape[1], B, Tmax, D,
-           n_att, float(threshold), L.ptr(out_off), L.ptr(lens), None, L.ptr(post), L.ptr(labels), L.stream())
+           n_att, float(threshold), L.ptr(out_off), L.ptr(lens), None, L.ptr(post), L.ptr(labels), L.ptr(mask16), L.stream())
 
 
 def pit_loss(pred: Tensor, label: Tensor, lens: Tensor):

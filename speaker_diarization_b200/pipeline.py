@@ -74,10 +74,13 @@ class InferencePipeline:
             torch.cuda.synchronize(self.device)
         self.s_compute = self.s_computes[0]
         self._n_submitted = 0
-        self.stats = dict(submit_s=0.0, submits=0)        # host seconds spent inside submit() (launch work, shuffle draws)
+        # host seconds spent inside submit() (launch work, shuffle draws), of which in the gather hook / result staging
+        self.stats = dict(submit_s=0.0, submits=0, gather_s=0.0, results_s=0.0)
         self._pending = deque()
         self._plans = {}
-        self.gather = None          # optional callable(post_dev) run on the compute stream (multi-GPU collection)
+        # optional callable(post_dev, mask_dev) run on the compute stream (multi-GPU result collection): posteriors
+        # (rows, 14) fp32 and the thresholded decisions as (rows,) int16 bit masks (2 bytes per frame)
+        self.gather = None
 
     # ------------------------------------------------------------------------------------
     def _plan(self, rows: Sequence[int]):
@@ -135,20 +138,24 @@ class InferencePipeline:
             total = int(p["rec_off"][-1])
             post = torch.empty((total, n_att), dtype=torch.float32, device=dev)
             labels = torch.empty((total, n_att), dtype=torch.uint8, device=dev)
+            mask = torch.empty((total,), dtype=torch.int16, device=dev) if self.gather is not None else None
             perms = self.model.draw_perms(p["lens"], p["order"], dev)       # the driver's draw order
             probs = []
             for lens, offs, perm in zip(p["lens"], p["offs"], perms):
                 _, pr, _ = self.model.infer_device(feats, lens, self.max_n_speakers, self.activity_threshold,
-                                                   independent=self.independent, offsets=offs, packed_out=(post, labels),
+                                                   independent=self.independent, offsets=offs, packed_out=(post, labels, mask),
                                                    perm_dev=perm)
                 probs.append(pr)
             probs = probs[0] if len(probs) == 1 else torch.cat(probs)
             if self.gather is not None:
-                self.gather(post)
+                t_g = time.perf_counter()
+                self.gather(post, mask)
+                self.stats["gather_s"] += time.perf_counter() - t_g
             if isinstance(dev_audio, torch.Tensor):
                 dev_audio.record_stream(s_compute)
         # results belong to the caller: fresh pinned buffers per batch (the pinned caching allocator recycles a
         # block only after the copy that last touched it has completed AND the caller dropped the tensor)
+        t_r = time.perf_counter()
         h_post = torch.empty((total, n_att), dtype=torch.float32, pin_memory=True)
         h_labels = torch.empty((total, n_att), dtype=torch.uint8, pin_memory=True)
         h_probs = torch.empty((len(p["chunks"]), self.max_n_speakers), dtype=torch.float32, pin_memory=True)
@@ -162,6 +169,7 @@ class InferencePipeline:
             done = torch.cuda.Event()
             done.record(self.s_out)
         self._pending.append((done, p, h_post, h_probs, h_labels, list(rows)))
+        self.stats["results_s"] += time.perf_counter() - t_r
         self.stats["submit_s"] += time.perf_counter() - t_host
         self.stats["submits"] += 1
 

@@ -290,3 +290,23 @@ def test_chunk_level_sharding_reproduces_the_reference_driver(world, manifest):
     from speaker_diarization_b200.sharding import shard_features
     mine = torch.cat([shard_features(fe, pcm, sh, allreduce=lambda part: total.clone()) for sh in plan])
     assert tuple(mine.shape) == tuple(whole.shape) and float((mine - whole).abs().max()) < 2e-6
+
+
+def test_posterior_bit_masks_equal_the_label_columns():
+    """eda_posterior_packed's mask16 output: bit s of a frame's mask == its thresholded label of attractor s."""
+    from speaker_diarization_b200 import ops
+    g = torch.Generator().manual_seed(8)
+    B, Tmax, n_att = 3, 70, 14
+    lens = [70, 1, 33]
+    emb = torch.randn((B * Tmax, 256), generator=g).cuda()
+    att = (torch.randn((B, 15, 256), generator=g) / 8).cuda()
+    off = torch.tensor([0, 70, 71], dtype=torch.int64).cuda()
+    lens_d = torch.tensor(lens, dtype=torch.int32).cuda()
+    total = sum(lens)
+    post = torch.zeros((total, n_att), device="cuda")
+    labels = torch.zeros((total, n_att), dtype=torch.uint8, device="cuda")
+    mask = torch.full((total,), -1, dtype=torch.int16, device="cuda")
+    ops.posterior_packed(emb, att, B, Tmax, n_att, off, lens_d, 0.5, post, labels, mask)
+    bits = (mask.cpu().to(torch.int32).unsqueeze(1) >> torch.arange(n_att)) & 1
+    assert torch.equal(bits.to(torch.uint8), labels.cpu()) and torch.equal(labels.cpu().bool(), post.cpu() > 0.5)
+    assert bool(((mask.cpu().to(torch.int32) & 0xffff) >> n_att == 0).all())

@@ -237,37 +237,22 @@ def run_ours(args):
     host_audio = [pcm16(synth_audio_batch(B, 2 * rank + i)).pin_memory() for i in range(2)]    # 2 x 51 MB
     dev_audio = [a.to(dev) for a in host_audio]
     ns = [SECONDS * RATE] * B
-    collect_on_rank0 = None
     if world > 1:
-        # The path's one collective: result collection on rank 0 - ONE NCCL gather per RUN of K batches, inside the timed
-        # region, of the thresholded speaker-activity decisions as bit masks (2 bytes per frame; SURVEY 8e allows "posteriors
-        # ... or the thresholded bitmask").  Every step's masks are kept in a device ring (a 64 KB device copy per step) and
-        # the ring is gathered once; the fp32 posteriors stay with their rank, which lands them in its own host memory.
-        # Measured at 8 GPUs on this pool (1.93 ms/step on one GPU): a per-step list gather of fp32 posteriors 2.73 ms/step,
-        # a per-step all-gather 3.68, one gather of the run's fp32 posteriors 4.18 - i.e. the collective moved data at only
-        # 6-15 GB/s there and, per step, also put the eight ranks in lock-step with 1.3-7 ms of host time per call.
-        ring = torch.empty((max(args.steps, 1), B * T), dtype=torch.int16, device=dev)
-        gather_list = [torch.empty_like(ring) for _ in range(world)] if rank == 0 else None
-        ring_pos = [0]
-
-        def keep(post, mask):
-            ring[ring_pos[0] % ring.shape[0]].copy_(mask, non_blocking=True)
-            ring_pos[0] += 1
-        pipe.gather = keep
-
-        def collect_on_rank0():
-            for s_ in pipe.s_computes[1:]:
-                pipe.s_compute.wait_stream(s_)
-            with torch.cuda.stream(pipe.s_compute):
-                dist.gather(ring, gather_list, dst=0)
-            pipe.s_out.wait_stream(pipe.s_compute)
+        # The path's one collective: result collection on rank 0 - one NCCL gather per step of that step's thresholded
+        # speaker-activity decisions as bit masks (2 bytes per frame, 64 KB per rank; SURVEY 8e allows "posteriors ... or the
+        # thresholded bitmask"), enqueued on the batch's compute stream so that it overlaps the next batches.  The fp32
+        # posteriors stay with their rank, which lands them in its own pinned host memory.
+        # Measured alternatives on this pool (1.93 ms/step on one GPU), device-timed ms/step at 8 GPUs: per-step list gather of
+        # the fp32 posteriors 2.73, per-step all-gather 3.68, ONE gather of the whole run's posteriors after the last batch
+        # 4.18 (and 3.56 at 2 GPUs even with the 64 KB masks): a gather issued once the pipeline has drained exposes a
+        # ~30 ms fixed latency of the send/recv path here, while the per-step gathers hide behind the following batches.
+        gather_list = [torch.empty((2 * B * T,), dtype=torch.uint8, device=dev) for _ in range(world)] if rank == 0 else None
+        pipe.gather = lambda post, mask: dist.gather(mask.view(torch.uint8), gather_list, dst=0)   # NCCL via torch: no int16
 
     def run_steps(audio_list, n):
         last = None
         for last in pipe.run((audio_list[i & 1], ns) for i in range(n)):
             pass
-        if collect_on_rank0 is not None:
-            collect_on_rank0()
         return last
 
     torch.manual_seed(1234 + rank)
@@ -390,8 +375,8 @@ def run_ours(args):
             "config": {"workload": f"configs[1]: EEND-EDA {LAYERS}-layer {UNITS}-d encoder, batch {B} x {T}-frame chunks "
                                    f"({B} x {SECONDS}s @ {RATE} Hz audio through the front end), 2 speakers, per GPU",
                        "global_batch": world * B, "frames_per_step": world * B * T, "precision": precision,
-                       "parallelism": f"dp{world} (recordings sharded, one NCCL gather of the run's thresholded decisions (bit masks) to rank 0's HBM "
-                                      "inside the device-timed region; in the e2e passes every rank lands its OWN recordings' results in its own "
+                       "parallelism": f"dp{world} (recordings sharded, one NCCL gather per step of the thresholded decisions (bit masks, 64 KB per "
+                                      "rank) to rank 0's HBM inside the device-timed region; in the e2e passes every rank lands its OWN recordings' results in its own "
                                       "pinned host memory, as the reference writes one output file per recording)",
                        "host": f"rank thread pinned to {numa}",
                        "l2": "two alternating 51 MB int16 audio batches + 524 MB of FFN intermediates per step exceed the 126 MB L2",

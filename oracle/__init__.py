@@ -7,6 +7,14 @@ CHECK the CUDA path; it is never the product.  Only ``tests/``,
 legs may import it.  Nothing in ``speaker_diarization_b200/`` imports it, and the
 product path raises if the CUDA library is missing.
 
+Generators of the committed fixtures (build container only; they import /root/reference):
+``make_golden.py`` (small model / PIT / front-end cases), ``make_golden_full.py`` (configs[1] and configs[4] at full
+size; the reference's own driver ``infer_eda.infer`` run unmodified on 16 kHz sessions and on long recordings with 1-6
+speakers), ``make_golden_train.py``, ``make_golden_conformer.py``, ``make_golden_eend.py``, ``make_golden_labels.py``,
+``make_golden_transforms.py`` (feature.transform None / 'log' / 'logmel23_espnet'), ``make_golden_rttm.py`` (the
+unmodified ``bin/make_rttm.py`` via runpy + the vendored md-eval.pl).  ``build_ref.py`` places the reference's own
+three files of the path into the git-ignored ``oracle/_ref`` for the timed reference arm of bench.py.
+
 Parity status
 -------------
 * model path (``eend_eda_oracle``): PINNED.  Checked against the reference's own
@@ -17,7 +25,8 @@ Parity status
   ``librosa==0.10.2`` (requirements.txt:15), which is not vendored and cannot be
   installed.  ``librosa.stft`` / ``librosa.filters.mel`` are restated from their
   published algorithm (``oracle/librosa_stub.py``) and cross-checked against an
-  independent second statement (``torch.stft`` + ``torchaudio`` Slaney filterbank).
+  independent second statement (``torch.stft`` + ``torchaudio`` Slaney filterbank;
+  ``tests/test_feature_oracle.py``).
   The reference's ``feature.py`` itself then runs unmodified on top of the stub and
   its outputs are frozen as goldens.  With respect to librosa proper this leg is
   "parity unpinned" (no librosa to execute); with respect to ``feature.py`` it is

@@ -277,7 +277,11 @@ def run_ours(args):
         return last
 
     torch.manual_seed(1234 + rank)
-    run_steps(dev_audio, max(3, args.warmup))
+    # the pipeline keeps 3 batches in flight and hands out freshly allocated pinned result buffers: its allocators and the
+    # three stream slots reach their steady state only after depth + a few batches, whatever W says (more untimed warm-up
+    # than asked for is harmless; with 3 warm-up steps one-time costs of ~50 ms fell into the timed region)
+    WARM = max(8, args.warmup)
+    run_steps(dev_audio, WARM)
     torch.cuda.synchronize()
     if world > 1:
         collect_results()                      # connections of the send/recv path are made here, not in a timed call
@@ -304,7 +308,7 @@ def run_ours(args):
     # ---- end to end through the public API with HOST buffers (pinned), result read back ----
     # K steps per pass, E2E_PASSES passes: the median pass is the value, min / max show the spread (one host hiccup
     # inside a single 40 ms window used to halve the number)
-    run_steps(host_audio, 2)
+    run_steps(host_audio, 6)
     torch.cuda.synchronize()
     passes = []
     for _ in range(E2E_PASSES):
@@ -392,7 +396,7 @@ def run_ours(args):
                                             "per model call) with torch.set_num_threads(1) (train.py:87-88)"}}
         out = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 4), "higher_is_better": True,
+            "warmup": WARM, "ms_per_step": round(ms_step, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "bf16x3": "bf16x3(f32 accum)", "bf16": "bf16"}[precision],
             "data": "synthetic",
             "config": {"workload": f"configs[1]: EEND-EDA {LAYERS}-layer {UNITS}-d encoder, batch {B} x {T}-frame chunks "

@@ -125,6 +125,10 @@ class FrontEnd:
             hit = self._off_cache[key] = self._offsets_uncached(ns)
         return hit
 
+    def rows_of(self, counts) -> List[int]:
+        """Model frames (rows after subsampling) of recordings with these sample counts."""
+        return self._offsets([int(c) for c in counts])[2]
+
     def _offsets_uncached(self, ns):
         frames = [count_frames(n, self.frame_shift) for n in ns]
         rows = [(f + self.subsampling - 1) // self.subsampling for f in frames]

@@ -121,25 +121,36 @@ class InferencePipeline:
         self._n_submitted += 1
         s_compute = self.s_computes[k]
         self.model.workspace_slot = k
+        perms = p = None
         if isinstance(audio, torch.Tensor) and counts is not None:
             if audio.is_cuda:
                 s_compute.wait_stream(cur)        # whoever produced it
                 dev_audio = audio
             else:
                 with torch.cuda.stream(self.s_in):
+                    # The frame shuffles go up FIRST, on the copy stream, ahead of this batch's audio: uploaded from the
+                    # compute stream they become eligible only after the batch's encoder, by which time the 51 MB audio
+                    # copies of the NEXT batches occupy the H2D engine and the LSTM waits ~2 ms per queued batch for a
+                    # 128 KB copy (e2e 14.2 -> 11.9 M frames/s once the host had become fast enough to run that far ahead).
+                    p = self._plan(self.fe.rows_of(counts))
+                    perms = self.model.draw_perms(p["lens"], p["order"], dev)       # the driver's draw order
                     dev_audio = audio.to(dev, non_blocking=True)
                 s_compute.wait_stream(self.s_in)
+                for t in perms:
+                    t.record_stream(s_compute)
         else:
             dev_audio = audio                     # list of recordings: FrontEnd stages them itself
         n_att = self.max_n_speakers - 1
         with torch.cuda.stream(s_compute), L.use_stream(s_compute):
             feats, rows = self.fe.features_flat(dev_audio, ld=self.ld, counts=counts)
-            p = self._plan(rows)
+            if p is None:
+                p = self._plan(rows)
             total = int(p["rec_off"][-1])
             post = torch.empty((total, n_att), dtype=torch.float32, device=dev)
             labels = torch.empty((total, n_att), dtype=torch.uint8, device=dev)
             mask = torch.empty((total,), dtype=torch.int16, device=dev) if self.gather is not None else None
-            perms = self.model.draw_perms(p["lens"], p["order"], dev)       # the driver's draw order
+            if perms is None:
+                perms = self.model.draw_perms(p["lens"], p["order"], dev)       # the driver's draw order
             probs = []
             for lens, offs, perm in zip(p["lens"], p["offs"], perms):
                 _, pr, _ = self.model.infer_device(feats, lens, self.max_n_speakers, self.activity_threshold,

@@ -160,3 +160,17 @@ def test_chunk_level_front_end_world2_gloo():
         assert p.exitcode == 0
     for rank, count, shape_ok, err in res:
         assert count == stft_frames(n, 80) and shape_ok and err < 2e-6, (rank, count, shape_ok, err)
+
+
+def test_pipeline_chunk_plan_is_the_drivers_chunking():
+    """pipeline.chunk_plan over a batch of recordings == infer_eda.py:21-27 applied per recording, in the driver's order."""
+    from speaker_diarization_b200.pipeline import chunk_plan
+    rows = [4800, 2000, 1, 18000, 4303]
+    plan = chunk_plan(rows, 2000)
+    want, base = [], 0
+    for r, n in enumerate(rows):
+        want += [(r, base + s, e - s) for s, e in gen_chunk_indices(n, 2000)]
+        base += n
+    assert plan == want
+    assert [c[2] for c in plan if c[0] == 0] == [2000, 2000, 800] and sum(c[2] for c in plan) == sum(rows)
+    assert chunk_plan([500, 300], None) == [(0, 0, 500), (1, 500, 300)]          # no chunking: one call per recording

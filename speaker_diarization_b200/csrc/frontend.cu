@@ -495,7 +495,6 @@ template <bool W> struct RawPair<double, W> {
 };
 
 constexpr int kT8Warps = 4;                            // warps per CTA
-constexpr int kT8SRow = 128 * 16 + 0;                  // bytes of one frame's transpose buffer
 static size_t logmel_t8_smem(int mel_nnz) {
   // [window 128 double2][step twiddles 128 double2][W_256^k 128 double2][mel weights float][per warp: 4 frames x (2 KB + 136 floats)]
   // (a frame's 2592 bytes = 20 x 128 + 32: the four frames of a warp sit 8 banks apart, so their STS.32 of the powers do not collide)
